@@ -1,0 +1,367 @@
+#!/usr/bin/env python
+"""Generate the golden fixtures under tests/golden/ from the UNMODIFIED reference.
+
+Run in the build container only (needs /root/reference, which does not exist on
+the GPU box):
+
+    python tests/golden/make_golden.py            # all fixtures
+    python tests/golden/make_golden.py leaf edge  # a subset
+
+The reference (crazyMessi/dipole-normal-prop @ 431bb62) has no tests and no
+golden vectors of its own, so parity is pinned on outputs of the
+reference itself run here on its CPU torch path.  The reference module is
+imported read-only; the only shims are OUTSIDE the hot-path math:
+
+  * `open3d`, `pymeshlab`, `gurobipy` are absent -> empty stub modules so that
+    `import field_utils` succeeds (util.py:7, util.py:533, field_utils.py:619).
+  * `torch.symeig` was removed from torch -> `torch.linalg.eigh` (same order),
+    needed by util.pca_eigen_values (util.py:495-500).
+  * `Tensor.cuda` -> identity: strongest_field_propagation_points calls
+    `pts.cuda()` unconditionally (field_utils.py:355); the oracle is the CPU path.
+  * `util.divide_pc` is broken at HEAD (util.py:338-341); patches come from
+    `util.merge_nodes(pc, *util._divide_pc(...), min_patch)[0]`, the upstream
+    composition.
+  * The PointCNN stage (out of scope, needs torch_geometric) is replaced by
+    seeded random per-patch flips and seeded per-point weights.
+
+To record the greedy decision sequence without touching the drivers, the
+module attribute `field_utils.field_grad` is wrapped by a recorder that stores
+the sources of every call and then forwards to the original function.
+"""
+import os
+import sys
+import time
+import types
+
+import numpy as np
+import torch
+
+REF = os.environ.get("DNP_REFERENCE", "/root/reference")
+OUT = os.path.dirname(os.path.abspath(__file__))
+
+
+def import_reference():
+    for name in ("open3d", "pymeshlab", "gurobipy"):
+        if name not in sys.modules:
+            sys.modules[name] = types.ModuleType(name)
+    # torch.symeig survives only as a stub that raises; replace it unconditionally
+    torch.symeig = lambda A, eigenvectors=True, upper=True: torch.linalg.eigh(A)
+    torch.Tensor.cuda = lambda self, *a, **k: self
+    sys.path.insert(0, REF)
+    cwd = os.getcwd()
+    os.chdir(REF)
+    try:
+        import field_utils as ref_fu  # noqa
+        import util as ref_util  # noqa
+    finally:
+        os.chdir(cwd)
+    return ref_fu, ref_util
+
+
+def rand_cloud(gen, n, cols=6, scale=1.0):
+    xyz = (torch.rand(n, 3, generator=gen) - 0.5) * scale
+    if cols == 3:
+        return xyz.float()
+    nrm = torch.randn(n, 3, generator=gen)
+    nrm = nrm / nrm.norm(dim=-1, keepdim=True)
+    return torch.cat([xyz, nrm], dim=1).float()
+
+
+def sphere_cloud(gen, n, r=0.45, noise=0.002, centre=(0.0, 0.0, 0.0)):
+    d = torch.randn(n, 3, generator=gen)
+    d = d / d.norm(dim=-1, keepdim=True)
+    xyz = d * r + torch.randn(n, 3, generator=gen) * noise + torch.tensor(centre)
+    return torch.cat([xyz, d], dim=1).float()
+
+
+def load_xyz(ref_util, name):
+    return ref_util.xyz2tensor(open(os.path.join(REF, "data", name)).read()).float()
+
+
+def save(name, **arrays):
+    path = os.path.join(OUT, name + ".npz")
+    np.savez_compressed(path, **{k: (v.numpy() if isinstance(v, torch.Tensor) else np.asarray(v))
+                                 for k, v in arrays.items()})
+    print(f"wrote {path} ({os.path.getsize(path) / 1024:.1f} KiB)")
+
+
+# ---------------------------------------------------------------- leaf functions
+def gen_leaf(fu, util):
+    out = {}
+    sizes = [(1, 1), (1, 7), (7, 1), (33, 31), (255, 257), (256, 256), (1000, 333)]
+    for k, (S, M) in enumerate(sizes):
+        g = torch.Generator().manual_seed(1234 + k)
+        src = rand_cloud(g, S)
+        tgt = rand_cloud(g, M)
+        out[f"c{k}_src"] = src
+        out[f"c{k}_tgt"] = tgt
+        out[f"c{k}_phi32"] = fu.potential(src, tgt)
+        out[f"c{k}_E32"] = fu.field_grad(src, tgt)
+        out[f"c{k}_E32_eps1e-6"] = fu.field_grad(src, tgt[:, :3], eps=1e-6)
+        out[f"c{k}_phi64"] = fu.potential(src.double(), tgt.double())
+        out[f"c{k}_E64"] = fu.field_grad(src.double(), tgt.double())
+    out["n_cases"] = len(sizes)
+    # recursion semantics (field_utils.py:23-44,73-94) exercised with a small max_pts
+    g = torch.Generator().manual_seed(99)
+    src = rand_cloud(g, 257)
+    tgt = rand_cloud(g, 301)
+    out["rec_src"], out["rec_tgt"] = src, tgt
+    out["rec_phi32"] = fu.potential(src, tgt, max_pts=100)
+    out["rec_E32"] = fu.field_grad(src, tgt, max_pts=100)
+    out["rec_E64"] = fu.field_grad(src.double(), tgt.double(), max_pts=100)
+    out["rec_phi64"] = fu.potential(src.double(), tgt.double(), max_pts=100)
+    # coincident pairs: S == T (field_utils.py:98-106 masks them in field_grad;
+    # potential has no mask and zeroes every target whose leaf total is NaN, :53-54)
+    g = torch.Generator().manual_seed(7)
+    cl = rand_cloud(g, 300)
+    out["self_pc"] = cl
+    out["self_E32"] = fu.field_grad(cl, cl)
+    out["self_E64"] = fu.field_grad(cl.double(), cl.double())
+    out["self_phi32"] = fu.potential(cl, cl)
+    # coincident-pair exclusion equals removing the source: one
+    # duplicate of target 5 appended to the sources
+    src2 = torch.cat([rand_cloud(g, 64), cl[5:6]], dim=0)
+    out["dup_src"] = src2
+    out["dup_E32"] = fu.field_grad(src2, cl)
+    out["dup_E64"] = fu.field_grad(src2.double(), cl.double())
+    # analytic sphere: phi(centre) = N / r^2
+    g = torch.Generator().manual_seed(11)
+    sp = sphere_cloud(g, 8192, noise=0.0)
+    probes = torch.tensor([[0.0, 0.0, 0.0], [0.1, -0.05, 0.02], [0.9, 0.9, 0.9]])
+    out["sphere_pc"] = sp
+    out["sphere_probes"] = probes
+    out["sphere_phi32"] = fu.potential(sp, probes)
+    out["sphere_phi64"] = fu.potential(sp.double(), probes.double())
+    save("leaf", **out)
+
+
+# ---------------------------------------------------------------- edge scores
+def gen_edge(fu, util):
+    out = {}
+    g = torch.Generator().manual_seed(4321)
+    pairs = [(120, 200), (100, 100), (257, 64), (1, 50)]
+    for k, (s, t) in enumerate(pairs):
+        S = sphere_cloud(g, s, r=0.3, noise=0.01, centre=(-0.1, 0.0, 0.0))
+        T = sphere_cloud(g, t, r=0.3, noise=0.01, centre=(0.15, 0.05, 0.0))
+        if k % 2:
+            T[:, 3:] *= -1
+        w, invw = fu.field_edge_calculator(S, T)
+        out[f"e{k}_S"], out[f"e{k}_T"] = S, T
+        out[f"e{k}_w"], out[f"e{k}_invw"] = np.asarray(w), np.asarray(invw)
+        wb = fu.field_edge_calculator_bool(S, T)
+        wc = fu.field_edge_calculator_count(S, T)
+        out[f"e{k}_bool"] = np.asarray(wb)
+        out[f"e{k}_count"] = np.asarray(wc)
+        S64, T64 = S.double(), T.double()
+        out[f"e{k}_w64"] = np.asarray(fu.field_edge_calculator(S64, T64)[0])
+    out["n_cases"] = len(pairs)
+    cl = sphere_cloud(g, 150, r=0.3, noise=0.01)
+    out["selfall_pc"] = cl
+    out["selfall_w"] = np.asarray(fu.self_interaction_all(cl))
+    save("edge", **out)
+
+
+# ---------------------------------------------------------------- orientation transfer
+def gen_transfer(fu, util):
+    out = {}
+    g = torch.Generator().manual_seed(2024)
+    ref = sphere_cloud(g, 500, r=0.4, noise=0.0)
+    tgt = sphere_cloud(g, 700, r=0.4, noise=0.003)
+    scr = (torch.rand(700, generator=g) < 0.5)
+    tgt6 = tgt.clone()
+    tgt6[scr, 3:] *= -1
+    out["ref"], out["tgt3"], out["tgt6"] = ref, tgt[:, :3].clone(), tgt6.clone()
+    out["out3"] = fu.reference_field(ref, tgt[:, :3].clone())
+    out["out6"] = fu.reference_field(ref, tgt6.clone())
+    save("transfer", **out)
+
+
+# ---------------------------------------------------------------- lattice test
+def gen_lattice(fu, util):
+    out = {}
+    out["grid"] = util.gen_grid()
+    ok = load_xyz(util, "ok.xyz")
+    ok_t, _ = util.Transform.trans(ok)
+    out["ok_mean"] = fu.measure_mean_potential(ok_t)
+    out["ok_mean_flipped"] = fu.measure_mean_potential(
+        torch.cat([ok_t[:, :3], -ok_t[:, 3:]], dim=1))
+    out["ok_phi"] = fu.potential(ok_t, util.gen_grid())
+    out["ok_mean64"] = fu.measure_mean_potential(ok_t.double())
+    g = torch.Generator().manual_seed(5)
+    sp = sphere_cloud(g, 4000)
+    out["sphere_pc"] = sp
+    out["sphere_mean"] = fu.measure_mean_potential(sp)
+    out["sphere_mean64"] = fu.measure_mean_potential(sp.double())
+    save("lattice", **out)
+
+
+# ---------------------------------------------------------------- drivers
+class Recorder:
+    """Wraps field_utils.field_grad to log (first source row) of each call."""
+
+    def __init__(self, fu):
+        self.fu = fu
+        self.orig = fu.field_grad
+        self.calls = []
+
+    def __enter__(self):
+        def wrapped(sources, means, *a, **k):
+            self.calls.append((sources[0].clone(), int(sources.shape[0]), int(means.shape[0])))
+            return self.orig(sources, means, *a, **k)
+        self.fu.field_grad = wrapped
+        return self
+
+    def __exit__(self, *exc):
+        self.fu.field_grad = self.orig
+
+
+def match_rows(xyz_all, rows):
+    """index of each row (xyz) in xyz_all (exact match; clouds have no duplicates)."""
+    lut = {tuple(p.tolist()): i for i, p in enumerate(xyz_all)}
+    return np.array([lut[tuple(r[:3].tolist())] for r in rows], dtype=np.int64)
+
+
+def scramble(pc, g, frac=0.5):
+    flip = torch.rand(pc.shape[0], generator=g) < frac
+    pc = pc.clone()
+    pc[flip, 3:] *= -1
+    return pc
+
+
+def gen_points(fu, util):
+    """cfg1: strongest_field_propagation_points on data/ok.xyz (field_utils.py:353-388)."""
+    ok = load_xyz(util, "ok.xyz")
+    ok_t, _ = util.Transform.trans(ok)
+    g = torch.Generator().manual_seed(31337)
+    pc_in = scramble(ok_t, g)
+    out = {"pc_in": pc_in}
+    for tag, n, diffuse in (("n512", 512, False), ("n2000", 2000, True), ("full", pc_in.shape[0], False)):
+        pts = pc_in[:n].clone()
+        t0 = time.time()
+        with Recorder(fu) as rec:
+            res = fu.strongest_field_propagation_points(pts, diffuse=diffuse, starting_point=0)
+        dt = time.time() - t0
+        order = match_rows(pc_in[:n, :3], [c[0] for c in rec.calls])
+        # normal of the chosen point at the time it became a source (after the flip decision)
+        src_n = torch.stack([c[0][3:] for c in rec.calls])
+        flipped = ((src_n * pc_in[order, 3:]).sum(-1) < 0).numpy()
+        out[f"{tag}_n"] = n
+        out[f"{tag}_diffuse"] = diffuse
+        out[f"{tag}_order"] = order.astype(np.int32)
+        out[f"{tag}_flipped"] = flipped
+        out[f"{tag}_normals"] = res[:, 3:]
+        out[f"{tag}_mean_potential"] = fu.measure_mean_potential(res)
+        out[f"{tag}_ref_seconds"] = dt
+        print(f"points {tag}: N={n} ref CPU {dt:.1f}s")
+    save("points_prop", **out)
+
+
+def make_patches(util, pc, n_part, min_patch):
+    idx, ijk = util._divide_pc(pc[:, :3], n_part, min_patch=min_patch)
+    merged, _ = util.merge_nodes(pc, idx, ijk, min_patch)
+    return merged
+
+
+def patch_csr(patches):
+    perm = torch.cat(patches).numpy().astype(np.int64)
+    off = np.zeros(len(patches) + 1, dtype=np.int64)
+    off[1:] = np.cumsum([len(p) for p in patches])
+    return perm, off
+
+
+def gen_patches(fu, util):
+    """cfg2: strongest_field_propagation on data/fandisk.xyz (field_utils.py:286-348)."""
+    fd = load_xyz(util, "fandisk.xyz")
+    fd_t, _ = util.Transform.trans(fd)
+    patches = make_patches(util, fd_t, 30, 100)
+    P = len(patches)
+    g = torch.Generator().manual_seed(777)
+    # stand-in for the network stage: seeded per-patch flips, seeded weights
+    pc_in = fd_t.clone()
+    for p in patches:
+        if torch.rand(1, generator=g).item() < 0.5:
+            pc_in[p, 3:] *= -1
+    weights = torch.rand(pc_in.shape[0], generator=g) * 0.9 + 0.05
+    perm, off = patch_csr(patches)
+    out = {"pc_in": pc_in, "weights": weights, "perm": perm, "offsets": off, "P": P}
+    kept = [(i, p) for i, p in enumerate(patches) if i % 3 != 0]   # "network-kept" subset
+    out["kept_ids"] = np.array([i for i, _ in kept], dtype=np.int64)
+    first_pt = {int(p[0]): i for i, p in enumerate(patches)}
+    for tag, diffuse, use_w in (("plain", False, False), ("diffuse_w", True, True)):
+        pts = pc_in.clone()
+        t0 = time.time()
+        with Recorder(fu) as rec:
+            fu.strongest_field_propagation(pts, kept, [p.clone() for p in patches], diffuse=diffuse,
+                                           weights=weights.clone() if use_w else None)
+        dt = time.time() - t0
+        # sources of call k are pts[mask] for call 0 (sorted) and pts[patch] afterwards
+        order = []
+        for k, c in enumerate(rec.calls):
+            row = match_rows(pc_in[:, :3], [c[0]])[0]
+            if k == 0:
+                pid = [i for i, p in enumerate(patches) if int(p.min()) == row][0]
+            else:
+                pid = first_pt[int(row)]
+            order.append(pid)
+        out[f"{tag}_order"] = np.array(order, dtype=np.int32)
+        out[f"{tag}_normals"] = pts[:, 3:]
+        out[f"{tag}_ref_seconds"] = dt
+        out[f"{tag}_mean_potential"] = fu.measure_mean_potential(pts)
+        print(f"patches {tag}: N={pts.shape[0]} P={P} ref CPU {dt:.1f}s")
+    save("patch_prop", **out)
+
+
+def gen_reps(fu, util):
+    """cfg3 stand-in: strongest_field_propagation_reps (field_utils.py:207-282) on a noisy sphere pair."""
+    g = torch.Generator().manual_seed(4242)
+    a = sphere_cloud(g, 5000, r=0.33, noise=0.002, centre=(-0.12, 0.0, 0.0))
+    b = sphere_cloud(g, 3000, r=0.2, noise=0.002, centre=(0.3, 0.1, 0.05))
+    pc = torch.cat([a, b], dim=0)
+    pc, _ = util.Transform.trans(pc)
+    patches = make_patches(util, pc, 8, 60)
+    P = len(patches)
+    pc_in = pc.clone()
+    for p in patches:
+        if torch.rand(1, generator=g).item() < 0.5:
+            pc_in[p, 3:] *= -1
+    max_rep = 40
+    reps = []
+    for p in patches:
+        pm = torch.randperm(p.shape[0], generator=g)
+        reps.append((p[pm[:max_rep]], p[pm[max_rep:]]))
+    rep_perm, rep_off = patch_csr([r for r, _ in reps])
+    rest_perm, rest_off = patch_csr([r for _, r in reps])
+    out = {"pc_in": pc_in, "rep_perm": rep_perm, "rep_off": rep_off,
+           "rest_perm": rest_perm, "rest_off": rest_off, "P": P}
+    first_pt = {int(r[0]): i for i, (r, _) in enumerate(reps)}
+    for tag, diffuse in (("plain", False), ("diffuse", True)):
+        pts = pc_in.clone()
+        t0 = time.time()
+        with Recorder(fu) as rec:
+            fu.strongest_field_propagation_reps(pts, [(r.clone(), q.clone()) for r, q in reps], diffuse=diffuse)
+        dt = time.time() - t0
+        order = []
+        for k, c in enumerate(rec.calls[:P]):       # last call is the reps -> non-reps field
+            row = match_rows(pc_in[:, :3], [c[0]])[0]
+            if k == 0:
+                pid = [i for i, (r, _) in enumerate(reps) if int(r.min()) == row][0]
+            else:
+                pid = first_pt[int(row)]
+            order.append(pid)
+        out[f"{tag}_order"] = np.array(order, dtype=np.int32)
+        out[f"{tag}_normals"] = pts[:, 3:]
+        out[f"{tag}_ref_seconds"] = dt
+        print(f"reps {tag}: N={pts.shape[0]} P={P} ref CPU {dt:.1f}s")
+    save("reps_prop", **out)
+
+
+GENERATORS = {"leaf": gen_leaf, "edge": gen_edge, "transfer": gen_transfer, "lattice": gen_lattice,
+              "points": gen_points, "patches": gen_patches, "reps": gen_reps}
+
+if __name__ == "__main__":
+    torch.manual_seed(0)
+    np.random.seed(0)
+    fu, util = import_reference()
+    which = sys.argv[1:] or list(GENERATORS)
+    for name in which:
+        GENERATORS[name](fu, util)
