@@ -1,0 +1,317 @@
+// dnp_abi.cu -- the extern "C" boundary of libdipole.so (see include/dipole.h).
+//
+// Every entry point validates its arguments, never throws, never allocates an
+// output, and reports failures through a negative return code plus a
+// thread-local message (dnp_last_error).  The library holds no mutable global
+// state besides cached device properties and a launch counter, so it is safe to
+// call from many host threads (the reference does: util.py:187-196,308-327).
+#include <stdarg.h>
+#include <stdio.h>
+#include <string.h>
+
+#include "dnp_common.cuh"
+#include "dnp_pairs.h"
+#include "dnp_scores.h"
+
+namespace dnp {
+
+static thread_local char t_error[512] = "";
+
+void set_error(const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(t_error, sizeof(t_error), fmt, ap);
+    va_end(ap);
+}
+
+int cuda_fail(cudaError_t err, const char* what) {
+    set_error("CUDA error %d (%s) in %s", (int)err, cudaGetErrorString(err), what);
+    return DNP_ERR_CUDA;
+}
+
+static int invalid(const char* msg) {
+    set_error("invalid argument: %s", msg);
+    return DNP_ERR_INVALID;
+}
+
+}  // namespace dnp
+
+using namespace dnp;
+
+#define DNP_REQUIRE(cond, msg) \
+    do {                       \
+        if (!(cond)) return invalid(msg); \
+    } while (0)
+
+extern "C" {
+
+const char* dnp_last_error(void) { return t_error; }
+
+int dnp_version(void) { return 100; }
+
+int dnp_device_info(int* sm_count, int* sm_clock_khz, int* cc_major, int* cc_minor) {
+    int dev = 0;
+    DNP_CHECK_CUDA(cudaGetDevice(&dev));
+    cudaDeviceProp prop;
+    DNP_CHECK_CUDA(cudaGetDeviceProperties(&prop, dev));
+    int clock_khz = 0;
+    DNP_CHECK_CUDA(cudaDeviceGetAttribute(&clock_khz, cudaDevAttrClockRate, dev));
+    if (sm_count) *sm_count = prop.multiProcessorCount;
+    if (sm_clock_khz) *sm_clock_khz = clock_khz;
+    if (cc_major) *cc_major = prop.major;
+    if (cc_minor) *cc_minor = prop.minor;
+    return DNP_OK;
+}
+
+size_t dnp_pairs_workspace_bytes(int64_t S, int64_t M) { return pairs_workspace_bytes(S, M); }
+
+int64_t dnp_launch_count(void) { return launch_count(); }
+
+// ------------------------------------------------------------------ potential
+int dnp_potential_f32(const float* src, int64_t S, int64_t ld_s, const int64_t* src_idx,
+                      const float* tgt, int64_t M, int64_t ld_t,
+                      float* phi, int accumulate,
+                      void* workspace, size_t workspace_bytes, void* stream) {
+    DNP_REQUIRE(S >= 0 && M >= 0, "negative size");
+    if (M == 0) return DNP_OK;
+    DNP_REQUIRE(tgt && phi, "null target or output pointer");
+    DNP_REQUIRE(S == 0 || src, "null source pointer");
+    DNP_REQUIRE(ld_s >= 6 && ld_t >= 3, "row stride too small (sources need 6 columns, targets 3)");
+    PairEpilogue ep;
+    ep.mode = accumulate ? DNP_EPI_ACCUM : DNP_EPI_STORE;
+    ep.out = phi;
+    ep.ld_out = 1;
+    return run_pairs(true, src, S, ld_s, src_idx, tgt, M, ld_t, 0, 0.f, ep, workspace, workspace_bytes,
+                     (cudaStream_t)stream);
+}
+
+int dnp_lattice_mean_potential_f32(const float* src, int64_t S, int64_t ld_s,
+                                   int n, float* phi_opt, float* mean_out,
+                                   void* workspace, size_t workspace_bytes, void* stream) {
+    DNP_REQUIRE(S >= 0 && n > 0 && n <= 256, "bad size");
+    DNP_REQUIRE(mean_out, "null output pointer");
+    DNP_REQUIRE(S == 0 || src, "null source pointer");
+    DNP_REQUIRE(ld_s >= 6, "row stride too small");
+    const int64_t M = (int64_t)n * n * n;
+    const size_t need = pairs_workspace_bytes(S, M);
+    if (!workspace || workspace_bytes < need) {
+        set_error("workspace too small: need %zu bytes, got %zu", need, workspace_bytes);
+        return DNP_ERR_WORKSPACE;
+    }
+    // per-node potentials live in the caller's buffer or at the tail of the workspace
+    const size_t phi_off = (need - 1024 - (size_t)((M * 4 + 255) / 256 * 256));
+    float* phi = phi_opt ? phi_opt : reinterpret_cast<float*>(reinterpret_cast<unsigned char*>(workspace) + phi_off);
+    PairEpilogue ep;
+    ep.mode = DNP_EPI_STORE;
+    ep.out = phi;
+    ep.ld_out = 1;
+    int rc = run_pairs(true, src, S, ld_s, nullptr, nullptr, M, 3, n, 0.f, ep, workspace, phi_off,
+                       (cudaStream_t)stream);
+    if (rc != DNP_OK) return rc;
+    return run_sum(phi, M, 1, 1.0f / (float)M, mean_out, (cudaStream_t)stream);
+}
+
+// ------------------------------------------------------------------ field
+int dnp_field_apply_f32(const float* src, int64_t S, int64_t ld_s, const int64_t* src_idx,
+                        const float* tgt, int64_t M, int64_t ld_t,
+                        const int64_t* tgt_idx, const uint8_t* tgt_skip,
+                        float eps, int mode,
+                        float* out, int64_t ld_out, float* normals, int64_t ld_n,
+                        int32_t* nonfinite,
+                        void* workspace, size_t workspace_bytes, void* stream) {
+    DNP_REQUIRE(S >= 0 && M >= 0, "negative size");
+    if (M == 0) return DNP_OK;
+    DNP_REQUIRE(tgt, "null target pointer");
+    DNP_REQUIRE(S == 0 || src, "null source pointer");
+    DNP_REQUIRE(ld_s >= 6 && ld_t >= 3, "row stride too small (sources need 6 columns, targets 3)");
+    DNP_REQUIRE(mode >= DNP_EPI_STORE && mode <= DNP_EPI_DOT, "unknown epilogue mode");
+    const bool needs_out = mode == DNP_EPI_STORE || mode == DNP_EPI_ACCUM || mode == DNP_EPI_NORMALIZE ||
+                           mode == DNP_EPI_DOT;
+    const bool needs_n = mode == DNP_EPI_SIGN_GE || mode == DNP_EPI_SIGN_GT || mode == DNP_EPI_DOT;
+    DNP_REQUIRE(!needs_out || (out && ld_out >= (mode == DNP_EPI_DOT ? 1 : 3)), "bad output pointer / stride");
+    DNP_REQUIRE(!needs_n || (normals && ld_n >= 3), "bad normals pointer / stride");
+    DNP_REQUIRE(eps >= 0.f, "eps must be >= 0");
+    PairEpilogue ep;
+    ep.mode = mode;
+    ep.out = out;
+    ep.ld_out = ld_out;
+    ep.normals = normals;
+    ep.ld_n = ld_n;
+    ep.tgt_idx = tgt_idx;
+    ep.tgt_skip = tgt_skip;
+    ep.nonfinite = nonfinite;
+    return run_pairs(false, src, S, ld_s, src_idx, tgt, M, ld_t, 0, eps, ep, workspace, workspace_bytes,
+                     (cudaStream_t)stream);
+}
+
+int dnp_field_grad_f32(const float* src, int64_t S, int64_t ld_s,
+                       const float* tgt, int64_t M, int64_t ld_t,
+                       float eps, float* E, int64_t ld_e, int accumulate,
+                       void* workspace, size_t workspace_bytes, void* stream) {
+    return dnp_field_apply_f32(src, S, ld_s, nullptr, tgt, M, ld_t, nullptr, nullptr, eps,
+                               accumulate ? DNP_EPI_ACCUM : DNP_EPI_STORE, E, ld_e, nullptr, 0, nullptr,
+                               workspace, workspace_bytes, stream);
+}
+
+// ------------------------------------------------------------------ edge score (single pair)
+int dnp_edge_interaction_f32(const float* S_pts, int64_t S, int64_t ld_s,
+                             const float* T_pts, int64_t T, int64_t ld_t,
+                             float eps, float* interaction,
+                             void* workspace, size_t workspace_bytes, void* stream) {
+    DNP_REQUIRE(S >= 0 && T >= 0, "negative size");
+    DNP_REQUIRE(interaction, "null output pointer");
+    DNP_REQUIRE(ld_s >= 6 && ld_t >= 6, "both patches need 6 columns");
+    DNP_REQUIRE(T == 0 || T_pts, "null target pointer");
+    const size_t need = pairs_workspace_bytes(S, T);
+    if (!workspace || workspace_bytes < need) {
+        set_error("workspace too small: need %zu bytes, got %zu", need, workspace_bytes);
+        return DNP_ERR_WORKSPACE;
+    }
+    const int64_t Tn = T < 1 ? 1 : T;
+    const size_t dot_off = need - 1024 - (size_t)((Tn * 4 + 255) / 256 * 256);
+    float* dots = reinterpret_cast<float*>(reinterpret_cast<unsigned char*>(workspace) + dot_off);
+    if (T > 0) {
+        int rc = dnp_field_apply_f32(S_pts, S, ld_s, nullptr, T_pts, T, ld_t, nullptr, nullptr, eps, DNP_EPI_DOT,
+                                     dots, 1, const_cast<float*>(T_pts) + 3, ld_t, nullptr, workspace, dot_off,
+                                     stream);
+        if (rc != DNP_OK) return rc;
+    }
+    return run_sum(dots, T, 1, 1.0f, interaction, (cudaStream_t)stream);
+}
+
+// ------------------------------------------------------------------ host-buffer entry points
+namespace {
+
+struct DeviceGuard {
+    int prev = -1;
+    bool ok = false;
+    explicit DeviceGuard(int device) {
+        if (cudaGetDevice(&prev) == cudaSuccess && cudaSetDevice(device) == cudaSuccess) ok = true;
+    }
+    ~DeviceGuard() {
+        if (prev >= 0) cudaSetDevice(prev);
+    }
+};
+
+// copies a strided [rows, cols] host matrix into a dense device matrix
+cudaError_t upload_rows(float* dst, const float* src_host, int64_t rows, int64_t cols, int64_t ld,
+                        cudaStream_t stream) {
+    if (rows == 0) return cudaSuccess;
+    return cudaMemcpy2DAsync(dst, cols * sizeof(float), src_host, ld * sizeof(float), cols * sizeof(float), rows,
+                             cudaMemcpyHostToDevice, stream);
+}
+
+int host_pairs(bool potential, const float* src_host, int64_t S, int64_t ld_s, const float* tgt_host, int64_t M,
+               int64_t ld_t, float eps, float* out_host, int device) {
+    DNP_REQUIRE(S >= 0 && M >= 0, "negative size");
+    if (M == 0) return DNP_OK;
+    DNP_REQUIRE(tgt_host && out_host, "null target or output pointer");
+    DNP_REQUIRE(S == 0 || src_host, "null source pointer");
+    DNP_REQUIRE(ld_s >= 6 && ld_t >= 3, "row stride too small");
+    DeviceGuard guard(device);
+    if (!guard.ok) {
+        set_error("cannot select CUDA device %d", device);
+        return DNP_ERR_NO_DEVICE;
+    }
+    const int ncomp = potential ? 1 : 3;
+    const size_t ws_bytes = pairs_workspace_bytes(S, M);
+    const size_t src_bytes = (size_t)(S > 0 ? S : 1) * 6 * sizeof(float);
+    const size_t tgt_bytes = (size_t)M * 3 * sizeof(float);
+    const size_t out_bytes = (size_t)M * ncomp * sizeof(float);
+    cudaStream_t stream;
+    DNP_CHECK_CUDA(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
+    unsigned char* base = nullptr;
+    const size_t a256 = 256;
+    auto up = [&](size_t v) { return (v + a256 - 1) / a256 * a256; };
+    const size_t total = up(src_bytes) + up(tgt_bytes) + up(out_bytes) + ws_bytes;
+    cudaError_t e = cudaMallocAsync(reinterpret_cast<void**>(&base), total, stream);
+    if (e != cudaSuccess) { cudaStreamDestroy(stream); return cuda_fail(e, "cudaMallocAsync"); }
+    float* d_src = reinterpret_cast<float*>(base);
+    float* d_tgt = reinterpret_cast<float*>(base + up(src_bytes));
+    float* d_out = reinterpret_cast<float*>(base + up(src_bytes) + up(tgt_bytes));
+    void* d_ws = base + up(src_bytes) + up(tgt_bytes) + up(out_bytes);
+    int rc = DNP_OK;
+    do {
+        if ((e = upload_rows(d_src, src_host, S, 6, ld_s, stream)) != cudaSuccess) { rc = cuda_fail(e, "upload sources"); break; }
+        if ((e = upload_rows(d_tgt, tgt_host, M, 3, ld_t, stream)) != cudaSuccess) { rc = cuda_fail(e, "upload targets"); break; }
+        PairEpilogue ep;
+        ep.mode = DNP_EPI_STORE;
+        ep.out = d_out;
+        ep.ld_out = ncomp;
+        rc = run_pairs(potential, d_src, S, 6, nullptr, d_tgt, M, 3, 0, eps, ep, d_ws, ws_bytes, stream);
+        if (rc != DNP_OK) break;
+        if ((e = cudaMemcpyAsync(out_host, d_out, out_bytes, cudaMemcpyDeviceToHost, stream)) != cudaSuccess) { rc = cuda_fail(e, "download"); break; }
+    } while (0);
+    cudaFreeAsync(base, stream);
+    e = cudaStreamSynchronize(stream);
+    cudaStreamDestroy(stream);
+    if (rc == DNP_OK && e != cudaSuccess) rc = cuda_fail(e, "cudaStreamSynchronize");
+    return rc;
+}
+
+}  // namespace
+
+int dnp_field_grad_host_f32(const float* src_host, int64_t S, int64_t ld_s,
+                            const float* tgt_host, int64_t M, int64_t ld_t,
+                            float eps, float* E_host, int device) {
+    DNP_REQUIRE(eps >= 0.f, "eps must be >= 0");
+    return host_pairs(false, src_host, S, ld_s, tgt_host, M, ld_t, eps, E_host, device);
+}
+
+int dnp_potential_host_f32(const float* src_host, int64_t S, int64_t ld_s,
+                           const float* tgt_host, int64_t M, int64_t ld_t,
+                           float* phi_host, int device) {
+    return host_pairs(true, src_host, S, ld_s, tgt_host, M, ld_t, 0.f, phi_host, device);
+}
+
+}  // extern "C"
+
+// ------------------------------------------------------------------ scores, drivers, measurement
+extern "C" {
+
+int dnp_edge_interactions_batched_f32(const float* pts, int64_t ld,
+                                      const int64_t* perm, const int64_t* offsets, int64_t P,
+                                      const int64_t* edges, int64_t n_edges,
+                                      float eps, float* out, void* stream) {
+    DNP_REQUIRE(n_edges >= 0 && P >= 0, "negative size");
+    if (n_edges == 0) return DNP_OK;
+    DNP_REQUIRE(pts && perm && offsets && edges && out, "null pointer");
+    DNP_REQUIRE(ld >= 6, "points need 6 columns");
+    DNP_REQUIRE(eps >= 0.f, "eps must be >= 0");
+    return run_edge_interactions_batched(pts, ld, perm, offsets, P, edges, n_edges, eps, out, (cudaStream_t)stream);
+}
+
+int dnp_patch_interactions_f32(const float* E, int64_t ld_e, const float* normals, int64_t ld_n,
+                               const int64_t* perm, const int64_t* offsets, int64_t P,
+                               const uint8_t* active, float* out,
+                               int32_t* best_idx, float* best_val, void* stream) {
+    DNP_REQUIRE(P >= 0, "negative size");
+    if (P == 0) return DNP_OK;
+    DNP_REQUIRE(E && normals && perm && offsets && out, "null pointer");
+    DNP_REQUIRE(ld_e >= 3 && ld_n >= 3, "row stride too small");
+    DNP_REQUIRE((best_idx == nullptr) == (best_val == nullptr), "best_idx and best_val go together");
+    return run_patch_interactions(E, ld_e, normals, ld_n, perm, offsets, P, active, out, best_idx, best_val,
+                                  (cudaStream_t)stream);
+}
+
+int64_t dnp_points_max_n(void) { return points_max_n(); }
+
+int dnp_points_propagate_f32(float* pts, int64_t N, int64_t ld, int64_t starting_point,
+                             float eps, int diffuse,
+                             int32_t* order_opt, uint8_t* flipped_opt, void* stream) {
+    DNP_REQUIRE(N >= 0, "negative size");
+    if (N == 0) return DNP_OK;
+    DNP_REQUIRE(pts, "null pointer");
+    DNP_REQUIRE(ld >= 6, "points need 6 columns");
+    DNP_REQUIRE(starting_point >= 0 && starting_point < N, "starting_point out of range");
+    DNP_REQUIRE(N < 0x7ffffffe, "N too large");
+    DNP_REQUIRE(eps >= 0.f, "eps must be >= 0");
+    return run_points_propagate(pts, N, ld, starting_point, eps, diffuse, order_opt, flipped_opt,
+                                (cudaStream_t)stream);
+}
+
+int dnp_microbench(int kind, int iters, float* ms_out, double* ops_out, void* stream) {
+    return run_microbench(kind, iters, ms_out, ops_out, (cudaStream_t)stream);
+}
+
+}  // extern "C"

@@ -1,0 +1,474 @@
+// dnp_pairs.cu -- all-pairs dipole potential / field kernels (K1, K2, K6, K7).
+//
+// Replaces the leaf bodies of field_utils.potential (field_utils.py:46-55) and
+// field_utils.field_grad (field_utils.py:96-116) and the recursive chunking
+// around them (:23-44, :73-94): memory is O(S + M), nothing is materialised per
+// pair.
+//
+// Design (B200, sm_100a):
+//   * sources are re-packed once per call into a 48-byte "lane-duplicated" row
+//     [x x y y | z z nx nx | ny ny nz nz]; the TMA unit streams 12 KB tiles of it
+//     into a 3-stage shared-memory ring (cp.async.bulk + mbarrier, SASS UBLKCP).
+//   * every thread keeps 2*TP targets in registers.  Two targets share one
+//     64-bit register pair, and the whole per-pair arithmetic runs on packed
+//     FFMA2/FMUL2/FADD2 (two FP32 ops per lane per instruction): 20 packed
+//     instructions + 2 MUFU.RSQ + 2 MUFU.RCP + 4 FMNMX per (2 targets x 1 source).
+//     The FP32 pipe is the bound; the issue slots it frees cover the SFU, the
+//     NaN-laundering FMNMX and the broadcast LDS.128 loads.
+//   * no tensor cores: the 1/(|R|^3+eps) weight is per pair, not a contraction.
+//   * coincident pairs: rsqrt(0)=inf makes r=0*inf NaN, so the weight w becomes
+//     NaN and max(w, 0) returns 0 (FMNMX drops the NaN operand); the R-parallel
+//     coefficient uses the clamped rsqrt so it stays finite and multiplies R=0.
+//   * per-target sums are flushed into a second-level accumulator after every
+//     256-source tile, and (for nsplit > 1) source ranges are reduced by a second
+//     kernel in a fixed order: deterministic, no float atomics.
+#include <stdlib.h>
+
+#include "dnp_common.cuh"
+#include "dnp_pairs.h"
+
+namespace dnp {
+
+namespace {
+
+constexpr int kBlock = 128;                      // threads per CTA
+constexpr int kTileSrc = 256;                    // sources per shared-memory stage
+constexpr int kStages = 3;                       // TMA ring depth
+constexpr int kSrcBytes = 48;                    // packed bytes per source
+constexpr uint32_t kTileBytes = kTileSrc * kSrcBytes;
+constexpr size_t kSmemBytes = size_t(kStages) * kTileBytes + kStages * sizeof(uint64_t);
+constexpr float kRsqrtClamp = 1.152921504606847e18f;   // 2^60: clamp^2 is finite (field: c = d w u^2)
+constexpr float kRsqrtClampPhi = 1.099511627776e12f;   // 2^40: clamp^3 is finite (potential: d u^3)
+
+// ------------------------------------------------------------------ source packing
+__global__ void pack_sources_kernel(const float* __restrict__ src, int64_t S, int64_t ld_s,
+                                    const int64_t* __restrict__ idx, int64_t S_pad,
+                                    float4* __restrict__ packed) {
+    const int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= S_pad) return;
+    float v[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};   // padding rows: a null dipole
+    if (s < S) {
+        const float* p = src + (idx ? idx[s] : s) * ld_s;
+#pragma unroll
+        for (int c = 0; c < 6; ++c) v[c] = __ldg(p + c);
+    }
+    packed[3 * s + 0] = make_float4(v[0], v[0], v[1], v[1]);
+    packed[3 * s + 1] = make_float4(v[2], v[2], v[3], v[3]);
+    packed[3 * s + 2] = make_float4(v[4], v[4], v[5], v[5]);
+}
+
+// ------------------------------------------------------------------ epilogue (K7)
+__device__ __forceinline__ float zero_nonfinite(float v, int& bad) {
+    // (v - v) is NaN for both Inf and NaN
+    if (!(fabsf(v) <= 3.402823466e38f)) { ++bad; return 0.f; }
+    return v;
+}
+
+__device__ __forceinline__ void apply_field_epilogue(const PairEpilogue& ep, int64_t r,
+                                                     float ex, float ey, float ez) {
+    int bad = 0;
+    ex = zero_nonfinite(ex, bad);          // field_utils.py:114-115
+    ey = zero_nonfinite(ey, bad);
+    ez = zero_nonfinite(ez, bad);
+    if (bad && ep.nonfinite) atomicAdd(ep.nonfinite, bad);
+    switch (ep.mode) {
+        case DNP_EPI_STORE: {
+            float* o = ep.out + r * ep.ld_out;
+            o[0] = ex; o[1] = ey; o[2] = ez;
+        } break;
+        case DNP_EPI_ACCUM: {
+            float* o = ep.out + r * ep.ld_out;
+            o[0] += ex; o[1] += ey; o[2] += ez;
+        } break;
+        case DNP_EPI_SIGN_GE:
+        case DNP_EPI_SIGN_GT: {
+            float* n = ep.normals + r * ep.ld_n;
+            const float nx = n[0], ny = n[1], nz = n[2];
+            // same evaluation order as (E * n).sum(-1): ((ex*nx + ey*ny) + ez*nz), no contraction
+            const float dot = __fadd_rn(__fadd_rn(__fmul_rn(ex, nx), __fmul_rn(ey, ny)), __fmul_rn(ez, nz));
+            const bool keep = ep.mode == DNP_EPI_SIGN_GE ? (dot >= 0.f) : (dot > 0.f);
+            const float sgn = keep ? 1.f : -1.f;
+            n[0] = nx * sgn; n[1] = ny * sgn; n[2] = nz * sgn;
+        } break;
+        case DNP_EPI_NORMALIZE: {
+            float* o = ep.out + r * ep.ld_out;
+            const float len = __fsqrt_rn(__fadd_rn(__fadd_rn(__fmul_rn(ex, ex), __fmul_rn(ey, ey)), __fmul_rn(ez, ez)));
+            if (len != 0.f) { ex = __fdiv_rn(ex, len); ey = __fdiv_rn(ey, len); ez = __fdiv_rn(ez, len); }
+            o[0] = ex; o[1] = ey; o[2] = ez;
+        } break;
+        case DNP_EPI_DOT: {
+            const float* n = ep.normals + r * ep.ld_n;
+            ep.out[r * ep.ld_out] =
+                __fadd_rn(__fadd_rn(__fmul_rn(ex, n[0]), __fmul_rn(ey, n[1])), __fmul_rn(ez, n[2]));
+        } break;
+        default: break;
+    }
+}
+
+__device__ __forceinline__ void apply_potential_epilogue(const PairEpilogue& ep, int64_t r, float phi) {
+    int bad = 0;
+    phi = zero_nonfinite(phi, bad);        // field_utils.py:53-54
+    if (bad && ep.nonfinite) atomicAdd(ep.nonfinite, bad);
+    float* o = ep.out + r * ep.ld_out;
+    if (ep.mode == DNP_EPI_ACCUM) *o += phi; else *o = phi;
+}
+
+// lattice node i of util.gen_grid (util.py:26-36), same float operations
+__device__ __forceinline__ void lattice_node(int64_t i, int n, float& x, float& y, float& z) {
+    const int zi = (int)(i % n), xy = (int)(i / n), yi = xy % n, xi = xy / n;
+    const float fn = (float)n;
+    x = __fmul_rn(__fsub_rn(__fdiv_rn((float)xi, fn), 0.5f), 2.f);
+    y = __fmul_rn(__fsub_rn(__fdiv_rn((float)yi, fn), 0.5f), 2.f);
+    z = __fmul_rn(__fsub_rn(__fdiv_rn((float)zi, fn), 0.5f), 2.f);
+}
+
+// ------------------------------------------------------------------ per-pair arithmetic, packed
+struct SrcX2 { f32x2 px, py, pz, nx, ny, nz; };
+
+// field: E += w n - 3 c R  with w = 1/(r^3+eps), c = (n.R) w / r^2     (20 packed FP32 ops)
+__device__ __forceinline__ void pair_field_x2(const SrcX2& s, f32x2 qx, f32x2 qy, f32x2 qz, f32x2 eps2,
+                                              f32x2& ax, f32x2& ay, f32x2& az,
+                                              f32x2& bx, f32x2& by, f32x2& bz) {
+    const f32x2 rx = sub2(s.px, qx), ry = sub2(s.py, qy), rz = sub2(s.pz, qz);
+    const f32x2 r2 = fma2(rz, rz, fma2(ry, ry, mul2(rx, rx)));
+    float r2a, r2b;
+    unpack2(r2, r2a, r2b);
+    const float ua = rsqrt_sfu(r2a), ub = rsqrt_sfu(r2b);                 // +inf on a coincident pair
+    const f32x2 u = pack2(ua, ub);
+    const f32x2 uc = pack2(fminf(ua, kRsqrtClamp), fminf(ub, kRsqrtClamp));
+    const f32x2 r = mul2(r2, u);                                          // 0*inf = NaN on a coincident pair
+    const f32x2 den = fma2(r2, r, eps2);                                  // |R|^3 + eps
+    float da, db;
+    unpack2(den, da, db);
+    const f32x2 w = pack2(fmaxf(rcp_sfu(da), 0.f), fmaxf(rcp_sfu(db), 0.f));   // NaN -> 0
+    const f32x2 d = fma2(s.nz, rz, fma2(s.ny, ry, mul2(s.nx, rx)));       // n.R (exactly 0 when R = 0)
+    const f32x2 c = mul2(mul2(d, w), mul2(uc, uc));
+    ax = fma2(w, s.nx, ax); ay = fma2(w, s.ny, ay); az = fma2(w, s.nz, az);
+    bx = fma2(c, rx, bx);   by = fma2(c, ry, by);   bz = fma2(c, rz, bz);
+}
+
+// potential: phi += (n.R) / r^3                                         (12 packed FP32 ops)
+__device__ __forceinline__ void pair_potential_x2(const SrcX2& s, f32x2 qx, f32x2 qy, f32x2 qz, f32x2& phi) {
+    const f32x2 rx = sub2(s.px, qx), ry = sub2(s.py, qy), rz = sub2(s.pz, qz);
+    const f32x2 r2 = fma2(rz, rz, fma2(ry, ry, mul2(rx, rx)));
+    float r2a, r2b;
+    unpack2(r2, r2a, r2b);
+    // coincident pair: n.R is exactly 0 and the clamped rsqrt^3 stays finite, so the pair adds 0
+    const f32x2 uc = pack2(fminf(rsqrt_sfu(r2a), kRsqrtClampPhi), fminf(rsqrt_sfu(r2b), kRsqrtClampPhi));
+    const f32x2 d = fma2(s.nz, rz, fma2(s.ny, ry, mul2(s.nx, rx)));
+    phi = fma2(d, mul2(mul2(uc, uc), uc), phi);
+}
+
+// ------------------------------------------------------------------ the all-pairs kernel
+// grid.x = target tiles of kBlock*2*TP targets, grid.y = source splits.
+template <int TP, bool kPotential>
+__global__ void __launch_bounds__(kBlock, (TP >= 4 ? 3 : (TP == 2 ? 5 : 8)))
+pairs_kernel(const ulonglong2* __restrict__ packed, int tiles_total, int nsplit,
+             const float* __restrict__ tgt, int64_t M, int64_t ld_t, int lattice_n,
+             float eps, float* __restrict__ partial, PairEpilogue ep) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    ulonglong2* stage_buf = reinterpret_cast<ulonglong2*>(smem_raw);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem_raw + size_t(kStages) * kTileBytes);
+
+    const int tid = threadIdx.x;
+    const int64_t tile_base = (int64_t)blockIdx.x * (kBlock * 2 * TP);
+    const int split = blockIdx.y;
+    const int t_begin = (int)((int64_t)tiles_total * split / nsplit);
+    const int t_end = (int)((int64_t)tiles_total * (split + 1) / nsplit);
+    const int n_tiles = t_end - t_begin;
+
+    if (tid == 0) {
+#pragma unroll
+        for (int s = 0; s < kStages; ++s) mbar_init(&bars[s], 1);
+        mbar_init_fence();
+    }
+    __syncthreads();
+    if (tid == 0) {
+        for (int i = 0; i < kStages && i < n_tiles; ++i) {
+            mbar_arrive_expect_tx(&bars[i], kTileBytes);
+            tma_bulk_g2s(stage_buf + size_t(i) * kTileSrc * 3,
+                         packed + size_t(t_begin + i) * kTileSrc * 3, kTileBytes, &bars[i]);
+        }
+    }
+
+    // ---- targets: lane a of pair j is target tile_base + (2j)*kBlock + tid, lane b the next kBlock
+    f32x2 qx[TP], qy[TP], qz[TP];
+    int64_t row[2 * TP];
+#pragma unroll
+    for (int j = 0; j < 2 * TP; ++j) {
+        const int64_t m = tile_base + (int64_t)j * kBlock + tid;
+        row[j] = -1;
+        if (m < M) {
+            const int64_t r = ep.tgt_idx ? ep.tgt_idx[m] : m;
+            if (!(ep.tgt_skip && ep.tgt_skip[r])) row[j] = r;
+        }
+    }
+#pragma unroll
+    for (int j = 0; j < TP; ++j) {
+        float x[2] = {0.f, 0.f}, y[2] = {0.f, 0.f}, z[2] = {0.f, 0.f};
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            const int64_t r = row[2 * j + h];
+            if (r >= 0) {
+                if (lattice_n > 0) lattice_node(r, lattice_n, x[h], y[h], z[h]);
+                else { const float* q = tgt + r * ld_t; x[h] = __ldg(q); y[h] = __ldg(q + 1); z[h] = __ldg(q + 2); }
+            }
+        }
+        qx[j] = pack2(x[0], x[1]); qy[j] = pack2(y[0], y[1]); qz[j] = pack2(z[0], z[1]);
+    }
+
+    const f32x2 zero2 = pack2(0.f, 0.f);
+    const f32x2 eps2 = pack2(eps, eps);
+    const f32x2 m3 = pack2(-3.f, -3.f);
+    // second-level totals (one per component per target pair)
+    f32x2 tx[TP], ty[TP], tz[TP];
+#pragma unroll
+    for (int j = 0; j < TP; ++j) { tx[j] = zero2; ty[j] = zero2; tz[j] = zero2; }
+
+    for (int it = 0; it < n_tiles; ++it) {
+        const int st = it % kStages;
+        mbar_wait(&bars[st], (uint32_t)((it / kStages) & 1));
+        const ulonglong2* sp = stage_buf + size_t(st) * kTileSrc * 3;
+
+        if (kPotential) {
+            f32x2 phi[TP];
+#pragma unroll
+            for (int j = 0; j < TP; ++j) phi[j] = zero2;
+#pragma unroll 2
+            for (int s = 0; s < kTileSrc; ++s) {
+                const ulonglong2 A = sp[3 * s], B = sp[3 * s + 1], C = sp[3 * s + 2];
+                const SrcX2 src{A.x, A.y, B.x, B.y, C.x, C.y};
+#pragma unroll
+                for (int j = 0; j < TP; ++j) pair_potential_x2(src, qx[j], qy[j], qz[j], phi[j]);
+            }
+#pragma unroll
+            for (int j = 0; j < TP; ++j) tx[j] = add2(tx[j], phi[j]);
+        } else {
+            f32x2 ax[TP], ay[TP], az[TP], bx[TP], by[TP], bz[TP];
+#pragma unroll
+            for (int j = 0; j < TP; ++j) { ax[j] = ay[j] = az[j] = bx[j] = by[j] = bz[j] = zero2; }
+#pragma unroll 2
+            for (int s = 0; s < kTileSrc; ++s) {
+                const ulonglong2 A = sp[3 * s], B = sp[3 * s + 1], C = sp[3 * s + 2];
+                const SrcX2 src{A.x, A.y, B.x, B.y, C.x, C.y};
+#pragma unroll
+                for (int j = 0; j < TP; ++j)
+                    pair_field_x2(src, qx[j], qy[j], qz[j], eps2, ax[j], ay[j], az[j], bx[j], by[j], bz[j]);
+            }
+#pragma unroll
+            for (int j = 0; j < TP; ++j) {               // tile sum = a - 3 b, folded into the totals
+                tx[j] = add2(tx[j], fma2(bx[j], m3, ax[j]));
+                ty[j] = add2(ty[j], fma2(by[j], m3, ay[j]));
+                tz[j] = add2(tz[j], fma2(bz[j], m3, az[j]));
+            }
+        }
+
+        __syncthreads();                                  // every warp is done with stage `st`
+        if (tid == 0 && it + kStages < n_tiles) {
+            mbar_arrive_expect_tx(&bars[st], kTileBytes);
+            tma_bulk_g2s(stage_buf + size_t(st) * kTileSrc * 3,
+                         packed + size_t(t_begin + it + kStages) * kTileSrc * 3, kTileBytes, &bars[st]);
+        }
+    }
+
+    // ---- write-out: direct epilogue, or one partial row per source split
+#pragma unroll
+    for (int j = 0; j < TP; ++j) {
+        float ex[2], ey[2], ez[2];
+        unpack2(tx[j], ex[0], ex[1]);
+        unpack2(ty[j], ey[0], ey[1]);
+        unpack2(tz[j], ez[0], ez[1]);
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            const int64_t r = row[2 * j + h];
+            if (r < 0) continue;
+            const int64_t m = tile_base + (int64_t)(2 * j + h) * kBlock + tid;
+            if (kPotential) {
+                if (partial) partial[(int64_t)split * M + m] = ex[h];
+                else apply_potential_epilogue(ep, r, ex[h]);
+            } else {
+                if (partial) {
+                    float* o = partial + ((int64_t)split * M + m) * 3;
+                    o[0] = ex[h]; o[1] = ey[h]; o[2] = ez[h];
+                } else {
+                    apply_field_epilogue(ep, r, ex[h], ey[h], ez[h]);
+                }
+            }
+        }
+    }
+}
+
+// ------------------------------------------------------------------ fixed-order reduction over source splits
+template <bool kPotential>
+__global__ void split_reduce_kernel(const float* __restrict__ partial, int nsplit, int64_t M, PairEpilogue ep) {
+    const int64_t m = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (m >= M) return;
+    const int64_t r = ep.tgt_idx ? ep.tgt_idx[m] : m;
+    if (ep.tgt_skip && ep.tgt_skip[r]) return;
+    if (kPotential) {
+        float acc = 0.f;
+        for (int k = 0; k < nsplit; ++k) acc += partial[(int64_t)k * M + m];
+        apply_potential_epilogue(ep, r, acc);
+    } else {
+        float ex = 0.f, ey = 0.f, ez = 0.f;
+        for (int k = 0; k < nsplit; ++k) {
+            const float* p = partial + ((int64_t)k * M + m) * 3;
+            ex += p[0]; ey += p[1]; ez += p[2];
+        }
+        apply_field_epilogue(ep, r, ex, ey, ez);
+    }
+}
+
+// single-CTA deterministic sum (fixed strided order + fixed tree); scale applied last
+__global__ void __launch_bounds__(1024) sum_kernel(const float* __restrict__ in, int64_t n, int64_t stride,
+                                                   float scale, float* __restrict__ out) {
+    __shared__ float warp_part[32];
+    float acc = 0.f;
+    for (int64_t i = threadIdx.x; i < n; i += blockDim.x) acc += in[i * stride];
+    acc = warp_sum(acc);
+    if ((threadIdx.x & 31) == 0) warp_part[threadIdx.x >> 5] = acc;
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        float v = threadIdx.x < (blockDim.x >> 5) ? warp_part[threadIdx.x] : 0.f;
+        v = warp_sum(v);
+        if (threadIdx.x == 0) *out = v * scale;
+    }
+}
+
+std::atomic<int64_t> g_launches{0};
+
+// tuning overrides, read once (immutable afterwards, so the library stays re-entrant)
+int env_int(const char* name) {
+    const char* v = getenv(name);
+    return v ? atoi(v) : 0;
+}
+
+inline int64_t round_up(int64_t a, int64_t b) { return (a + b - 1) / b * b; }
+
+}  // namespace
+
+int64_t launch_count() { return g_launches.load(); }
+void count_launch(int n) { g_launches.fetch_add(n); }
+
+// ------------------------------------------------------------------ planning
+int sm_count_cached() {
+    static std::atomic<int> cached[64];
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
+    int v = cached[dev].load();
+    if (v == 0) {
+        cudaDeviceProp prop;
+        v = (cudaGetDeviceProperties(&prop, dev) == cudaSuccess) ? prop.multiProcessorCount : 148;
+        cached[dev].store(v);
+    }
+    return v;
+}
+
+PairPlan make_pair_plan(int64_t S, int64_t M, int sm_count, int force_tp, int force_nsplit) {
+    PairPlan p;
+    p.tiles_total = (int)((S + kTileSrc - 1) / kTileSrc);
+    if (p.tiles_total < 1) p.tiles_total = 1;
+    p.S_pad = (int64_t)p.tiles_total * kTileSrc;
+    // targets per thread: enough CTAs to cover the machine, then as many registers-resident targets as possible
+    const int64_t full_tp4 = (int64_t)sm_count * 3 * kBlock * 8;
+    const int64_t full_tp2 = (int64_t)sm_count * 5 * kBlock * 4;
+    p.tp = (M >= full_tp4) ? 4 : (M >= full_tp2 / 2 ? 2 : 1);
+    if (force_tp <= 0) force_tp = env_int("DNP_FORCE_TP");
+    if (force_nsplit <= 0) force_nsplit = env_int("DNP_FORCE_NSPLIT");
+    if (force_tp == 1 || force_tp == 2 || force_tp == 4) p.tp = force_tp;
+    const int resident = p.tp >= 4 ? 3 : (p.tp == 2 ? 5 : 8);
+    p.m_tiles = (int)((M + (int64_t)kBlock * 2 * p.tp - 1) / ((int64_t)kBlock * 2 * p.tp));
+    if (p.m_tiles < 1) p.m_tiles = 1;
+    // source splits: pick the split count whose CTA count fills whole waves best
+    const int64_t wave = (int64_t)sm_count * resident;
+    int best = 1;
+    double best_eff = -1.0;
+    const int max_split = (int)((p.tiles_total < 64) ? p.tiles_total : 64);
+    for (int k = 1; k <= max_split; ++k) {
+        if (k > 1 && p.tiles_total / k < 2) break;
+        const int64_t ctas = (int64_t)p.m_tiles * k;
+        const int64_t waves = (ctas + wave - 1) / wave;
+        double eff = (double)ctas / (double)(waves * wave);
+        if (ctas >= 6 * wave) eff = 1.0 - 1e-9 * k;                // deep enough: stop splitting
+        if (eff > best_eff + 0.01) { best_eff = eff; best = k; }
+    }
+    p.nsplit = best;
+    if (force_nsplit > 0) p.nsplit = force_nsplit > p.tiles_total ? p.tiles_total : force_nsplit;
+    p.packed_bytes = (size_t)round_up(p.S_pad * kSrcBytes, 256);
+    p.partial_bytes = p.nsplit > 1 ? (size_t)round_up((int64_t)p.nsplit * M * 3 * sizeof(float), 256) : 0;
+    return p;
+}
+
+size_t pairs_workspace_bytes(int64_t S, int64_t M) {
+    // exactly what run_pairs will carve (same plan), plus the per-target scratch
+    // row of the DOT / lattice paths and one scalar slot
+    if (S < 1) S = 1;
+    if (M < 1) M = 1;
+    const PairPlan p = make_pair_plan(S, M, sm_count_cached(), 0, 0);
+    return p.packed_bytes + p.partial_bytes + (size_t)round_up(M * 4, 256) + 1024;
+}
+
+// ------------------------------------------------------------------ launchers
+template <int TP, bool kPot>
+static int launch_pairs_tp(const PairPlan& plan, const ulonglong2* packed, const float* tgt, int64_t M,
+                           int64_t ld_t, int lattice_n, float eps, float* partial, const PairEpilogue& ep,
+                           cudaStream_t stream) {
+    dim3 grid((unsigned)plan.m_tiles, (unsigned)plan.nsplit);
+    pairs_kernel<TP, kPot><<<grid, kBlock, kSmemBytes, stream>>>(packed, plan.tiles_total, plan.nsplit, tgt, M,
+                                                                 ld_t, lattice_n, eps, partial, ep);
+    count_launch(1);
+    return DNP_OK;
+}
+
+int run_pairs(bool potential, const float* src, int64_t S, int64_t ld_s, const int64_t* src_idx,
+              const float* tgt, int64_t M, int64_t ld_t, int lattice_n, float eps,
+              const PairEpilogue& ep, void* workspace, size_t workspace_bytes, cudaStream_t stream,
+              int force_tp, int force_nsplit) {
+    if (M <= 0) return DNP_OK;
+    const PairPlan plan = make_pair_plan(S, M, sm_count_cached(), force_tp, force_nsplit);
+    if (!workspace || workspace_bytes < plan.packed_bytes + plan.partial_bytes) {
+        set_error("workspace too small: need %zu bytes, got %zu", plan.packed_bytes + plan.partial_bytes,
+                  workspace_bytes);
+        return DNP_ERR_WORKSPACE;
+    }
+    float4* packed = reinterpret_cast<float4*>(workspace);
+    float* partial = plan.nsplit > 1
+                         ? reinterpret_cast<float*>(reinterpret_cast<unsigned char*>(workspace) + plan.packed_bytes)
+                         : nullptr;
+    {
+        const int threads = 256;
+        const unsigned blocks = (unsigned)((plan.S_pad + threads - 1) / threads);
+        pack_sources_kernel<<<blocks, threads, 0, stream>>>(src, S < 0 ? 0 : S, ld_s, src_idx, plan.S_pad, packed);
+        count_launch(1);
+    }
+    const ulonglong2* pk = reinterpret_cast<const ulonglong2*>(packed);
+    int rc;
+#define DNP_LAUNCH(TP)                                                                                       \
+    rc = potential ? launch_pairs_tp<TP, true>(plan, pk, tgt, M, ld_t, lattice_n, eps, partial, ep, stream)  \
+                   : launch_pairs_tp<TP, false>(plan, pk, tgt, M, ld_t, lattice_n, eps, partial, ep, stream)
+    switch (plan.tp) {
+        case 4: DNP_LAUNCH(4); break;
+        case 2: DNP_LAUNCH(2); break;
+        default: DNP_LAUNCH(1); break;
+    }
+#undef DNP_LAUNCH
+    if (rc != DNP_OK) return rc;
+    if (plan.nsplit > 1) {
+        const int threads = 256;
+        const unsigned blocks = (unsigned)((M + threads - 1) / threads);
+        if (potential) split_reduce_kernel<true><<<blocks, threads, 0, stream>>>(partial, plan.nsplit, M, ep);
+        else split_reduce_kernel<false><<<blocks, threads, 0, stream>>>(partial, plan.nsplit, M, ep);
+        count_launch(1);
+    }
+    DNP_CHECK_CUDA(cudaGetLastError());
+    return DNP_OK;
+}
+
+int run_sum(const float* in, int64_t n, int64_t stride, float scale, float* out, cudaStream_t stream) {
+    sum_kernel<<<1, 1024, 0, stream>>>(in, n, stride, scale, out);
+    count_launch(1);
+    DNP_CHECK_CUDA(cudaGetLastError());
+    return DNP_OK;
+}
+
+}  // namespace dnp

@@ -1,0 +1,52 @@
+// dnp_pairs.h -- internal interface of the all-pairs kernels (dnp_pairs.cu).
+#pragma once
+
+#include <atomic>
+#include <cuda_runtime.h>
+#include <stddef.h>
+#include <stdint.h>
+
+#include "dipole.h"
+
+namespace dnp {
+
+// Fused epilogue description (K7).  Rows are addressed by r = tgt_idx ? tgt_idx[m] : m.
+struct PairEpilogue {
+    int mode = DNP_EPI_STORE;
+    float* out = nullptr;
+    int64_t ld_out = 3;
+    float* normals = nullptr;
+    int64_t ld_n = 6;
+    const int64_t* tgt_idx = nullptr;
+    const uint8_t* tgt_skip = nullptr;
+    int32_t* nonfinite = nullptr;
+};
+
+struct PairPlan {
+    int tp = 2;            // target pairs per thread (2*tp targets)
+    int nsplit = 1;        // source splits (grid.y)
+    int tiles_total = 1;   // 256-source tiles
+    int m_tiles = 1;       // target tiles (grid.x)
+    int64_t S_pad = 0;
+    size_t packed_bytes = 0;
+    size_t partial_bytes = 0;
+};
+
+int sm_count_cached();
+PairPlan make_pair_plan(int64_t S, int64_t M, int sm_count, int force_tp, int force_nsplit);
+size_t pairs_workspace_bytes(int64_t S, int64_t M);
+
+// potential == true: phi epilogue (STORE/ACCUM on a scalar per row).
+// lattice_n > 0: targets are the nodes of the n^3 lattice (tgt ignored).
+int run_pairs(bool potential, const float* src, int64_t S, int64_t ld_s, const int64_t* src_idx,
+              const float* tgt, int64_t M, int64_t ld_t, int lattice_n, float eps,
+              const PairEpilogue& ep, void* workspace, size_t workspace_bytes, cudaStream_t stream,
+              int force_tp = 0, int force_nsplit = 0);
+
+// out[0] = scale * sum_i in[i*stride], single CTA, fixed order.
+int run_sum(const float* in, int64_t n, int64_t stride, float scale, float* out, cudaStream_t stream);
+
+int64_t launch_count();
+void count_launch(int n);
+
+}  // namespace dnp

@@ -1,0 +1,181 @@
+// dnp_scores.cu -- patch-pair flip scores (K3) and per-patch interactions (K4).
+//
+// K3 replaces the per-edge chain field_grad -> (E*n).sum(-1).sum() -> .cpu()
+// of field_utils.field_edge_calculator (field_utils.py:145-160) for a whole
+// edge list in one launch: one CTA per edge, source patch staged through shared
+// memory, targets in registers, fixed-order block reduction, no atomics.
+// K4 replaces the list comprehension at field_utils.py:244,316 (one tiny launch
+// and one host sync per remaining patch per step) and the abs().argmax() at
+// :247,319 by two launches and no host synchronisation.
+#include "dnp_common.cuh"
+#include "dnp_pairs.h"
+#include "dnp_scores.h"
+
+namespace dnp {
+
+namespace {
+
+constexpr int kEdgeThreads = 256;
+constexpr int kEdgeChunk = 512;                   // sources staged per pass (12 KB)
+constexpr float kRsqrtClamp = 1.152921504606847e18f;
+
+// scalar twin of pair_field_x2 (dnp_pairs.cu): same formula, same SFU approximations
+__device__ __forceinline__ void pair_field_scalar(float px, float py, float pz, float nx, float ny, float nz,
+                                                  float qx, float qy, float qz, float eps,
+                                                  float& ax, float& ay, float& az, float& bx, float& by, float& bz) {
+    const float rx = px - qx, ry = py - qy, rz = pz - qz;
+    const float r2 = fmaf(rz, rz, fmaf(ry, ry, rx * rx));
+    const float u = rsqrt_sfu(r2);
+    const float uc = fminf(u, kRsqrtClamp);
+    const float den = fmaf(r2, r2 * u, eps);
+    const float w = fmaxf(rcp_sfu(den), 0.f);
+    const float d = fmaf(nz, rz, fmaf(ny, ry, nx * rx));
+    const float c = (d * w) * (uc * uc);
+    ax = fmaf(w, nx, ax); ay = fmaf(w, ny, ay); az = fmaf(w, nz, az);
+    bx = fmaf(c, rx, bx); by = fmaf(c, ry, by); bz = fmaf(c, rz, bz);
+}
+
+__device__ __forceinline__ float block_sum_256(float v, float* warp_part) {
+    v = warp_sum(v);
+    if ((threadIdx.x & 31) == 0) warp_part[threadIdx.x >> 5] = v;
+    __syncthreads();
+    float r = 0.f;
+    if (threadIdx.x < 32) {
+        r = threadIdx.x < (blockDim.x >> 5) ? warp_part[threadIdx.x] : 0.f;
+        r = warp_sum(r);
+    }
+    return r;   // valid in warp 0
+}
+
+__global__ void __launch_bounds__(kEdgeThreads)
+edge_interactions_kernel(const float* __restrict__ pts, int64_t ld, const int64_t* __restrict__ perm,
+                         const int64_t* __restrict__ offsets, const int64_t* __restrict__ edges, float eps,
+                         float* __restrict__ out) {
+    __shared__ float4 s_src[kEdgeChunk * 2];      // [x y z nx] [ny nz 0 0]
+    __shared__ float warp_part[32];
+    const int64_t e = blockIdx.x;
+    const int64_t ps = edges[2 * e], pt = edges[2 * e + 1];
+    const int64_t s0 = offsets[ps], ns = offsets[ps + 1] - s0;
+    const int64_t t0 = offsets[pt], nt = offsets[pt + 1] - t0;
+    float total = 0.f;
+    for (int64_t tb = 0; tb < nt; tb += kEdgeThreads) {
+        const int64_t t = tb + threadIdx.x;
+        float qx = 0.f, qy = 0.f, qz = 0.f, tnx = 0.f, tny = 0.f, tnz = 0.f;
+        if (t < nt) {
+            const float* q = pts + perm[t0 + t] * ld;
+            qx = q[0]; qy = q[1]; qz = q[2]; tnx = q[3]; tny = q[4]; tnz = q[5];
+        }
+        float ex = 0.f, ey = 0.f, ez = 0.f;
+        for (int64_t sb = 0; sb < ns; sb += kEdgeChunk) {
+            const int n_here = (int)min((int64_t)kEdgeChunk, ns - sb);
+            __syncthreads();
+            for (int i = threadIdx.x; i < n_here; i += kEdgeThreads) {
+                const float* p = pts + perm[s0 + sb + i] * ld;
+                s_src[2 * i] = make_float4(p[0], p[1], p[2], p[3]);
+                s_src[2 * i + 1] = make_float4(p[4], p[5], 0.f, 0.f);
+            }
+            __syncthreads();
+            float ax = 0.f, ay = 0.f, az = 0.f, bx = 0.f, by = 0.f, bz = 0.f;
+#pragma unroll 4
+            for (int i = 0; i < n_here; ++i) {
+                const float4 A = s_src[2 * i], B = s_src[2 * i + 1];
+                pair_field_scalar(A.x, A.y, A.z, A.w, B.x, B.y, qx, qy, qz, eps, ax, ay, az, bx, by, bz);
+            }
+            ex += fmaf(-3.f, bx, ax); ey += fmaf(-3.f, by, ay); ez += fmaf(-3.f, bz, az);
+        }
+        if (t < nt) total += __fadd_rn(__fadd_rn(__fmul_rn(ex, tnx), __fmul_rn(ey, tny)), __fmul_rn(ez, tnz));
+    }
+    __syncthreads();
+    const float r = block_sum_256(total, warp_part);
+    if (threadIdx.x == 0) out[e] = r;
+}
+
+// out[p] = sum_{t in patch p} E_t . n_t  (0 for inactive patches)
+__global__ void __launch_bounds__(kEdgeThreads)
+patch_interactions_kernel(const float* __restrict__ E, int64_t ld_e, const float* __restrict__ normals,
+                          int64_t ld_n, const int64_t* __restrict__ perm, const int64_t* __restrict__ offsets,
+                          const uint8_t* __restrict__ active, float* __restrict__ out) {
+    __shared__ float warp_part[32];
+    const int64_t p = blockIdx.x;
+    if (active && !active[p]) {
+        if (threadIdx.x == 0) out[p] = 0.f;
+        return;
+    }
+    const int64_t t0 = offsets[p], nt = offsets[p + 1] - t0;
+    float acc = 0.f;
+    for (int64_t t = threadIdx.x; t < nt; t += kEdgeThreads) {
+        const int64_t r = perm[t0 + t];
+        const float* e = E + r * ld_e;
+        const float* n = normals + r * ld_n;
+        acc += __fadd_rn(__fadd_rn(__fmul_rn(e[0], n[0]), __fmul_rn(e[1], n[1])), __fmul_rn(e[2], n[2]));
+    }
+    const float r = block_sum_256(acc, warp_part);
+    if (threadIdx.x == 0) out[p] = r;
+}
+
+// first maximal |out[p]| among active patches (torch abs().argmax() on the remaining list)
+__global__ void __launch_bounds__(1024)
+patch_argmax_kernel(const float* __restrict__ vals, const uint8_t* __restrict__ active, int64_t P,
+                    int32_t* __restrict__ best_idx, float* __restrict__ best_val) {
+    __shared__ unsigned long long warp_best[32];
+    unsigned long long best = 0ull;
+    for (int64_t p = threadIdx.x; p < P; p += blockDim.x) {
+        if (active && !active[p]) continue;
+        const unsigned long long k =
+            ((unsigned long long)__float_as_uint(fabsf(vals[p])) << 32) | (0xffffffffu - (uint32_t)p);
+        if (k > best) best = k;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const unsigned long long other = __shfl_xor_sync(0xffffffffu, best, o);
+        if (other > best) best = other;
+    }
+    if ((threadIdx.x & 31) == 0) warp_best[threadIdx.x >> 5] = best;
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        best = threadIdx.x < (blockDim.x >> 5) ? warp_best[threadIdx.x] : 0ull;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const unsigned long long other = __shfl_xor_sync(0xffffffffu, best, o);
+            if (other > best) best = other;
+        }
+        if (threadIdx.x == 0) {
+            if (best == 0ull) { *best_idx = -1; *best_val = 0.f; }
+            else {
+                const int32_t idx = (int32_t)(0xffffffffu - (uint32_t)best);
+                *best_idx = idx;
+                *best_val = vals[idx];
+            }
+        }
+    }
+}
+
+}  // namespace
+
+int run_edge_interactions_batched(const float* pts, int64_t ld, const int64_t* perm, const int64_t* offsets,
+                                  int64_t P, const int64_t* edges, int64_t n_edges, float eps, float* out,
+                                  cudaStream_t stream) {
+    (void)P;
+    if (n_edges <= 0) return DNP_OK;
+    edge_interactions_kernel<<<(unsigned)n_edges, kEdgeThreads, 0, stream>>>(pts, ld, perm, offsets, edges, eps, out);
+    count_launch(1);
+    DNP_CHECK_CUDA(cudaGetLastError());
+    return DNP_OK;
+}
+
+int run_patch_interactions(const float* E, int64_t ld_e, const float* normals, int64_t ld_n, const int64_t* perm,
+                           const int64_t* offsets, int64_t P, const uint8_t* active, float* out,
+                           int32_t* best_idx, float* best_val, cudaStream_t stream) {
+    if (P <= 0) return DNP_OK;
+    patch_interactions_kernel<<<(unsigned)P, kEdgeThreads, 0, stream>>>(E, ld_e, normals, ld_n, perm, offsets, active,
+                                                                       out);
+    count_launch(1);
+    if (best_idx && best_val) {
+        patch_argmax_kernel<<<1, 1024, 0, stream>>>(out, active, P, best_idx, best_val);
+        count_launch(1);
+    }
+    DNP_CHECK_CUDA(cudaGetLastError());
+    return DNP_OK;
+}
+
+}  // namespace dnp

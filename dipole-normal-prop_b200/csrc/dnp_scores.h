@@ -1,0 +1,24 @@
+// dnp_scores.h -- internal interface of the score / driver kernels
+// (dnp_scores.cu, dnp_points.cu, dnp_microbench.cu).
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace dnp {
+
+int run_edge_interactions_batched(const float* pts, int64_t ld, const int64_t* perm, const int64_t* offsets,
+                                  int64_t P, const int64_t* edges, int64_t n_edges, float eps, float* out,
+                                  cudaStream_t stream);
+
+int run_patch_interactions(const float* E, int64_t ld_e, const float* normals, int64_t ld_n, const int64_t* perm,
+                           const int64_t* offsets, int64_t P, const uint8_t* active, float* out,
+                           int32_t* best_idx, float* best_val, cudaStream_t stream);
+
+int64_t points_max_n();
+int run_points_propagate(float* pts, int64_t N, int64_t ld, int64_t start, float eps, int diffuse,
+                         int32_t* order, uint8_t* flipped, cudaStream_t stream);
+
+int run_microbench(int kind, int iters, float* ms_out, double* ops_out, cudaStream_t stream);
+
+}  // namespace dnp

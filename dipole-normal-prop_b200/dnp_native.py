@@ -1,0 +1,312 @@
+"""ctypes binding of libdipole.so (include/dipole.h) for PyTorch tensors.
+
+PyTorch is plumbing here: it owns device memory and streams.  All arithmetic of
+the dipole hot path happens in the hand-written sm_100a kernels behind the C
+ABI.  There is NO CPU fallback: importing this module without the built library
+or calling it without a CUDA device raises.
+"""
+import ctypes
+import os
+import threading
+
+import torch
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libdipole.so")
+
+DNP_OK = 0
+EPI_STORE, EPI_ACCUM, EPI_SIGN_GE, EPI_SIGN_GT, EPI_NORMALIZE, EPI_DOT = range(6)
+
+# every symbol include/dipole.h declares: (name, restype, argtypes)
+_vp, _i64, _i32, _f32 = ctypes.c_void_p, ctypes.c_int64, ctypes.c_int, ctypes.c_float
+_sz = ctypes.c_size_t
+SYMBOLS = [
+    ("dnp_last_error", ctypes.c_char_p, []),
+    ("dnp_version", _i32, []),
+    ("dnp_device_info", _i32, [ctypes.POINTER(_i32)] * 4),
+    ("dnp_pairs_workspace_bytes", _sz, [_i64, _i64]),
+    ("dnp_potential_f32", _i32, [_vp, _i64, _i64, _vp, _vp, _i64, _i64, _vp, _i32, _vp, _sz, _vp]),
+    ("dnp_lattice_mean_potential_f32", _i32, [_vp, _i64, _i64, _i32, _vp, _vp, _vp, _sz, _vp]),
+    ("dnp_field_grad_f32", _i32, [_vp, _i64, _i64, _vp, _i64, _i64, _f32, _vp, _i64, _i32, _vp, _sz, _vp]),
+    ("dnp_field_apply_f32", _i32, [_vp, _i64, _i64, _vp, _vp, _i64, _i64, _vp, _vp, _f32, _i32,
+                                   _vp, _i64, _vp, _i64, _vp, _vp, _sz, _vp]),
+    ("dnp_edge_interaction_f32", _i32, [_vp, _i64, _i64, _vp, _i64, _i64, _f32, _vp, _vp, _sz, _vp]),
+    ("dnp_edge_interactions_batched_f32", _i32, [_vp, _i64, _vp, _vp, _i64, _vp, _i64, _f32, _vp, _vp]),
+    ("dnp_patch_interactions_f32", _i32, [_vp, _i64, _vp, _i64, _vp, _vp, _i64, _vp, _vp, _vp, _vp, _vp]),
+    ("dnp_points_max_n", _i64, []),
+    ("dnp_points_propagate_f32", _i32, [_vp, _i64, _i64, _i64, _f32, _i32, _vp, _vp, _vp]),
+    ("dnp_field_grad_host_f32", _i32, [_vp, _i64, _i64, _vp, _i64, _i64, _f32, _vp, _i32]),
+    ("dnp_potential_host_f32", _i32, [_vp, _i64, _i64, _vp, _i64, _i64, _vp, _i32]),
+    ("dnp_launch_count", _i64, []),
+    ("dnp_microbench", _i32, [_i32, _i32, ctypes.POINTER(_f32), ctypes.POINTER(ctypes.c_double), _vp]),
+]
+
+_lib = None
+_lock = threading.Lock()
+
+
+class DipoleError(RuntimeError):
+    pass
+
+
+def load():
+    """Load libdipole.so (once).  Fails loudly if the CUDA extension is missing."""
+    global _lib
+    if _lib is None:
+        with _lock:
+            if _lib is None:
+                if not os.path.exists(LIB_PATH):
+                    raise ImportError(
+                        f"{LIB_PATH} is missing: build it with `python __graft_entry__.py` "
+                        "(or `make -C dipole-normal-prop_b200/csrc`). There is no CPU fallback.")
+                lib = ctypes.CDLL(LIB_PATH)
+                for name, restype, argtypes in SYMBOLS:
+                    fn = getattr(lib, name)
+                    fn.restype = restype
+                    fn.argtypes = argtypes
+                _lib = lib
+    return _lib
+
+
+def _check(rc):
+    if rc != DNP_OK:
+        raise DipoleError(f"libdipole error {rc}: {load().dnp_last_error().decode()}")
+
+
+def require_cuda():
+    if not torch.cuda.is_available():
+        raise DipoleError("dipole-normal-prop_b200 needs a CUDA (sm_100a) device; there is no CPU fallback")
+
+
+def _stream(t):
+    return ctypes.c_void_p(torch.cuda.current_stream(t.device).cuda_stream)
+
+
+def _rows(t, min_cols, name):
+    """Validate a [N, >=min_cols] float32 CUDA tensor; returns (tensor, ld) with unit column stride."""
+    if not isinstance(t, torch.Tensor):
+        raise TypeError(f"{name} must be a torch.Tensor")
+    if t.dtype != torch.float32:
+        raise TypeError(f"{name} must be float32 (got {t.dtype}); the B200 kernels are FP32-only")
+    if not t.is_cuda:
+        raise ValueError(f"{name} must be a CUDA tensor")
+    if t.dim() != 2 or t.shape[1] < min_cols:
+        raise ValueError(f"{name} must be [N, >={min_cols}] (got {tuple(t.shape)})")
+    if t.shape[0] > 0 and (t.stride(1) != 1 or t.stride(0) < t.shape[1]):
+        t = t.contiguous()
+    n = t.shape[0]
+    ld = t.stride(0) if n > 1 else max(int(t.stride(0)) if n == 1 else 0, t.shape[1])
+    return t, int(ld)
+
+
+def _ptr(t):
+    return ctypes.c_void_p(t.data_ptr()) if t is not None else ctypes.c_void_p(0)
+
+
+def _workspace(S, M, device):
+    nbytes = load().dnp_pairs_workspace_bytes(int(S), int(M))
+    return torch.empty(nbytes, dtype=torch.uint8, device=device), nbytes
+
+
+def _idx(t, device, name):
+    if t is None:
+        return None
+    if t.dtype != torch.int64 or t.device != device or not t.is_contiguous():
+        t = t.to(device=device, dtype=torch.int64).contiguous()
+    return t
+
+
+def _mask(t, device, name):
+    if t is None:
+        return None
+    if t.dtype == torch.bool:
+        t = t.to(device).contiguous().view(torch.uint8)
+    elif t.dtype != torch.uint8:
+        raise TypeError(f"{name} must be bool or uint8")
+    return t.to(device).contiguous()
+
+
+# ------------------------------------------------------------------ leaf calls (device tensors)
+def potential(sources, targets, out=None, accumulate=False, src_idx=None):
+    lib = load()
+    src, ld_s = _rows(sources, 6, "sources")
+    tgt, ld_t = _rows(targets, 3, "targets")
+    M = tgt.shape[0]
+    if out is None:
+        out = torch.empty(M, dtype=torch.float32, device=tgt.device)
+    src_idx = _idx(src_idx, tgt.device, "src_idx")
+    S = src.shape[0] if src_idx is None else src_idx.numel()
+    if M == 0:
+        return out
+    with torch.cuda.device(tgt.device):
+        ws, nbytes = _workspace(S, M, tgt.device)
+        _check(lib.dnp_potential_f32(_ptr(src), S, ld_s, _ptr(src_idx), _ptr(tgt), M, ld_t, _ptr(out),
+                                     int(accumulate), _ptr(ws), nbytes, _stream(tgt)))
+    return out
+
+
+def lattice_mean_potential(sources, n=10, want_phi=False):
+    lib = load()
+    src, ld_s = _rows(sources, 6, "pc")
+    dev = src.device
+    mean = torch.empty((), dtype=torch.float32, device=dev)
+    phi = torch.empty(n ** 3, dtype=torch.float32, device=dev) if want_phi else None
+    with torch.cuda.device(dev):
+        ws, nbytes = _workspace(src.shape[0], n ** 3, dev)
+        _check(lib.dnp_lattice_mean_potential_f32(_ptr(src), src.shape[0], ld_s, int(n), _ptr(phi), _ptr(mean),
+                                                  _ptr(ws), nbytes, _stream(src)))
+    return (mean, phi) if want_phi else mean
+
+
+def field_apply(sources, targets, eps, mode, out=None, ld_out=None, normals=None, src_idx=None, tgt_idx=None,
+                tgt_skip=None, nonfinite=None):
+    """General all-pairs field call with a fused epilogue (dnp_field_apply_f32).
+
+    `targets` is the FULL row array; tgt_idx / tgt_skip select rows of it, and
+    `out` / `normals` are addressed by the same rows."""
+    lib = load()
+    src, ld_s = _rows(sources, 6, "sources")
+    tgt, ld_t = _rows(targets, 3, "targets")
+    dev = tgt.device
+    src_idx = _idx(src_idx, dev, "src_idx")
+    tgt_idx = _idx(tgt_idx, dev, "tgt_idx")
+    tgt_skip = _mask(tgt_skip, dev, "tgt_skip")
+    S = src.shape[0] if src_idx is None else src_idx.numel()
+    M = tgt.shape[0] if tgt_idx is None else tgt_idx.numel()
+    ld_n = 0
+    if normals is not None:
+        if normals.dtype != torch.float32 or not normals.is_cuda or normals.stride(-1) != 1:
+            raise ValueError("normals must be a float32 CUDA view with unit column stride")
+        ld_n = normals.stride(0) if normals.dim() == 2 else 3
+    if out is not None and ld_out is None:
+        ld_out = out.stride(0) if out.dim() == 2 else 1
+    if M == 0:
+        return out
+    with torch.cuda.device(dev):
+        ws, nbytes = _workspace(S, M, dev)
+        _check(lib.dnp_field_apply_f32(_ptr(src), S, ld_s, _ptr(src_idx), _ptr(tgt), M, ld_t, _ptr(tgt_idx),
+                                       _ptr(tgt_skip), float(eps), int(mode), _ptr(out), int(ld_out or 0),
+                                       _ptr(normals), int(ld_n), _ptr(nonfinite), _ptr(ws), nbytes, _stream(tgt)))
+    return out
+
+
+def field_grad(sources, targets, eps=1e-5, out=None, accumulate=False):
+    tgt, _ = _rows(targets, 3, "targets")
+    if out is None:
+        out = torch.empty(tgt.shape[0], 3, dtype=torch.float32, device=tgt.device)
+    return field_apply(sources, tgt, eps, EPI_ACCUM if accumulate else EPI_STORE, out=out)
+
+
+def edge_interaction(S_pts, T_pts, eps=1e-5):
+    """sum_t n_t . E_S(t) as a 0-d device tensor (dnp_edge_interaction_f32)."""
+    lib = load()
+    s, ld_s = _rows(S_pts, 6, "sources")
+    t, ld_t = _rows(T_pts, 6, "means")
+    out = torch.empty((), dtype=torch.float32, device=t.device)
+    with torch.cuda.device(t.device):
+        ws, nbytes = _workspace(s.shape[0], t.shape[0], t.device)
+        _check(lib.dnp_edge_interaction_f32(_ptr(s), s.shape[0], ld_s, _ptr(t), t.shape[0], ld_t, float(eps),
+                                            _ptr(out), _ptr(ws), nbytes, _stream(t)))
+    return out
+
+
+def edge_interactions_batched(pts, perm, offsets, edges, eps=1e-5):
+    lib = load()
+    p, ld = _rows(pts, 6, "pts")
+    dev = p.device
+    perm = _idx(perm, dev, "perm")
+    offsets = _idx(offsets, dev, "offsets")
+    edges = _idx(edges, dev, "edges")
+    nE = edges.shape[0]
+    out = torch.empty(nE, dtype=torch.float32, device=dev)
+    with torch.cuda.device(dev):
+        _check(lib.dnp_edge_interactions_batched_f32(_ptr(p), ld, _ptr(perm), _ptr(offsets), offsets.numel() - 1,
+                                                     _ptr(edges), nE, float(eps), _ptr(out), _stream(p)))
+    return out
+
+
+def patch_interactions(E, pts, perm, offsets, active=None, want_best=True):
+    """out[p] = sum_{t in p} E_t . n_t ; optionally the first abs-argmax over active patches."""
+    lib = load()
+    p, ld = _rows(pts, 6, "pts")
+    e, ld_e = _rows(E, 3, "E")
+    dev = p.device
+    P = offsets.numel() - 1
+    out = torch.empty(P, dtype=torch.float32, device=dev)
+    best_idx = torch.empty((), dtype=torch.int32, device=dev) if want_best else None
+    best_val = torch.empty((), dtype=torch.float32, device=dev) if want_best else None
+    active = _mask(active, dev, "active")
+    normals = p[:, 3:]
+    with torch.cuda.device(dev):
+        _check(lib.dnp_patch_interactions_f32(_ptr(e), ld_e, _ptr(normals), ld, _ptr(perm), _ptr(offsets), P,
+                                              _ptr(active), _ptr(out), _ptr(best_idx), _ptr(best_val), _stream(p)))
+    return out, best_idx, best_val
+
+
+def points_propagate(pts, diffuse=False, starting_point=0, eps=1e-6, want_trace=False):
+    """In-place per-point greedy propagation on a [N,6] float32 CUDA tensor."""
+    lib = load()
+    if pts.dtype != torch.float32 or not pts.is_cuda or pts.dim() != 2 or pts.shape[1] != 6:
+        raise ValueError("pts must be a [N,6] float32 CUDA tensor")
+    if pts.stride(1) != 1:
+        raise ValueError("pts must have unit column stride")
+    N = pts.shape[0]
+    order = torch.empty(N, dtype=torch.int32, device=pts.device) if want_trace else None
+    flipped = torch.empty(N, dtype=torch.uint8, device=pts.device) if want_trace else None
+    with torch.cuda.device(pts.device):
+        _check(lib.dnp_points_propagate_f32(_ptr(pts), N, pts.stride(0) if N > 1 else 6, int(starting_point),
+                                            float(eps), int(bool(diffuse)), _ptr(order), _ptr(flipped), _stream(pts)))
+    return (order, flipped) if want_trace else None
+
+
+# ------------------------------------------------------------------ host-buffer calls (CPU tensors in, CPU tensors out)
+def _host_rows(t, min_cols, name):
+    if t.dtype != torch.float32:
+        raise TypeError(f"{name} must be float32 (got {t.dtype})")
+    if t.dim() != 2 or t.shape[1] < min_cols:
+        raise ValueError(f"{name} must be [N, >={min_cols}]")
+    if t.shape[0] > 0 and (t.stride(1) != 1 or t.stride(0) < t.shape[1]):
+        t = t.contiguous()
+    return t, int(t.stride(0) if t.shape[0] > 1 else t.shape[1])
+
+
+def field_grad_host(sources, targets, eps=1e-5, device=None, out=None):
+    require_cuda()
+    lib = load()
+    s, ld_s = _host_rows(sources, 6, "sources")
+    t, ld_t = _host_rows(targets, 3, "means")
+    if out is None:
+        out = torch.empty(t.shape[0], 3, dtype=torch.float32)
+    dev = torch.cuda.current_device() if device is None else int(device)
+    _check(lib.dnp_field_grad_host_f32(_ptr(s), s.shape[0], ld_s, _ptr(t), t.shape[0], ld_t, float(eps), _ptr(out), dev))
+    return out
+
+
+def potential_host(sources, targets, device=None, out=None):
+    require_cuda()
+    lib = load()
+    s, ld_s = _host_rows(sources, 6, "sources")
+    t, ld_t = _host_rows(targets, 3, "means")
+    if out is None:
+        out = torch.empty(t.shape[0], dtype=torch.float32)
+    dev = torch.cuda.current_device() if device is None else int(device)
+    _check(lib.dnp_potential_host_f32(_ptr(s), s.shape[0], ld_s, _ptr(t), t.shape[0], ld_t, _ptr(out), dev))
+    return out
+
+
+# ------------------------------------------------------------------ measurement helpers
+def launch_count():
+    return int(load().dnp_launch_count())
+
+
+def device_info():
+    vals = [ctypes.c_int(0) for _ in range(4)]
+    _check(load().dnp_device_info(*[ctypes.byref(v) for v in vals]))
+    return {"sm_count": vals[0].value, "sm_clock_khz": vals[1].value, "cc": (vals[2].value, vals[3].value)}
+
+
+def microbench(kind, iters=2000):
+    ms, ops = ctypes.c_float(0), ctypes.c_double(0)
+    _check(load().dnp_microbench(int(kind), int(iters), ctypes.byref(ms), ctypes.byref(ops),
+                                 ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)))
+    return ms.value, ops.value

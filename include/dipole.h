@@ -1,0 +1,179 @@
+/*
+ * dipole.h -- C ABI of libdipole.so, the B200 (sm_100a) implementation of the
+ * dipole-field hot path of crazyMessi/dipole-normal-prop.
+ *
+ * The reference has no FFI: its boundary is the Python function set of
+ * field_utils.py.  Each entry point below names the
+ * reference function (file:line, commit 431bb62) whose device work it replaces.
+ * INTEGRATION.md shows the ctypes binding a maintainer of the reference adds.
+ *
+ * Rules common to every entry point
+ *   - plain pointers and sizes only; no torch / C++ types cross the boundary.
+ *   - pointers are DEVICE pointers unless the name ends in _host; the caller
+ *     owns every buffer, the library never allocates outputs.
+ *   - `ld_*` are row strides in float elements, so views such as pc[:, :3]
+ *     (stride 6) or E[:, :3] need no copy.  A point row is [x y z nx ny nz].
+ *   - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream).
+ *     Work is enqueued asynchronously; nothing synchronises unless stated.
+ *   - scratch memory comes from the caller: query dnp_pairs_workspace_bytes()
+ *     and pass a device buffer at least that large (256-byte aligned).
+ *   - return value: DNP_OK (0) or a negative DNP_ERR_* code; dnp_last_error()
+ *     returns a thread-local message.  Nothing throws across the ABI.
+ *   - re-entrant: no global mutable state (the reference calls this path from
+ *     many Python threads, util.py:187-196,308-327).
+ *   - float32 only (the file pipelines of the reference are float32,
+ *     util.py:61,66); there is no CPU fallback.
+ */
+#ifndef DIPOLE_H_
+#define DIPOLE_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#if defined(__GNUC__)
+#define DNP_API __attribute__((visibility("default")))
+#else
+#define DNP_API
+#endif
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DNP_OK 0
+#define DNP_ERR_INVALID (-1)   /* bad argument */
+#define DNP_ERR_CUDA (-2)      /* a CUDA runtime call failed */
+#define DNP_ERR_WORKSPACE (-3) /* workspace missing or too small */
+#define DNP_ERR_NO_DEVICE (-4) /* no sm_100 device visible */
+
+/* fused epilogues of the all-pairs field kernel (K7 in SURVEY.md section 2.2) */
+#define DNP_EPI_STORE 0     /* out[r,0:3]  = E_r                      field_utils.py:96-116        */
+#define DNP_EPI_ACCUM 1     /* out[r,0:3] += E_r                      field_utils.py:261,330,335,380 */
+#define DNP_EPI_SIGN_GE 2   /* n_r *= (E_r.n_r >= 0 ? 1 : -1)         field_utils.py:196-199       */
+#define DNP_EPI_SIGN_GT 3   /* n_r *= (E_r.n_r >  0 ? 1 : -1)         field_utils.py:273-276       */
+#define DNP_EPI_NORMALIZE 4 /* out[r,0:3] = E_r/|E_r| (raw E if 0)    field_utils.py:191-194       */
+#define DNP_EPI_DOT 5       /* out[r]      = E_r.n_r                  field_utils.py:147-148       */
+
+DNP_API const char* dnp_last_error(void);
+DNP_API int dnp_version(void);
+
+/* SM count and clocks of the current device (for roofline arithmetic). */
+DNP_API int dnp_device_info(int* sm_count, int* sm_clock_khz, int* cc_major, int* cc_minor);
+
+/* Scratch bytes needed by any dnp_* pairs call with at most S sources and M targets. */
+DNP_API size_t dnp_pairs_workspace_bytes(int64_t S, int64_t M);
+
+/* ------------------------------------------------------------------ a1: potential
+ * replaces field_utils.potential (field_utils.py:12-55):
+ *   phi[m] (+)= sum_s n_s . (p_s - q_m) / |p_s - q_m|^3.
+ * `eps` does not exist here because the reference never uses it.  The recursive
+ * halving (`recursive`, `max_pts`) has no equivalent: memory is O(S + M).
+ * A coincident (source, target) pair contributes 0 (the reference zeroes the
+ * whole leaf total of that target instead -- degenerate input).
+ * Non-finite totals are written as 0 (field_utils.py:53-54).
+ * src_idx (optional, may be NULL): gather sources src[src_idx[i]], i < S.      */
+DNP_API int dnp_potential_f32(const float* src, int64_t S, int64_t ld_s, const int64_t* src_idx,
+                      const float* tgt, int64_t M, int64_t ld_t,
+                      float* phi, int accumulate,
+                      void* workspace, size_t workspace_bytes, void* stream);
+
+/* ------------------------------------------------------------------ a3: lattice test
+ * replaces field_utils.measure_mean_potential + util.gen_grid
+ * (field_utils.py:7-9, util.py:26-36): potential on the n^3 lattice
+ * ((i/n^2, i/n%n, i%n)/n - 0.5)*2 generated in-kernel, and its mean.
+ * phi_opt: optional [n^3] output (may be NULL); mean_out: 1 float (device).     */
+DNP_API int dnp_lattice_mean_potential_f32(const float* src, int64_t S, int64_t ld_s,
+                                   int n, float* phi_opt, float* mean_out,
+                                   void* workspace, size_t workspace_bytes, void* stream);
+
+/* ------------------------------------------------------------------ a2: field
+ * replaces field_utils.field_grad (field_utils.py:61-116):
+ *   E[m] = -sum_s (3 (n_s.Rh) Rh - n_s) / (|R|^3 + eps),  R = p_s - q_m,
+ * coincident pairs contribute exactly 0 (:98-106); non-finite components are
+ * written as 0 (:114-115) and counted in *nonfinite (optional device int).      */
+DNP_API int dnp_field_grad_f32(const float* src, int64_t S, int64_t ld_s,
+                       const float* tgt, int64_t M, int64_t ld_t,
+                       float eps, float* E, int64_t ld_e, int accumulate,
+                       void* workspace, size_t workspace_bytes, void* stream);
+
+/* General form used by the drivers (a5-a9): gathers, target mask, fused epilogue.
+ *   sources : src[src_idx[i]] (i < S) or src[i] if src_idx == NULL
+ *   targets : row r = tgt_idx[k] (k < M) or r = k; skipped if tgt_skip && tgt_skip[r]
+ *   mode    : DNP_EPI_*; `out` / `normals` are addressed by the same row r
+ *             (out: ld_out, normals: ld_n; normals needed for SIGN_* and DOT).
+ *   nonfinite: optional device counter incremented per zeroed component.        */
+DNP_API int dnp_field_apply_f32(const float* src, int64_t S, int64_t ld_s, const int64_t* src_idx,
+                        const float* tgt, int64_t M, int64_t ld_t,
+                        const int64_t* tgt_idx, const uint8_t* tgt_skip,
+                        float eps, int mode,
+                        float* out, int64_t ld_out, float* normals, int64_t ld_n,
+                        int32_t* nonfinite,
+                        void* workspace, size_t workspace_bytes, void* stream);
+
+/* ------------------------------------------------------------------ a4: patch-pair flip score
+ * replaces the device work of field_utils.field_edge_calculator
+ * (field_utils.py:145-160): interaction[0] = sum_t n_t . E_S(t) (device float).
+ * The caller forms w = (2 I) / |S| * |T| and (w, -w) as the reference does.    */
+DNP_API int dnp_edge_interaction_f32(const float* S_pts, int64_t S, int64_t ld_s,
+                             const float* T_pts, int64_t T, int64_t ld_t,
+                             float eps, float* interaction,
+                             void* workspace, size_t workspace_bytes, void* stream);
+
+/* Batched form (K3): patches in CSR (perm[offsets[p] .. offsets[p+1]) are rows of
+ * pts), edges[e] = (source patch, target patch); out[e] = sum_t n_t . E_S(t).
+ * One CTA per edge, deterministic reduction, no atomics.                        */
+DNP_API int dnp_edge_interactions_batched_f32(const float* pts, int64_t ld,
+                                      const int64_t* perm, const int64_t* offsets, int64_t P,
+                                      const int64_t* edges, int64_t n_edges,
+                                      float eps, float* out, void* stream);
+
+/* ------------------------------------------------------------------ a9: per-patch interaction
+ * replaces the list comprehension at field_utils.py:244,316 and the
+ * abs().argmax() at :247,319:  out[p] = sum_{t in patch p} E_t . n_t for every
+ * patch with active[p] != 0 (0 elsewhere);  best[0] = index of the first
+ * maximal |out[p]| among active patches (as float bits of an int32 in best_idx),
+ * best_val[0] = its signed value.  One launch, no host synchronisation.        */
+DNP_API int dnp_patch_interactions_f32(const float* E, int64_t ld_e, const float* normals, int64_t ld_n,
+                               const int64_t* perm, const int64_t* offsets, int64_t P,
+                               const uint8_t* active, float* out,
+                               int32_t* best_idx, float* best_val, void* stream);
+
+/* ------------------------------------------------------------------ a6: per-point greedy propagation
+ * replaces field_utils.strongest_field_propagation_points (field_utils.py:353-388)
+ * entirely on the device: N-1 sequential steps of {add the chosen point's field
+ * to every other point, masked E.n, abs-argmax (first maximum), flip if < 0},
+ * IEEE arithmetic in the reference's evaluation order so that the decision
+ * sequence is the reference's.  pts[N,6] (ld) is updated in place.
+ * order_opt[N] / flipped_opt[N] (optional) receive the visit order and flips.
+ * All state lives in the shared memory of one thread-block cluster, so N is
+ * limited to dnp_points_max_n() (about 97 000 points); larger N is an error.  */
+DNP_API int64_t dnp_points_max_n(void);
+DNP_API int dnp_points_propagate_f32(float* pts, int64_t N, int64_t ld, int64_t starting_point,
+                             float eps, int diffuse,
+                             int32_t* order_opt, uint8_t* flipped_opt, void* stream);
+
+/* ------------------------------------------------------------------ host-buffer entry points
+ * Same math with HOST pointers: the call stages inputs to the device, runs the
+ * kernels and copies the result back before returning (synchronous).  This is
+ * what a CPU-tensor caller of the reference API reaches, and what bench.py
+ * times as `e2e`.  `device` = CUDA ordinal.                                     */
+DNP_API int dnp_field_grad_host_f32(const float* src_host, int64_t S, int64_t ld_s,
+                            const float* tgt_host, int64_t M, int64_t ld_t,
+                            float eps, float* E_host, int device);
+DNP_API int dnp_potential_host_f32(const float* src_host, int64_t S, int64_t ld_s,
+                           const float* tgt_host, int64_t M, int64_t ld_t,
+                           float* phi_host, int device);
+
+/* ------------------------------------------------------------------ measurement helpers
+ * Launch counter: number of libdipole kernels launched by this process
+ * (bench.py reports it as gpu_launches).                                        */
+DNP_API int64_t dnp_launch_count(void);
+/* Issue-rate microbenchmarks for the roofline denominators (kind: 0 = FFMA,
+ * 1 = FFMA2 (packed f32x2), 2 = MUFU.RSQ, 3 = the field inner loop on
+ * shared-memory-resident sources).  Returns elapsed ms and the operation count. */
+DNP_API int dnp_microbench(int kind, int iters, float* ms_out, double* ops_out, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DIPOLE_H_ */
