@@ -1,0 +1,356 @@
+#!/usr/bin/env python
+"""Benchmark of the dipole-field hot path (BASELINE.json metric: dipole pair-interactions/sec).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--points P]
+
+A "step" is one field_grad pass (field_utils.py:61-116) of S = P replicated sources over this GPU's shard
+of M = P targets (BASELINE config 5, the synthetic all-pairs sweep at 1M x 1M per GPU).  Multi-GPU runs
+shard the TARGETS over the ranks with the sources replicated and no data-path collective (weak scaling:
+the global target set grows with N).  One JSON line is printed by rank 0.
+
+  value        pairs/s, inputs resident in HBM, K steps between barrier+synchronize, max over ranks
+  e2e          the same metric through the reference-facing call field_utils.field_grad(host tensors):
+               pinned host buffers in, host tensor out, H2D/D2H copies inside the timed region
+  roofline     the all-pairs kernel against the FP32 FMA pipe (35 flop/pair); the kernel
+               durations come from CUDA events recorded by the library around each launch in the timed region
+  cpu_baseline the torch port of the reference's CPU path (oracle/torch_port.py) on the box's host cores,
+               bounded sample (rank 0, N = 1 only)
+
+`--impl reference` times that CPU port on the same metric and config (bounded sample per step).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.join(ROOT, "dipole-normal-prop_b200"))
+sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+
+METRIC = "dipole_pair_interactions_per_sec"
+UNIT = "pairs/s"
+FLOP_PER_PAIR_FIELD = 35.0      # 23 FP32-pipe instructions + 2 SFU ops
+FLOP_PER_PAIR_POTENTIAL = 18.0
+EPS = 1e-5
+
+
+def cloud(n, seed, cols=6, pin=False):
+    """Seeded synthetic cloud: positions uniform in [-0.5, 0.5]^3, unit moments."""
+    g = torch.Generator().manual_seed(seed)
+    xyz = torch.rand(n, 3, generator=g) - 0.5
+    if cols == 6:
+        nr = torch.randn(n, 3, generator=g)
+        xyz = torch.cat([xyz, nr / nr.norm(dim=-1, keepdim=True)], 1)
+    out = xyz.float().contiguous()
+    return out.pin_memory() if pin else out
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled every 200 ms while the timed region runs."""
+    QUERY = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+             "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+             "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def __enter__(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.QUERY}", "--format=csv,noheader,nounits",
+                 "-lms", "200"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except OSError:
+            self.proc = None
+        return self
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def __exit__(self, *exc):
+        if self.proc:
+            time.sleep(0.25)
+            self.proc.terminate()
+            self.thread.join(timeout=2)
+
+    def summary(self):
+        mhz, mx, reasons, power = [], [], set(), []
+        for r in self.rows:
+            try:
+                mhz.append(float(r[0])); mx.append(float(r[1])); power.append(float(r[2]))
+            except (ValueError, IndexError):
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        if not mhz:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        mhz.sort()
+        return {"sm_mhz": mhz[len(mhz) // 2], "sm_max_mhz": max(mx), "reasons": sorted(reasons),
+                "samples": len(mhz), "power_w_max": max(power)}
+
+
+# ---------------------------------------------------------------------------------------------- CPU arm
+def time_cpu_port(n_src, n_tgt, repeats=1):
+    """Seconds per field_grad(n_src x n_tgt) of the torch port on all host cores (best of `repeats`)."""
+    from oracle import torch_port
+    src, tgt = cloud(n_src, 1), cloud(n_tgt, 2, cols=3)
+    best = float("inf")
+    for _ in range(repeats):
+        t0 = time.perf_counter()
+        torch_port.field_grad(src, tgt, eps=EPS)
+        best = min(best, time.perf_counter() - t0)
+    return best
+
+
+def cpu_baseline_block(n):
+    torch.set_num_threads(os.cpu_count() or 1)
+    time_cpu_port(2048, 2048)                          # warm the thread pool and the allocator
+    m = 2 * n                                          # > max_pts = 15000 at the default n: the chunking runs too
+    sec = time_cpu_port(n, m)
+    return {"value": n * m / sec, "unit": UNIT, "cores": torch.get_num_threads(), "kind": "port",
+            "host_cpus": os.cpu_count(),
+            "sample": f"oracle/torch_port.field_grad (the reference's op chain and chunking, field_utils.py:61-116), "
+                      f"float32, {n} sources x {m} targets = {n * m:.3e} pairs, one run of {sec:.1f} s"}
+
+
+def run_reference_arm(args, rank, world):
+    """`--impl reference`: the reference's CPU torch path (ported op for op, see oracle/torch_port.py) on this
+    box's host cores.  Rank 0 alone runs; each step is a bounded sample of the workload."""
+    if rank != 0:
+        return
+    torch.set_num_threads(os.cpu_count() or 1)
+    n = args.cpu_points
+    for _ in range(args.warmup):
+        time_cpu_port(n, n, 1)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        time_cpu_port(n, n, 1)
+    sec = time.perf_counter() - t0
+    value = args.steps * n * n / sec
+    sample = (f"each step = oracle/torch_port.field_grad on {n} x {n} float32 points ({n * n:.3e} pairs), a bounded "
+              f"sample of the {args.points} x {args.points} per-GPU workload; the reference is pure Python/torch and "
+              f"does not travel to this box, so its op chain is ported (bit-exact vs tests/golden/leaf.npz)")
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": sec / args.steps * 1e3,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": workload_config(args, world),
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": torch.get_num_threads(), "kind": "port",
+                         "host_cpus": os.cpu_count(), "sample": sample},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0}), flush=True)
+
+
+def workload_config(args, world):
+    return {"workload": f"field_grad all-pairs sweep (BASELINE config 5): {args.points} replicated sources x "
+                        f"{args.points} targets per GPU, eps={EPS}, uniform synthetic cloud",
+            "sources": args.points, "targets_per_gpu": args.points, "targets_total": args.points * world,
+            "sharding": "targets block-sharded over ranks, sources replicated, no data-path collective",
+            "l2": "256 MiB scratch buffer rewritten between timed steps (inputs are smaller than the 126 MB L2; "
+                  "the kernel is FP32-pipe bound, not memory bound)"}
+
+
+# ---------------------------------------------------------------------------------------------- GPU arm
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--points", type=int, default=1 << 20, help="sources (replicated) and targets per GPU")
+    ap.add_argument("--cpu-points", type=int, default=8192, help="side of the CPU sample (reference arm / baseline)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extras", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+
+    if args.impl == "reference":
+        run_reference_arm(args, rank, world)
+        return
+
+    import torch.distributed as dist
+    import dnp_native as dn
+    import field_utils
+
+    dn.require_cuda()                                   # no CPU fallback: fail loudly without a GPU
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    P = args.points
+    src_host = cloud(P, 1, pin=True)                                    # replicated sources
+    tgt_host = cloud(P, 2000 + rank, cols=3, pin=True)                 # this rank's target shard
+    src, tgt = src_host.to(dev), tgt_host.to(dev)
+    E = torch.empty(P, 3, dtype=torch.float32, device=dev)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    pairs_per_step = float(P) * float(P)
+
+    def step():
+        flush.zero_()
+        dn.field_grad(src, tgt, eps=EPS, out=E)
+
+    # roofline denominator measured on this box in this process: FP32 FMA issue rate (packed FFMA2)
+    mb_ms, mb_ops = dn.microbench(1, 4000)
+    fma_per_s = mb_ops / (mb_ms * 1e-3)
+    sfu_ms, sfu_ops = dn.microbench(2, 4000)
+    info = dn.device_info()
+
+    for _ in range(args.warmup):
+        step()
+    barrier()
+    launches0 = dn.launch_count()
+    dn.profile_begin()
+    with ClockSampler(local_rank) as clocks:
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        barrier()
+        e0.record()
+        for _ in range(args.steps):
+            step()
+        e1.record()
+        barrier()
+    kernel_ms = dn.profile_end()
+    launches = dn.launch_count() - launches0
+    ms_total = e0.elapsed_time(e1)
+
+    # ---- end to end through the reference-facing API with host buffers
+    def e2e_step():
+        return field_utils.field_grad(src_host, tgt_host, eps=EPS)
+
+    e2e_step()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        out_host = e2e_step()
+    barrier()
+    e2e_s = time.perf_counter() - t0
+    assert not out_host.is_cuda and out_host.shape == (P, 3)
+
+    t = torch.tensor([ms_total, e2e_s * 1e3], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_total, e2e_ms = t.tolist()
+
+    if rank == 0:
+        value = world * pairs_per_step * args.steps / (ms_total * 1e-3)
+        k_ms = sum(kernel_ms) / max(len(kernel_ms), 1)
+        achieved = pairs_per_step * FLOP_PER_PAIR_FIELD / (k_ms * 1e-3) / 1e12
+        peak = 2.0 * fma_per_s / 1e12
+        nominal = info["sm_count"] * 128 * 2 * info["sm_clock_khz"] * 1e3 / 1e12
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms_total / args.steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": workload_config(args, world),
+            "e2e": {"value": world * pairs_per_step * args.steps / (e2e_ms * 1e-3), "unit": UNIT,
+                    "h2d_bytes_per_step": int(src_host.numel() * 4 + tgt_host.numel() * 4),
+                    "d2h_bytes_per_step": int(P * 3 * 4),
+                    "api": "field_utils.field_grad(host float32 tensors) -> dnp_field_grad_host_f32"},
+            "gpu_launches": int(launches),
+            "clocks": clocks.summary(),
+            "roofline": {
+                "bound": "fp32", "kernel": "dnp::pairs_kernel<TP,false> (all-pairs field)",
+                "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak,
+                "peak_source": "measured on this GPU in this process: packed FFMA2 issue microbenchmark "
+                               "(dnp_microbench kind 1) x 2 flop; MEASURED_PEAKS.json holds only HBM and bf16 peaks",
+                "nominal_peak": nominal, "frac_of_nominal": achieved / nominal,
+                "flop_per_pair": FLOP_PER_PAIR_FIELD, "pairs_per_launch": pairs_per_step,
+                "kernel_ms_avg": k_ms, "kernel_launches_timed": len(kernel_ms),
+                "kernel_share_of_step": k_ms * len(kernel_ms) / ms_total if ms_total else None,
+                "pairs_per_s_kernel": pairs_per_step / (k_ms * 1e-3),
+                "fp32_instr_per_pair_executed": 20, "sfu_per_pair_executed": 2,
+                "sfu_peak_gops": sfu_ops / (sfu_ms * 1e-3) / 1e9,
+                "sfu_frac": 2.0 * pairs_per_step / (k_ms * 1e-3) / (sfu_ops / (sfu_ms * 1e-3)),
+                "hbm_algorithmic_gbs": (P * 24 + P * 12 + P * 12) / (k_ms * 1e-3) / 1e9,
+                "traffic": None},
+        }
+        if not args.no_extras:
+            line["extras"] = extras(dn, field_utils, dev, src, tgt)
+        if world == 1 and not args.no_cpu_baseline:
+            line["cpu_baseline"] = cpu_baseline_block(args.cpu_points)
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def extras(dn, field_utils, dev, src, tgt):
+    """Other rows of the hot path, timed outside the headline region (CUDA events, best of 3)."""
+    import numpy as np
+
+    def best_ms(fn, reps=3):
+        fn()
+        torch.cuda.synchronize()
+        best = float("inf")
+        for _ in range(reps):
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            fn()
+            b.record()
+            torch.cuda.synchronize()
+            best = min(best, a.elapsed_time(b))
+        return best
+
+    P = src.shape[0]
+    out = {}
+    phi = torch.empty(P, device=dev)
+    ms = best_ms(lambda: dn.potential(src, tgt, out=phi), 2)
+    out["potential_pairs_per_s"] = P * P / ms * 1e3
+    out["potential_frac_fp32_nominal"] = P * P / ms * 1e3 * FLOP_PER_PAIR_POTENTIAL / (148 * 128 * 2 * 1.965e9)
+    ms = best_ms(lambda: dn.lattice_mean_potential(src))
+    out["lattice_test_ms"] = ms
+    out["lattice_pairs_per_s"] = P * 1000 / ms * 1e3
+    # streamed sign phase (HBM-bound): 24 B read + 12 B written per point
+    big = torch.randn(1 << 24, 6, device=dev)
+    Eb = torch.randn(1 << 24, 3, device=dev)
+    ms = best_ms(lambda: dn.field_sign(Eb, big))
+    out["field_sign_gbs"] = (1 << 24) * 36 / ms / 1e6
+    del big, Eb
+    # cfg1 / cfg2 drivers on the shipped demo clouds (inputs from the committed golden fixtures)
+    gdir = os.path.join(ROOT, "tests", "golden")
+    try:
+        g = np.load(os.path.join(gdir, "points_prop.npz"))
+        pc = torch.from_numpy(g["pc_in"]).to(dev)
+
+        def run_points():
+            work = pc.clone()
+            field_utils.strongest_field_propagation_points(work)
+            return field_utils.measure_mean_potential(work)
+        out["cfg1_ok_xyz_points_propagation_ms"] = best_ms(run_points)
+        out["cfg1_reference_cpu_s_build_container"] = float(g["full_ref_seconds"])
+        g = np.load(os.path.join(gdir, "patch_prop.npz"))
+        pc2 = torch.from_numpy(g["pc_in"]).to(dev)
+        patches = [torch.from_numpy(g["perm"][g["offsets"][i]:g["offsets"][i + 1]]).to(dev)
+                   for i in range(int(g["P"]))]
+
+        def run_patches():
+            work = pc2.clone()
+            field_utils.strongest_field_propagation(work, [], patches)
+            return field_utils.measure_mean_potential(work)
+        out["cfg2_fandisk_patch_propagation_ms"] = best_ms(run_patches)
+        out["cfg2_reference_cpu_s_build_container"] = float(g["plain_ref_seconds"])
+    except OSError:
+        pass
+    return out
+
+
+if __name__ == "__main__":
+    main()

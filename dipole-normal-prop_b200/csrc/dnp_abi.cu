@@ -271,14 +271,18 @@ extern "C" {
 
 int dnp_edge_interactions_batched_f32(const float* pts, int64_t ld,
                                       const int64_t* perm, const int64_t* offsets, int64_t P,
+                                      const int64_t* tgt_perm, const int64_t* tgt_offsets,
                                       const int64_t* edges, int64_t n_edges,
                                       float eps, float* out, void* stream) {
     DNP_REQUIRE(n_edges >= 0 && P >= 0, "negative size");
     if (n_edges == 0) return DNP_OK;
     DNP_REQUIRE(pts && perm && offsets && edges && out, "null pointer");
+    DNP_REQUIRE((tgt_perm == nullptr) == (tgt_offsets == nullptr), "tgt_perm and tgt_offsets go together");
     DNP_REQUIRE(ld >= 6, "points need 6 columns");
     DNP_REQUIRE(eps >= 0.f, "eps must be >= 0");
-    return run_edge_interactions_batched(pts, ld, perm, offsets, P, edges, n_edges, eps, out, (cudaStream_t)stream);
+    return run_edge_interactions_batched(pts, ld, perm, offsets, P, tgt_perm ? tgt_perm : perm,
+                                         tgt_offsets ? tgt_offsets : offsets, edges, n_edges, eps, out,
+                                         (cudaStream_t)stream);
 }
 
 int dnp_patch_interactions_f32(const float* E, int64_t ld_e, const float* normals, int64_t ld_n,
@@ -292,6 +296,25 @@ int dnp_patch_interactions_f32(const float* E, int64_t ld_e, const float* normal
     DNP_REQUIRE((best_idx == nullptr) == (best_val == nullptr), "best_idx and best_val go together");
     return run_patch_interactions(E, ld_e, normals, ld_n, perm, offsets, P, active, out, best_idx, best_val,
                                   (cudaStream_t)stream);
+}
+
+int dnp_patch_covariance_f32(const float* pts, int64_t ld, const int64_t* perm, const int64_t* offsets, int64_t P,
+                             double* cov, void* stream) {
+    DNP_REQUIRE(P >= 0, "negative size");
+    if (P == 0) return DNP_OK;
+    DNP_REQUIRE(pts && perm && offsets && cov, "null pointer");
+    DNP_REQUIRE(ld >= 3, "points need 3 columns");
+    return run_patch_covariance(pts, ld, perm, offsets, P, cov, (cudaStream_t)stream);
+}
+
+int dnp_field_sign_f32(const float* E, int64_t ld_e, float* normals, int64_t ld_n,
+                       const int64_t* idx, int64_t n, int mode, void* stream) {
+    DNP_REQUIRE(n >= 0, "negative size");
+    if (n == 0) return DNP_OK;
+    DNP_REQUIRE(E && normals, "null pointer");
+    DNP_REQUIRE(ld_e >= 3 && ld_n >= 3, "row stride too small");
+    DNP_REQUIRE(mode == DNP_EPI_SIGN_GE || mode == DNP_EPI_SIGN_GT, "mode must be DNP_EPI_SIGN_GE or DNP_EPI_SIGN_GT");
+    return run_field_sign(E, ld_e, normals, ld_n, idx, n, mode == DNP_EPI_SIGN_GE, (cudaStream_t)stream);
 }
 
 int64_t dnp_points_max_n(void) { return points_max_n(); }
@@ -308,6 +331,16 @@ int dnp_points_propagate_f32(float* pts, int64_t N, int64_t ld, int64_t starting
     DNP_REQUIRE(eps >= 0.f, "eps must be >= 0");
     return run_points_propagate(pts, N, ld, starting_point, eps, diffuse, order_opt, flipped_opt,
                                 (cudaStream_t)stream);
+}
+
+int dnp_profile_begin(void) {
+    profile_begin();
+    return DNP_OK;
+}
+
+int dnp_profile_end(float* kernel_ms_host, int capacity, int* n_kernels) {
+    DNP_REQUIRE(capacity >= 0, "negative capacity");
+    return profile_end(kernel_ms_host, capacity, n_kernels);
 }
 
 int dnp_microbench(int kind, int iters, float* ms_out, double* ops_out, void* stream) {

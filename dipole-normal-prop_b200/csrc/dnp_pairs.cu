@@ -24,6 +24,8 @@
 //     kernel in a fixed order: deterministic, no float atomics.
 #include <stdlib.h>
 
+#include <vector>
+
 #include "dnp_common.cuh"
 #include "dnp_pairs.h"
 
@@ -337,6 +339,22 @@ __global__ void __launch_bounds__(1024) sum_kernel(const float* __restrict__ in,
 
 std::atomic<int64_t> g_launches{0};
 
+// per-thread kernel timer (dnp_profile_begin / dnp_profile_end): event pairs recorded on the launching
+// stream around every all-pairs kernel launched by THIS host thread while it is armed.
+struct KernelTimer {
+    bool armed = false;
+    std::vector<cudaEvent_t> events;   // start0, stop0, start1, stop1, ...
+};
+thread_local KernelTimer t_timer;
+
+void timer_mark(cudaStream_t stream) {
+    if (!t_timer.armed) return;
+    cudaEvent_t ev;
+    if (cudaEventCreate(&ev) != cudaSuccess) return;
+    cudaEventRecord(ev, stream);
+    t_timer.events.push_back(ev);
+}
+
 // tuning overrides, read once (immutable afterwards, so the library stays re-entrant)
 int env_int(const char* name) {
     const char* v = getenv(name);
@@ -348,6 +366,29 @@ inline int64_t round_up(int64_t a, int64_t b) { return (a + b - 1) / b * b; }
 }  // namespace
 
 int64_t launch_count() { return g_launches.load(); }
+
+void profile_begin() {
+    for (cudaEvent_t ev : t_timer.events) cudaEventDestroy(ev);
+    t_timer.events.clear();
+    t_timer.armed = true;
+}
+
+int profile_end(float* ms_out, int capacity, int* n_out) {
+    t_timer.armed = false;
+    const int n = (int)(t_timer.events.size() / 2);
+    int rc = DNP_OK;
+    for (int i = 0; i < n; ++i) {
+        float ms = 0.f;
+        cudaError_t e = cudaEventSynchronize(t_timer.events[2 * i + 1]);
+        if (e == cudaSuccess) e = cudaEventElapsedTime(&ms, t_timer.events[2 * i], t_timer.events[2 * i + 1]);
+        if (e != cudaSuccess && rc == DNP_OK) rc = cuda_fail(e, "kernel timer");
+        if (ms_out && i < capacity) ms_out[i] = ms;
+    }
+    for (cudaEvent_t ev : t_timer.events) cudaEventDestroy(ev);
+    t_timer.events.clear();
+    if (n_out) *n_out = n;
+    return rc;
+}
 void count_launch(int n) { g_launches.fetch_add(n); }
 
 // ------------------------------------------------------------------ planning
@@ -414,8 +455,10 @@ static int launch_pairs_tp(const PairPlan& plan, const ulonglong2* packed, const
                            int64_t ld_t, int lattice_n, float eps, float* partial, const PairEpilogue& ep,
                            cudaStream_t stream) {
     dim3 grid((unsigned)plan.m_tiles, (unsigned)plan.nsplit);
+    timer_mark(stream);
     pairs_kernel<TP, kPot><<<grid, kBlock, kSmemBytes, stream>>>(packed, plan.tiles_total, plan.nsplit, tgt, M,
                                                                  ld_t, lattice_n, eps, partial, ep);
+    timer_mark(stream);
     count_launch(1);
     return DNP_OK;
 }

@@ -46,6 +46,9 @@ int run_pairs(bool potential, const float* src, int64_t S, int64_t ld_s, const i
 // out[0] = scale * sum_i in[i*stride], single CTA, fixed order.
 int run_sum(const float* in, int64_t n, int64_t stride, float scale, float* out, cudaStream_t stream);
 
+void profile_begin();
+int profile_end(float* ms_out, int capacity, int* n_out);
+
 int64_t launch_count();
 void count_launch(int n);
 

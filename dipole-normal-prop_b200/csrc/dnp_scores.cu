@@ -49,20 +49,21 @@ __device__ __forceinline__ float block_sum_256(float v, float* warp_part) {
 
 __global__ void __launch_bounds__(kEdgeThreads)
 edge_interactions_kernel(const float* __restrict__ pts, int64_t ld, const int64_t* __restrict__ perm,
-                         const int64_t* __restrict__ offsets, const int64_t* __restrict__ edges, float eps,
+                         const int64_t* __restrict__ offsets, const int64_t* __restrict__ tperm,
+                         const int64_t* __restrict__ toffsets, const int64_t* __restrict__ edges, float eps,
                          float* __restrict__ out) {
     __shared__ float4 s_src[kEdgeChunk * 2];      // [x y z nx] [ny nz 0 0]
     __shared__ float warp_part[32];
     const int64_t e = blockIdx.x;
     const int64_t ps = edges[2 * e], pt = edges[2 * e + 1];
     const int64_t s0 = offsets[ps], ns = offsets[ps + 1] - s0;
-    const int64_t t0 = offsets[pt], nt = offsets[pt + 1] - t0;
+    const int64_t t0 = toffsets[pt], nt = toffsets[pt + 1] - t0;
     float total = 0.f;
     for (int64_t tb = 0; tb < nt; tb += kEdgeThreads) {
         const int64_t t = tb + threadIdx.x;
         float qx = 0.f, qy = 0.f, qz = 0.f, tnx = 0.f, tny = 0.f, tnz = 0.f;
         if (t < nt) {
-            const float* q = pts + perm[t0 + t] * ld;
+            const float* q = pts + tperm[t0 + t] * ld;
             qx = q[0]; qy = q[1]; qz = q[2]; tnx = q[3]; tny = q[4]; tnz = q[5];
         }
         float ex = 0.f, ey = 0.f, ez = 0.f;
@@ -150,14 +151,78 @@ patch_argmax_kernel(const float* __restrict__ vals, const uint8_t* __restrict__ 
     }
 }
 
+
+// per-patch xyz covariance about the patch mean, divided by the patch size
+// (util.pca_eigen_values, util.py:495-497), accumulated in double in a fixed
+// order: one CTA per patch, two passes (mean, then second moments).
+__device__ __forceinline__ double block_sum_f64(double v, double* scratch) {
+    __syncthreads();
+    scratch[threadIdx.x] = v;
+    __syncthreads();
+    for (int o = kEdgeThreads / 2; o > 0; o >>= 1) {
+        if (threadIdx.x < o) scratch[threadIdx.x] += scratch[threadIdx.x + o];
+        __syncthreads();
+    }
+    return scratch[0];
+}
+
+__global__ void __launch_bounds__(kEdgeThreads)
+patch_covariance_kernel(const float* __restrict__ pts, int64_t ld, const int64_t* __restrict__ perm,
+                        const int64_t* __restrict__ offsets, double* __restrict__ cov) {
+    __shared__ double scratch[kEdgeThreads];
+    const int64_t p = blockIdx.x;
+    const int64_t t0 = offsets[p], nt = offsets[p + 1] - t0;
+    double m[3] = {0.0, 0.0, 0.0};
+    for (int64_t t = threadIdx.x; t < nt; t += kEdgeThreads) {
+        const float* q = pts + perm[t0 + t] * ld;
+        m[0] += q[0]; m[1] += q[1]; m[2] += q[2];
+    }
+    const double inv = nt > 0 ? 1.0 / (double)nt : 0.0;
+#pragma unroll
+    for (int c = 0; c < 3; ++c) m[c] = block_sum_f64(m[c], scratch) * inv;
+    double c6[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};   // xx xy xz yy yz zz
+    for (int64_t t = threadIdx.x; t < nt; t += kEdgeThreads) {
+        const float* q = pts + perm[t0 + t] * ld;
+        const double x = q[0] - m[0], y = q[1] - m[1], z = q[2] - m[2];
+        c6[0] += x * x; c6[1] += x * y; c6[2] += x * z; c6[3] += y * y; c6[4] += y * z; c6[5] += z * z;
+    }
+#pragma unroll
+    for (int c = 0; c < 6; ++c) c6[c] = block_sum_f64(c6[c], scratch) * inv;
+    if (threadIdx.x == 0) {
+        double* o = cov + 9 * p;
+        o[0] = c6[0]; o[1] = c6[1]; o[2] = c6[2];
+        o[3] = c6[1]; o[4] = c6[3]; o[5] = c6[4];
+        o[6] = c6[2]; o[7] = c6[4]; o[8] = c6[5];
+    }
+}
+
+// streamed per-point sign: n_r *= (E_r . n_r > 0 ? 1 : -1)  (>= for DNP_EPI_SIGN_GE)
+// field_utils.py:267-271,337-342,382-385 (strict >) and :196-199 (>=).  36 bytes of HBM traffic per point.
+__global__ void __launch_bounds__(256)
+field_sign_kernel(const float* __restrict__ E, int64_t ld_e, float* __restrict__ normals, int64_t ld_n,
+                  const int64_t* __restrict__ idx, int64_t n, int ge) {
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; k < n; k += stride) {
+        const int64_t r = idx ? idx[k] : k;
+        const float* e = E + r * ld_e;
+        float* nr = normals + r * ld_n;
+        const float nx = nr[0], ny = nr[1], nz = nr[2];
+        const float dot = __fadd_rn(__fadd_rn(__fmul_rn(e[0], nx), __fmul_rn(e[1], ny)), __fmul_rn(e[2], nz));
+        const float sgn = (ge ? (dot >= 0.f) : (dot > 0.f)) ? 1.f : -1.f;
+        nr[0] = nx * sgn; nr[1] = ny * sgn; nr[2] = nz * sgn;
+    }
+}
+
 }  // namespace
 
 int run_edge_interactions_batched(const float* pts, int64_t ld, const int64_t* perm, const int64_t* offsets,
-                                  int64_t P, const int64_t* edges, int64_t n_edges, float eps, float* out,
+                                  int64_t P, const int64_t* tgt_perm, const int64_t* tgt_offsets,
+                                  const int64_t* edges, int64_t n_edges, float eps, float* out,
                                   cudaStream_t stream) {
     (void)P;
     if (n_edges <= 0) return DNP_OK;
-    edge_interactions_kernel<<<(unsigned)n_edges, kEdgeThreads, 0, stream>>>(pts, ld, perm, offsets, edges, eps, out);
+    edge_interactions_kernel<<<(unsigned)n_edges, kEdgeThreads, 0, stream>>>(pts, ld, perm, offsets, tgt_perm,
+                                                                             tgt_offsets, edges, eps, out);
     count_launch(1);
     DNP_CHECK_CUDA(cudaGetLastError());
     return DNP_OK;
@@ -174,6 +239,26 @@ int run_patch_interactions(const float* E, int64_t ld_e, const float* normals, i
         patch_argmax_kernel<<<1, 1024, 0, stream>>>(out, active, P, best_idx, best_val);
         count_launch(1);
     }
+    DNP_CHECK_CUDA(cudaGetLastError());
+    return DNP_OK;
+}
+
+int run_patch_covariance(const float* pts, int64_t ld, const int64_t* perm, const int64_t* offsets, int64_t P,
+                         double* cov, cudaStream_t stream) {
+    if (P <= 0) return DNP_OK;
+    patch_covariance_kernel<<<(unsigned)P, kEdgeThreads, 0, stream>>>(pts, ld, perm, offsets, cov);
+    count_launch(1);
+    DNP_CHECK_CUDA(cudaGetLastError());
+    return DNP_OK;
+}
+
+int run_field_sign(const float* E, int64_t ld_e, float* normals, int64_t ld_n, const int64_t* idx, int64_t n,
+                   int ge, cudaStream_t stream) {
+    if (n <= 0) return DNP_OK;
+    const int64_t want = (n + 255) / 256;
+    const int64_t cap = (int64_t)sm_count_cached() * 16;
+    field_sign_kernel<<<(unsigned)(want < cap ? want : cap), 256, 0, stream>>>(E, ld_e, normals, ld_n, idx, n, ge);
+    count_launch(1);
     DNP_CHECK_CUDA(cudaGetLastError());
     return DNP_OK;
 }

@@ -8,12 +8,19 @@
 namespace dnp {
 
 int run_edge_interactions_batched(const float* pts, int64_t ld, const int64_t* perm, const int64_t* offsets,
-                                  int64_t P, const int64_t* edges, int64_t n_edges, float eps, float* out,
+                                  int64_t P, const int64_t* tgt_perm, const int64_t* tgt_offsets,
+                                  const int64_t* edges, int64_t n_edges, float eps, float* out,
                                   cudaStream_t stream);
 
 int run_patch_interactions(const float* E, int64_t ld_e, const float* normals, int64_t ld_n, const int64_t* perm,
                            const int64_t* offsets, int64_t P, const uint8_t* active, float* out,
                            int32_t* best_idx, float* best_val, cudaStream_t stream);
+
+int run_patch_covariance(const float* pts, int64_t ld, const int64_t* perm, const int64_t* offsets, int64_t P,
+                         double* cov, cudaStream_t stream);
+
+int run_field_sign(const float* E, int64_t ld_e, float* normals, int64_t ld_n, const int64_t* idx, int64_t n,
+                   int ge, cudaStream_t stream);
 
 int64_t points_max_n();
 int run_points_propagate(float* pts, int64_t N, int64_t ld, int64_t start, float eps, int diffuse,

@@ -31,13 +31,17 @@ SYMBOLS = [
     ("dnp_field_apply_f32", _i32, [_vp, _i64, _i64, _vp, _vp, _i64, _i64, _vp, _vp, _f32, _i32,
                                    _vp, _i64, _vp, _i64, _vp, _vp, _sz, _vp]),
     ("dnp_edge_interaction_f32", _i32, [_vp, _i64, _i64, _vp, _i64, _i64, _f32, _vp, _vp, _sz, _vp]),
-    ("dnp_edge_interactions_batched_f32", _i32, [_vp, _i64, _vp, _vp, _i64, _vp, _i64, _f32, _vp, _vp]),
+    ("dnp_edge_interactions_batched_f32", _i32, [_vp, _i64, _vp, _vp, _i64, _vp, _vp, _vp, _i64, _f32, _vp, _vp]),
     ("dnp_patch_interactions_f32", _i32, [_vp, _i64, _vp, _i64, _vp, _vp, _i64, _vp, _vp, _vp, _vp, _vp]),
+    ("dnp_field_sign_f32", _i32, [_vp, _i64, _vp, _i64, _vp, _i64, _i32, _vp]),
+    ("dnp_patch_covariance_f32", _i32, [_vp, _i64, _vp, _vp, _i64, _vp, _vp]),
     ("dnp_points_max_n", _i64, []),
     ("dnp_points_propagate_f32", _i32, [_vp, _i64, _i64, _i64, _f32, _i32, _vp, _vp, _vp]),
     ("dnp_field_grad_host_f32", _i32, [_vp, _i64, _i64, _vp, _i64, _i64, _f32, _vp, _i32]),
     ("dnp_potential_host_f32", _i32, [_vp, _i64, _i64, _vp, _i64, _i64, _vp, _i32]),
     ("dnp_launch_count", _i64, []),
+    ("dnp_profile_begin", _i32, []),
+    ("dnp_profile_end", _i32, [ctypes.POINTER(_f32), _i32, ctypes.POINTER(_i32)]),
     ("dnp_microbench", _i32, [_i32, _i32, ctypes.POINTER(_f32), ctypes.POINTER(ctypes.c_double), _vp]),
 ]
 
@@ -210,37 +214,83 @@ def edge_interaction(S_pts, T_pts, eps=1e-5):
     return out
 
 
-def edge_interactions_batched(pts, perm, offsets, edges, eps=1e-5):
+def edge_interactions_batched(pts, perm, offsets, edges, eps=1e-5, tgt_perm=None, tgt_offsets=None):
+    """out[e] = sum_{t in target patch} n_t . E_{source patch}(t) for every edge, one launch.
+    tgt_perm / tgt_offsets: optional second CSR for the target side (a rank's slice of every patch)."""
     lib = load()
     p, ld = _rows(pts, 6, "pts")
     dev = p.device
     perm = _idx(perm, dev, "perm")
     offsets = _idx(offsets, dev, "offsets")
+    tgt_perm = _idx(tgt_perm, dev, "tgt_perm")
+    tgt_offsets = _idx(tgt_offsets, dev, "tgt_offsets")
     edges = _idx(edges, dev, "edges")
     nE = edges.shape[0]
     out = torch.empty(nE, dtype=torch.float32, device=dev)
     with torch.cuda.device(dev):
         _check(lib.dnp_edge_interactions_batched_f32(_ptr(p), ld, _ptr(perm), _ptr(offsets), offsets.numel() - 1,
-                                                     _ptr(edges), nE, float(eps), _ptr(out), _stream(p)))
+                                                     _ptr(tgt_perm), _ptr(tgt_offsets), _ptr(edges), nE,
+                                                     float(eps), _ptr(out), _stream(p)))
     return out
 
 
 def patch_interactions(E, pts, perm, offsets, active=None, want_best=True):
-    """out[p] = sum_{t in p} E_t . n_t ; optionally the first abs-argmax over active patches."""
+    """out[p] = sum_{t in p} E_t . n_t for active patches.  With want_best also returns `best`, an int32[2]
+    device tensor: best[0] = first abs-argmax over active patches, best[1] = float bits of its signed value
+    (read both with ONE device->host copy: see best_to_host)."""
     lib = load()
     p, ld = _rows(pts, 6, "pts")
     e, ld_e = _rows(E, 3, "E")
     dev = p.device
+    perm = _idx(perm, dev, "perm")
+    offsets = _idx(offsets, dev, "offsets")
     P = offsets.numel() - 1
     out = torch.empty(P, dtype=torch.float32, device=dev)
-    best_idx = torch.empty((), dtype=torch.int32, device=dev) if want_best else None
-    best_val = torch.empty((), dtype=torch.float32, device=dev) if want_best else None
+    best = torch.empty(2, dtype=torch.int32, device=dev) if want_best else None
     active = _mask(active, dev, "active")
     normals = p[:, 3:]
     with torch.cuda.device(dev):
-        _check(lib.dnp_patch_interactions_f32(_ptr(e), ld_e, _ptr(normals), ld, _ptr(perm), _ptr(offsets), P,
-                                              _ptr(active), _ptr(out), _ptr(best_idx), _ptr(best_val), _stream(p)))
-    return out, best_idx, best_val
+        _check(lib.dnp_patch_interactions_f32(
+            _ptr(e), ld_e, _ptr(normals), ld, _ptr(perm), _ptr(offsets), P, _ptr(active), _ptr(out),
+            _ptr(best), ctypes.c_void_p(best.data_ptr() + 4) if want_best else ctypes.c_void_p(0), _stream(p)))
+    return out, best
+
+
+def best_to_host(best):
+    """(patch index, signed interaction) from the `best` tensor of patch_interactions: one D2H copy."""
+    b = best.cpu()
+    return int(b[0]), float(b[1:].view(torch.float32)[0])
+
+
+def field_sign(E, pts, idx=None, strict=True):
+    """In place: n_r *= sign(E_r . n_r) for r in idx (all rows if None); strict -> (> 0), else (>= 0)."""
+    lib = load()
+    if pts.dtype != torch.float32 or not pts.is_cuda or pts.dim() != 2 or pts.shape[1] < 6 or pts.stride(1) != 1:
+        raise ValueError("pts must be a [N,6] float32 CUDA tensor with unit column stride")
+    e, ld_e = _rows(E, 3, "E")
+    dev = pts.device
+    idx = _idx(idx, dev, "idx")
+    n = pts.shape[0] if idx is None else idx.numel()
+    if n == 0:
+        return
+    normals = pts[:, 3:]
+    with torch.cuda.device(dev):
+        _check(lib.dnp_field_sign_f32(_ptr(e), ld_e, _ptr(normals), int(pts.stride(0)), _ptr(idx), n,
+                                      EPI_SIGN_GT if strict else EPI_SIGN_GE, _stream(pts)))
+
+
+def patch_covariance(pts, perm, offsets):
+    """[P,3,3] float64 covariance (about the mean, / patch size) of every CSR patch."""
+    lib = load()
+    p, ld = _rows(pts, 3, "pts")
+    dev = p.device
+    perm = _idx(perm, dev, "perm")
+    offsets = _idx(offsets, dev, "offsets")
+    P = offsets.numel() - 1
+    cov = torch.empty(P, 3, 3, dtype=torch.float64, device=dev)
+    with torch.cuda.device(dev):
+        _check(lib.dnp_patch_covariance_f32(_ptr(p), ld, _ptr(perm), _ptr(offsets), P, _ptr(cov), _stream(p)))
+    return cov
 
 
 def points_propagate(pts, diffuse=False, starting_point=0, eps=1e-6, want_trace=False):
@@ -297,6 +347,18 @@ def potential_host(sources, targets, device=None, out=None):
 # ------------------------------------------------------------------ measurement helpers
 def launch_count():
     return int(load().dnp_launch_count())
+
+
+def profile_begin():
+    _check(load().dnp_profile_begin())
+
+
+def profile_end(capacity=4096):
+    """Durations (ms) of the all-pairs kernels this thread launched since profile_begin()."""
+    buf = (ctypes.c_float * capacity)()
+    n = ctypes.c_int(0)
+    _check(load().dnp_profile_end(buf, capacity, ctypes.byref(n)))
+    return [buf[i] for i in range(min(n.value, capacity))]
 
 
 def device_info():

@@ -1,0 +1,389 @@
+"""Drop-in for the dipole hot path of the reference's field_utils.py
+(crazyMessi/dipole-normal-prop @ 431bb62), backed by libdipole.so (sm_100a).
+
+Put this directory in front of the reference checkout on PYTHONPATH and
+orient_simple.py / orient_pointcloud.py / orient_large.py /
+reference_orientation.py / dipole_api.py / graph_dipole.py pick it up through
+their `import field_utils` / `from field_utils import *` unchanged: names,
+positional order, keyword names, defaults and return conventions are the
+reference's.  The greedy propagation control flow
+stays in Python/PyTorch as in the reference; every all-pairs evaluation, patch
+reduction and sign test is one call into the CUDA library.
+
+There is NO CPU fallback.  CPU tensors are accepted the way the reference
+accepts them (result on the input's device), but the arithmetic always runs on
+the current CUDA device through the host-buffer entry points of the C ABI.
+float64 inputs raise TypeError unless ALLOW_FLOAT64_CAST is set (the kernels
+are FP32; SURVEY.md section 7 "dtype").
+
+Known, documented divergences (DESIGN.md "Parity"):
+  * `potential`: a coincident (source, target) pair contributes 0; the reference
+    zeroes the whole leaf total of that target instead (field_utils.py:53-54), a
+    result that depends on its chunking.  Degenerate input only.
+  * `recursive` / `max_pts` are accepted and ignored: memory is O(S + M).
+  * the NaN/Inf warnings of field_grad (field_utils.py:110-113) are not printed;
+    non-finite components are zeroed in the kernel epilogue without a host sync.
+"""
+import torch
+import numpy as np
+
+try:  # the reference re-exports `util` through `from field_utils import *` (orient_simple.py:5,13)
+    import util
+except Exception:  # reference checkout (or its open3d dependency) not importable: hot-path helpers only
+    import dnp_util as util
+
+import dnp_native as _dn
+
+ALLOW_FLOAT64_CAST = False
+
+_EPS_DEFAULT = 1e-5
+_EPS_POINTS = 1e-6      # field_utils.py:362,380
+
+
+# ---------------------------------------------------------------------------- plumbing
+def _cuda_device():
+    _dn.require_cuda()
+    return torch.device("cuda", torch.cuda.current_device())
+
+
+def _check_dtype(t, name):
+    if not isinstance(t, torch.Tensor):
+        raise TypeError(f"{name} must be a torch.Tensor (got {type(t).__name__})")
+    if t.dtype == torch.float32:
+        return t, None
+    if t.dtype == torch.float64 and ALLOW_FLOAT64_CAST:
+        return t.float(), torch.float64
+    raise TypeError(f"{name} must be float32 (got {t.dtype}); the B200 kernels compute in FP32 "
+                    "(set field_utils.ALLOW_FLOAT64_CAST = True to cast explicitly)")
+
+
+def _both_cuda(a, b):
+    """True if both tensors are CUDA, False if both are CPU (served by the host-buffer ABI calls)."""
+    if a.is_cuda != b.is_cuda:
+        raise ValueError("sources and means must be on the same device")
+    return a.is_cuda
+
+
+class _Work:
+    """A CUDA float32 [N,6] working tensor for the in-place drivers.  It IS the caller's tensor when that is
+    already a CUDA float32 tensor with unit column stride (the reference mutates its argument in place:
+    orient_simple.py:24 ignores the return value); otherwise a device copy whose normals are written back."""
+
+    def __init__(self, pts, name="pts"):
+        t, self.cast_back = _check_dtype(pts, name)
+        if t.dim() != 2 or t.shape[1] != 6:
+            raise ValueError(f"{name} must be [N,6] (got {tuple(pts.shape)})")
+        self.orig = pts
+        if t is pts and pts.is_cuda and (pts.shape[0] <= 1 or (pts.stride(1) == 1 and pts.stride(0) >= 6)):
+            self.t = pts
+            self.alias = True
+        else:
+            dev = pts.device if pts.is_cuda else _cuda_device()
+            self.t = t.detach().to(dev, copy=True).contiguous()
+            self.alias = False
+
+    def finish(self):
+        if not self.alias:
+            self.orig[:, 3:] = self.t[:, 3:].to(device=self.orig.device, dtype=self.orig.dtype)
+
+
+def _index_list(idx_list, dev):
+    out = []
+    for idx in idx_list:
+        idx = torch.as_tensor(idx)
+        if idx.dtype == torch.bool:
+            idx = torch.nonzero(idx).flatten()
+        out.append(idx.to(device=dev, dtype=torch.int64).flatten())
+    return out
+
+
+def _csr(idx_list, dev):
+    """(perm, offsets) of a list of index tensors: perm[offsets[p]:offsets[p+1]] are the rows of patch p."""
+    sizes = [int(i.numel()) for i in idx_list]
+    offsets = torch.zeros(len(idx_list) + 1, dtype=torch.int64)
+    if sizes:
+        offsets[1:] = torch.tensor(sizes, dtype=torch.int64).cumsum(0)
+    perm = torch.cat(idx_list) if idx_list else torch.zeros(0, dtype=torch.int64, device=dev)
+    return perm.contiguous(), offsets.to(dev)
+
+
+def _flattest_patch(pts, perm, offsets):
+    """argmin_p |smallest eigenvalue of cov(xyz of patch p)|, first on ties (field_utils.py:230-233,303-306)."""
+    cov = _dn.patch_covariance(pts, perm, offsets).cpu().numpy()
+    lam0 = np.linalg.eigvalsh(cov)[:, 0]
+    return int(np.argmin(np.abs(lam0)))
+
+
+# ---------------------------------------------------------------------------- a1-a3: leaf functions
+def measure_mean_potential(pc: torch.Tensor):
+    """field_utils.py:7-9: mean dipole potential over the 10x10x10 lattice of util.gen_grid (util.py:26-36).
+    The lattice is generated inside the kernel.  Returns a 0-d tensor on pc's device."""
+    t, cast = _check_dtype(pc, "pc")
+    if t.is_cuda:
+        out = _dn.lattice_mean_potential(t)
+    else:
+        out = _dn.lattice_mean_potential(t.to(_cuda_device())).cpu()
+    return out.to(cast) if cast else out
+
+
+def potential(sources, means, eps=1e-5, recursive=True, max_pts=15000):
+    """field_utils.py:12-55.  phi[m] = sum_s n_s . (p_s - q_m) / |p_s - q_m|^3.
+    `eps` is unused by the reference as well; `recursive` / `max_pts` are ignored (no chunking needed)."""
+    s, cast = _check_dtype(sources, "sources")
+    m, cast_m = _check_dtype(means, "means")
+    if _both_cuda(s, m):
+        out = _dn.potential(s, m)
+    else:
+        out = _dn.potential_host(s, m)
+    return out.to(cast) if cast else out
+
+
+def field_grad(sources, means, eps=1e-5, recursive=True, max_pts=15000):
+    """field_utils.py:61-116.  E[m] = -sum_s (3 (n_s.Rh) Rh - n_s) / (|R|^3 + eps), R = p_s - q_m;
+    coincident pairs contribute exactly 0 (:98-106); non-finite components are zeroed (:114-115)."""
+    s, cast = _check_dtype(sources, "sources")
+    m, cast_m = _check_dtype(means, "means")
+    if _both_cuda(s, m):
+        out = _dn.field_grad(s, m, eps=eps)
+    else:
+        out = _dn.field_grad_host(s, m, eps=eps)
+    return out.to(cast) if cast else out
+
+
+# ---------------------------------------------------------------------------- a4: patch-pair flip scores
+def _edge_interaction(S, T):
+    s, _ = _check_dtype(S, "sources")
+    t, _ = _check_dtype(T, "means")
+    if s.shape[1] < 6 or t.shape[1] < 6:
+        raise ValueError("both patches need 6 columns")
+    if not _both_cuda(s, t):
+        dev = _cuda_device()
+        s, t = s.to(dev), t.to(dev)
+    return _dn.edge_interaction(s, t, eps=_EPS_DEFAULT)
+
+
+def field_edge_calculator(sources, means, if_save=False):
+    """field_utils.py:145-160: w = (2 sum_t n_t.E_S(t)) / |S| * |T| (precedence as written at :155);
+    returns (numpy 0-d float32 array, numpy float32) = (w, -w)."""
+    st_interaction = _edge_interaction(sources, means)
+    w = (st_interaction * 2) / sources.shape[0] * means.shape[0]
+    w = w.detach().cpu().numpy()
+    invw = w * -1
+    return w, invw
+
+
+def field_edge_calculator_bool(sources, means, if_save=False):
+    """field_utils.py:129-134."""
+    w, invw = field_edge_calculator(sources, means, if_save)
+    if w > 0:
+        return 1, -1
+    else:
+        return -1, 1
+
+
+def field_edge_calculator_count(sources, means, if_save=False):
+    """field_utils.py:137-143 (the score is evaluated, then replaced by |S||T|)."""
+    w, invw = field_edge_calculator(sources, means, if_save)
+    w = sources.shape[0] * means.shape[0]
+    if w > 0:
+        return w, -w
+    else:
+        return -w, w
+
+
+def field_edge_calculator_batched(pc, patches, edges):
+    """All edges of a patch graph in ONE launch (K3; no reference counterpart -- the reference calls
+    field_edge_calculator once per edge from Python threads, util.py:199-211,308-327).
+    pc [N,6]; patches: list of index tensors; edges: [nE,2] (source patch, target patch).
+    Returns (w, invw) float32 numpy arrays laid out like BiEdge.w / BiEdge.invw (graph.py:121-129)."""
+    work, _ = _check_dtype(pc, "pc")
+    dev = work.device if work.is_cuda else _cuda_device()
+    work = work.to(dev)
+    idx = _index_list(patches, dev)
+    perm, offsets = _csr(idx, dev)
+    edges = torch.as_tensor(edges, dtype=torch.int64).reshape(-1, 2).to(dev).contiguous()
+    inter = _dn.edge_interactions_batched(work, perm, offsets, edges, eps=_EPS_DEFAULT)
+    sizes = (offsets[1:] - offsets[:-1]).to(torch.float32)
+    w = (inter * 2) / sizes[edges[:, 0]] * sizes[edges[:, 1]]
+    w = w.cpu().numpy()
+    return w, w * -1
+
+
+def self_interaction(nxyz, eps=1e-5):
+    """field_utils.py:163-171: score between a random half of the patch and the other half."""
+    assert nxyz.shape[1] == 6
+    num = nxyz.shape[0]
+    mask = torch.ones(num, dtype=torch.bool)
+    mask[torch.randperm(nxyz.shape[0])[:int(num / 2)]] = False
+    mask = mask.to(nxyz.device)
+    w, _ = field_edge_calculator(nxyz[mask], nxyz[~mask])
+    return w
+
+
+def self_interaction_all(nxyz, eps=1e-5):
+    """field_utils.py:174-177."""
+    assert nxyz.shape[1] == 6
+    w, _ = field_edge_calculator(nxyz, nxyz)
+    return w
+
+
+def random_self_interaction(nxyz, eps=1e-5):
+    """field_utils.py:179-186: self score after flipping a random half of the normals."""
+    assert nxyz.shape[1] == 6
+    rand_flip = np.zeros(nxyz.shape[0], dtype=bool)
+    rand_flip[np.random.permutation(nxyz.shape[0])[:int(nxyz.shape[0] / 2)]] = True
+    rand_n = nxyz.clone()
+    rand_n[torch.from_numpy(rand_flip).to(nxyz.device), 3:] *= -1
+    w, _ = field_edge_calculator(rand_n, rand_n)
+    return w
+
+
+# ---------------------------------------------------------------------------- a5: orientation transfer
+def reference_field(pc1, pc2):
+    """field_utils.py:188-201.  3-column target: returns a NEW [M,6] tensor with normals E/|E| (rows with
+    |E| = 0 keep the raw E).  6-column target: flips pc2's normals IN PLACE where E.n < 0 and returns pc2."""
+    with torch.no_grad():
+        src, _ = _check_dtype(pc1, "pc1")
+        tgt, cast = _check_dtype(pc2, "pc2")
+        if tgt.dim() != 2 or tgt.shape[1] not in (3, 6):
+            raise ValueError("pc2 must have 3 or 6 columns")
+        dev = tgt.device if tgt.is_cuda else _cuda_device()
+        src_d = src.to(dev)
+        if tgt.shape[1] == 3:
+            out = torch.empty(tgt.shape[0], 6, dtype=torch.float32, device=dev)
+            out[:, :3] = tgt.to(dev)
+            _dn.field_apply(src_d, out, _EPS_DEFAULT, _dn.EPI_NORMALIZE, out=out[:, 3:])
+            out = out.to(pc2.device)
+            return out.to(cast) if cast else out
+        work = _Work(pc2, "pc2")
+        _dn.field_apply(src_d.to(work.t.device), work.t, _EPS_DEFAULT, _dn.EPI_SIGN_GE, normals=work.t[:, 3:])
+        work.finish()
+        return pc2
+
+
+# ---------------------------------------------------------------------------- a8: patch propagation on representatives
+def strongest_field_propagation_reps(input_pc, reps, diffuse=False, weights=None):
+    """field_utils.py:207-282.  reps = [(rep_idx, rest_idx)] per patch.  Mutates input_pc[:, 3:]; returns None."""
+    input_pc = input_pc.detach()
+    with torch.no_grad():
+        work = _Work(input_pc, "input_pc")
+        pts = work.t
+        dev = pts.device
+        N = pts.shape[0]
+        if weights is not None:
+            weights = weights.to(device=dev, dtype=torch.float32).clamp(0.1, 1)          # :212-215
+            pts[:, 3:] = pts[:, 3:] * weights[:, None]
+
+        rep_idx = _index_list([rep for rep, rest in reps], dev)
+        rest_idx = _index_list([rest for rep, rest in reps], dev)
+        P = len(rep_idx)
+        perm, offsets = _csr(rep_idx, dev)            # perm = every representative row
+        E = torch.zeros(N, 3, dtype=torch.float32, device=dev)
+        oriented = torch.zeros(N, dtype=torch.uint8, device=dev)
+        settled = torch.ones(N, dtype=torch.uint8, device=dev)     # NOT non_oriented_pts_mask (:223-227)
+        settled[perm] = 0
+        scratch_mask = torch.zeros(N, dtype=torch.uint8, device=dev)
+        active = torch.ones(P, dtype=torch.uint8, device=dev)
+
+        start = _flattest_patch(pts, perm, offsets)                                       # :230-233
+        patch = rep_idx[start]
+        active[start] = 0
+        oriented[patch] = 1
+        settled[patch] = 1
+        _dn.field_apply(pts, pts, _EPS_DEFAULT, _dn.EPI_STORE, out=E, src_idx=patch,      # :239
+                        tgt_idx=perm, tgt_skip=settled)
+
+        for _ in range(P - 1):
+            _, best = _dn.patch_interactions(E, pts, perm, offsets, active)               # :244-247
+            j, value = _dn.best_to_host(best)
+            patch = rep_idx[j]
+            if value < 0:                                                                 # :250-252
+                pts[patch, 3:] *= -1
+                pts[rest_idx[j], 3:] *= -1
+            active[j] = 0
+            oriented[patch] = 1
+            settled[patch] = 1
+            if diffuse:                                                                   # :256-261
+                scratch_mask[patch] = 1
+                _dn.field_apply(pts, pts, _EPS_DEFAULT, _dn.EPI_ACCUM, out=E, src_idx=patch,
+                                tgt_idx=perm, tgt_skip=scratch_mask)
+                scratch_mask[patch] = 0
+            else:                                                                         # :264-265
+                _dn.field_apply(pts, pts, _EPS_DEFAULT, _dn.EPI_ACCUM, out=E, src_idx=patch,
+                                tgt_idx=perm, tgt_skip=settled)
+
+        if diffuse:                                                                       # :267-271
+            _dn.field_sign(E, pts, idx=perm, strict=True)
+
+        rest_rows = torch.nonzero(oriented == 0).flatten()                                # :273-276
+        if rest_rows.numel() > 0:
+            src_rows = torch.nonzero(oriented).flatten()
+            _dn.field_apply(pts, pts, _EPS_DEFAULT, _dn.EPI_SIGN_GT, normals=pts[:, 3:],
+                            src_idx=src_rows, tgt_idx=rest_rows)
+
+        if weights is not None:                                                           # :280-282
+            pts[:, 3:] = pts[:, 3:] / weights[:, None]
+        work.finish()
+
+
+# ---------------------------------------------------------------------------- a7: patch propagation on all points
+def strongest_field_propagation(pts, patches, all_patches, diffuse=False, weights=None):
+    """field_utils.py:286-348.  patches = [(i, idx)] network-kept, all_patches = [idx].  Mutates pts[:, 3:]."""
+    with torch.no_grad():
+        work = _Work(pts, "pts")
+        p = work.t
+        dev = p.device
+        N = p.shape[0]
+        if weights is not None:
+            weights = weights.to(device=dev, dtype=torch.float32).clamp(0.1, 1)          # :288-291
+            p[:, 3:] = p[:, 3:] * weights[:, None]
+
+        idx = _index_list(all_patches, dev)
+        P = len(idx)
+        perm, offsets = _csr(idx, dev)
+        E = torch.zeros(N, 3, dtype=torch.float32, device=dev)
+        oriented = torch.zeros(N, dtype=torch.uint8, device=dev)      # pts_mask (:296)
+        scratch_mask = torch.zeros(N, dtype=torch.uint8, device=dev)
+        active = torch.ones(P, dtype=torch.uint8, device=dev)
+
+        start = _flattest_patch(p, perm, offsets)                                         # :303-306
+        patch = idx[start]
+        active[start] = 0
+        oriented[patch] = 1
+        _dn.field_apply(p, p, _EPS_DEFAULT, _dn.EPI_STORE, out=E, src_idx=patch, tgt_skip=oriented)   # :311
+
+        for _ in range(P - 1):
+            _, best = _dn.patch_interactions(E, p, perm, offsets, active)                 # :316-319
+            j, value = _dn.best_to_host(best)
+            patch = idx[j]
+            if value < 0:                                                                 # :322-323
+                p[patch, 3:] *= -1
+            active[j] = 0
+            oriented[patch] = 1
+            if diffuse:                                                                   # :326-331
+                scratch_mask[patch] = 1
+                _dn.field_apply(p, p, _EPS_DEFAULT, _dn.EPI_ACCUM, out=E, src_idx=patch, tgt_skip=scratch_mask)
+                scratch_mask[patch] = 0
+            else:                                                                         # :333-335
+                _dn.field_apply(p, p, _EPS_DEFAULT, _dn.EPI_ACCUM, out=E, src_idx=patch, tgt_skip=oriented)
+
+        if diffuse:                                                                       # :337-342
+            kept = _index_list([entry[1] for entry in patches], dev)
+            if kept:
+                _dn.field_sign(E, p, idx=torch.cat(kept), strict=True)
+
+        if weights is not None:                                                           # :346-348
+            p[:, 3:] = p[:, 3:] / weights[:, None]
+        work.finish()
+
+
+# ---------------------------------------------------------------------------- a6: per-point propagation
+def strongest_field_propagation_points(pts: torch.Tensor, diffuse=False, starting_point=0, verbose=False):
+    """field_utils.py:353-388.  The N-1 greedy steps run inside one persistent cluster kernel
+    (dnp_points_propagate_f32) in the reference's float32 evaluation order.  Mutates pts[:, 3:], returns pts.
+    `verbose` only opened an interactive viewer in the reference (:366-367) and is ignored."""
+    with torch.no_grad():
+        work = _Work(pts, "pts")
+        _dn.points_propagate(work.t, diffuse=diffuse, starting_point=int(starting_point), eps=_EPS_POINTS)
+        work.finish()
+    return pts

@@ -121,9 +121,13 @@ DNP_API int dnp_edge_interaction_f32(const float* S_pts, int64_t S, int64_t ld_s
 
 /* Batched form (K3): patches in CSR (perm[offsets[p] .. offsets[p+1]) are rows of
  * pts), edges[e] = (source patch, target patch); out[e] = sum_t n_t . E_S(t).
- * One CTA per edge, deterministic reduction, no atomics.                        */
+ * One CTA per edge, deterministic reduction, no atomics.
+ * tgt_perm / tgt_offsets (optional, both or neither): a second CSR used for the
+ * TARGET side of every edge -- a rank of a multi-GPU job passes its slice of each
+ * patch here, and the per-edge partial sums are combined with one allreduce.   */
 DNP_API int dnp_edge_interactions_batched_f32(const float* pts, int64_t ld,
                                       const int64_t* perm, const int64_t* offsets, int64_t P,
+                                      const int64_t* tgt_perm, const int64_t* tgt_offsets,
                                       const int64_t* edges, int64_t n_edges,
                                       float eps, float* out, void* stream);
 
@@ -137,6 +141,21 @@ DNP_API int dnp_patch_interactions_f32(const float* E, int64_t ld_e, const float
                                const int64_t* perm, const int64_t* offsets, int64_t P,
                                const uint8_t* active, float* out,
                                int32_t* best_idx, float* best_val, void* stream);
+
+/* Streamed per-point sign (K7 without a field evaluation): for k < n, r = idx ? idx[k] : k,
+ *   n_r *= (E_r . n_r > 0 ? 1 : -1)    mode DNP_EPI_SIGN_GT  field_utils.py:267-271,337-342,382-385
+ *   n_r *= (E_r . n_r >= 0 ? 1 : -1)   mode DNP_EPI_SIGN_GE  field_utils.py:196-199
+ * HBM-bound: 24 bytes read + 12 written per point.                              */
+DNP_API int dnp_field_sign_f32(const float* E, int64_t ld_e, float* normals, int64_t ld_n,
+                       const int64_t* idx, int64_t n, int mode, void* stream);
+
+/* Start-patch selection support: cov[p] (row-major 3x3, double) = covariance of
+ * the xyz of patch p about its mean, divided by the patch size -- the matrix
+ * util.pca_eigen_values (util.py:495-497) hands to symeig at
+ * field_utils.py:230,303.  One CTA per patch, fixed summation order.            */
+DNP_API int dnp_patch_covariance_f32(const float* pts, int64_t ld,
+                             const int64_t* perm, const int64_t* offsets, int64_t P,
+                             double* cov, void* stream);
 
 /* ------------------------------------------------------------------ a6: per-point greedy propagation
  * replaces field_utils.strongest_field_propagation_points (field_utils.py:353-388)
@@ -168,6 +187,13 @@ DNP_API int dnp_potential_host_f32(const float* src_host, int64_t S, int64_t ld_
  * Launch counter: number of libdipole kernels launched by this process
  * (bench.py reports it as gpu_launches).                                        */
 DNP_API int64_t dnp_launch_count(void);
+/* Per-thread kernel timer for the roofline numbers: between dnp_profile_begin() and
+ * dnp_profile_end(), every all-pairs kernel launched by the CALLING host thread is
+ * bracketed by CUDA events on its own stream (no synchronisation is added).
+ * dnp_profile_end() waits for them and writes one duration (ms) per launch into
+ * kernel_ms_host[0 .. min(capacity, *n_kernels)).  State is thread-local.        */
+DNP_API int dnp_profile_begin(void);
+DNP_API int dnp_profile_end(float* kernel_ms_host, int capacity, int* n_kernels);
 /* Issue-rate microbenchmarks for the roofline denominators (kind: 0 = FFMA,
  * 1 = FFMA2 (packed f32x2), 2 = MUFU.RSQ, 3 = the field inner loop on
  * shared-memory-resident sources).  Returns elapsed ms and the operation count. */

@@ -355,7 +355,27 @@ def gen_reps(fu, util):
     save("reps_prop", **out)
 
 
-GENERATORS = {"leaf": gen_leaf, "edge": gen_edge, "transfer": gen_transfer, "lattice": gen_lattice,
+def gen_signatures(fu, util):
+    """Names, parameter names and defaults of every hot-path function, so the
+    drop-in's signatures can be compared with the reference's on a box without the reference."""
+    import inspect
+    import json
+    names = ["measure_mean_potential", "potential", "field_grad", "field_edge_calculator",
+             "field_edge_calculator_bool", "field_edge_calculator_count", "self_interaction",
+             "self_interaction_all", "random_self_interaction", "reference_field",
+             "strongest_field_propagation_reps", "strongest_field_propagation",
+             "strongest_field_propagation_points"]
+    out = {}
+    for n in names:
+        sig = inspect.signature(getattr(fu, n))
+        out[n] = [[p.name, None if p.default is inspect.Parameter.empty else repr(p.default)]
+                  for p in sig.parameters.values()]
+    path = os.path.join(OUT, "signatures.json")
+    json.dump({"field_utils": out, "reexports": ["torch", "np", "util"]}, open(path, "w"), indent=1)
+    print(f"wrote {path}")
+
+
+GENERATORS = {"signatures": gen_signatures, "leaf": gen_leaf, "edge": gen_edge, "transfer": gen_transfer, "lattice": gen_lattice,
               "points": gen_points, "patches": gen_patches, "reps": gen_reps}
 
 if __name__ == "__main__":
