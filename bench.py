@@ -149,6 +149,16 @@ def run_reference_arm(args, rank, world):
         "gpu_launches": 0}), flush=True)
 
 
+def ncu_traffic(points):
+    """DRAM bytes per launch of the dominant kernel from the committed `ncu --set full` capture (profiles/),
+    or None when no capture exists for this size."""
+    try:
+        t = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))[f"pairs_kernel_field_{points}x{points}"]
+        return t["dram_bytes_read"] + t["dram_bytes_write"]
+    except (OSError, KeyError, ValueError):
+        return None
+
+
 def workload_config(args, world):
     return {"workload": f"field_grad all-pairs sweep (BASELINE config 5): {args.points} replicated sources x "
                         f"{args.points} targets per GPU, eps={EPS}, uniform synthetic cloud",
@@ -280,7 +290,7 @@ def main():
                 "sfu_peak_gops": sfu_ops / (sfu_ms * 1e-3) / 1e9,
                 "sfu_frac": 2.0 * pairs_per_step / (k_ms * 1e-3) / (sfu_ops / (sfu_ms * 1e-3)),
                 "hbm_algorithmic_gbs": (P * 24 + P * 12 + P * 12) / (k_ms * 1e-3) / 1e9,
-                "traffic": None},
+                "traffic": ncu_traffic(P)},
         }
         if not args.no_extras:
             line["extras"] = extras(dn, field_utils, dev, src, tgt)

@@ -195,8 +195,10 @@ DNP_API int64_t dnp_launch_count(void);
 DNP_API int dnp_profile_begin(void);
 DNP_API int dnp_profile_end(float* kernel_ms_host, int capacity, int* n_kernels);
 /* Issue-rate microbenchmarks for the roofline denominators (kind: 0 = FFMA,
- * 1 = FFMA2 (packed f32x2), 2 = MUFU.RSQ, 3 = the field inner loop on
- * shared-memory-resident sources).  Returns elapsed ms and the operation count. */
+ * 1 = FFMA2 (packed f32x2), 2 = MUFU.RSQ, 3 = the field kernel's instruction mix,
+ * 4/5/6 = register-file bandwidth probes: FFMA2 / FFMA with three distinct register
+ * operands, FFMA2 with one operand shared by consecutive instructions).
+ * Returns elapsed ms and the operation count.                                     */
 DNP_API int dnp_microbench(int kind, int iters, float* ms_out, double* ops_out, void* stream);
 
 #ifdef __cplusplus
