@@ -347,7 +347,7 @@ struct KernelTimer {
 };
 thread_local KernelTimer t_timer;
 
-void timer_mark(cudaStream_t stream) {
+void timer_mark_impl(cudaStream_t stream) {
     if (!t_timer.armed) return;
     cudaEvent_t ev;
     if (cudaEventCreate(&ev) != cudaSuccess) return;
@@ -363,9 +363,28 @@ int env_int(const char* name) {
 
 inline int64_t round_up(int64_t a, int64_t b) { return (a + b - 1) / b * b; }
 
+bool stream_is_capturing(cudaStream_t stream) {
+    cudaStreamCaptureStatus st = cudaStreamCaptureStatusNone;
+    if (cudaStreamIsCapturing(stream, &st) != cudaSuccess) { cudaGetLastError(); return false; }
+    return st != cudaStreamCaptureStatusNone;
+}
+
 }  // namespace
 
 int64_t launch_count() { return g_launches.load(); }
+
+void timer_mark(cudaStream_t stream) { timer_mark_impl(stream); }
+
+int run_split_reduce(bool potential, const float* partial, int nsplit, int64_t M, const PairEpilogue& ep,
+                     cudaStream_t stream) {
+    const int threads = 256;
+    const unsigned blocks = (unsigned)((M + threads - 1) / threads);
+    if (potential) split_reduce_kernel<true><<<blocks, threads, 0, stream>>>(partial, nsplit, M, ep);
+    else split_reduce_kernel<false><<<blocks, threads, 0, stream>>>(partial, nsplit, M, ep);
+    count_launch(1);
+    DNP_CHECK_CUDA(cudaGetLastError());
+    return DNP_OK;
+}
 
 void profile_begin() {
     for (cudaEvent_t ev : t_timer.events) cudaEventDestroy(ev);
@@ -446,7 +465,12 @@ size_t pairs_workspace_bytes(int64_t S, int64_t M) {
     if (S < 1) S = 1;
     if (M < 1) M = 1;
     const PairPlan p = make_pair_plan(S, M, sm_count_cached(), 0, 0);
-    return p.packed_bytes + p.partial_bytes + (size_t)round_up(M * 4, 256) + 1024;
+    size_t core = p.packed_bytes + p.partial_bytes;
+    if (use_const_path(S, M, 0)) {
+        const size_t c = cpairs_workspace_bytes(S, M);
+        if (c > core) core = c;
+    }
+    return core + (size_t)round_up(M * 4, 256) + 1024;
 }
 
 // ------------------------------------------------------------------ launchers
@@ -466,8 +490,12 @@ static int launch_pairs_tp(const PairPlan& plan, const ulonglong2* packed, const
 int run_pairs(bool potential, const float* src, int64_t S, int64_t ld_s, const int64_t* src_idx,
               const float* tgt, int64_t M, int64_t ld_t, int lattice_n, float eps,
               const PairEpilogue& ep, void* workspace, size_t workspace_bytes, cudaStream_t stream,
-              int force_tp, int force_nsplit) {
+              int force_tp, int force_nsplit, const float* src_host_dense) {
     if (M <= 0) return DNP_OK;
+    if (force_tp <= 0 && force_nsplit <= 0 && use_const_path(S, M, lattice_n) &&
+        (src_host_dense || !stream_is_capturing(stream)))     // the by-value path synchronises once: never under capture
+        return run_cpairs(potential, src, S, ld_s, src_idx, src_host_dense, tgt, M, ld_t, eps, ep, workspace,
+                          workspace_bytes, stream);
     const PairPlan plan = make_pair_plan(S, M, sm_count_cached(), force_tp, force_nsplit);
     if (!workspace || workspace_bytes < plan.packed_bytes + plan.partial_bytes) {
         set_error("workspace too small: need %zu bytes, got %zu", plan.packed_bytes + plan.partial_bytes,
@@ -496,14 +524,8 @@ int run_pairs(bool potential, const float* src, int64_t S, int64_t ld_s, const i
     }
 #undef DNP_LAUNCH
     if (rc != DNP_OK) return rc;
-    if (plan.nsplit > 1) {
-        const int threads = 256;
-        const unsigned blocks = (unsigned)((M + threads - 1) / threads);
-        if (potential) split_reduce_kernel<true><<<blocks, threads, 0, stream>>>(partial, plan.nsplit, M, ep);
-        else split_reduce_kernel<false><<<blocks, threads, 0, stream>>>(partial, plan.nsplit, M, ep);
-        count_launch(1);
-    }
     DNP_CHECK_CUDA(cudaGetLastError());
+    if (plan.nsplit > 1) return run_split_reduce(potential, partial, plan.nsplit, M, ep, stream);
     return DNP_OK;
 }
 

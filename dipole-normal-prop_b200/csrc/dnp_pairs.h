@@ -32,6 +32,16 @@ struct PairPlan {
     size_t partial_bytes = 0;
 };
 
+// plan of the constant-bank path (dnp_cpairs.cu)
+struct CPairPlan {
+    int lanes = 2;         // concurrent launch lanes (streams), each with its own partial rows
+    int n_chunks = 1;      // launches (1280 sources each)
+    int m_tiles = 1;       // CTAs per launch (1024 targets each)
+    int64_t S_pad = 0;
+    size_t packed_bytes = 0;
+    size_t partial_bytes = 0;
+};
+
 int sm_count_cached();
 PairPlan make_pair_plan(int64_t S, int64_t M, int sm_count, int force_tp, int force_nsplit);
 size_t pairs_workspace_bytes(int64_t S, int64_t M);
@@ -41,7 +51,20 @@ size_t pairs_workspace_bytes(int64_t S, int64_t M);
 int run_pairs(bool potential, const float* src, int64_t S, int64_t ld_s, const int64_t* src_idx,
               const float* tgt, int64_t M, int64_t ld_t, int lattice_n, float eps,
               const PairEpilogue& ep, void* workspace, size_t workspace_bytes, cudaStream_t stream,
-              int force_tp = 0, int force_nsplit = 0);
+              int force_tp = 0, int force_nsplit = 0, const float* src_host_dense = nullptr);
+
+// Large calls: sources passed by value through the kernel-parameter constant bank (dnp_cpairs.cu).
+bool use_const_path(int64_t S, int64_t M, int lattice_n);
+CPairPlan make_cpair_plan(int64_t S, int64_t M, int sm_count);
+size_t cpairs_workspace_bytes(int64_t S, int64_t M);
+int run_cpairs(bool potential, const float* src, int64_t S, int64_t ld_s, const int64_t* src_idx,
+               const float* src_host_dense, const float* tgt, int64_t M, int64_t ld_t, float eps,
+               const PairEpilogue& ep, void* workspace, size_t workspace_bytes, cudaStream_t stream);
+// fixed-order sum of `nsplit` partial row sets + the fused epilogue
+int run_split_reduce(bool potential, const float* partial, int nsplit, int64_t M, const PairEpilogue& ep,
+                     cudaStream_t stream);
+// records one event of the armed per-thread kernel timer (no-op otherwise)
+void timer_mark(cudaStream_t stream);
 
 // out[0] = scale * sum_i in[i*stride], single CTA, fixed order.
 int run_sum(const float* in, int64_t n, int64_t stride, float scale, float* out, cudaStream_t stream);
