@@ -153,7 +153,7 @@ def ncu_traffic(points):
     """DRAM bytes per launch of the dominant kernel from the committed `ncu --set full` capture (profiles/),
     or None when no capture exists for this size."""
     try:
-        t = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))[f"cpairs_kernel_field_1280x{points}"]
+        t = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))[f"cpairs_kernel_field_896x{points}"]
         return t["dram_bytes_read"] + t["dram_bytes_write"]
     except (OSError, KeyError, ValueError):
         return None
@@ -264,7 +264,7 @@ def main():
         # one timed region per step: the fork->join span of the step's chunk launches (dnp_cpairs.cu runs them on
         # overlapping lanes, so single-launch durations are not separable; the region is what the events see)
         k_ms = sum(kernel_ms) / max(len(kernel_ms), 1)
-        chunk_launches = (P + 1279) // 1280
+        chunk_launches = ((P + 223) // 224 * 224 + 895) // 896        # blocks of 896 sources (dnp_cpairs.cu)
         achieved = pairs_per_step * FLOP_PER_PAIR_FIELD / (k_ms * 1e-3) / 1e12
         peak = 2.0 * fma_per_s / 1e12
         nominal = info["sm_count"] * 128 * 2 * info["sm_clock_khz"] * 1e3 / 1e12
@@ -281,17 +281,17 @@ def main():
             "clocks": clocks.summary(),
             "roofline": {
                 "bound": "fp32", "kernel": "dnp::cpairs_kernel<false> (all-pairs field, sources by value in uniform "
-                                           "registers; one launch = 1280 sources x all targets)",
+                                           "registers; one launch = 896 sources x all targets)",
                 "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak,
                 "peak_source": "measured on this GPU in this process: packed FFMA2 issue microbenchmark "
                                "(dnp_microbench kind 1) x 2 flop; MEASURED_PEAKS.json holds only HBM and bf16 peaks",
                 "nominal_peak": nominal, "frac_of_nominal": achieved / nominal,
-                "flop_per_pair": FLOP_PER_PAIR_FIELD, "pairs_per_launch": 1280.0 * P,
+                "flop_per_pair": FLOP_PER_PAIR_FIELD, "pairs_per_launch": 896.0 * P,
                 "launches_per_step": chunk_launches, "kernel_ms_avg": k_ms / chunk_launches,
                 "region_ms_avg": k_ms, "regions_timed": len(kernel_ms),
                 "kernel_share_of_step": k_ms * len(kernel_ms) / ms_total if ms_total else None,
                 "pairs_per_s_kernel": pairs_per_step / (k_ms * 1e-3),
-                "fp32_instr_per_pair_executed": 20, "sfu_per_pair_executed": 2,
+                "fp32_instr_per_pair_executed": 19, "sfu_per_pair_executed": 2,
                 "sfu_peak_gops": sfu_ops / (sfu_ms * 1e-3) / 1e9,
                 "sfu_frac": 2.0 * pairs_per_step / (k_ms * 1e-3) / (sfu_ops / (sfu_ms * 1e-3)),
                 "hbm_algorithmic_gbs": chunk_launches * (P * 12 + 2 * P * 12) / (k_ms * 1e-3) / 1e9,

@@ -8,10 +8,10 @@
 // A source is the same for every lane, so it belongs in a UNIFORM register: FFMA2/FMUL2/FADD2 take a
 // `UR.F32` operand that is broadcast to both halves and costs no register-file read.  The only way to
 // fill uniform registers at speed is the constant bank (LDCU), and the only per-launch constant bank a
-// re-entrant library can own is the kernel-parameter bank: every launch carries a block of kCChunk
-// sources BY VALUE (30 720 of the 32 764 parameter bytes), and the kernel streams it with LDCU.64.
+// re-entrant library can own is the kernel-parameter bank: every launch carries a block of sources BY
+// VALUE (896 field sources = 32 256 of the 32 764 parameter bytes), streamed by the kernel with LDCU.64.
 //
-//   * one launch = kCChunk sources x all targets; launches rotate over L "lanes" (streams), lane l
+//   * one launch = one block of sources x all targets; launches rotate over L "lanes" (streams), lane l
 //     accumulating chunks l, l+L, ... into its own partial rows, so consecutive launches overlap and
 //     the tail of one wave is filled by the head of the next; a fixed-order reduction over the lanes
 //     ends the call (deterministic, no float atomics).
@@ -19,8 +19,8 @@
 //     copied to a pinned staging buffer and the stream is synchronised ONCE per call (24 B/source,
 //     0.5 ms per million).  The path is therefore only taken for calls worth milliseconds of GPU time
 //     (use_const_path); everything smaller keeps the fully asynchronous shared-memory kernel.
-//   * arithmetic per pair is identical to dnp_pairs.cu (same 20 packed FP32 ops + 2 MUFU, same
-//     coincident-pair handling), replacing field_utils.py:96-116 / :46-55.
+//   * arithmetic per pair: 19 packed FP32 operations + 2 MUFU (field), 12 + 1 (potential), the same
+//     coincident-pair handling as dnp_pairs.cu; replaces field_utils.py:96-116 / :46-55.
 #include <stdlib.h>
 #include <string.h>
 
@@ -33,16 +33,24 @@ namespace {
 
 constexpr int kCBlock = 128;                   // threads per CTA
 constexpr int kCTP = 4;                        // target pairs per thread (8 targets)
-constexpr int kCFold = 256;                    // sources between folds into the second-level totals
-constexpr int kCChunk = 1280;                  // sources per launch (5 folds)
+// Sources per launch and per fold into the second-level totals.  A field source travels as 9 floats
+// [x y z | nx ny nz | -3nx -3ny -3nz] (the -3 of E = w (n - 3 (n.R) u^2 R) rides on a second copy of the
+// moment so that it costs nothing per pair), a potential source as 6.
+template <bool kPotential>
+struct Blk {
+    static constexpr int kStride = kPotential ? 6 : 9;
+    static constexpr int kFold = kPotential ? 256 : 224;
+    static constexpr int kChunk = kPotential ? 1280 : 896;      // 30 720 B / 32 256 B of parameters
+};
 constexpr int kCMaxLanes = 8;
 constexpr float kRsqrtClamp = 1.152921504606847e18f;   // 2^60
 constexpr float kRsqrtClampPhi = 1.099511627776e12f;   // 2^40
 
+template <bool kPotential>
 struct SrcBlock {
-    float v[kCChunk * 6];                      // rows [x y z nx ny nz]
+    float v[Blk<kPotential>::kChunk * Blk<kPotential>::kStride];
 };
-static_assert(sizeof(SrcBlock) == 30720, "parameter block size");
+static_assert(sizeof(SrcBlock<false>) == 32256 && sizeof(SrcBlock<true>) == 30720, "parameter block size");
 
 struct CTargets {
     const float* tgt;
@@ -69,7 +77,7 @@ __global__ void pack_sources24_kernel(const float* __restrict__ src, int64_t S, 
 
 template <bool kPotential>
 __global__ void __launch_bounds__(kCBlock, 3)
-cpairs_kernel(const __grid_constant__ SrcBlock blk, int n_src, CTargets T, float eps,
+cpairs_kernel(const __grid_constant__ SrcBlock<kPotential> blk, int n_src, CTargets T, float eps,
               float* __restrict__ part, int first) {
     constexpr int TP = kCTP;
     const int tid = threadIdx.x;
@@ -95,18 +103,18 @@ cpairs_kernel(const __grid_constant__ SrcBlock blk, int n_src, CTargets T, float
 
     const f32x2 zero2 = pack2(0.f, 0.f);
     const f32x2 eps2 = pack2(eps, eps);
-    const f32x2 m3 = pack2(-3.f, -3.f);
     f32x2 tx[TP], ty[TP], tz[TP];
 #pragma unroll
     for (int j = 0; j < TP; ++j) { tx[j] = zero2; ty[j] = zero2; tz[j] = zero2; }
 
-    for (int s0 = 0; s0 < n_src; s0 += kCFold) {
+    constexpr int kFold = Blk<kPotential>::kFold;
+    for (int s0 = 0; s0 < n_src; s0 += kFold) {
         if (kPotential) {
             f32x2 phi[TP];
 #pragma unroll
             for (int j = 0; j < TP; ++j) phi[j] = zero2;
 #pragma unroll 2
-            for (int s = s0; s < s0 + kCFold; ++s) {
+            for (int s = s0; s < s0 + kFold; ++s) {
                 const float px = blk.v[6 * s], py = blk.v[6 * s + 1], pz = blk.v[6 * s + 2];
                 const float nx = blk.v[6 * s + 3], ny = blk.v[6 * s + 4], nz = blk.v[6 * s + 5];
                 const f32x2 px2 = pack2(px, px), py2 = pack2(py, py), pz2 = pack2(pz, pz);
@@ -125,41 +133,43 @@ cpairs_kernel(const __grid_constant__ SrcBlock blk, int n_src, CTargets T, float
 #pragma unroll
             for (int j = 0; j < TP; ++j) tx[j] = add2(tx[j], phi[j]);
         } else {
-            f32x2 ax[TP], ay[TP], az[TP], bx[TP], by[TP], bz[TP];
+            // 19 packed FP32 operations per (2 targets x 1 source), field_utils.py:96-109 regrouped as
+            //   E += w (n + t R),  t = (m.R) u^2,  m = -3 n,  u = rsqrt(r2),  w = 1 / (r2^2 u + eps).
+            f32x2 ax[TP], ay[TP], az[TP];
 #pragma unroll
-            for (int j = 0; j < TP; ++j) { ax[j] = ay[j] = az[j] = bx[j] = by[j] = bz[j] = zero2; }
-#pragma unroll 2
-            for (int s = s0; s < s0 + kCFold; ++s) {
-                const float px = blk.v[6 * s], py = blk.v[6 * s + 1], pz = blk.v[6 * s + 2];
-                const float nx = blk.v[6 * s + 3], ny = blk.v[6 * s + 4], nz = blk.v[6 * s + 5];
+            for (int j = 0; j < TP; ++j) { ax[j] = ay[j] = az[j] = zero2; }
+#pragma unroll 4
+            for (int s = s0; s < s0 + kFold; ++s) {
+                const float px = blk.v[9 * s], py = blk.v[9 * s + 1], pz = blk.v[9 * s + 2];
+                const float nx = blk.v[9 * s + 3], ny = blk.v[9 * s + 4], nz = blk.v[9 * s + 5];
+                const float mx = blk.v[9 * s + 6], my = blk.v[9 * s + 7], mz = blk.v[9 * s + 8];
                 const f32x2 px2 = pack2(px, px), py2 = pack2(py, py), pz2 = pack2(pz, pz);
                 const f32x2 nx2 = pack2(nx, nx), ny2 = pack2(ny, ny), nz2 = pack2(nz, nz);
+                const f32x2 mx2 = pack2(mx, mx), my2 = pack2(my, my), mz2 = pack2(mz, mz);
 #pragma unroll
                 for (int j = 0; j < TP; ++j) {
-                    // same 20 packed operations as pair_field_x2 (dnp_pairs.cu)
                     const f32x2 rx = sub2(px2, qx[j]), ry = sub2(py2, qy[j]), rz = sub2(pz2, qz[j]);
                     const f32x2 r2 = fma2(rz, rz, fma2(ry, ry, mul2(rx, rx)));
                     float r2a, r2b;
                     unpack2(r2, r2a, r2b);
-                    const float ua = rsqrt_sfu(r2a), ub = rsqrt_sfu(r2b);
+                    const float ua = rsqrt_sfu(r2a), ub = rsqrt_sfu(r2b);           // +inf on a coincident pair
                     const f32x2 u = pack2(ua, ub);
                     const f32x2 uc = pack2(fminf(ua, kRsqrtClamp), fminf(ub, kRsqrtClamp));
-                    const f32x2 r = mul2(r2, u);
-                    const f32x2 den = fma2(r2, r, eps2);
+                    const f32x2 den = fma2(mul2(r2, r2), u, eps2);                  // |R|^3 + eps; 0*inf = NaN if R = 0
                     float da, db;
                     unpack2(den, da, db);
-                    const f32x2 w = pack2(fmaxf(rcp_sfu(da), 0.f), fmaxf(rcp_sfu(db), 0.f));
-                    const f32x2 d = fma2(nz2, rz, fma2(ny2, ry, mul2(nx2, rx)));
-                    const f32x2 c = mul2(mul2(d, w), mul2(uc, uc));
-                    ax[j] = fma2(w, nx2, ax[j]); ay[j] = fma2(w, ny2, ay[j]); az[j] = fma2(w, nz2, az[j]);
-                    bx[j] = fma2(c, rx, bx[j]);  by[j] = fma2(c, ry, by[j]);  bz[j] = fma2(c, rz, bz[j]);
+                    const f32x2 w = pack2(fmaxf(rcp_sfu(da), 0.f), fmaxf(rcp_sfu(db), 0.f));   // NaN -> 0
+                    const f32x2 d = fma2(mz2, rz, fma2(my2, ry, mul2(mx2, rx)));    // -3 n.R (exactly 0 when R = 0)
+                    const f32x2 t = mul2(d, mul2(uc, uc));                          // -3 t; finite: the clamped u
+                    const f32x2 vx = fma2(t, rx, nx2), vy = fma2(t, ry, ny2), vz = fma2(t, rz, nz2);
+                    ax[j] = fma2(w, vx, ax[j]); ay[j] = fma2(w, vy, ay[j]); az[j] = fma2(w, vz, az[j]);
                 }
             }
 #pragma unroll
             for (int j = 0; j < TP; ++j) {
-                tx[j] = add2(tx[j], fma2(bx[j], m3, ax[j]));
-                ty[j] = add2(ty[j], fma2(by[j], m3, ay[j]));
-                tz[j] = add2(tz[j], fma2(bz[j], m3, az[j]));
+                tx[j] = add2(tx[j], ax[j]);
+                ty[j] = add2(ty[j], ay[j]);
+                tz[j] = add2(tz[j], az[j]);
             }
         }
     }
@@ -260,10 +270,12 @@ bool use_const_path(int64_t S, int64_t M, int lattice_n) {
     return S >= 16384 && M >= 131072;
 }
 
-CPairPlan make_cpair_plan(int64_t S, int64_t M, int sm_count) {
+CPairPlan make_cpair_plan(bool potential, int64_t S, int64_t M, int sm_count) {
     CPairPlan p;
-    p.S_pad = round_up(S < 1 ? 1 : S, kCFold);
-    p.n_chunks = (int)((p.S_pad + kCChunk - 1) / kCChunk);
+    const int fold = potential ? Blk<true>::kFold : Blk<false>::kFold;
+    const int chunk = potential ? Blk<true>::kChunk : Blk<false>::kChunk;
+    p.S_pad = round_up(S < 1 ? 1 : S, fold);
+    p.n_chunks = (int)((p.S_pad + chunk - 1) / chunk);
     p.m_tiles = (int)((M + (int64_t)kCBlock * 2 * kCTP - 1) / ((int64_t)kCBlock * 2 * kCTP));
     if (p.m_tiles < 1) p.m_tiles = 1;
     // enough lanes for >= ~2.2 waves of CTAs in flight, so that wave tails overlap the next launch
@@ -276,14 +288,61 @@ CPairPlan make_cpair_plan(int64_t S, int64_t M, int sm_count) {
     if (lanes > p.n_chunks) lanes = p.n_chunks;
     p.lanes = lanes;
     p.packed_bytes = (size_t)round_up(p.S_pad * 6 * (int64_t)sizeof(float), 256);
-    p.partial_bytes = (size_t)round_up((int64_t)p.lanes * (M < 1 ? 1 : M) * 3 * (int64_t)sizeof(float), 256);
+    p.partial_bytes = (size_t)round_up((int64_t)p.lanes * (M < 1 ? 1 : M) * (potential ? 1 : 3) * (int64_t)sizeof(float), 256);
     return p;
 }
 
 size_t cpairs_workspace_bytes(int64_t S, int64_t M) {
-    const CPairPlan p = make_cpair_plan(S, M, sm_count_cached());
-    return p.packed_bytes + p.partial_bytes;
+    const CPairPlan f = make_cpair_plan(false, S, M, sm_count_cached());
+    const CPairPlan p = make_cpair_plan(true, S, M, sm_count_cached());
+    const size_t a = f.packed_bytes + f.partial_bytes, b = p.packed_bytes + p.partial_bytes;
+    return a > b ? a : b;
 }
+
+namespace {
+
+// one chunk of dense host rows [x y z nx ny nz] -> the by-value block (null dipoles past `n_have`)
+template <bool kPotential>
+void fill_block(SrcBlock<kPotential>& blk, const float* rows, int64_t n_have, int n_src) {
+    constexpr int ST = Blk<kPotential>::kStride;
+    if (kPotential) {
+        if (n_have > 0) memcpy(blk.v, rows, (size_t)n_have * 6 * sizeof(float));
+    } else {
+        for (int64_t i = 0; i < n_have; ++i) {
+            const float* r = rows + 6 * i;
+            float* o = blk.v + ST * i;
+            o[0] = r[0]; o[1] = r[1]; o[2] = r[2];
+            o[3] = r[3]; o[4] = r[4]; o[5] = r[5];
+            o[6] = r[3] * -3.f; o[7] = r[4] * -3.f; o[8] = r[5] * -3.f;
+        }
+    }
+    if (n_have < n_src) memset(blk.v + n_have * ST, 0, (size_t)(n_src - n_have) * ST * sizeof(float));
+}
+
+template <bool kPotential>
+int launch_chunks(const CPairPlan& plan, const float* host_rows, int64_t host_valid, const CTargets& T, float eps,
+                  float* partial) {
+    constexpr int kChunk = Blk<kPotential>::kChunk;
+    const int ncomp = kPotential ? 1 : 3;
+    SrcBlock<kPotential> blk;
+    for (int k = 0; k < plan.n_chunks; ++k) {
+        const int l = k % plan.lanes;
+        const int64_t s_begin = (int64_t)k * kChunk;
+        const int n_src = (int)((plan.S_pad - s_begin < kChunk) ? (plan.S_pad - s_begin) : kChunk);
+        int64_t n_have = host_valid - s_begin;
+        if (n_have < 0) n_have = 0;
+        if (n_have > n_src) n_have = n_src;
+        fill_block<kPotential>(blk, host_rows + s_begin * 6, n_have, n_src);
+        float* part = partial + (size_t)l * T.M * ncomp;
+        cpairs_kernel<kPotential><<<plan.m_tiles, kCBlock, 0, t_lanes.lane[l]>>>(blk, n_src, T, eps, part,
+                                                                                  k < plan.lanes);
+    }
+    count_launch(plan.n_chunks);
+    DNP_CHECK_CUDA(cudaGetLastError());
+    return DNP_OK;
+}
+
+}  // namespace
 
 // src_host_dense: optional dense [S,6] HOST copy of the sources (the host entry points have one); when
 // NULL the device sources are packed and staged through pinned memory (one stream synchronisation).
@@ -291,7 +350,7 @@ int run_cpairs(bool potential, const float* src, int64_t S, int64_t ld_s, const 
                const float* src_host_dense, const float* tgt, int64_t M, int64_t ld_t, float eps,
                const PairEpilogue& ep, void* workspace, size_t workspace_bytes, cudaStream_t stream) {
     if (M <= 0) return DNP_OK;
-    const CPairPlan plan = make_cpair_plan(S, M, sm_count_cached());
+    const CPairPlan plan = make_cpair_plan(potential, S, M, sm_count_cached());
     if (!workspace || workspace_bytes < plan.packed_bytes + plan.partial_bytes) {
         set_error("workspace too small: need %zu bytes, got %zu", plan.packed_bytes + plan.partial_bytes,
                   workspace_bytes);
@@ -304,7 +363,7 @@ int run_cpairs(bool potential, const float* src, int64_t S, int64_t ld_s, const 
     float* partial = reinterpret_cast<float*>(reinterpret_cast<unsigned char*>(workspace) + plan.packed_bytes);
 
     const float* host_rows = src_host_dense;
-    int64_t host_valid = S;                      // rows of host_rows that exist (the rest are null dipoles)
+    int64_t host_valid = S < 0 ? 0 : S;          // rows of host_rows that exist (the rest are null dipoles)
     if (!host_rows) {
         const int threads = 256;
         const unsigned blocks = (unsigned)((plan.S_pad + threads - 1) / threads);
@@ -318,34 +377,18 @@ int run_cpairs(bool potential, const float* src, int64_t S, int64_t ld_s, const 
         host_valid = plan.S_pad;
     }
 
-    CTargets T{tgt, M, ld_t, ep.tgt_idx, ep.tgt_skip};
-    const int ncomp = potential ? 1 : 3;
+    const CTargets T{tgt, M, ld_t, ep.tgt_idx, ep.tgt_skip};
     timer_mark(stream);
     DNP_CHECK_CUDA(cudaEventRecord(t_lanes.fork, stream));
     for (int l = 0; l < plan.lanes; ++l) DNP_CHECK_CUDA(cudaStreamWaitEvent(t_lanes.lane[l], t_lanes.fork, 0));
-    SrcBlock blk;
-    for (int k = 0; k < plan.n_chunks; ++k) {
-        const int l = k % plan.lanes;
-        const int64_t s_begin = (int64_t)k * kCChunk;
-        const int n_src = (int)((plan.S_pad - s_begin < kCChunk) ? (plan.S_pad - s_begin) : kCChunk);
-        int64_t n_have = host_valid - s_begin;
-        if (n_have < 0) n_have = 0;
-        if (n_have > n_src) n_have = n_src;
-        if (n_have > 0) memcpy(blk.v, host_rows + s_begin * 6, (size_t)n_have * 6 * sizeof(float));
-        if (n_have < n_src) memset(blk.v + n_have * 6, 0, (size_t)(n_src - n_have) * 6 * sizeof(float));
-        float* part = partial + (size_t)l * M * ncomp;
-        if (potential)
-            cpairs_kernel<true><<<plan.m_tiles, kCBlock, 0, t_lanes.lane[l]>>>(blk, n_src, T, eps, part, k < plan.lanes);
-        else
-            cpairs_kernel<false><<<plan.m_tiles, kCBlock, 0, t_lanes.lane[l]>>>(blk, n_src, T, eps, part, k < plan.lanes);
-    }
-    count_launch(plan.n_chunks);
-    DNP_CHECK_CUDA(cudaGetLastError());
-    for (int l = 0; l < plan.lanes; ++l) {
-        DNP_CHECK_CUDA(cudaEventRecord(t_lanes.done[l], t_lanes.lane[l]));
-        DNP_CHECK_CUDA(cudaStreamWaitEvent(stream, t_lanes.done[l], 0));
+    const int rc = potential ? launch_chunks<true>(plan, host_rows, host_valid, T, eps, partial)
+                             : launch_chunks<false>(plan, host_rows, host_valid, T, eps, partial);
+    for (int l = 0; l < plan.lanes; ++l) {       // always re-join, also after a failed launch
+        cudaEventRecord(t_lanes.done[l], t_lanes.lane[l]);
+        cudaStreamWaitEvent(stream, t_lanes.done[l], 0);
     }
     timer_mark(stream);
+    if (rc != DNP_OK) return rc;
     return run_split_reduce(potential, partial, plan.lanes, M, ep, stream);
 }
 

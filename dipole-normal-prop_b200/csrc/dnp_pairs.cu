@@ -6,22 +6,23 @@
 // pair.
 //
 // Design (B200, sm_100a):
-//   * sources are re-packed once per call into a 48-byte "lane-duplicated" row
-//     [x x y y | z z nx nx | ny ny nz nz]; the TMA unit streams 12 KB tiles of it
-//     into a 3-stage shared-memory ring (cp.async.bulk + mbarrier, SASS UBLKCP).
-//   * every thread keeps 2*TP targets in registers.  Two targets share one
-//     64-bit register pair, and the whole per-pair arithmetic runs on packed
-//     FFMA2/FMUL2/FADD2 (two FP32 ops per lane per instruction): 20 packed
-//     instructions + 2 MUFU.RSQ + 2 MUFU.RCP + 4 FMNMX per (2 targets x 1 source).
-//     The FP32 pipe is the bound; the issue slots it frees cover the SFU, the
-//     NaN-laundering FMNMX and the broadcast LDS.128 loads.
+//   * sources are re-packed once per call into 48-byte rows [x y z nx | ny nz mx my | mz 0 0 0] with
+//     m = -3 n; the TMA unit streams 12 KB tiles of them into a 3-stage shared-memory ring
+//     (cp.async.bulk + mbarrier, SASS UBLKCP) and every warp reads a source with broadcast LDS.128.
+//   * every thread keeps 2*TP targets in registers.  Two targets share one 64-bit register pair and the
+//     whole per-pair arithmetic runs on packed FFMA2/FMUL2/FADD2 (two FP32 ops per lane per instruction)
+//     whose source-side operand is a 32-bit register broadcast to both halves (`R.F32`): 19 packed
+//     instructions + 2 MUFU.RSQ + 2 MUFU.RCP + 4 FMNMX per (2 targets x 1 source),
+//         E += w (n + t R),  t = (m.R) u^2,  u = rsqrt(r2),  w = 1 / (r2^2 u + eps).
+//     Large calls take the by-value kernel of dnp_cpairs.cu instead, where the source operand is a
+//     uniform register and costs no register-file read at all.
 //   * no tensor cores: the 1/(|R|^3+eps) weight is per pair, not a contraction.
-//   * coincident pairs: rsqrt(0)=inf makes r=0*inf NaN, so the weight w becomes
-//     NaN and max(w, 0) returns 0 (FMNMX drops the NaN operand); the R-parallel
-//     coefficient uses the clamped rsqrt so it stays finite and multiplies R=0.
-//   * per-target sums are flushed into a second-level accumulator after every
-//     256-source tile, and (for nsplit > 1) source ranges are reduced by a second
-//     kernel in a fixed order: deterministic, no float atomics.
+//   * coincident pairs: rsqrt(0)=inf makes r2^2 u = 0*inf NaN, so the weight w becomes NaN and
+//     max(w, 0) returns 0 (FMNMX drops the NaN operand); t uses the clamped rsqrt so it stays finite
+//     (and is exactly 0 because m.R = 0).
+//   * per-target sums are flushed into a second-level accumulator after every 256-source tile, and
+//     (for nsplit > 1) source ranges are reduced by a second kernel in a fixed order: deterministic,
+//     no float atomics.
 #include <stdlib.h>
 
 #include <vector>
@@ -54,9 +55,9 @@ __global__ void pack_sources_kernel(const float* __restrict__ src, int64_t S, in
 #pragma unroll
         for (int c = 0; c < 6; ++c) v[c] = __ldg(p + c);
     }
-    packed[3 * s + 0] = make_float4(v[0], v[0], v[1], v[1]);
-    packed[3 * s + 1] = make_float4(v[2], v[2], v[3], v[3]);
-    packed[3 * s + 2] = make_float4(v[4], v[4], v[5], v[5]);
+    packed[3 * s + 0] = make_float4(v[0], v[1], v[2], v[3]);
+    packed[3 * s + 1] = make_float4(v[4], v[5], v[3] * -3.f, v[4] * -3.f);
+    packed[3 * s + 2] = make_float4(v[5] * -3.f, 0.f, 0.f, 0.f);
 }
 
 // ------------------------------------------------------------------ epilogue (K7)
@@ -125,12 +126,18 @@ __device__ __forceinline__ void lattice_node(int64_t i, int n, float& x, float& 
 }
 
 // ------------------------------------------------------------------ per-pair arithmetic, packed
-struct SrcX2 { f32x2 px, py, pz, nx, ny, nz; };
+// one source, broadcast to both halves of every packed operation (ptxas emits the `R.F32` operand form)
+struct SrcX2 {
+    f32x2 px, py, pz, nx, ny, nz, mx, my, mz;
+    __device__ __forceinline__ SrcX2(const float4& A, const float4& B, const float4& C)
+        : px(pack2(A.x, A.x)), py(pack2(A.y, A.y)), pz(pack2(A.z, A.z)), nx(pack2(A.w, A.w)),
+          ny(pack2(B.x, B.x)), nz(pack2(B.y, B.y)), mx(pack2(B.z, B.z)), my(pack2(B.w, B.w)),
+          mz(pack2(C.x, C.x)) {}
+};
 
-// field: E += w n - 3 c R  with w = 1/(r^3+eps), c = (n.R) w / r^2     (20 packed FP32 ops)
+// field: E += w (n + t R) with w = 1/(r^3+eps), t = (m.R) / r^2, m = -3 n            (19 packed FP32 ops)
 __device__ __forceinline__ void pair_field_x2(const SrcX2& s, f32x2 qx, f32x2 qy, f32x2 qz, f32x2 eps2,
-                                              f32x2& ax, f32x2& ay, f32x2& az,
-                                              f32x2& bx, f32x2& by, f32x2& bz) {
+                                              f32x2& ax, f32x2& ay, f32x2& az) {
     const f32x2 rx = sub2(s.px, qx), ry = sub2(s.py, qy), rz = sub2(s.pz, qz);
     const f32x2 r2 = fma2(rz, rz, fma2(ry, ry, mul2(rx, rx)));
     float r2a, r2b;
@@ -138,15 +145,14 @@ __device__ __forceinline__ void pair_field_x2(const SrcX2& s, f32x2 qx, f32x2 qy
     const float ua = rsqrt_sfu(r2a), ub = rsqrt_sfu(r2b);                 // +inf on a coincident pair
     const f32x2 u = pack2(ua, ub);
     const f32x2 uc = pack2(fminf(ua, kRsqrtClamp), fminf(ub, kRsqrtClamp));
-    const f32x2 r = mul2(r2, u);                                          // 0*inf = NaN on a coincident pair
-    const f32x2 den = fma2(r2, r, eps2);                                  // |R|^3 + eps
+    const f32x2 den = fma2(mul2(r2, r2), u, eps2);                        // |R|^3 + eps; 0*inf = NaN if R = 0
     float da, db;
     unpack2(den, da, db);
     const f32x2 w = pack2(fmaxf(rcp_sfu(da), 0.f), fmaxf(rcp_sfu(db), 0.f));   // NaN -> 0
-    const f32x2 d = fma2(s.nz, rz, fma2(s.ny, ry, mul2(s.nx, rx)));       // n.R (exactly 0 when R = 0)
-    const f32x2 c = mul2(mul2(d, w), mul2(uc, uc));
-    ax = fma2(w, s.nx, ax); ay = fma2(w, s.ny, ay); az = fma2(w, s.nz, az);
-    bx = fma2(c, rx, bx);   by = fma2(c, ry, by);   bz = fma2(c, rz, bz);
+    const f32x2 d = fma2(s.mz, rz, fma2(s.my, ry, mul2(s.mx, rx)));       // -3 n.R (exactly 0 when R = 0)
+    const f32x2 t = mul2(d, mul2(uc, uc));
+    const f32x2 vx = fma2(t, rx, s.nx), vy = fma2(t, ry, s.ny), vz = fma2(t, rz, s.nz);
+    ax = fma2(w, vx, ax); ay = fma2(w, vy, ay); az = fma2(w, vz, az);
 }
 
 // potential: phi += (n.R) / r^3                                         (12 packed FP32 ops)
@@ -165,11 +171,11 @@ __device__ __forceinline__ void pair_potential_x2(const SrcX2& s, f32x2 qx, f32x
 // grid.x = target tiles of kBlock*2*TP targets, grid.y = source splits.
 template <int TP, bool kPotential>
 __global__ void __launch_bounds__(kBlock, (TP >= 4 ? 3 : (TP == 2 ? 5 : 8)))
-pairs_kernel(const ulonglong2* __restrict__ packed, int tiles_total, int nsplit,
+pairs_kernel(const float4* __restrict__ packed, int tiles_total, int nsplit,
              const float* __restrict__ tgt, int64_t M, int64_t ld_t, int lattice_n,
              float eps, float* __restrict__ partial, PairEpilogue ep) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
-    ulonglong2* stage_buf = reinterpret_cast<ulonglong2*>(smem_raw);
+    float4* stage_buf = reinterpret_cast<float4*>(smem_raw);
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem_raw + size_t(kStages) * kTileBytes);
 
     const int tid = threadIdx.x;
@@ -221,7 +227,6 @@ pairs_kernel(const ulonglong2* __restrict__ packed, int tiles_total, int nsplit,
 
     const f32x2 zero2 = pack2(0.f, 0.f);
     const f32x2 eps2 = pack2(eps, eps);
-    const f32x2 m3 = pack2(-3.f, -3.f);
     // second-level totals (one per component per target pair)
     f32x2 tx[TP], ty[TP], tz[TP];
 #pragma unroll
@@ -230,7 +235,7 @@ pairs_kernel(const ulonglong2* __restrict__ packed, int tiles_total, int nsplit,
     for (int it = 0; it < n_tiles; ++it) {
         const int st = it % kStages;
         mbar_wait(&bars[st], (uint32_t)((it / kStages) & 1));
-        const ulonglong2* sp = stage_buf + size_t(st) * kTileSrc * 3;
+        const float4* sp = stage_buf + size_t(st) * kTileSrc * 3;
 
         if (kPotential) {
             f32x2 phi[TP];
@@ -238,30 +243,28 @@ pairs_kernel(const ulonglong2* __restrict__ packed, int tiles_total, int nsplit,
             for (int j = 0; j < TP; ++j) phi[j] = zero2;
 #pragma unroll 2
             for (int s = 0; s < kTileSrc; ++s) {
-                const ulonglong2 A = sp[3 * s], B = sp[3 * s + 1], C = sp[3 * s + 2];
-                const SrcX2 src{A.x, A.y, B.x, B.y, C.x, C.y};
+                const SrcX2 src(sp[3 * s], sp[3 * s + 1], sp[3 * s + 2]);
 #pragma unroll
                 for (int j = 0; j < TP; ++j) pair_potential_x2(src, qx[j], qy[j], qz[j], phi[j]);
             }
 #pragma unroll
             for (int j = 0; j < TP; ++j) tx[j] = add2(tx[j], phi[j]);
         } else {
-            f32x2 ax[TP], ay[TP], az[TP], bx[TP], by[TP], bz[TP];
+            f32x2 ax[TP], ay[TP], az[TP];
 #pragma unroll
-            for (int j = 0; j < TP; ++j) { ax[j] = ay[j] = az[j] = bx[j] = by[j] = bz[j] = zero2; }
+            for (int j = 0; j < TP; ++j) { ax[j] = ay[j] = az[j] = zero2; }
 #pragma unroll 2
             for (int s = 0; s < kTileSrc; ++s) {
-                const ulonglong2 A = sp[3 * s], B = sp[3 * s + 1], C = sp[3 * s + 2];
-                const SrcX2 src{A.x, A.y, B.x, B.y, C.x, C.y};
+                const SrcX2 src(sp[3 * s], sp[3 * s + 1], sp[3 * s + 2]);
 #pragma unroll
                 for (int j = 0; j < TP; ++j)
-                    pair_field_x2(src, qx[j], qy[j], qz[j], eps2, ax[j], ay[j], az[j], bx[j], by[j], bz[j]);
+                    pair_field_x2(src, qx[j], qy[j], qz[j], eps2, ax[j], ay[j], az[j]);
             }
 #pragma unroll
-            for (int j = 0; j < TP; ++j) {               // tile sum = a - 3 b, folded into the totals
-                tx[j] = add2(tx[j], fma2(bx[j], m3, ax[j]));
-                ty[j] = add2(ty[j], fma2(by[j], m3, ay[j]));
-                tz[j] = add2(tz[j], fma2(bz[j], m3, az[j]));
+            for (int j = 0; j < TP; ++j) {               // tile sums folded into the totals
+                tx[j] = add2(tx[j], ax[j]);
+                ty[j] = add2(ty[j], ay[j]);
+                tz[j] = add2(tz[j], az[j]);
             }
         }
 
@@ -475,7 +478,7 @@ size_t pairs_workspace_bytes(int64_t S, int64_t M) {
 
 // ------------------------------------------------------------------ launchers
 template <int TP, bool kPot>
-static int launch_pairs_tp(const PairPlan& plan, const ulonglong2* packed, const float* tgt, int64_t M,
+static int launch_pairs_tp(const PairPlan& plan, const float4* packed, const float* tgt, int64_t M,
                            int64_t ld_t, int lattice_n, float eps, float* partial, const PairEpilogue& ep,
                            cudaStream_t stream) {
     dim3 grid((unsigned)plan.m_tiles, (unsigned)plan.nsplit);
@@ -512,7 +515,7 @@ int run_pairs(bool potential, const float* src, int64_t S, int64_t ld_s, const i
         pack_sources_kernel<<<blocks, threads, 0, stream>>>(src, S < 0 ? 0 : S, ld_s, src_idx, plan.S_pad, packed);
         count_launch(1);
     }
-    const ulonglong2* pk = reinterpret_cast<const ulonglong2*>(packed);
+    const float4* pk = packed;
     int rc;
 #define DNP_LAUNCH(TP)                                                                                       \
     rc = potential ? launch_pairs_tp<TP, true>(plan, pk, tgt, M, ld_t, lattice_n, eps, partial, ep, stream)  \

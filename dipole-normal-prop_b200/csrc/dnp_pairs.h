@@ -35,7 +35,7 @@ struct PairPlan {
 // plan of the constant-bank path (dnp_cpairs.cu)
 struct CPairPlan {
     int lanes = 2;         // concurrent launch lanes (streams), each with its own partial rows
-    int n_chunks = 1;      // launches (1280 sources each)
+    int n_chunks = 1;      // launches (896 field / 1280 potential sources each)
     int m_tiles = 1;       // CTAs per launch (1024 targets each)
     int64_t S_pad = 0;
     size_t packed_bytes = 0;
@@ -55,7 +55,7 @@ int run_pairs(bool potential, const float* src, int64_t S, int64_t ld_s, const i
 
 // Large calls: sources passed by value through the kernel-parameter constant bank (dnp_cpairs.cu).
 bool use_const_path(int64_t S, int64_t M, int lattice_n);
-CPairPlan make_cpair_plan(int64_t S, int64_t M, int sm_count);
+CPairPlan make_cpair_plan(bool potential, int64_t S, int64_t M, int sm_count);
 size_t cpairs_workspace_bytes(int64_t S, int64_t M);
 int run_cpairs(bool potential, const float* src, int64_t S, int64_t ld_s, const int64_t* src_idx,
                const float* src_host_dense, const float* tgt, int64_t M, int64_t ld_t, float eps,
