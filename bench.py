@@ -248,10 +248,15 @@ def main():
     e2e_step()
     barrier()
     t0 = time.perf_counter()
+    e2e_calls = []
     for _ in range(args.steps):
+        t1 = time.perf_counter()
         out_host = e2e_step()
+        e2e_calls.append((time.perf_counter() - t1) * 1e3)
     barrier()
     e2e_s = time.perf_counter() - t0
+    if os.environ.get("DNP_BENCH_DEBUG"):
+        print("e2e per call ms:", ["%.1f" % v for v in e2e_calls], file=sys.stderr)
     assert not out_host.is_cuda and out_host.shape == (P, 3)
 
     t = torch.tensor([ms_total, e2e_s * 1e3], dtype=torch.float64, device=dev)

@@ -9,6 +9,8 @@
 #include <stdio.h>
 #include <string.h>
 
+#include <chrono>
+
 #include "dnp_common.cuh"
 #include "dnp_pairs.h"
 #include "dnp_scores.h"
@@ -220,6 +222,9 @@ int host_pairs(bool potential, const float* src_host, int64_t S, int64_t ld_s, c
     const size_t src_bytes = (size_t)(S > 0 ? S : 1) * 6 * sizeof(float);
     const size_t tgt_bytes = (size_t)M * 3 * sizeof(float);
     const size_t out_bytes = (size_t)M * ncomp * sizeof(float);
+    const bool trace = getenv("DNP_HOST_TRACE") != nullptr;
+    auto now = [] { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
+    const double t_0 = now();
     cudaStream_t stream;
     DNP_CHECK_CUDA(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
     unsigned char* base = nullptr;
@@ -228,6 +233,8 @@ int host_pairs(bool potential, const float* src_host, int64_t S, int64_t ld_s, c
     const size_t total = up(src_bytes) + up(tgt_bytes) + up(out_bytes) + ws_bytes;
     cudaError_t e = cudaMallocAsync(reinterpret_cast<void**>(&base), total, stream);
     if (e != cudaSuccess) { cudaStreamDestroy(stream); return cuda_fail(e, "cudaMallocAsync"); }
+    const double t_alloc = now();
+    double t_up = 0, t_launch = 0, t_dl = 0;
     float* d_src = reinterpret_cast<float*>(base);
     float* d_tgt = reinterpret_cast<float*>(base + up(src_bytes));
     float* d_out = reinterpret_cast<float*>(base + up(src_bytes) + up(tgt_bytes));
@@ -238,18 +245,25 @@ int host_pairs(bool potential, const float* src_host, int64_t S, int64_t ld_s, c
         const bool by_value = ld_s == 6 && use_const_path(S, M, 0);
         if (!by_value && (e = upload_rows(d_src, src_host, S, 6, ld_s, stream)) != cudaSuccess) { rc = cuda_fail(e, "upload sources"); break; }
         if ((e = upload_rows(d_tgt, tgt_host, M, 3, ld_t, stream)) != cudaSuccess) { rc = cuda_fail(e, "upload targets"); break; }
+        t_up = now();
         PairEpilogue ep;
         ep.mode = DNP_EPI_STORE;
         ep.out = d_out;
         ep.ld_out = ncomp;
         rc = run_pairs(potential, d_src, S, 6, nullptr, d_tgt, M, 3, 0, eps, ep, d_ws, ws_bytes, stream, 0, 0,
                        by_value ? src_host : nullptr);
+        t_launch = now();
         if (rc != DNP_OK) break;
         if ((e = cudaMemcpyAsync(out_host, d_out, out_bytes, cudaMemcpyDeviceToHost, stream)) != cudaSuccess) { rc = cuda_fail(e, "download"); break; }
     } while (0);
+    t_dl = now();
     cudaFreeAsync(base, stream);
     e = cudaStreamSynchronize(stream);
+    const double t_sync = now();
     cudaStreamDestroy(stream);
+    if (trace)
+        fprintf(stderr, "[dnp host] alloc %.2f upload %.2f enqueue %.2f download-enqueue %.2f sync %.2f destroy %.2f ms\n",
+                t_alloc - t_0, t_up - t_alloc, t_launch - t_up, t_dl - t_launch, t_sync - t_dl, now() - t_sync);
     if (rc == DNP_OK && e != cudaSuccess) rc = cuda_fail(e, "cudaStreamSynchronize");
     return rc;
 }
