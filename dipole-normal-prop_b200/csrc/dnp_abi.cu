@@ -336,11 +336,14 @@ int dnp_field_sign_f32(const float* E, int64_t ld_e, float* normals, int64_t ld_
     return run_field_sign(E, ld_e, normals, ld_n, idx, n, mode == DNP_EPI_SIGN_GE, (cudaStream_t)stream);
 }
 
-int64_t dnp_points_max_n(void) { return points_max_n(); }
+int64_t dnp_points_max_n(void) { return points_grid_max_n(); }
+
+size_t dnp_points_workspace_bytes(int64_t N) { return points_workspace_bytes(N); }
 
 int dnp_points_propagate_f32(float* pts, int64_t N, int64_t ld, int64_t starting_point,
                              float eps, int diffuse,
-                             int32_t* order_opt, uint8_t* flipped_opt, void* stream) {
+                             int32_t* order_opt, uint8_t* flipped_opt,
+                             void* workspace, size_t workspace_bytes, void* stream) {
     DNP_REQUIRE(N >= 0, "negative size");
     if (N == 0) return DNP_OK;
     DNP_REQUIRE(pts, "null pointer");
@@ -348,8 +351,8 @@ int dnp_points_propagate_f32(float* pts, int64_t N, int64_t ld, int64_t starting
     DNP_REQUIRE(starting_point >= 0 && starting_point < N, "starting_point out of range");
     DNP_REQUIRE(N < 0x7ffffffe, "N too large");
     DNP_REQUIRE(eps >= 0.f, "eps must be >= 0");
-    return run_points_propagate(pts, N, ld, starting_point, eps, diffuse, order_opt, flipped_opt,
-                                (cudaStream_t)stream);
+    return run_points_propagate(pts, N, ld, starting_point, eps, diffuse, order_opt, flipped_opt, workspace,
+                                workspace_bytes, (cudaStream_t)stream);
 }
 
 int dnp_profile_begin(void) {

@@ -20,6 +20,8 @@
 // CPU float32 path bit for bit (tests/golden/points_prop.npz).
 // This stage is latency-bound (about a thousand cycles per step), not
 // FLOP-bound; the all-pairs throughput kernels are in dnp_pairs.cu.
+#include <stdlib.h>
+
 #include "dnp_common.cuh"
 #include "dnp_pairs.h"
 #include "dnp_scores.h"
@@ -102,6 +104,36 @@ size_t point_smem_bytes(int cap) {
     return sizeof(Candidate) * (2 * kMaxCluster + kWarps) + size_t(cap) * 9 * sizeof(float) + size_t(cap) + 16;
 }
 
+// One step's sweep over the points this CTA owns (field_utils.py:379-380 with the leaf :96-116, then :369):
+//   E[m] += field of the current source at m (m != cur, IEEE ops in the reference's order),
+//   best = max over unvisited points of key(E[m].n[m], m).
+__device__ __forceinline__ void sweep_points(const PointSmem& sm, int n_local, int64_t base, int64_t cur,
+                                             float px, float py, float pz, float p3, float p4, float p5, float eps,
+                                             unsigned long long& best, int& best_i) {
+    for (int i = threadIdx.x; i < n_local; i += kPtThreads) {
+        const int64_t m = base + i;
+        float ex = sm.ex[i], ey = sm.ey[i], ez = sm.ez[i];
+        if (m != cur) {
+            const float rx = __fsub_rn(px, sm.qx[i]), ry = __fsub_rn(py, sm.qy[i]), rz = __fsub_rn(pz, sm.qz[i]);
+            const float r = __fsqrt_rn(__fadd_rn(__fadd_rn(__fmul_rn(rx, rx), __fmul_rn(ry, ry)), __fmul_rn(rz, rz)));
+            if (r != 0.f) {
+                const float ux = __fdiv_rn(rx, r), uy = __fdiv_rn(ry, r), uz = __fdiv_rn(rz, r);
+                const float d3 = __fmul_rn(3.f, __fadd_rn(__fadd_rn(__fmul_rn(p3, ux), __fmul_rn(p4, uy)), __fmul_rn(p5, uz)));
+                const float den = __fadd_rn(__fmul_rn(__fmul_rn(r, r), r), eps);
+                ex = __fsub_rn(ex, __fdiv_rn(__fsub_rn(__fmul_rn(d3, ux), p3), den));
+                ey = __fsub_rn(ey, __fdiv_rn(__fsub_rn(__fmul_rn(d3, uy), p4), den));
+                ez = __fsub_rn(ez, __fdiv_rn(__fsub_rn(__fmul_rn(d3, uz), p5), den));
+                sm.ex[i] = ex; sm.ey[i] = ey; sm.ez[i] = ez;
+            }
+        }
+        if (!sm.visited[i]) {
+            const float v = __fadd_rn(__fadd_rn(__fmul_rn(ex, sm.nx[i]), __fmul_rn(ey, sm.ny[i])), __fmul_rn(ez, sm.nz[i]));
+            const unsigned long long k = make_key(v, m);
+            if (best_i < 0 || k > best) { best = k; best_i = i; }
+        }
+    }
+}
+
 __global__ void __launch_bounds__(kPtThreads, 1)
 points_propagate_kernel(float* __restrict__ pts, int64_t N, int64_t ld, int cap, int64_t start, float eps,
                         int diffuse, int32_t* __restrict__ order, uint8_t* __restrict__ flipped) {
@@ -137,28 +169,7 @@ points_propagate_kernel(float* __restrict__ pts, int64_t N, int64_t ld, int cap,
         //      interaction = (E * n).sum(-1) over unvisited points      (:369)
         unsigned long long best = 0ull;
         int best_i = -1;
-        for (int i = tid; i < n_local; i += kPtThreads) {
-            const int64_t m = base + i;
-            float ex = sm.ex[i], ey = sm.ey[i], ez = sm.ez[i];
-            if (m != cur) {
-                const float rx = __fsub_rn(px, sm.qx[i]), ry = __fsub_rn(py, sm.qy[i]), rz = __fsub_rn(pz, sm.qz[i]);
-                const float r = __fsqrt_rn(__fadd_rn(__fadd_rn(__fmul_rn(rx, rx), __fmul_rn(ry, ry)), __fmul_rn(rz, rz)));
-                if (r != 0.f) {
-                    const float ux = __fdiv_rn(rx, r), uy = __fdiv_rn(ry, r), uz = __fdiv_rn(rz, r);
-                    const float d3 = __fmul_rn(3.f, __fadd_rn(__fadd_rn(__fmul_rn(p3, ux), __fmul_rn(p4, uy)), __fmul_rn(p5, uz)));
-                    const float den = __fadd_rn(__fmul_rn(__fmul_rn(r, r), r), eps);
-                    ex = __fsub_rn(ex, __fdiv_rn(__fsub_rn(__fmul_rn(d3, ux), p3), den));
-                    ey = __fsub_rn(ey, __fdiv_rn(__fsub_rn(__fmul_rn(d3, uy), p4), den));
-                    ez = __fsub_rn(ez, __fdiv_rn(__fsub_rn(__fmul_rn(d3, uz), p5), den));
-                    sm.ex[i] = ex; sm.ey[i] = ey; sm.ez[i] = ez;
-                }
-            }
-            if (!sm.visited[i]) {
-                const float v = __fadd_rn(__fadd_rn(__fmul_rn(ex, sm.nx[i]), __fmul_rn(ey, sm.ny[i])), __fmul_rn(ez, sm.nz[i]));
-                const unsigned long long k = make_key(v, m);
-                if (best_i < 0 || k > best) { best = k; best_i = i; }
-            }
-        }
+        sweep_points(sm, n_local, base, cur, px, py, pz, p3, p4, p5, eps, best, best_i);
         if (step == N) break;   // the last iteration only spreads the last source's field
 
         // ---- abs().argmax(): warp -> CTA -> cluster                                 (:372-373)
@@ -230,17 +241,214 @@ points_propagate_kernel(float* __restrict__ pts, int64_t N, int64_t ld, int cap,
     cluster_barrier();   // no CTA may exit while a peer can still address its shared memory
 }
 
+
+// ------------------------------------------------------------------ N beyond one cluster: cooperative grid
+// Same algorithm and the same arithmetic (sweep_points), but the point state is spread over the shared
+// memory of up to one CTA per SM and a step ends with a grid-wide exchange through L2: every CTA
+// publishes its winner in slots[step & 1][cta], arrives on a monotonically increasing counter, and warp 0
+// of every CTA picks the global winner once all CTAs of the step have arrived.  The kernel is launched
+// cooperatively, so all CTAs are co-resident and the spin cannot deadlock.
+__device__ __forceinline__ unsigned int ld_acquire_u32(const unsigned int* p) {
+    unsigned int v;
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+
+__global__ void __launch_bounds__(kPtThreads, 1)
+points_propagate_grid_kernel(float* __restrict__ pts, int64_t N, int64_t ld, int cap, int64_t start, float eps,
+                             int diffuse, int32_t* __restrict__ order, uint8_t* __restrict__ flipped,
+                             Candidate* __restrict__ slots, unsigned int* __restrict__ counter) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const PointSmem sm = carve(smem_raw, cap);
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const uint32_t rank = blockIdx.x, ncta = gridDim.x;
+    const int64_t base = (int64_t)rank * cap;
+    const int n_local = (int)max((int64_t)0, min((int64_t)cap, N - base));
+
+    for (int i = tid; i < n_local; i += kPtThreads) {
+        const float* p = pts + (base + i) * ld;
+        sm.qx[i] = p[0]; sm.qy[i] = p[1]; sm.qz[i] = p[2];
+        sm.nx[i] = p[3]; sm.ny[i] = p[4]; sm.nz[i] = p[5];
+        sm.ex[i] = 0.f; sm.ey[i] = 0.f; sm.ez[i] = 0.f;
+        sm.visited[i] = (base + i == start);
+    }
+    int64_t cur = start;
+    float px, py, pz, p3, p4, p5;
+    {
+        const float* p = pts + start * ld;
+        px = p[0]; py = p[1]; pz = p[2]; p3 = p[3]; p4 = p[4]; p5 = p[5];
+    }
+    if (rank == 0 && tid == 0) {
+        if (order) order[0] = (int32_t)start;
+        if (flipped) flipped[0] = 0;
+    }
+    Candidate* win_smem = sm.cand;      // the cluster exchange buffer is free here: slot 0 holds the step's winner
+    __syncthreads();
+
+    for (int64_t step = 1; step <= N; ++step) {
+        unsigned long long best = 0ull;
+        int best_i = -1;
+        sweep_points(sm, n_local, base, cur, px, py, pz, p3, p4, p5, eps, best, best_i);
+        if (step == N) break;
+
+        const unsigned long long wbest = warp_max_u64(best);
+        if (best_i >= 0 && best == wbest && wbest != 0ull) {
+            Candidate c;
+            c.key = best;
+            c.qx = sm.qx[best_i]; c.qy = sm.qy[best_i]; c.qz = sm.qz[best_i];
+            c.nx = sm.nx[best_i]; c.ny = sm.ny[best_i]; c.nz = sm.nz[best_i];
+            sm.warp_cand[warp] = c;
+        } else if (lane == 0 && wbest == 0ull) {
+            sm.warp_cand[warp].key = 0ull;
+        }
+        __syncthreads();
+        Candidate* slot = slots + (size_t)(step & 1) * ncta;
+        if (warp == 0) {
+            const unsigned long long k = lane < kWarps ? sm.warp_cand[lane].key : 0ull;
+            const unsigned long long cbest = warp_max_u64(k);
+            const uint32_t src_warp = __ffs(__ballot_sync(0xffffffffu, lane < kWarps && k == cbest)) - 1;
+            if (lane == 0) {
+                const uint4* w = reinterpret_cast<const uint4*>(&sm.warp_cand[src_warp]);
+                uint4 v0 = w[0], v1 = w[1];
+                if (cbest == 0ull) { v0.x = 0u; v0.y = 0u; }
+                uint4* dst = reinterpret_cast<uint4*>(&slot[rank]);
+                __stcg(dst, v0);
+                __stcg(dst + 1, v1);
+                __threadfence();
+                atomicAdd(counter, 1u);
+                const unsigned int target = (unsigned int)step * ncta;       // < 2^32: checked by the launcher
+                while (ld_acquire_u32(counter) < target) { }
+            }
+            __syncwarp();
+            // the winners of all CTAs: lanes scan them in strides of 32 (L2 reads, never L1)
+            unsigned long long gbest = 0ull;
+            uint32_t gsrc = 0;
+            for (uint32_t r = lane; r < ncta; r += 32) {
+                const unsigned long long kk = __ldcg(&slot[r].key);
+                if (kk > gbest) { gbest = kk; gsrc = r; }
+            }
+            const unsigned long long all = warp_max_u64(gbest);
+            const uint32_t owner = __ffs(__ballot_sync(0xffffffffu, gbest == all)) - 1;
+            if ((uint32_t)lane == owner) {
+                const uint4* w = reinterpret_cast<const uint4*>(&slot[gsrc]);
+                uint4* d = reinterpret_cast<uint4*>(win_smem);
+                d[0] = __ldcg(w);
+                d[1] = __ldcg(w + 1);
+            }
+        }
+        __syncthreads();
+        const Candidate win = *win_smem;
+        const unsigned long long gbest = win.key;
+        const int64_t idx = (int64_t)(0x7fffffffu - ((uint32_t)gbest >> 1));
+        const bool flip = (gbest & 1ull) != 0ull;
+        const float sgn = flip ? -1.f : 1.f;
+        cur = idx;
+        px = win.qx; py = win.qy; pz = win.qz;
+        p3 = win.nx * sgn; p4 = win.ny * sgn; p5 = win.nz * sgn;
+        const int64_t li = idx - base;
+        if (li >= 0 && li < n_local && tid == (int)(li % kPtThreads)) {
+            sm.visited[li] = 1;
+            sm.nx[li] = p3; sm.ny[li] = p4; sm.nz[li] = p5;
+            if (order) order[step] = (int32_t)idx;
+            if (flipped) flipped[step] = flip ? 1 : 0;
+        }
+        // win_smem is rewritten only after the next step's first __syncthreads, which every thread
+        // reaches after it has copied `win` above.
+    }
+
+    __syncthreads();
+    for (int i = tid; i < n_local; i += kPtThreads) {
+        float nx = sm.nx[i], ny = sm.ny[i], nz = sm.nz[i];
+        if (diffuse) {
+            const float v = __fadd_rn(__fadd_rn(__fmul_rn(sm.ex[i], nx), __fmul_rn(sm.ey[i], ny)), __fmul_rn(sm.ez[i], nz));
+            const float sg = v > 0.f ? 1.f : -1.f;
+            nx *= sg; ny *= sg; nz *= sg;
+        }
+        float* p = pts + (base + i) * ld;
+        p[3] = nx; p[4] = ny; p[5] = nz;
+    }
+}
+
+constexpr size_t kGridWsHeader = 256;      // the arrival counter, alone in its sectors
+
 }  // namespace
 
 int64_t points_max_n() {
-    // 227 KB of shared memory per CTA, 37 bytes of state per point, up to 16 CTAs
+    // one cluster: 227 KB of shared memory per CTA, 37 bytes of state per point, up to 16 CTAs
     const size_t avail = 227 * 1024 - point_smem_bytes(0);
     return (int64_t)(avail / 37) * kMaxCluster;
 }
 
+int64_t points_grid_max_n() {
+    // cooperative grid: one CTA per SM, the same 37 bytes of shared memory per point
+    const size_t avail = 227 * 1024 - point_smem_bytes(0);
+    return (int64_t)(avail / 37) * sm_count_cached();
+}
+
+size_t points_workspace_bytes(int64_t N) {
+    if (N <= points_max_n()) return 0;                       // the single-cluster kernel needs no scratch
+    return kGridWsHeader + 2 * (size_t)sm_count_cached() * sizeof(Candidate);
+}
+
+static int run_points_propagate_grid(float* pts, int64_t N, int64_t ld, int64_t start, float eps, int diffuse,
+                                     int32_t* order, uint8_t* flipped, void* workspace, size_t workspace_bytes,
+                                     cudaStream_t stream) {
+    if (N > points_grid_max_n()) {
+        set_error("N=%lld exceeds the capacity of dnp_points_propagate_f32 (%lld points on this device)",
+                  (long long)N, (long long)points_grid_max_n());
+        return DNP_ERR_INVALID;
+    }
+    const size_t need = points_workspace_bytes(N);
+    if (!workspace || workspace_bytes < need) {
+        set_error("workspace too small: need %zu bytes (dnp_points_workspace_bytes), got %zu", need, workspace_bytes);
+        return DNP_ERR_WORKSPACE;
+    }
+    static std::atomic<int> attr_done{0};
+    if (!attr_done.load()) {
+        DNP_CHECK_CUDA(cudaFuncSetAttribute(points_propagate_grid_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                            227 * 1024));
+        attr_done.store(1);
+    }
+    // about 2048 points per CTA (4 per thread) until every SM has one: fewer CTAs make the per-step exchange cheaper
+    const int sms = sm_count_cached();
+    int ncta = (int)((N + 2047) / 2048);
+    if (ncta > sms) ncta = sms;
+    while (point_smem_bytes((int)((N + ncta - 1) / ncta)) > 227 * 1024 && ncta < sms) ++ncta;
+    const int cap = (int)((N + ncta - 1) / ncta);
+    const size_t smem = point_smem_bytes(cap);
+    int per_sm = 0;
+    DNP_CHECK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, points_propagate_grid_kernel, kPtThreads, smem));
+    if (per_sm < 1 || (int64_t)per_sm * sms < ncta) {
+        set_error("cannot co-schedule %d CTAs for N=%lld", ncta, (long long)N);
+        return DNP_ERR_CUDA;
+    }
+    unsigned int* counter = reinterpret_cast<unsigned int*>(workspace);
+    Candidate* slots = reinterpret_cast<Candidate*>(reinterpret_cast<unsigned char*>(workspace) + kGridWsHeader);
+    DNP_CHECK_CUDA(cudaMemsetAsync(counter, 0, kGridWsHeader, stream));
+    cudaLaunchConfig_t cfg = {};
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeCooperative;
+    attr[0].val.cooperative = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    cfg.gridDim = dim3(ncta);
+    cfg.blockDim = dim3(kPtThreads);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = stream;
+    DNP_CHECK_CUDA(cudaLaunchKernelEx(&cfg, points_propagate_grid_kernel, pts, N, ld, cap, start, eps, diffuse, order,
+                                      flipped, slots, counter));
+    count_launch(1);
+    return DNP_OK;
+}
+
 int run_points_propagate(float* pts, int64_t N, int64_t ld, int64_t start, float eps, int diffuse,
-                         int32_t* order, uint8_t* flipped, cudaStream_t stream) {
+                         int32_t* order, uint8_t* flipped, void* workspace, size_t workspace_bytes,
+                         cudaStream_t stream) {
     if (N <= 0) return DNP_OK;
+    const bool force_grid = getenv("DNP_POINTS_FORCE_GRID") != nullptr;           // tests: grid kernel at any N
+    if (N > points_max_n() || (force_grid && workspace))
+        return run_points_propagate_grid(pts, N, ld, start, eps, diffuse, order, flipped, workspace, workspace_bytes,
+                                         stream);
     static std::atomic<int> attr_done{0};
     if (!attr_done.load()) {
         DNP_CHECK_CUDA(cudaFuncSetAttribute(points_propagate_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,

@@ -22,9 +22,12 @@ int run_patch_covariance(const float* pts, int64_t ld, const int64_t* perm, cons
 int run_field_sign(const float* E, int64_t ld_e, float* normals, int64_t ld_n, const int64_t* idx, int64_t n,
                    int ge, cudaStream_t stream);
 
-int64_t points_max_n();
+int64_t points_max_n();        // single-cluster capacity
+int64_t points_grid_max_n();   // cooperative-grid capacity (one CTA per SM)
+size_t points_workspace_bytes(int64_t N);
 int run_points_propagate(float* pts, int64_t N, int64_t ld, int64_t start, float eps, int diffuse,
-                         int32_t* order, uint8_t* flipped, cudaStream_t stream);
+                         int32_t* order, uint8_t* flipped, void* workspace, size_t workspace_bytes,
+                         cudaStream_t stream);
 
 int run_microbench(int kind, int iters, float* ms_out, double* ops_out, cudaStream_t stream);
 

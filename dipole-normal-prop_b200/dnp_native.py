@@ -36,7 +36,8 @@ SYMBOLS = [
     ("dnp_field_sign_f32", _i32, [_vp, _i64, _vp, _i64, _vp, _i64, _i32, _vp]),
     ("dnp_patch_covariance_f32", _i32, [_vp, _i64, _vp, _vp, _i64, _vp, _vp]),
     ("dnp_points_max_n", _i64, []),
-    ("dnp_points_propagate_f32", _i32, [_vp, _i64, _i64, _i64, _f32, _i32, _vp, _vp, _vp]),
+    ("dnp_points_workspace_bytes", _sz, [_i64]),
+    ("dnp_points_propagate_f32", _i32, [_vp, _i64, _i64, _i64, _f32, _i32, _vp, _vp, _vp, _sz, _vp]),
     ("dnp_field_grad_host_f32", _i32, [_vp, _i64, _i64, _vp, _i64, _i64, _f32, _vp, _i32]),
     ("dnp_potential_host_f32", _i32, [_vp, _i64, _i64, _vp, _i64, _i64, _vp, _i32]),
     ("dnp_launch_count", _i64, []),
@@ -304,8 +305,12 @@ def points_propagate(pts, diffuse=False, starting_point=0, eps=1e-6, want_trace=
     order = torch.empty(N, dtype=torch.int32, device=pts.device) if want_trace else None
     flipped = torch.empty(N, dtype=torch.uint8, device=pts.device) if want_trace else None
     with torch.cuda.device(pts.device):
+        # DNP_POINTS_FORCE_GRID (tests): run the cooperative-grid kernel at any N, so size its scratch
+        nbytes = lib.dnp_points_workspace_bytes((1 << 20) if os.environ.get("DNP_POINTS_FORCE_GRID") else N)
+        ws = torch.empty(nbytes, dtype=torch.uint8, device=pts.device) if nbytes else None
         _check(lib.dnp_points_propagate_f32(_ptr(pts), N, pts.stride(0) if N > 1 else 6, int(starting_point),
-                                            float(eps), int(bool(diffuse)), _ptr(order), _ptr(flipped), _stream(pts)))
+                                            float(eps), int(bool(diffuse)), _ptr(order), _ptr(flipped),
+                                            _ptr(ws), nbytes, _stream(pts)))
     return (order, flipped) if want_trace else None
 
 

@@ -164,12 +164,17 @@ DNP_API int dnp_patch_covariance_f32(const float* pts, int64_t ld,
  * IEEE arithmetic in the reference's evaluation order so that the decision
  * sequence is the reference's.  pts[N,6] (ld) is updated in place.
  * order_opt[N] / flipped_opt[N] (optional) receive the visit order and flips.
- * All state lives in the shared memory of one thread-block cluster, so N is
- * limited to dnp_points_max_n() (about 97 000 points); larger N is an error.  */
+ * All state lives in shared memory: one thread-block cluster (<= 16 CTAs, DSMEM
+ * exchange, about 97 000 points) or, beyond that, a cooperative grid of one CTA
+ * per SM that exchanges the step winner through L2 (dnp_points_max_n() points,
+ * about 900 000 on a B200).  The grid variant needs dnp_points_workspace_bytes(N)
+ * bytes of device scratch (0 for the cluster variant; workspace may then be NULL). */
 DNP_API int64_t dnp_points_max_n(void);
+DNP_API size_t dnp_points_workspace_bytes(int64_t N);
 DNP_API int dnp_points_propagate_f32(float* pts, int64_t N, int64_t ld, int64_t starting_point,
                              float eps, int diffuse,
-                             int32_t* order_opt, uint8_t* flipped_opt, void* stream);
+                             int32_t* order_opt, uint8_t* flipped_opt,
+                             void* workspace, size_t workspace_bytes, void* stream);
 
 /* ------------------------------------------------------------------ host-buffer entry points
  * Same math with HOST pointers: the call stages inputs to the device, runs the

@@ -191,8 +191,25 @@ ORC_API double orc_mean_potential_f64(const float *src, int64_t S, int64_t lds, 
  * With one source the leaf's sum over sources is the identity, so every step
  * is element-wise and this loop reproduces the reference bit for bit as long
  * as the compiler does not contract a*b+c (build with -ffp-contract=off). */
+static void points_propagate_impl(float *pts, int64_t N, int64_t start, float eps, int diffuse,
+                                  int64_t max_steps, int32_t *order, uint8_t *flipped);
+
 ORC_API void orc_points_propagate_f32(float *pts, int64_t N, int64_t start, float eps,
                                       int diffuse, int32_t *order, uint8_t *flipped)
+{
+    points_propagate_impl(pts, N, start, eps, diffuse, N, order, flipped);
+}
+
+/* The first `max_steps` greedy steps only (no diffuse epilogue): the prefix of the decision trace of a
+ * cloud too large to run to the end on the CPU.  order/flipped entries 0..max_steps are written. */
+ORC_API void orc_points_propagate_prefix_f32(float *pts, int64_t N, int64_t start, float eps,
+                                             int64_t max_steps, int32_t *order, uint8_t *flipped)
+{
+    points_propagate_impl(pts, N, start, eps, 0, max_steps, order, flipped);
+}
+
+static void points_propagate_impl(float *pts, int64_t N, int64_t start, float eps, int diffuse,
+                                  int64_t max_steps, int32_t *order, uint8_t *flipped)
 {
     float *E = (float *)calloc((size_t)(3 * N), sizeof(float));
     uint8_t *visited = (uint8_t *)calloc((size_t)N, 1);
@@ -200,7 +217,7 @@ ORC_API void orc_points_propagate_f32(float *pts, int64_t N, int64_t start, floa
     visited[cur] = 1;
     if (order) order[0] = (int32_t)cur;
     if (flipped) flipped[0] = 0;
-    for (int64_t step = 1; step <= N; ++step) {
+    for (int64_t step = 1; step <= N && step <= max_steps; ++step) {
         /* add the field of `cur` to every other point, then pick the next one */
         const float *p = pts + 6 * cur;
         float best = -1.0f; int64_t best_i = -1; float best_val = 0.0f;

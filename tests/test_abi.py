@@ -131,6 +131,6 @@ def test_argument_validation_without_a_gpu():
     assert rc == -1 and b"stride" in lib.dnp_last_error()
     rc = lib.dnp_field_sign_f32(one, 3, one, 3, None, 4, 0, None)
     assert rc == -1 and b"mode" in lib.dnp_last_error()
-    rc = lib.dnp_points_propagate_f32(one, 10, 6, 11, 1e-6, 0, None, None, None)
+    rc = lib.dnp_points_propagate_f32(one, 10, 6, 11, 1e-6, 0, None, None, None, 0, None)
     assert rc == -1 and b"starting_point" in lib.dnp_last_error()
     assert lib.dnp_field_grad_f32(None, 0, 6, None, 0, 3, 1e-5, None, 3, 0, None, 0, None) == 0   # empty is OK

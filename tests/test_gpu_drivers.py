@@ -88,6 +88,69 @@ def test_points_propagation_large_cluster(orc, dev):
     assert abs(s.mean()) > 0.99
 
 
+# ------------------------------------------------------------------ a6 beyond one cluster: cooperative grid kernel
+@pytest.mark.parametrize("tag", ["n512", "n2000", "full"])
+def test_points_propagation_grid_kernel_bit_exact(golden, dev, tag, monkeypatch):
+    """The grid kernel forced at golden sizes: same decision trace and normals as the reference."""
+    import dnp_native
+    monkeypatch.setenv("DNP_POINTS_FORCE_GRID", "1")
+    g = golden("points_prop")
+    n, diffuse = int(g[f"{tag}_n"]), bool(g[f"{tag}_diffuse"])
+    pts = torch.from_numpy(g["pc_in"][:n].copy()).to(dev)
+    launches = dnp_native.launch_count()
+    order, flipped = dnp_native.points_propagate(pts, diffuse=diffuse, want_trace=True)
+    assert dnp_native.launch_count() == launches + 1
+    assert np.array_equal(order.cpu().numpy(), g[f"{tag}_order"])
+    assert np.array_equal(flipped.cpu().numpy().astype(bool), g[f"{tag}_flipped"])
+    assert np.array_equal(pts[:, 3:].cpu().numpy(), g[f"{tag}_normals"])
+
+
+@pytest.mark.parametrize("n", [1, 2, 33, 2049, 6200])
+def test_points_propagation_grid_kernel_sizes(fu, orc, dev, n, monkeypatch):
+    monkeypatch.setenv("DNP_POINTS_FORCE_GRID", "1")
+    g = torch.Generator().manual_seed(100 + n)
+    d = torch.randn(n, 3, generator=g)
+    d = d / d.norm(dim=-1, keepdim=True)
+    pc = torch.cat([d * 0.45 + torch.randn(n, 3, generator=g) * 0.01, d], 1).float()
+    pc[torch.rand(n, generator=g) < 0.5, 3:] *= -1
+    want, order, flipped = orc.points_propagate(pc.numpy(), diffuse=True, starting_point=n // 2)
+    pts = pc.clone().to(dev)
+    fu.strongest_field_propagation_points(pts, diffuse=True, starting_point=n // 2)
+    assert np.array_equal(pts.cpu().numpy(), want)
+
+
+def test_points_propagation_beyond_one_cluster(fu, orc, dev):
+    """N = 120 000 (the shipped 100 000-point clouds need this): more points than one cluster holds, so the
+    cooperative-grid kernel runs.  The oracle cannot finish this size in test time; it pins the first 300
+    decisions, and size-independent properties cover the rest."""
+    import dnp_native
+    n = 120000
+    assert n > 97000 and dnp_native.load().dnp_points_workspace_bytes(n) > 0
+    g = torch.Generator().manual_seed(19)
+    d = torch.randn(n, 3, generator=g)
+    d = d / d.norm(dim=-1, keepdim=True)
+    pc = torch.cat([d * 0.45 + torch.randn(n, 3, generator=g) * 0.002, d], 1).float()
+    scramble = torch.rand(n, generator=g) < 0.5
+    pc[scramble, 3:] *= -1
+    pts = pc.clone().to(dev)
+    order, flipped = dnp_native.points_propagate(pts, want_trace=True)
+    order, flipped = order.cpu().numpy(), flipped.cpu().numpy().astype(bool)
+    want_order, want_flipped = orc.points_propagate_prefix(pc.numpy(), 300)
+    assert np.array_equal(order[:301], want_order)
+    assert np.array_equal(flipped[:301], want_flipped)
+    assert np.array_equal(np.sort(order), np.arange(n))                   # every point visited exactly once
+    out = pts.cpu().numpy()
+    assert np.array_equal(out[:, :3], pc.numpy()[:, :3])
+    was_flipped = np.zeros(n, dtype=bool)
+    was_flipped[order] = flipped
+    assert np.array_equal(out[:, 3:], pc.numpy()[:, 3:] * np.where(was_flipped, -1.0, 1.0)[:, None].astype(np.float32))
+    side = np.sign((out[:, :3] * out[:, 3:]).sum(-1))                    # a sphere: one consistent side
+    assert abs(side.mean()) > 0.99
+    again = pc.clone().to(dev)                                            # deterministic
+    fu.strongest_field_propagation_points(again)
+    assert torch.equal(again, pts)
+
+
 def test_points_propagation_too_large(fu, dev):
     import dnp_native
     n = int(dnp_native.load().dnp_points_max_n()) + 1
