@@ -369,7 +369,38 @@ def extras(dn, field_utils, dev, src, tgt):
         out["cfg2_reference_cpu_s_build_container"] = float(g["plain_ref_seconds"])
     except OSError:
         pass
+    # cfg1 at the size of the shipped 100 000-point clouds (flower/galera/boxunion.xyz): cooperative-grid kernel
+    big_pc = surface_cloud(100000, 7).to(dev)
+    out["points_propagation_100k_ms"] = best_ms(lambda: field_utils.strongest_field_propagation_points(big_pc.clone()), 1)
+    # cfg4 stand-in (data/interpolate/*.xyz are not shipped): 100 000 oriented reference points -> 1M-point target
+    ref_pc = surface_cloud(100000, 8).to(dev)
+    tgt3 = surface_cloud(1 << 20, 9)[:, :3].contiguous().to(dev)
+    out["cfg4_reference_field_100k_x_1M_ms"] = best_ms(lambda: field_utils.reference_field(ref_pc, tgt3), 2)
+    # cfg3 stand-in (data/lion.xyz is not shipped): 1M surface points, 1000 spatially coherent patches of ~1000
+    # points, 500 representatives each (orient_large.py:48-52), diffuse, then the lattice test
+    pc3 = surface_cloud(1 << 20, 10)
+    key = ((pc3[:, :3] + 0.6) * 8).long().clamp(0, 15)
+    order = torch.argsort(key[:, 0] * 256 + key[:, 1] * 16 + key[:, 2], stable=True)
+    chunks = torch.chunk(order, 1000)
+    reps = [(c[:500].to(dev), c[500:].to(dev)) for c in chunks]
+    pc3 = pc3.to(dev)
+
+    def run_reps():
+        work = pc3.clone()
+        field_utils.strongest_field_propagation_reps(work, reps, diffuse=True)
+        return field_utils.measure_mean_potential(work)
+    out["cfg3_reps_propagation_1M_pts_1000_patches_ms"] = best_ms(run_reps, 1)
     return out
+
+
+def surface_cloud(n, seed):
+    """Noisy unit-normal sphere of radius 0.45 with a seeded 50 % sign scramble."""
+    g = torch.Generator().manual_seed(seed)
+    d = torch.randn(n, 3, generator=g)
+    d = d / d.norm(dim=-1, keepdim=True)
+    pc = torch.cat([d * 0.45 + torch.randn(n, 3, generator=g) * 0.002, d], 1).float()
+    pc[torch.rand(n, generator=g) < 0.5, 3:] *= -1
+    return pc.contiguous()
 
 
 if __name__ == "__main__":

@@ -87,6 +87,11 @@ class _Work:
             self.orig[:, 3:] = self.t[:, 3:].to(device=self.orig.device, dtype=self.orig.dtype)
 
 
+def _clear(mask, j):
+    """mask[j] = 0 for a Python int j without the host-to-device scalar copy `mask[j] = 0` makes."""
+    mask.narrow(0, int(j), 1).zero_()
+
+
 def _index_list(idx_list, dev):
     out = []
     for idx in idx_list:
@@ -281,15 +286,15 @@ def strongest_field_propagation_reps(input_pc, reps, diffuse=False, weights=None
         E = torch.zeros(N, 3, dtype=torch.float32, device=dev)
         oriented = torch.zeros(N, dtype=torch.uint8, device=dev)
         settled = torch.ones(N, dtype=torch.uint8, device=dev)     # NOT non_oriented_pts_mask (:223-227)
-        settled[perm] = 0
+        settled.index_fill_(0, perm, 0)
         scratch_mask = torch.zeros(N, dtype=torch.uint8, device=dev)
         active = torch.ones(P, dtype=torch.uint8, device=dev)
 
         start = _flattest_patch(pts, perm, offsets)                                       # :230-233
         patch = rep_idx[start]
-        active[start] = 0
-        oriented[patch] = 1
-        settled[patch] = 1
+        _clear(active, start)
+        oriented.index_fill_(0, patch, 1)
+        settled.index_fill_(0, patch, 1)
         _dn.field_apply(pts, pts, _EPS_DEFAULT, _dn.EPI_STORE, out=E, src_idx=patch,      # :239
                         tgt_idx=perm, tgt_skip=settled)
 
@@ -300,14 +305,14 @@ def strongest_field_propagation_reps(input_pc, reps, diffuse=False, weights=None
             if value < 0:                                                                 # :250-252
                 pts[patch, 3:] *= -1
                 pts[rest_idx[j], 3:] *= -1
-            active[j] = 0
-            oriented[patch] = 1
-            settled[patch] = 1
+            _clear(active, j)
+            oriented.index_fill_(0, patch, 1)
+            settled.index_fill_(0, patch, 1)
             if diffuse:                                                                   # :256-261
-                scratch_mask[patch] = 1
+                scratch_mask.index_fill_(0, patch, 1)
                 _dn.field_apply(pts, pts, _EPS_DEFAULT, _dn.EPI_ACCUM, out=E, src_idx=patch,
                                 tgt_idx=perm, tgt_skip=scratch_mask)
-                scratch_mask[patch] = 0
+                scratch_mask.index_fill_(0, patch, 0)
             else:                                                                         # :264-265
                 _dn.field_apply(pts, pts, _EPS_DEFAULT, _dn.EPI_ACCUM, out=E, src_idx=patch,
                                 tgt_idx=perm, tgt_skip=settled)
@@ -348,8 +353,8 @@ def strongest_field_propagation(pts, patches, all_patches, diffuse=False, weight
 
         start = _flattest_patch(p, perm, offsets)                                         # :303-306
         patch = idx[start]
-        active[start] = 0
-        oriented[patch] = 1
+        _clear(active, start)
+        oriented.index_fill_(0, patch, 1)
         _dn.field_apply(p, p, _EPS_DEFAULT, _dn.EPI_STORE, out=E, src_idx=patch, tgt_skip=oriented)   # :311
 
         for _ in range(P - 1):
@@ -358,12 +363,12 @@ def strongest_field_propagation(pts, patches, all_patches, diffuse=False, weight
             patch = idx[j]
             if value < 0:                                                                 # :322-323
                 p[patch, 3:] *= -1
-            active[j] = 0
-            oriented[patch] = 1
+            _clear(active, j)
+            oriented.index_fill_(0, patch, 1)
             if diffuse:                                                                   # :326-331
-                scratch_mask[patch] = 1
+                scratch_mask.index_fill_(0, patch, 1)
                 _dn.field_apply(p, p, _EPS_DEFAULT, _dn.EPI_ACCUM, out=E, src_idx=patch, tgt_skip=scratch_mask)
-                scratch_mask[patch] = 0
+                scratch_mask.index_fill_(0, patch, 0)
             else:                                                                         # :333-335
                 _dn.field_apply(p, p, _EPS_DEFAULT, _dn.EPI_ACCUM, out=E, src_idx=patch, tgt_skip=oriented)
 
