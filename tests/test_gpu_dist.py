@@ -1,0 +1,91 @@
+"""Multi-GPU parity with the real CUDA kernels and NCCL: world size 2, one process per
+GPU.  Needs two visible GPUs (skipped otherwise; `gpurun --gpus 2 -- python -m pytest tests/test_gpu_dist.py -m gpu`).
+The sharding / collective logic itself is covered on CPU with gloo in tests/test_dist.py."""
+import os
+import socket
+import sys
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+pytestmark = pytest.mark.gpu
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+PKG = os.path.join(ROOT, "dipole-normal-prop_b200")
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _cloud(n, seed):
+    g = torch.Generator().manual_seed(seed)
+    xyz = torch.rand(n, 3, generator=g) - 0.5
+    nr = torch.randn(n, 3, generator=g)
+    return torch.cat([xyz, nr / nr.norm(dim=-1, keepdim=True)], 1).float()
+
+
+def _worker(rank, world, port, out_dir):
+    for p in (ROOT, PKG):
+        if p not in sys.path:
+            sys.path.insert(0, p)
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    torch.cuda.set_device(rank)
+    dev = torch.device("cuda", rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+    import dnp_dist
+
+    src, tgt = _cloud(20001, 1).to(dev), _cloud(150003, 2).to(dev)      # uneven shards; large enough for the by-value kernel
+    E_full = dnp_dist.field_grad_sharded(src, tgt, gather=True)
+    phi_full = dnp_dist.potential_sharded(src, tgt, gather=True)
+    E_local = dnp_dist.field_grad_sharded(src, tgt)
+    mean = dnp_dist.measure_mean_potential_sharded(src)
+    perm = torch.randperm(20001, generator=torch.Generator().manual_seed(3)).to(dev)
+    offsets = torch.tensor([0, 400, 401, 1200, 2500, 3010, 20001])
+    edges = torch.tensor([[0, 1], [1, 0], [2, 3], [3, 2], [4, 0], [1, 1], [5, 4]])
+    w, invw = dnp_dist.edge_scores_sharded(src, perm, offsets, edges)
+    torch.save({"E_full": E_full.cpu(), "phi_full": phi_full.cpu(), "E_local": E_local.cpu(), "mean": mean.cpu(),
+                "w": w.cpu(), "range": dnp_dist.shard_range(150003, rank, world)}, os.path.join(out_dir, f"rank{rank}.pt"))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.timeout(600)
+def test_world_size_2_nccl(tmp_path, dev):
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs (gpurun --gpus 2)")
+    import dnp_native as dn
+    import field_utils
+    world = 2
+    mp.spawn(_worker, args=(world, _free_port(), str(tmp_path)), nprocs=world, join=True)
+    res = [torch.load(os.path.join(tmp_path, f"rank{r}.pt")) for r in range(world)]
+    src, tgt = _cloud(20001, 1).to(dev), _cloud(150003, 2).to(dev)
+    E = dn.field_grad(src, tgt).cpu()
+    phi = dn.potential(src, tgt).cpu()
+    mag = E.norm(dim=-1)
+    for r in range(world):
+        a, b = res[r]["range"]
+        # shards of the same kernels: FP32 tolerance (the lane / split plans depend on the shard size)
+        assert bool(((res[r]["E_full"] - E).norm(dim=-1) <= 1e-4 * mag + 1e-6 * mag.max()).all())
+        assert torch.equal(res[r]["E_full"][a:b], res[r]["E_local"])
+        assert bool(((res[r]["phi_full"] - phi).abs() <= 1e-4 * phi.abs() + 1e-5 * phi.abs().max()).all())
+    assert torch.equal(res[0]["E_full"], res[1]["E_full"])              # all_gather: identical on every rank
+    want_mean = field_utils.measure_mean_potential(src).item()
+    for r in range(world):
+        assert abs(res[r]["mean"].item() - want_mean) <= 1e-4 * abs(want_mean)
+    assert torch.equal(res[0]["w"], res[1]["w"])                        # all_reduce: identical on every rank
+    perm = torch.randperm(20001, generator=torch.Generator().manual_seed(3)).to(dev)
+    offsets = [0, 400, 401, 1200, 2500, 3010, 20001]
+    edges = [[0, 1], [1, 0], [2, 3], [3, 2], [4, 0], [1, 1], [5, 4]]
+    for e, (s_p, t_p) in enumerate(edges):
+        S = src[perm[offsets[s_p]:offsets[s_p + 1]]]
+        T = src[perm[offsets[t_p]:offsets[t_p + 1]]]
+        want, _ = field_utils.field_edge_calculator(S, T)
+        got = res[0]["w"][e].item()
+        assert abs(got - float(want)) <= 2e-4 * abs(float(want)) + 1e-3, (e, got, float(want))
+    np.save(os.path.join(tmp_path, "ok.npy"), np.zeros(1))
