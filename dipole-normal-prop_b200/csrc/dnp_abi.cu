@@ -355,6 +355,42 @@ int dnp_points_propagate_f32(float* pts, int64_t N, int64_t ld, int64_t starting
                                 workspace_bytes, (cudaStream_t)stream);
 }
 
+// ------------------------------------------------------------------ "xie" interaction (dnp_xie.cu)
+static int xie_matrix_abi(bool field, const float* src, int64_t S, int64_t ld_s, const float* tgt, int64_t M,
+                          int64_t ld_t, float C, const double* rad2, float* out, int64_t ld_o, void* stream) {
+    DNP_REQUIRE(S >= 0 && M >= 0, "negative size");
+    if (S == 0 || M == 0) return DNP_OK;
+    DNP_REQUIRE(src && tgt && out, "null pointer");
+    DNP_REQUIRE(ld_s >= 6 && ld_t >= (field ? 3 : 6), "row stride too small (sources need 6 columns, targets 6 / 3)");
+    DNP_REQUIRE(ld_o >= (field ? 3 * S : S), "output row stride too small");
+    return run_xie_matrix(field, src, S, ld_s, tgt, M, ld_t, C, rad2, out, ld_o, (cudaStream_t)stream);
+}
+
+int dnp_xie_interaction_f32(const float* src, int64_t S, int64_t ld_s, const float* tgt, int64_t M, int64_t ld_t,
+                            float C, const double* src_radius2_opt, float* inter, int64_t ld_o, void* stream) {
+    return xie_matrix_abi(false, src, S, ld_s, tgt, M, ld_t, C, src_radius2_opt, inter, ld_o, stream);
+}
+
+int dnp_xie_field_f32(const float* src, int64_t S, int64_t ld_s, const float* tgt, int64_t M, int64_t ld_t,
+                      float C, const double* src_radius2_opt, float* field, int64_t ld_o, void* stream) {
+    return xie_matrix_abi(true, src, S, ld_s, tgt, M, ld_t, C, src_radius2_opt, field, ld_o, stream);
+}
+
+int64_t dnp_xie_max_n(int knn) { return xie_max_n(knn != 0); }
+
+size_t dnp_xie_workspace_bytes(int64_t N, int64_t T) { return xie_workspace_bytes(N, T); }
+
+int dnp_xie_propagate_in_order_f32(const float* pts, int64_t N, int64_t ld, const int64_t* order, int64_t T,
+                                   float C, const double* radius2_opt, int diffuse, uint8_t* flips,
+                                   float* interactions, void* workspace, size_t workspace_bytes, void* stream) {
+    DNP_REQUIRE(N >= 0 && T >= 0, "negative size");
+    if (N == 0 || T == 0) return DNP_OK;
+    DNP_REQUIRE(pts && order && flips && interactions, "null pointer");
+    DNP_REQUIRE(ld >= 6, "points need 6 columns");
+    return run_xie_propagate(pts, N, ld, order, T, C, radius2_opt, diffuse, flips, interactions, workspace,
+                             workspace_bytes, (cudaStream_t)stream);
+}
+
 int dnp_profile_begin(void) {
     profile_begin();
     return DNP_OK;

@@ -3,6 +3,7 @@
 #pragma once
 
 #include <cuda_runtime.h>
+#include <stddef.h>
 #include <stdint.h>
 
 namespace dnp {
@@ -28,6 +29,15 @@ size_t points_workspace_bytes(int64_t N);
 int run_points_propagate(float* pts, int64_t N, int64_t ld, int64_t start, float eps, int diffuse,
                          int32_t* order, uint8_t* flipped, void* workspace, size_t workspace_bytes,
                          cudaStream_t stream);
+
+// "xie" reflected-normal interaction (dnp_xie.cu)
+int run_xie_matrix(bool field, const float* src, int64_t S, int64_t ld_s, const float* tgt, int64_t M, int64_t ld_t,
+                   float C, const double* rad2, float* out, int64_t ld_o, cudaStream_t stream);
+int64_t xie_max_n(bool knn);
+size_t xie_workspace_bytes(int64_t N, int64_t T);
+int run_xie_propagate(const float* pts, int64_t N, int64_t ld, const int64_t* order, int64_t T, float C,
+                      const double* rad2, int diffuse, uint8_t* flips, float* inter, void* workspace,
+                      size_t workspace_bytes, cudaStream_t stream);
 
 int run_microbench(int kind, int iters, float* ms_out, double* ops_out, cudaStream_t stream);
 

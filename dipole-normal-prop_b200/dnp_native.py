@@ -38,6 +38,11 @@ SYMBOLS = [
     ("dnp_points_max_n", _i64, []),
     ("dnp_points_workspace_bytes", _sz, [_i64]),
     ("dnp_points_propagate_f32", _i32, [_vp, _i64, _i64, _i64, _f32, _i32, _vp, _vp, _vp, _sz, _vp]),
+    ("dnp_xie_interaction_f32", _i32, [_vp, _i64, _i64, _vp, _i64, _i64, _f32, _vp, _vp, _i64, _vp]),
+    ("dnp_xie_field_f32", _i32, [_vp, _i64, _i64, _vp, _i64, _i64, _f32, _vp, _vp, _i64, _vp]),
+    ("dnp_xie_max_n", _i64, [_i32]),
+    ("dnp_xie_workspace_bytes", _sz, [_i64, _i64]),
+    ("dnp_xie_propagate_in_order_f32", _i32, [_vp, _i64, _i64, _vp, _i64, _f32, _vp, _i32, _vp, _vp, _vp, _sz, _vp]),
     ("dnp_field_grad_host_f32", _i32, [_vp, _i64, _i64, _vp, _i64, _i64, _f32, _vp, _i32]),
     ("dnp_potential_host_f32", _i32, [_vp, _i64, _i64, _vp, _i64, _i64, _vp, _i32]),
     ("dnp_launch_count", _i64, []),
@@ -312,6 +317,64 @@ def points_propagate(pts, diffuse=False, starting_point=0, eps=1e-6, want_trace=
                                             float(eps), int(bool(diffuse)), _ptr(order), _ptr(flipped),
                                             _ptr(ws), nbytes, _stream(pts)))
     return (order, flipped) if want_trace else None
+
+
+# ------------------------------------------------------------------ "xie" interaction
+def knn_radius2(sources, targets, k, chunk=2048):
+    """Squared distance (float64) from every source to its k-th nearest target: the kNN mask of
+    field_utils.py:447-455 as one radius per source.  Plumbing in torch; exact differences of the float
+    coordinates in double, the same expression the kernels evaluate."""
+    s = sources[:, :3].double()
+    t = targets[:, :3].double()
+    k = min(int(k), t.shape[0])
+    out = torch.empty(s.shape[0], dtype=torch.float64, device=s.device)
+    for a in range(0, s.shape[0], chunk):
+        d = s[a:a + chunk, None, :] - t[None, :, :]
+        d2 = (d[..., 0] * d[..., 0] + d[..., 1] * d[..., 1]) + d[..., 2] * d[..., 2]
+        out[a:a + chunk] = torch.topk(d2, k, dim=1, largest=False).values[:, -1]
+    return out
+
+
+def xie_matrix(sources, targets, C=3.0, radius2=None, field=False):
+    """[M, S] interaction matrix (field=False, targets need normals) or [M, S, 3] field (field=True)."""
+    lib = load()
+    src, ld_s = _rows(sources, 6, "source")
+    tgt, ld_t = _rows(targets, 3 if field else 6, "target")
+    S, M = src.shape[0], tgt.shape[0]
+    out = torch.empty((M, S, 3) if field else (M, S), dtype=torch.float32, device=tgt.device)
+    if S == 0 or M == 0:
+        return out
+    if radius2 is not None:
+        radius2 = radius2.to(device=tgt.device, dtype=torch.float64).contiguous()
+    fn = lib.dnp_xie_field_f32 if field else lib.dnp_xie_interaction_f32
+    with torch.cuda.device(tgt.device):
+        _check(fn(_ptr(src), S, ld_s, _ptr(tgt), M, ld_t, float(C), _ptr(radius2), _ptr(out),
+                  3 * S if field else S, _stream(tgt)))
+    return out
+
+
+def xie_propagate_in_order(pts, order, C=3.0, radius2=None, diffuse=False):
+    """(flips[T, N] bool, interactions[T, N] float32) of the in-order propagation, one launch."""
+    lib = load()
+    p, ld = _rows(pts, 6, "pts")
+    dev = p.device
+    order = _idx(torch.as_tensor(order), dev, "order")
+    if order.dim() != 2 or order.shape[1] != p.shape[0]:
+        raise ValueError(f"order must be [T, N={p.shape[0]}] (got {tuple(order.shape)})")
+    T, N = order.shape
+    if N > 0 and (int(order.min()) < 0 or int(order.max()) >= N):
+        raise ValueError("order holds indices outside [0, N)")
+    flips = torch.zeros(T, N, dtype=torch.uint8, device=dev)
+    inter = torch.zeros(T, N, dtype=torch.float32, device=dev)
+    if radius2 is not None:
+        radius2 = radius2.to(device=dev, dtype=torch.float64).contiguous()
+    with torch.cuda.device(dev):
+        nbytes = lib.dnp_xie_workspace_bytes(N, T) if diffuse else 0
+        ws = torch.empty(nbytes, dtype=torch.uint8, device=dev) if nbytes else None
+        _check(lib.dnp_xie_propagate_in_order_f32(_ptr(p), N, ld, _ptr(order), T, float(C), _ptr(radius2),
+                                                  int(bool(diffuse)), _ptr(flips), _ptr(inter), _ptr(ws), nbytes,
+                                                  _stream(p)))
+    return flips.bool(), inter
 
 
 # ------------------------------------------------------------------ host-buffer calls (CPU tensors in, CPU tensors out)

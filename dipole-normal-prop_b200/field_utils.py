@@ -266,6 +266,58 @@ def reference_field(pc1, pc2):
         return pc2
 
 
+# ---------------------------------------------------------------------------- the "xie" interaction
+def _xie_inputs(source, target, knn_mask, need_target_normals):
+    s, cast = _check_dtype(source, "source")
+    t, _ = _check_dtype(target, "target")
+    if s.dim() != 2 or s.shape[1] < 6:
+        raise ValueError("source must be [N, 6]")
+    if t.dim() != 2 or t.shape[1] < (6 if need_target_normals else 3):
+        raise ValueError("target must be [M, 6]" if need_target_normals else "target must be [M, >=3]")
+    on_cuda = _both_cuda(s, t)
+    dev = t.device if on_cuda else _cuda_device()
+    s_d, t_d = s.to(dev), t.to(dev)
+    radius2 = _dn.knn_radius2(s_d, t_d, knn_mask) if knn_mask is not None and knn_mask > 0 else None
+    return s_d, t_d, radius2, cast, source.device
+
+
+def xie_field(source: torch.Tensor, target: torch.Tensor, eps, max_pts=5000, knn_mask=-1, C=3):
+    """field_utils.py:431-469.  [M, N, 3]: out[t, s] = (n_s - C (n_s.Rh) Rh) / |R|^3; a coincident pair keeps n_s.
+    `eps` is unused by the reference as well; `max_pts` (its chunking) is ignored.  Divergence: the reference's
+    recursion drops `knn_mask` and `C` for inputs above max_pts^2 pairs (:436-441 pass neither on); here they
+    apply at every size."""
+    with torch.no_grad():
+        s, t, radius2, cast, dev = _xie_inputs(source, target, knn_mask, False)
+        out = _dn.xie_matrix(s, t, C=C, radius2=radius2, field=True).to(dev)
+        return out.to(cast) if cast else out
+
+
+def xie_intersaction(source: torch.Tensor, target: torch.Tensor, eps, knn_mask, C):
+    """field_utils.py:509-519.  [M, N]: inter[t, s] = xie_field[t, s] . n_t, NaN / Inf -> 0 (no warning print)."""
+    with torch.no_grad():
+        s, t, radius2, cast, dev = _xie_inputs(source, target, knn_mask, True)
+        out = _dn.xie_matrix(s, t, C=C, radius2=radius2, field=False).to(dev)
+        return out.to(cast) if cast else out
+
+
+def xie_propagation_points_in_order(pts: torch.Tensor, eps, order, diffuse=False, verbose=False, points_weight=None,
+                                    knn_mask=-1, C=3):
+    """field_utils.py:569-605.  order [T, N]: T visiting orders; returns the bool tensor [T, N] `interactions < 0`
+    (flip status of every point in every chain).  The [N, N] interaction matrix is never formed: one cluster per
+    chain evaluates the visited point's row on the fly (dnp_xie_propagate_in_order_f32).  `points_weight` has no
+    effect in the reference either (:584-585 multiplies by ones); `eps` and `verbose` are unused."""
+    with torch.no_grad():
+        p, _ = _check_dtype(pts, "pts")
+        if p.dim() != 2 or p.shape[1] != 6:
+            raise ValueError("pts must be [N, 6]")
+        dev = p.device if p.is_cuda else _cuda_device()
+        p_d = p.to(dev)
+        radius2 = _dn.knn_radius2(p_d, p_d, knn_mask) if knn_mask is not None and knn_mask > 0 else None
+        order_t = torch.as_tensor(np.asarray(order) if not isinstance(order, torch.Tensor) else order).long()
+        flips, _ = _dn.xie_propagate_in_order(p_d, order_t, C=C, radius2=radius2, diffuse=diffuse)
+        return flips.to(pts.device)
+
+
 # ---------------------------------------------------------------------------- a8: patch propagation on representatives
 def strongest_field_propagation_reps(input_pc, reps, diffuse=False, weights=None):
     """field_utils.py:207-282.  reps = [(rep_idx, rest_idx)] per patch.  Mutates input_pc[:, 3:]; returns None."""

@@ -182,6 +182,42 @@ DNP_API int dnp_points_propagate_f32(float* pts, int64_t N, int64_t ld, int64_t 
                              int32_t* order_opt, uint8_t* flipped_opt,
                              void* workspace, size_t workspace_bytes, void* stream);
 
+/* ------------------------------------------------------------------ "xie" reflected-normal interaction
+ * (the fork's N x N propagation variant.)
+ * dnp_xie_field_f32 replaces field_utils.xie_field (field_utils.py:431-469):
+ *   field[t, s, 0:3] = (n_s - C (n_s.Rh) Rh) / |R|^3,  R = p_s - q_t,  Rh = R/|R|;
+ *   a coincident pair keeps the un-normalised n_s (:456-460).  `eps` is unused by the reference.
+ * dnp_xie_interaction_f32 replaces field_utils.xie_intersaction (:509-519):
+ *   inter[t, s] = field[t, s] . n_t, non-finite entries written as 0.
+ * Outputs are row-major over targets: inter[t * ld_o + s], field[t * ld_o + 3 s + c].
+ * src_radius2_opt (device doubles [S], may be NULL) carries the kNN mask of :447-455: source s only
+ * acts on targets with |R|^2 <= src_radius2_opt[s] (squared distance to its k-th nearest target,
+ * evaluated in double from the float coordinates).                                              */
+DNP_API int dnp_xie_interaction_f32(const float* src, int64_t S, int64_t ld_s,
+                            const float* tgt, int64_t M, int64_t ld_t,
+                            float C, const double* src_radius2_opt,
+                            float* inter, int64_t ld_o, void* stream);
+DNP_API int dnp_xie_field_f32(const float* src, int64_t S, int64_t ld_s,
+                      const float* tgt, int64_t M, int64_t ld_t,
+                      float C, const double* src_radius2_opt,
+                      float* field, int64_t ld_o, void* stream);
+
+/* replaces field_utils.xie_propagation_points_in_order (field_utils.py:569-605) without
+ * materialising the [N, N] matrix: T independent chains, chain t visits order[t * N + i],
+ * i = 0..N-1; the visited point's interaction with the points already weighted is summed (in
+ * double), its weight becomes -1 if the sum is < 0, else +1.  flips[t * N + p] = (sum < 0) and
+ * interactions[t * N + p] = the sum, as of the visit of p; with diffuse != 0 both are
+ * recomputed from the final weights (inter = mat w, :598-604).  One launch: one thread-block
+ * cluster per chain with the points in shared memory (N <= dnp_xie_max_n()).
+ * workspace: dnp_xie_workspace_bytes(N, T) device bytes, only needed with diffuse.            */
+DNP_API int64_t dnp_xie_max_n(int knn);
+DNP_API size_t dnp_xie_workspace_bytes(int64_t N, int64_t T);
+DNP_API int dnp_xie_propagate_in_order_f32(const float* pts, int64_t N, int64_t ld,
+                                   const int64_t* order, int64_t T,
+                                   float C, const double* radius2_opt, int diffuse,
+                                   uint8_t* flips, float* interactions,
+                                   void* workspace, size_t workspace_bytes, void* stream);
+
 /* ------------------------------------------------------------------ host-buffer entry points
  * Same math with HOST pointers: the call stages inputs to the device, runs the
  * kernels and copies the result back before returning (synchronous).  This is

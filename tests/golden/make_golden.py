@@ -375,8 +375,42 @@ def gen_signatures(fu, util):
     print(f"wrote {path}")
 
 
+def gen_xie(fu, util):
+    """the "xie" reflected-normal interaction (field_utils.py:431-469,509-519) and
+    the in-order propagation over T visiting orders (:569-605).  float32 = what the reference computes,
+    float64 = the same functions on .double() inputs (accuracy referee)."""
+    g = torch.Generator().manual_seed(4242)
+    out = {}
+    src, tgt = scramble(sphere_cloud(g, 200), g), scramble(sphere_cloud(g, 120), g)
+    tgt[:7] = src[:7]                                          # coincident pairs: the un-normalised branch (:456-460)
+    out["field_C3"] = fu.xie_field(src, tgt, 1e-2, C=3)
+    for C in (3, 2):
+        out[f"inter_C{C}"] = fu.xie_intersaction(src, tgt, 1e-2, -1, C)
+        out[f"inter64_C{C}"] = fu.xie_intersaction(src.double(), tgt.double(), 1e-2, -1, C)
+    out["src"], out["tgt"] = src, tgt
+    # knn mask (:447-455): each source keeps its k nearest targets
+    out["inter_knn16"] = fu.xie_intersaction(src, tgt, 1e-2, 16, 3)
+    # in-order propagation on the shipped cloud: T visiting orders (seeded permutations; the reference builds BFS
+    # routes of a kNN graph, graph.py:380-392 -- any order exercises the same arithmetic)
+    pc = scramble(load_xyz(util, "ok.xyz")[:1500], g)
+    N = pc.shape[0]
+    orders = np.stack([torch.randperm(N, generator=g).numpy() for _ in range(5)])
+    out["prop_pc"], out["prop_orders"] = pc, orders
+    for diffuse in (False, True):
+        for dt, tag in ((torch.float32, "f32"), (torch.float64, "f64")):
+            flips = fu.xie_propagation_points_in_order(pc.clone().to(dt), 1e-2, orders, diffuse=diffuse, knn_mask=-1, C=3)
+            out[f"prop_flips_{tag}_diffuse{int(diffuse)}"] = flips
+    import inspect
+    import json
+    sig = {n: [[p.name, None if p.default is inspect.Parameter.empty else repr(p.default)]
+               for p in inspect.signature(getattr(fu, n)).parameters.values()]
+           for n in ("xie_field", "xie_intersaction", "xie_propagation_points_in_order")}
+    json.dump(sig, open(os.path.join(OUT, "xie_signatures.json"), "w"), indent=1)
+    save("xie", **out)
+
+
 GENERATORS = {"signatures": gen_signatures, "leaf": gen_leaf, "edge": gen_edge, "transfer": gen_transfer, "lattice": gen_lattice,
-              "points": gen_points, "patches": gen_patches, "reps": gen_reps}
+              "points": gen_points, "patches": gen_patches, "reps": gen_reps, "xie": gen_xie}
 
 if __name__ == "__main__":
     torch.manual_seed(0)

@@ -196,3 +196,29 @@ def test_torch_port_is_the_reference_op_chain(golden):
     cl = torch.from_numpy(g["self_pc"])
     assert np.array_equal(tp.field_grad(cl, cl).numpy(), g["self_E32"])
     assert np.array_equal(tp.potential(cl, cl).numpy(), g["self_phi32"])
+
+
+# ------------------------------------------------------------------ the "xie" interaction
+def test_xie_interaction_matches_reference(golden, orc):
+    g = golden("xie")
+    src, tgt = g["src"], g["tgt"]
+    for C in (3, 2):
+        m = orc.xie_intersaction(src, tgt, C=C)
+        scale = np.abs(m).max()
+        assert np.abs(m - g[f"inter64_C{C}"]).max() <= 1e-12 * scale            # float64 restatement
+        assert np.abs(m - g[f"inter_C{C}"]).max() <= 2e-6 * scale              # the reference's own float32 output
+    f = orc.xie_field(src, tgt, C=3)
+    assert np.abs(f - g["field_C3"]).max() <= 2e-6 * np.abs(f).max()
+    # coincident pairs keep the un-normalised source normal (field_utils.py:456-460)
+    assert np.allclose(f[np.arange(7), np.arange(7)], src[:7, 3:], rtol=0, atol=1e-7)
+    mk = orc.xie_intersaction(src, tgt, C=3, knn_mask=16)
+    assert np.array_equal(mk != 0, g["inter_knn16"] != 0)                        # the same kNN mask
+    assert np.abs(mk - g["inter_knn16"]).max() <= 2e-6 * np.abs(mk).max()
+
+
+@pytest.mark.parametrize("diffuse", [False, True])
+def test_xie_propagation_in_order_matches_reference(golden, orc, diffuse):
+    g = golden("xie")
+    flips, _ = orc.xie_propagate_in_order(g["prop_pc"], g["prop_orders"], diffuse=diffuse)
+    assert np.array_equal(flips, g[f"prop_flips_f64_diffuse{int(diffuse)}"])
+    assert np.array_equal(flips, g[f"prop_flips_f32_diffuse{int(diffuse)}"])
