@@ -390,6 +390,14 @@ def extras(dn, field_utils, dev, src, tgt):
         field_utils.strongest_field_propagation_reps(work, reps, diffuse=True)
         return field_utils.measure_mean_potential(work)
     out["cfg3_reps_propagation_1M_pts_1000_patches_ms"] = best_ms(run_reps, 1)
+    # xie in-order propagation, 5 chains over 10 000 points (the server's tree_xie call)
+    pcx = surface_cloud(10000, 11).to(dev)
+    gx = torch.Generator().manual_seed(12)
+    orders = torch.stack([torch.randperm(10000, generator=gx) for _ in range(5)]).to(dev)
+    out["xie_in_order_10k_pts_5_chains_diffuse_ms"] = best_ms(
+        lambda: field_utils.xie_propagation_points_in_order(pcx, 1e-2, orders, diffuse=True), 2)
+    ms = best_ms(lambda: dn.xie_matrix(pcx, pcx), 2)
+    out["xie_matrix_10k_gbs_written"] = 10000 * 10000 * 4 / ms / 1e6
     return out
 
 
