@@ -391,6 +391,21 @@ int dnp_xie_propagate_in_order_f32(const float* pts, int64_t N, int64_t ld, cons
                              workspace_bytes, (cudaStream_t)stream);
 }
 
+// ------------------------------------------------------------------ voxel partition (dnp_partition.cu)
+size_t dnp_voxel_partition_workspace_bytes(int64_t N) { return voxel_partition_workspace_bytes(N); }
+
+int dnp_voxel_partition_f32(const float* pts, int64_t N, int64_t ld, int n_part, double range_lo, double range_hi,
+                            int64_t* perm, int64_t* offsets, int32_t* ijk, int64_t* counts, void* workspace,
+                            size_t workspace_bytes, void* stream) {
+    DNP_REQUIRE(N >= 0, "negative size");
+    DNP_REQUIRE(offsets && counts, "null pointer");
+    DNP_REQUIRE(N == 0 || (pts && perm && ijk), "null pointer");
+    DNP_REQUIRE(ld >= 3, "points need 3 columns");
+    DNP_REQUIRE(range_hi > range_lo, "empty range");
+    return run_voxel_partition(pts, N, ld, n_part, range_lo, range_hi, perm, offsets, ijk, counts, workspace,
+                               workspace_bytes, (cudaStream_t)stream);
+}
+
 int dnp_profile_begin(void) {
     profile_begin();
     return DNP_OK;

@@ -39,6 +39,12 @@ int run_xie_propagate(const float* pts, int64_t N, int64_t ld, const int64_t* or
                       const double* rad2, int diffuse, uint8_t* flips, float* inter, void* workspace,
                       size_t workspace_bytes, cudaStream_t stream);
 
+// voxel partition (dnp_partition.cu)
+size_t voxel_partition_workspace_bytes(int64_t N);
+int run_voxel_partition(const float* pts, int64_t N, int64_t ld, int n_part, double range_lo, double range_hi,
+                        int64_t* perm, int64_t* offsets, int32_t* ijk, int64_t* counts, void* workspace,
+                        size_t workspace_bytes, cudaStream_t stream);
+
 int run_microbench(int kind, int iters, float* ms_out, double* ops_out, cudaStream_t stream);
 
 }  // namespace dnp

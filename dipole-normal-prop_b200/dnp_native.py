@@ -43,6 +43,9 @@ SYMBOLS = [
     ("dnp_xie_max_n", _i64, [_i32]),
     ("dnp_xie_workspace_bytes", _sz, [_i64, _i64]),
     ("dnp_xie_propagate_in_order_f32", _i32, [_vp, _i64, _i64, _vp, _i64, _f32, _vp, _i32, _vp, _vp, _vp, _sz, _vp]),
+    ("dnp_voxel_partition_workspace_bytes", _sz, [_i64]),
+    ("dnp_voxel_partition_f32", _i32, [_vp, _i64, _i64, _i32, ctypes.c_double, ctypes.c_double, _vp, _vp, _vp, _vp,
+                                       _vp, _sz, _vp]),
     ("dnp_field_grad_host_f32", _i32, [_vp, _i64, _i64, _vp, _i64, _i64, _f32, _vp, _i32]),
     ("dnp_potential_host_f32", _i32, [_vp, _i64, _i64, _vp, _i64, _i64, _vp, _i32]),
     ("dnp_launch_count", _i64, []),
@@ -375,6 +378,29 @@ def xie_propagate_in_order(pts, order, C=3.0, radius2=None, diffuse=False):
                                                   int(bool(diffuse)), _ptr(flips), _ptr(inter), _ptr(ws), nbytes,
                                                   _stream(p)))
     return flips.bool(), inter
+
+
+# ------------------------------------------------------------------ voxel partition
+def voxel_partition(pts, n_part, ranges=(-1.5, 1.5)):
+    """CSR of the non-empty voxel cells of util._divide_pc: (perm[n_in] int64, offsets[n_cells+1] int64,
+    ijk[n_cells, 3] int32).  One device->host read of two counters sizes the outputs."""
+    lib = load()
+    p, ld = _rows(pts, 3, "pc_in")
+    dev = p.device
+    N = p.shape[0]
+    max_cells = min(N, (int(n_part) + 1) ** 3)
+    perm = torch.empty(N, dtype=torch.int64, device=dev)
+    offsets = torch.zeros(max_cells + 1, dtype=torch.int64, device=dev)
+    ijk = torch.empty(max_cells, 3, dtype=torch.int32, device=dev)
+    counts = torch.zeros(2, dtype=torch.int64, device=dev)
+    with torch.cuda.device(dev):
+        nbytes = lib.dnp_voxel_partition_workspace_bytes(N)
+        ws = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+        _check(lib.dnp_voxel_partition_f32(_ptr(p), N, ld, int(n_part), float(ranges[0]), float(ranges[1]),
+                                           _ptr(perm), _ptr(offsets), _ptr(ijk), _ptr(counts), _ptr(ws), nbytes,
+                                           _stream(p)))
+    n_cells, n_in = counts.tolist()
+    return perm[:n_in], offsets[:n_cells + 1], ijk[:n_cells]
 
 
 # ------------------------------------------------------------------ host-buffer calls (CPU tensors in, CPU tensors out)

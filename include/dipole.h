@@ -218,6 +218,23 @@ DNP_API int dnp_xie_propagate_in_order_f32(const float* pts, int64_t N, int64_t 
                                    uint8_t* flips, float* interactions,
                                    void* workspace, size_t workspace_bytes, void* stream);
 
+/* ------------------------------------------------------------------ voxel partition into patches
+ *   replaces util._divide_pc (util.py:110-150): cell (i, j, k),
+ * 0 <= i, j, k <= n_part, holds the points with l_t < x <= l_t + edge on every axis,
+ * l_t = edge * t + range_lo, edge = (range_hi - range_lo) / n_part (double arithmetic, float compare,
+ * as torch does).  Output is the CSR of the non-empty cells in lexicographic (i, j, k) order:
+ *   perm[offsets[c] .. offsets[c+1])  rows of cell c, ascending        (perm: [N] int64)
+ *   offsets[0 .. n_cells]                                              (offsets: [min(N, (n_part+1)^3) + 1] int64)
+ *   ijk[3c .. 3c+2]                   grid coordinates of cell c       (ijk: 3 x as many int32)
+ *   counts[0] = n_cells, counts[1] = points inside the box (= offsets[n_cells]); device int64[2].
+ * Points outside the box (or NaN) are in no cell, as in the reference.  n_part <= 255.
+ * Fully asynchronous; workspace: dnp_voxel_partition_workspace_bytes(N) device bytes.              */
+DNP_API size_t dnp_voxel_partition_workspace_bytes(int64_t N);
+DNP_API int dnp_voxel_partition_f32(const float* pts, int64_t N, int64_t ld,
+                            int n_part, double range_lo, double range_hi,
+                            int64_t* perm, int64_t* offsets, int32_t* ijk, int64_t* counts,
+                            void* workspace, size_t workspace_bytes, void* stream);
+
 /* ------------------------------------------------------------------ host-buffer entry points
  * Same math with HOST pointers: the call stages inputs to the device, runs the
  * kernels and copies the result back before returning (synchronous).  This is

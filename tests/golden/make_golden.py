@@ -409,8 +409,42 @@ def gen_xie(fu, util):
     save("xie", **out)
 
 
+def gen_partition(fu, util):
+    """voxel partition util._divide_pc (util.py:110-150) and the small-patch merge
+    util.merge_nodes (util.py:448-492), on the transformed demo clouds with the demos' own flags."""
+    import inspect
+    import json
+    out = {}
+    cases = [("fandisk", "fandisk.xyz", 30, 100), ("ok", "ok.xyz", 41, 100), ("hand", "hand.xyz", 10, 40)]
+    for tag, name, n_part, min_patch in cases:
+        pc, _ = util.Transform.trans(load_xyz(util, name))
+        if tag == "hand":
+            pc[::97, 0] = 7.0                                      # outside the (-1.5, 1.5] box: dropped by the reference
+            pc[5, :3] = torch.tensor([-1.5 + 3.0 / n_part, 0.0, 0.0])   # exactly on a cell boundary (belongs to the lower cell)
+        t0 = time.time()
+        idx, ijk = util._divide_pc(pc[:, :3], n_part, min_patch=min_patch)
+        dt = time.time() - t0
+        out[f"{tag}_pc"] = pc
+        out[f"{tag}_n_part"], out[f"{tag}_min_patch"] = n_part, min_patch
+        out[f"{tag}_cell_perm"], out[f"{tag}_cell_offsets"] = patch_csr([c[0] for c in idx])
+        out[f"{tag}_cell_ijk"] = torch.stack([c[0] for c in ijk]).numpy()
+        out[f"{tag}_divide_seconds"] = dt
+        t0 = time.time()
+        merged, merged_ijk = util.merge_nodes(pc, idx, ijk, min_patch)
+        out[f"{tag}_merge_seconds"] = time.time() - t0
+        out[f"{tag}_merged_perm"], out[f"{tag}_merged_offsets"] = patch_csr(merged)
+        out[f"{tag}_merged_ijk"] = np.concatenate([torch.stack(c).numpy() for c in merged_ijk])
+        out[f"{tag}_merged_ijk_offsets"] = np.concatenate([[0], np.cumsum([len(c) for c in merged_ijk])])
+        print(f"partition {tag}: N={pc.shape[0]} n_part={n_part}: {len(idx)} cells in {dt:.1f}s, {len(merged)} patches")
+    sig = {n: [[p.name, None if p.default is inspect.Parameter.empty else repr(p.default)]
+               for p in inspect.signature(getattr(util, n)).parameters.values()]
+           for n in ("_divide_pc", "divide_pc", "merge_nodes")}
+    json.dump(sig, open(os.path.join(OUT, "partition_signatures.json"), "w"), indent=1)
+    save("partition", **out)
+
+
 GENERATORS = {"signatures": gen_signatures, "leaf": gen_leaf, "edge": gen_edge, "transfer": gen_transfer, "lattice": gen_lattice,
-              "points": gen_points, "patches": gen_patches, "reps": gen_reps, "xie": gen_xie}
+              "points": gen_points, "patches": gen_patches, "reps": gen_reps, "xie": gen_xie, "partition": gen_partition}
 
 if __name__ == "__main__":
     torch.manual_seed(0)

@@ -222,3 +222,38 @@ def test_xie_propagation_in_order_matches_reference(golden, orc, diffuse):
     flips, _ = orc.xie_propagate_in_order(g["prop_pc"], g["prop_orders"], diffuse=diffuse)
     assert np.array_equal(flips, g[f"prop_flips_f64_diffuse{int(diffuse)}"])
     assert np.array_equal(flips, g[f"prop_flips_f32_diffuse{int(diffuse)}"])
+
+
+# ------------------------------------------------------------------ voxel partition + merge
+def _csr(parts):
+    return (np.concatenate(parts) if parts else np.zeros(0, dtype=np.int64),
+            np.concatenate([[0], np.cumsum([len(p) for p in parts])]))
+
+
+@pytest.mark.parametrize("tag", ["fandisk", "ok", "hand"])
+def test_partition_matches_reference(golden, orc, tag):
+    g = golden("partition")
+    idx, ijk = orc.divide_pc_cells(g[f"{tag}_pc"], int(g[f"{tag}_n_part"]))
+    perm, off = _csr(idx)
+    assert np.array_equal(perm, g[f"{tag}_cell_perm"]) and np.array_equal(off, g[f"{tag}_cell_offsets"])
+    assert np.array_equal(ijk, g[f"{tag}_cell_ijk"])
+    merged, mijk = orc.merge_nodes(idx, ijk, int(g[f"{tag}_min_patch"]))
+    perm, off = _csr(merged)
+    assert np.array_equal(perm, g[f"{tag}_merged_perm"]) and np.array_equal(off, g[f"{tag}_merged_offsets"])
+    assert np.array_equal(np.concatenate(mijk), g[f"{tag}_merged_ijk"])
+
+
+@pytest.mark.parametrize("tag", ["fandisk", "ok", "hand"])
+def test_fast_merge_equals_the_reference_scan(golden, tag):
+    """dnp_util.merge_nodes (cell -> owner map) against the reference's own merge output; host logic, no GPU."""
+    import dnp_util
+    import torch
+    g = golden("partition")
+    perm, off, ijk = g[f"{tag}_cell_perm"], g[f"{tag}_cell_offsets"], g[f"{tag}_cell_ijk"]
+    idx = [[torch.from_numpy(perm[off[c]:off[c + 1]])] for c in range(len(off) - 1)]
+    cells = [[torch.from_numpy(ijk[c])] for c in range(len(ijk))]
+    merged, mijk = dnp_util.merge_nodes(None, idx, cells, int(g[f"{tag}_min_patch"]))
+    p2, o2 = _csr([m.numpy() for m in merged])
+    assert np.array_equal(p2, g[f"{tag}_merged_perm"]) and np.array_equal(o2, g[f"{tag}_merged_offsets"])
+    assert np.array_equal(torch.stack([c for sub in mijk for c in sub]).numpy(), g[f"{tag}_merged_ijk"])
+    assert np.array_equal(np.concatenate([[0], np.cumsum([len(s) for s in mijk])]), g[f"{tag}_merged_ijk_offsets"])
