@@ -398,6 +398,17 @@ def extras(dn, field_utils, dev, src, tgt):
         lambda: field_utils.xie_propagation_points_in_order(pcx, 1e-2, orders, diffuse=True), 2)
     ms = best_ms(lambda: dn.xie_matrix(pcx, pcx), 2)
     out["xie_matrix_10k_gbs_written"] = 10000 * 10000 * 4 / ms / 1e6
+    # voxel partition + small-patch merge of the 1M-point cloud at --number_parts 41
+    import dnp_util
+    ms = best_ms(lambda: dn.voxel_partition(pc3, 41), 3)
+    out["partition_1M_pts_41_parts_ms"] = ms
+    out["partition_algorithmic_gbs"] = (1 << 20) * 20 / ms / 1e6        # 12 B/point read + 8 B/point of perm written
+    t0 = time.perf_counter()
+    idx, cells = dnp_util._divide_pc(pc3[:, :3], 41)
+    merged, _ = dnp_util.merge_nodes(pc3, idx, cells, 100)
+    torch.cuda.synchronize()
+    out["partition_plus_merge_python_api_ms"] = (time.perf_counter() - t0) * 1e3
+    out["partition_reference_cpu_s_build_container"] = "5.8 s for 10 000 points at n_part 41 (tests/golden/partition.npz, ok_divide_seconds)"
     return out
 
 
