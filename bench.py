@@ -409,6 +409,18 @@ def extras(dn, field_utils, dev, src, tgt):
     torch.cuda.synchronize()
     out["partition_plus_merge_python_api_ms"] = (time.perf_counter() - t0) * 1e3
     out["partition_reference_cpu_s_build_container"] = "5.8 s for 10 000 points at n_part 41 (tests/golden/partition.npz, ok_divide_seconds)"
+    # patch-graph flip solve (graph.MIQP): exhaustive walk at 36 patches, annealing at 300
+    gq = torch.Generator().manual_seed(99)
+
+    def couplings(n, density):
+        w = torch.triu(torch.randn(n, n, generator=gq, dtype=torch.float64), 1)
+        w = w * (torch.rand(n, n, generator=gq) < density)
+        return (w + w.T).to(dev)
+    a36, a300 = couplings(36, 0.4), couplings(300, 0.03)
+    ms = best_ms(lambda: dn.flip_solve(a36, -a36), 2)
+    out["flip_solve_36_patches_exhaustive_ms"] = ms
+    out["flip_solve_exhaustive_states_per_s"] = 2.0 ** 35 / (ms * 1e-3)
+    out["flip_solve_300_patches_anneal_ms"] = best_ms(lambda: dn.flip_solve(a300, -a300), 2)
     return out
 
 

@@ -406,6 +406,21 @@ int dnp_voxel_partition_f32(const float* pts, int64_t N, int64_t ld, int n_part,
                                workspace_bytes, (cudaStream_t)stream);
 }
 
+// ------------------------------------------------------------------ patch-graph flip solve (dnp_flip.cu)
+size_t dnp_flip_solve_workspace_bytes(int64_t n, int exact_max_n, int replicas) {
+    return flip_solve_workspace_bytes(n, exact_max_n, replicas);
+}
+
+int dnp_flip_solve_f64(const double* A, const double* B, int64_t n, int64_t ld, int exact_max_n, int replicas,
+                       int sweeps, uint64_t seed, uint8_t* x_out, double* obj_out, int32_t* status_out,
+                       void* workspace, size_t workspace_bytes, void* stream) {
+    DNP_REQUIRE(n >= 1, "flip solve needs at least one patch");
+    DNP_REQUIRE(A && B && x_out && obj_out && status_out, "null pointer");
+    DNP_REQUIRE(ld >= n, "row stride smaller than n");
+    return run_flip_solve(A, B, n, ld, exact_max_n, replicas, sweeps, seed, x_out, obj_out, status_out, workspace,
+                          workspace_bytes, (cudaStream_t)stream);
+}
+
 int dnp_profile_begin(void) {
     profile_begin();
     return DNP_OK;

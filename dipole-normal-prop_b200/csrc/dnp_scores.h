@@ -45,6 +45,12 @@ int run_voxel_partition(const float* pts, int64_t N, int64_t ld, int n_part, dou
                         int64_t* perm, int64_t* offsets, int32_t* ijk, int64_t* counts, void* workspace,
                         size_t workspace_bytes, cudaStream_t stream);
 
+// patch-graph flip solve (dnp_flip.cu)
+size_t flip_solve_workspace_bytes(int64_t n, int exact_max_n, int replicas);
+int run_flip_solve(const double* A, const double* B, int64_t n, int64_t ld, int exact_max_n, int replicas, int sweeps,
+                   uint64_t seed, uint8_t* x_out, double* obj_out, int32_t* status_out, void* workspace,
+                   size_t workspace_bytes, cudaStream_t stream);
+
 int run_microbench(int kind, int iters, float* ms_out, double* ops_out, cudaStream_t stream);
 
 }  // namespace dnp

@@ -46,6 +46,9 @@ SYMBOLS = [
     ("dnp_voxel_partition_workspace_bytes", _sz, [_i64]),
     ("dnp_voxel_partition_f32", _i32, [_vp, _i64, _i64, _i32, ctypes.c_double, ctypes.c_double, _vp, _vp, _vp, _vp,
                                        _vp, _sz, _vp]),
+    ("dnp_flip_solve_workspace_bytes", _sz, [_i64, _i32, _i32]),
+    ("dnp_flip_solve_f64", _i32, [_vp, _vp, _i64, _i64, _i32, _i32, _i32, ctypes.c_uint64, _vp, _vp, _vp, _vp, _sz,
+                                  _vp]),
     ("dnp_field_grad_host_f32", _i32, [_vp, _i64, _i64, _vp, _i64, _i64, _f32, _vp, _i32]),
     ("dnp_potential_host_f32", _i32, [_vp, _i64, _i64, _vp, _i64, _i64, _vp, _i32]),
     ("dnp_launch_count", _i64, []),
@@ -401,6 +404,47 @@ def voxel_partition(pts, n_part, ranges=(-1.5, 1.5)):
                                            _stream(p)))
     n_cells, n_in = counts.tolist()
     return perm[:n_in], offsets[:n_cells + 1], ijk[:n_cells]
+
+
+# ------------------------------------------------------------------ patch-graph flip solve
+FLIP_EXACT_MAX = 36      # exhaustive up to this many patches (2^35 states, a few ms); the ABI allows 40
+FLIP_BEST_FOUND, FLIP_EXHAUSTIVE, FLIP_BOUND_REACHED = 0, 1, 2
+
+
+def flip_solve(A, B, exact_max_n=FLIP_EXACT_MAX, replicas=None, sweeps=None, seed=0):
+    """argmax over x in {0,1}^n of graph.cal_loss(x, A, B) (graph.py:431-470).  A, B: [n, n] float64 CUDA
+    tensors.  Returns device tensors (x uint8 [n], obj float64 [2] = (objective, bound), status int32 [1]).
+    Annealing budget (n > exact_max_n) defaults to 2368 chains x 512 sweeps up to 256 patches and shrinks with
+    n^2 beyond (a sweep costs O(n^2 / 32) per chain), so that a solve stays in the 10-100 ms range."""
+    n_ = int(A.shape[0]) if hasattr(A, "shape") and len(A.shape) else 0
+    if sweeps is None:
+        sweeps = max(32, min(512, int(512 * (256.0 / max(n_, 1)) ** 2)))
+    if replicas is None:
+        replicas = 2368 if n_ <= 1024 else 592
+    lib = load()
+    for name, m in (("A", A), ("B", B)):
+        if not isinstance(m, torch.Tensor) or m.dtype != torch.float64 or not m.is_cuda:
+            raise TypeError(f"{name} must be a float64 CUDA tensor")
+        if m.dim() != 2 or m.shape[0] != m.shape[1] or m.shape != A.shape:
+            raise ValueError("A and B must be square matrices of the same shape")
+    n = A.shape[0]
+    dev = A.device
+    x = torch.zeros(n, dtype=torch.uint8, device=dev)
+    obj = torch.zeros(2, dtype=torch.float64, device=dev)
+    status = torch.full((1,), FLIP_EXHAUSTIVE, dtype=torch.int32, device=dev)
+    if n == 0:
+        return x, obj, status
+    A = A.contiguous()
+    B = B.contiguous()
+    with torch.cuda.device(dev):
+        nbytes = lib.dnp_flip_solve_workspace_bytes(n, int(exact_max_n), int(replicas))
+        if nbytes == 0:
+            raise DipoleError(f"flip solve supports 1..4096 patches (got {n})")
+        ws = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+        _check(lib.dnp_flip_solve_f64(_ptr(A), _ptr(B), n, n, int(exact_max_n), int(replicas), int(sweeps),
+                                      int(seed) & (2 ** 64 - 1), _ptr(x), _ptr(obj), _ptr(status), _ptr(ws), nbytes,
+                                      _stream(A)))
+    return x, obj, status
 
 
 # ------------------------------------------------------------------ host-buffer calls (CPU tensors in, CPU tensors out)

@@ -318,6 +318,58 @@ def xie_propagation_points_in_order(pts: torch.Tensor, eps, order, diffuse=False
         return flips.to(pts.device)
 
 
+# ---------------------------------------------------------------------------- flip vote
+def cal_loss(x, A, B):
+    """field_utils.py:606-615 (same sum as graph.cal_loss)."""
+    import graph
+    return graph.cal_loss(x, A, B)
+
+
+def MIQP(A, B):
+    """field_utils.py:618-643.  NOT graph.MIQP: this one sets the objective to `-cal_loss` (:628-629), i.e. it
+    returns the x in {0,1}^n MINIMISING cal_loss(x, A, B), and prints Gurobi's objective value (-cal_loss).
+    Solved on the GPU by dnp_flip_solve_f64 on (-A, -B)."""
+    import graph
+    x, obj, _, _ = graph._solve(A, B, False)
+    print('Obj: %g' % -obj)
+    return x
+
+
+def xie_propagation_points_onbfstree(pts: torch.Tensor, eps, diffuse=False, starting_point=0, verbose=False, k=10,
+                                     treshold=0.1, times=1, use_pw=False, knn_mask=-1, C=3):
+    """field_utils.py:654-709.  `times` BFS orders over the thresholded kNN graph, one propagation chain per order
+    (one launch, a cluster per chain), the chains aligned by the flip vote (MIQP on the pairwise disagreement
+    counts), then a per-point majority vote flips pts[:, 3:] in place.  Returns None like the reference."""
+    import graph
+    assert times % 2 == 1 and times > 0
+    with torch.no_grad():
+        starting_points = [starting_point]
+        np.random.seed(0)                                    # :660, the reference reseeds numpy here
+        while len(np.unique(starting_points)) < times:
+            t = np.random.randint(0, pts.shape[0])
+            if t not in starting_points:
+                starting_points.append(t)
+        xyz = pts[:, :3].cpu().numpy()
+        G, mean_k_dist = graph.getEMSTfromPC(xyz, k, treshold)
+        point_weight = mean_k_dist if use_pw else None
+        orders = np.zeros([times, len(pts)], dtype=int)
+        for i in range(times):
+            orders[i] = G.get_bfs_route(starting_points[i])
+        status_all = xie_propagation_points_in_order(pts.clone(), eps, orders, diffuse, verbose=False,
+                                                     points_weight=point_weight, knn_mask=knn_mask, C=C).T   # [N, times]
+        # pairwise disagreement / agreement counts of the chains (:682-686,696-700) as one integer mat-mul
+        f = status_all.to(torch.float64)
+        n = f.shape[0]
+        diff = f.T @ (1.0 - f)
+        A = diff + diff.T
+        B = n - A
+        status = MIQP(A.cpu().numpy(), B.cpu().numpy())
+        status = torch.as_tensor(status != 0, device=status_all.device)
+        aligned = status_all ^ status[None, :]
+        cnts = aligned.int().sum(dim=1)
+        pts[(cnts > times / 2).to(pts.device), 3:] *= -1
+
+
 # ---------------------------------------------------------------------------- a8: patch propagation on representatives
 def strongest_field_propagation_reps(input_pc, reps, diffuse=False, weights=None):
     """field_utils.py:207-282.  reps = [(rep_idx, rest_idx)] per patch.  Mutates input_pc[:, 3:]; returns None."""

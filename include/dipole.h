@@ -235,6 +235,23 @@ DNP_API int dnp_voxel_partition_f32(const float* pts, int64_t N, int64_t ld,
                             int64_t* perm, int64_t* offsets, int32_t* ijk, int64_t* counts,
                             void* workspace, size_t workspace_bytes, void* stream);
 
+/* ------------------------------------------------------------------ patch-graph flip solve
+ *   replaces graph.MIQP(A, B) (graph.py:444-470; objective graph.cal_loss,
+ * graph.py:431-442), which the reference hands to Gurobi (gurobipy, unpinned, absent here):
+ *     maximise  sum_ij A_ij (1 - (x_i - x_j)^2) + B_ij (x_i - x_j)^2   over x in {0,1}^n.
+ * A, B: device float64 [n, n] row-major with row stride ld (the matrices of BidGraph.to_matrix,
+ * graph.py:136-152; need not be symmetric).  n <= min(exact_max_n, 40): exhaustive enumeration (optimal);
+ * larger n (<= 4096): `replicas` annealing chains of `sweeps` sweeps + descent, deterministic in `seed`.
+ * x_out[n] (uint8, 1 = flip the patch), obj_out[0] = objective of x_out (double, as cal_loss),
+ * obj_out[1] = the bound sum of the larger of A, B per pair; status_out[0] = 1 exhaustive, 2 bound reached
+ * (both optimal), 0 best found.  Of the two globally flipped twins the one with fewer flips is returned
+ * (tie: x_0 = 0).  Fully asynchronous; all outputs are device pointers.                                   */
+DNP_API size_t dnp_flip_solve_workspace_bytes(int64_t n, int exact_max_n, int replicas);
+DNP_API int dnp_flip_solve_f64(const double* A, const double* B, int64_t n, int64_t ld,
+                       int exact_max_n, int replicas, int sweeps, uint64_t seed,
+                       uint8_t* x_out, double* obj_out, int32_t* status_out,
+                       void* workspace, size_t workspace_bytes, void* stream);
+
 /* ------------------------------------------------------------------ host-buffer entry points
  * Same math with HOST pointers: the call stages inputs to the device, runs the
  * kernels and copies the result back before returning (synchronous).  This is

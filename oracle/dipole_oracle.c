@@ -256,3 +256,56 @@ static void points_propagate_impl(float *pts, int64_t N, int64_t start, float ep
     }
     free(E); free(visited);
 }
+
+/* ---------------------------------------------------------------------------
+ * Patch-graph flip solve (graph.py:431-470).  The reference maximises
+ *   cal_loss(x) = sum_ij A_ij (1 - (x_i-x_j)^2) + B_ij (x_i-x_j)^2,  x in {0,1}^n
+ * with Gurobi (gurobipy: a third-party exact solver, not pinned by the reference
+ * and absent here).  An exact solver returns a global maximiser, so the oracle
+ * is plain enumeration: every x in ascending integer order (bit i = x_i),
+ * cal_loss evaluated term by term in the reference's loop order, first maximum
+ * kept.  n <= 26.
+ * ------------------------------------------------------------------------- */
+ORC_API double orc_cal_loss(const uint8_t *x, const double *A, const double *B, int64_t n)
+{
+    double obj = 0.0;
+    for (int64_t i = 0; i < n; ++i)
+        for (int64_t j = 0; j < n; ++j) {
+            const double d = (double)x[i] - (double)x[j];
+            obj += A[i * n + j] * (1.0 - d * d) + B[i * n + j] * d * d;
+        }
+    return obj;
+}
+
+ORC_API double orc_miqp_bruteforce(const double *A, const double *B, int64_t n, uint8_t *x_best,
+                                   int64_t *n_optimal /* states within 1e-12 relative of the maximum */)
+{
+    const uint64_t states = 1ull << n;
+    double best = -INFINITY;
+    uint64_t arg = 0;
+    double *vals = n_optimal ? (double *)malloc(sizeof(double) * states) : NULL;
+    #pragma omp parallel
+    {
+        uint8_t x[64];
+        double lbest = -INFINITY;
+        uint64_t larg = 0;
+        #pragma omp for schedule(static)
+        for (uint64_t s = 0; s < states; ++s) {
+            for (int64_t i = 0; i < n; ++i) x[i] = (uint8_t)((s >> i) & 1u);
+            const double v = orc_cal_loss(x, A, B, n);
+            if (vals) vals[s] = v;
+            if (v > lbest) { lbest = v; larg = s; }
+        }
+        #pragma omp critical
+        if (lbest > best || (lbest == best && larg < arg)) { best = lbest; arg = larg; }
+    }
+    for (int64_t i = 0; i < n; ++i) x_best[i] = (uint8_t)((arg >> i) & 1u);
+    if (n_optimal) {
+        int64_t c = 0;
+        const double tol = 1e-12 * (fabs(best) > 1.0 ? fabs(best) : 1.0);
+        for (uint64_t s = 0; s < states; ++s) c += vals[s] >= best - tol;
+        *n_optimal = c;
+        free(vals);
+    }
+    return best;
+}

@@ -443,8 +443,105 @@ def gen_partition(fu, util):
     save("partition", **out)
 
 
+def gen_graph(fu, util):
+    """the objective the reference hands to Gurobi (graph.cal_loss, graph.py:431-442),
+    the score container (BiEdge / BidGraph.to_matrix, graph.py:121-152) and the BFS routes of LinkedListGraph
+    (graph.py:257-318).  Gurobi itself is absent, so the maximiser is not recorded here (oracle: enumeration)."""
+    import inspect
+    import json
+    cwd = os.getcwd()
+    os.chdir(REF)
+    try:
+        import graph as ref_graph
+    finally:
+        os.chdir(cwd)
+    rng = np.random.default_rng(20260)
+    out = {}
+    for tag, n, sym in (("sym5", 5, True), ("sym12", 12, True), ("gen9", 9, False), ("sym40", 40, True)):
+        if sym:
+            W = np.triu(rng.normal(size=(n, n)), 1) * (rng.random((n, n)) < 0.5)
+            A = W + W.T
+            B = -A
+        else:
+            A = rng.normal(size=(n, n))
+            B = rng.normal(size=(n, n))
+        X = (rng.random((16, n)) < 0.5).astype(np.float64)
+        out[f"{tag}_A"], out[f"{tag}_B"], out[f"{tag}_X"] = A, B, X
+        out[f"{tag}_loss"] = np.array([ref_graph.cal_loss(x, A, B) for x in X])
+    # score container
+    G = ref_graph.BidGraph()
+    G.V = list(range(7))
+    edges = [(0, 1, 0.5, -0.5), (1, 2, -1.25, 1.25), (2, 6, 3.0, -3.0), (3, 4, 0.125, -0.125), (0, 5, -2.0, 2.0)]
+    for u, v, w, invw in edges:
+        G.E.append(ref_graph.BiEdge(u, v, np.float32(w), np.float32(invw)))
+    A, B = G.to_matrix()
+    out["container_edges"] = np.array(edges)
+    out["container_A"], out["container_B"] = A, B
+    # BFS routes
+    n = 60
+    L = ref_graph.LinkedListGraph(n)
+    pairs = []
+    for i in range(n):
+        for j in rng.choice(n, size=3, replace=False):
+            if i != int(j) and i // 20 == int(j) // 20:       # three components
+                w = float(rng.random())
+                L.add_edge(i, int(j), w)
+                L.add_edge(int(j), i, w)
+                pairs += [(i, int(j), w), (int(j), i, w)]
+    out["bfs_n"] = n
+    out["bfs_edges"] = np.array(pairs)
+    out["bfs_route_0"] = np.array(L.get_bfs_route(0))
+    out["bfs_route_33"] = np.array(L.get_bfs_route(33))
+    out["bfs_weighted_route_0"] = np.array(L.get_weighted_bfs_route(0))
+    out["bfs_weighted_route_45"] = np.array(L.get_weighted_bfs_route(45))
+    # BFS-tree propagation + flip vote (field_utils.py:654-709).  Its MIQP (field_utils.py:618-643, objective
+    # -cal_loss) needs Gurobi: replaced HERE ONLY by enumeration of the same objective (first minimiser in
+    # ascending integer order), so everything around the solve -- seeds, kNN graph, BFS routes, chains, counts,
+    # majority vote -- is the reference's own.  x and 1 - x tie, so the result is defined up to a global sign.
+    votes = {}
+
+    def enum_miqp(A, B):
+        n = len(A)
+        best, arg = None, None
+        for s_ in range(1 << n):
+            x = np.array([(s_ >> i) & 1 for i in range(n)], dtype=np.float64)
+            v = fu.cal_loss(x, A, B)
+            if best is None or v < best:
+                best, arg = v, x
+        votes["A"], votes["B"], votes["x"], votes["min_loss"] = np.array(A), np.array(B), arg, best
+        return arg
+    fu.MIQP = enum_miqp
+    g = torch.Generator().manual_seed(977)
+    pc = scramble(load_xyz(util, "ok.xyz")[:1500], g)
+    pc, _ = util.Transform.trans(pc)
+    for times in (1, 5):
+        work = pc.clone()
+        fu.xie_propagation_points_onbfstree(work, 1e-2, diffuse=True, starting_point=0, times=times, k=10, treshold=0.1)
+        out[f"tree_result_t{times}"] = work
+        out[f"tree_vote_A_t{times}"], out[f"tree_vote_B_t{times}"] = votes["A"], votes["B"]
+        out[f"tree_vote_x_t{times}"], out[f"tree_vote_min_t{times}"] = votes["x"], votes["min_loss"]
+    out["tree_pc"] = pc
+    sig = {}
+    fsig = {n: [[p.name, None if p.default is inspect.Parameter.empty else repr(p.default)]
+                for p in inspect.signature(getattr(fu, n)).parameters.values()]
+            for n in ("cal_loss", "xie_propagation_points_onbfstree")}
+    fsig["MIQP"] = [["A", None], ["B", None]]                   # field_utils.py:618 (replaced above, so written out)
+    json.dump(fsig, open(os.path.join(OUT, "graph_field_utils_signatures.json"), "w"), indent=1)
+    for name in ("cal_loss", "MIQP"):
+        sig[name] = [[p.name, None if p.default is inspect.Parameter.empty else repr(p.default)]
+                     for p in inspect.signature(getattr(ref_graph, name)).parameters.values()]
+    for cls, meths in (("BiEdge", ["__init__"]), ("BidGraph", ["__init__", "to_matrix", "add_edge"]),
+                       ("LinkedListGraph", ["__init__", "add_edge", "get_bfs_route", "get_weighted_bfs_route"])):
+        for m in meths:
+            sig[f"{cls}.{m}"] = [[p.name, None if p.default is inspect.Parameter.empty else repr(p.default)]
+                                 for p in inspect.signature(getattr(getattr(ref_graph, cls), m)).parameters.values()]
+    json.dump(sig, open(os.path.join(OUT, "graph_signatures.json"), "w"), indent=1)
+    save("graph", **out)
+
+
 GENERATORS = {"signatures": gen_signatures, "leaf": gen_leaf, "edge": gen_edge, "transfer": gen_transfer, "lattice": gen_lattice,
-              "points": gen_points, "patches": gen_patches, "reps": gen_reps, "xie": gen_xie, "partition": gen_partition}
+              "points": gen_points, "patches": gen_patches, "reps": gen_reps, "xie": gen_xie, "partition": gen_partition,
+              "graph": gen_graph}
 
 if __name__ == "__main__":
     torch.manual_seed(0)
