@@ -84,6 +84,11 @@ edge_interactions_kernel(const float* __restrict__ pts, int64_t ld, const int64_
             }
             ex += fmaf(-3.f, bx, ax); ey += fmaf(-3.f, by, ay); ez += fmaf(-3.f, bz, az);
         }
+        // non-finite field components are zeroed like the leaf does (field_utils.py:110-115): a NaN point makes
+        // the field of every target it touches vanish instead of poisoning the score
+        if (!(fabsf(ex) <= 3.402823466e38f)) ex = 0.f;
+        if (!(fabsf(ey) <= 3.402823466e38f)) ey = 0.f;
+        if (!(fabsf(ez) <= 3.402823466e38f)) ez = 0.f;
         if (t < nt) total += __fadd_rn(__fadd_rn(__fmul_rn(ex, tnx), __fmul_rn(ey, tny)), __fmul_rn(ez, tnz));
     }
     __syncthreads();

@@ -125,3 +125,222 @@ def install(util_module=None):
     util_module.merge_nodes = merge_nodes
     util_module.divide_pc = divide_pc
     return util_module
+
+
+# ---------------------------------------------------------------------------- patch graph
+# Host bookkeeping around the flip-score kernels, same names and results as the reference's util.py.
+def timer_factory():
+    """util.py:612-651: context-manager timer class with a shared running total."""
+    import time
+
+    class MyTimer(object):
+        total_count = 0
+
+        def __init__(self, msg='', count=True):
+            self.msg, self.count = msg, count
+
+        def __enter__(self):
+            self.start = time.perf_counter()
+            if self.msg:
+                print(f'started: {self.msg}')
+            return self
+
+        def __exit__(self, typ, value, traceback):
+            self.duration = time.perf_counter() - self.start
+            if self.count:
+                MyTimer.total_count += self.duration
+            if self.msg:
+                print(f'finished: {self.msg}. duration: {MyTimer.convert_to_time_format(self.duration)}')
+
+        @staticmethod
+        def print_total_time():
+            print('\n ----- \n')
+            print(f'total time: {MyTimer.convert_to_time_format(MyTimer.total_count)}')
+
+        @staticmethod
+        def convert_to_time_format(sec):
+            sec = round(sec, 2)
+            if sec < 60:
+                return f'{sec} [sec]'
+            minutes = int(sec / 60)
+            remaining_seconds = sec - (minutes * 60)
+            remaining_seconds = round(remaining_seconds, 2)
+            return f'{minutes}:{remaining_seconds} [min:sec]'
+
+    return MyTimer
+
+
+def orient_center(pred):
+    """util.py:39-44: flip the normals that point towards the centroid (in place)."""
+    cent = pred[:, :3].mean(dim=0)
+    flip_mask = ((pred[:, :3] - cent) * pred[:, 3:]).sum(dim=-1) < 0
+    pred[flip_mask, 3:] *= -1
+    return pred
+
+
+def npxyz2tensor(np_pc, append_normals=True):
+    """util.py:71-77: numpy [N, 3|6] -> tensor of the same dtype (float64 from the wire), zero normals appended."""
+    import numpy as np
+    if np_pc.shape[1] == 3 and append_normals:
+        np_pc = np.concatenate([np_pc, np.zeros((np_pc.shape[0], 3))], axis=1)
+    return torch.tensor(np_pc)
+
+
+def estimate_normals_torch(inputpc, max_nn):
+    """util.py:520-529, the reference's own fallback when open3d is missing: the eigenvector of the smallest
+    eigenvalue of the covariance of each point's max_nn nearest neighbours (self excluded).  The reference takes
+    the neighbours from torch_cluster.knn_graph; here a chunked distance + topk (estimator plumbing, not the
+    dipole path; unoriented normals, sign arbitrary as in the reference)."""
+    xyz = inputpc[:, :3]
+    n = xyz.shape[0]
+    k = min(max_nn, n - 1)
+    nbr = torch.empty(n, k, dtype=torch.int64, device=xyz.device)
+    chunk = max(1, min(n, (1 << 26) // max(n, 1)))
+    for lo in range(0, n, chunk):
+        d = torch.cdist(xyz[lo:lo + chunk].double(), xyz.double())
+        d[torch.arange(d.shape[0], device=xyz.device), torch.arange(lo, lo + d.shape[0], device=xyz.device)] = float('inf')
+        nbr[lo:lo + chunk] = d.topk(k, dim=1, largest=False).indices
+    x = xyz[nbr]
+    temp = x - x.mean(dim=1, keepdim=True)
+    cov = temp.transpose(1, 2) @ temp / x.shape[0]
+    _, v = torch.linalg.eigh(cov)
+    return torch.cat([xyz, v[:, :, 0].to(xyz.dtype)], dim=-1)
+
+
+def estimate_normals(inputpc, max_nn=30, keep_orientation=False):
+    """util.py:551-567: open3d's hybrid-radius PCA normals when open3d is importable, else the torch fallback."""
+    try:
+        import numpy as np
+        import open3d as o3d
+        pcd = o3d.geometry.PointCloud()
+        pcd.points = o3d.utility.Vector3dVector(np.array(inputpc[:, :3].cpu()))
+        pcd.estimate_normals(search_param=o3d.geometry.KDTreeSearchParamHybrid(radius=0.1, max_nn=max_nn))
+        out = torch.cat((inputpc[:, :3], torch.Tensor(np.array(pcd.normals)).to(inputpc.device)), dim=1)
+        if keep_orientation:
+            flip = (inputpc[:, 3:] * out[:, 3:]).sum(dim=-1) < 0
+            out[flip, 3:] *= -1
+    except (ModuleNotFoundError, AttributeError):
+        print('open3d not found, using torch_cluster instead')
+        out = estimate_normals_torch(inputpc, max_nn)
+    return out
+
+
+def _lzd_divide_pc(pc_in: torch.Tensor, n_part: int, ranges=(-1.5, 1.5), min_patch=0):
+    """util.py:85-108: cell of every point by searchsorted on linspace(lo, hi, n_part + 1) (left-closed cells,
+    key = x + y n + z n^2), patches in ascending key order with their rows ascending.  The reference groups the
+    rows with a Python loop over all points (:100-101); here one stable sort by key.  Returns (indices, patch_ijk)
+    with the reference's nesting: indices[c] = [LongTensor], patch_ijk[c] = [LongTensor([x, y, z])] (the cell of
+    the patch's first point, :106)."""
+    dev = pc_in.device
+    edges = torch.linspace(ranges[0], ranges[1], n_part + 1).to(device=dev, dtype=pc_in.dtype)
+    cell = torch.stack([torch.searchsorted(edges, pc_in[:, a].contiguous(), right=True) - 1 for a in range(3)], dim=1)
+    key = cell[:, 0] + cell[:, 1] * n_part + cell[:, 2] * n_part * n_part
+    skey, rows = torch.sort(key, stable=True)
+    _, counts = torch.unique_consecutive(skey, return_counts=True)
+    parts = torch.split(rows, counts.tolist())
+    indices = [[p] for p in parts]
+    patch_ijk = [[cell[p[0]]] for p in parts]
+    return indices, patch_ijk
+
+
+def _manhattan_neighbours(c):
+    x, y, z = c
+    return ((x - 1, y, z), (x + 1, y, z), (x, y - 1, z), (x, y + 1, z), (x, y, z - 1), (x, y, z + 1))
+
+
+def lzd_merge_nodes(pts, indices, ijk, min_patch):
+    """util.py:418-447: one pass over the cells in order; a cell with at most min_patch points is appended to the
+    neighbouring patch (a source cell at Manhattan distance 1) that currently counts the fewest points -- counts
+    as the reference keeps them, including its bookkeeping quirk of crediting the moved points to the FIRST
+    neighbour (:435).  The reference's O(P^2 |cells|^2) neighbour scan is a cell -> owner map here.
+    Returns (new_indices, new_ijk, ijk_source)."""
+    import numpy as np
+    ijk = [c[0] for c in ijk]
+    indices = [c[0] for c in indices]
+    n0 = len(indices)
+    cell_of = [tuple(int(v) for v in c) for c in ijk]
+    by_cell = {}
+    for i, c in enumerate(cell_of):
+        by_cell.setdefault(c, []).append(i)
+    owner = list(range(n0))                      # current patch of every original cell
+    sources = [[i] for i in range(n0)]
+    pt_count = np.array([len(i) for i in indices])
+    for i in range(n0):
+        count = pt_count[i]
+        if count > min_patch:
+            continue
+        near = set()
+        for s in sources[i]:
+            for c in _manhattan_neighbours(cell_of[s]):
+                for o in by_cell.get(c, ()):
+                    if owner[o] != i:
+                        near.add(owner[o])
+        if not near:
+            continue
+        neighbor = np.array(sorted(near))
+        smallest = int(neighbor[np.argmin(pt_count[neighbor])])
+        for s in sources[i]:
+            owner[s] = smallest
+        sources[smallest] += sources[i]
+        sources[i] = []
+        pt_count[neighbor[0]] += count
+        pt_count[i] = 0
+    new_indices, new_ijk, ijk_source = [], [], []
+    for i in range(n0):
+        if not sources[i]:
+            continue
+        new_indices.append(torch.cat([indices[j] for j in sources[i]]))
+        new_ijk.append(ijk[i])
+        ijk_source.append([ijk[j] for j in sources[i]])
+    return new_indices, new_ijk, ijk_source
+
+
+def graph_edges(ijk_source):
+    """Patch pairs (i < j, lexicographic) owning two cells at Manhattan distance 1: the pairs util.py:199-203
+    keeps, found through a cell map instead of the all-pairs scan."""
+    cell_patch = {}
+    for p, cells in enumerate(ijk_source):
+        for c in cells:
+            cell_patch.setdefault(tuple(int(v) for v in c), set()).add(p)
+    edges = set()
+    for p, cells in enumerate(ijk_source):
+        for c in cells:
+            for nb in _manhattan_neighbours(tuple(int(v) for v in c)):
+                for q in cell_patch.get(nb, ()):
+                    if q > p:
+                        edges.add((p, q))
+    return sorted(edges)
+
+
+def divide_pc_to_graph(pc_in: torch.Tensor, n_part: int, ranges=(-1.5, 1.5), min_patch=0, edge_calculator=None,
+                       point_estimator=None):
+    """util.py:160-212.  Grid patches -> per-patch orientation (point_estimator, in place on pc_in) -> BidGraph
+    with one flip score per adjacent patch pair.  When edge_calculator is this package's
+    field_utils.field_edge_calculator, all scores come from ONE launch of the batched edge kernel
+    (dnp_edge_interactions_batched_f32) instead of one call per edge.  Returns (G, indices)."""
+    import numpy as np
+    import field_utils
+    from graph import BidGraph, BiEdge
+    MyTimer = timer_factory()
+    with MyTimer('lzd_divide_pc'):
+        indices, ijk = _lzd_divide_pc(pc_in, n_part, ranges, min_patch)
+    with MyTimer('merge nodes'):
+        indices, ijk, ijk_source = lzd_merge_nodes(pc_in, indices, ijk, min_patch)
+    with MyTimer('point estimator'):
+        if point_estimator is not None:
+            for idx in indices:          # the reference starts one Python thread per patch; the device serialises them anyway
+                pc_in[idx] = point_estimator(pc_in[idx])
+    with MyTimer('edge calculator'):
+        G = BidGraph()
+        G.V = [i for i in range(len(indices))]
+        pairs = graph_edges(ijk_source)
+        assert edge_calculator is not None or not pairs
+        if pairs and edge_calculator is field_utils.field_edge_calculator:
+            w, invw = field_utils.field_edge_calculator_batched(pc_in, indices, np.asarray(pairs, dtype=np.int64))
+            for (i, j), a, b in zip(pairs, w, invw):
+                G.E.append(BiEdge(i, j, np.asarray(a), b))
+        else:
+            for i, j in pairs:
+                w, invw = edge_calculator(pc_in[indices[i]], pc_in[indices[j]])
+                G.E.append(BiEdge(i, j, w, invw))
+    return G, indices

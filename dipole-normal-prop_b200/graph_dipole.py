@@ -1,12 +1,18 @@
 """The thin per-cloud wrappers of the reference's graph_dipole.py whose signatures are kept
 (SURVEY.md section 8a row a10): Transform -> propagate in place -> lattice sign test -> inverse transform.
 
-Only these two functions are provided.  The rest of the reference's graph_dipole.py (patch-graph
-construction, the Gurobi MIQP flip solve, the folder batch runner, the import-time mkdir of a Windows
-path at graph_dipole.py:9-25) is out of scope and keeps working from the reference checkout, where it
-picks up this package's field_utils through `import field_utils`.
+Provided: the per-cloud wrappers (:27-42) and graph_dipole_server_api (:87-117), the grid-partition ->
+per-patch orientation -> flip scores -> flip solve pipeline the fork's server calls.  Not provided: the
+file/folder batch runners around them (open3d IO, ground-truth metrics, viewers) and the import-time
+mkdir of a Windows path (:9-25).
 """
+import numpy as np
+import torch
+
+import dnp_util
 import field_utils
+from graph import *        # noqa: F401,F403  (the reference does the same, graph_dipole.py:6)
+from graph import MIQP
 
 util = field_utils.util
 
@@ -25,3 +31,39 @@ def st_propagation_points_file(input_pc, verbose=True):
     """graph_dipole.py:35-36."""
     return propagate_points_file(input_pc, field_utils.strongest_field_propagation_points, diffuse=True,
                                  starting_point=0, verbose=verbose)
+
+
+def xie_tree_propagation_points_file(input_pc, eps=1e-2, verbose=True, times=1, use_pw=False):
+    """graph_dipole.py:41-42."""
+    return propagate_points_file(input_pc, field_utils.xie_propagation_points_onbfstree, eps=eps, diffuse=True,
+                                 starting_point=0, verbose=verbose, times=times, use_pw=use_pw, knn_mask=-1)
+
+
+def graph_dipole_server_api(xyz_data, config):
+    """graph_dipole.py:87-117 for config['divide_method'] == 'grid_partition': normals -> Transform -> patch graph
+    (per-patch greedy orientation, one batched flip-score launch) -> flip solve -> flipped patches; returns the
+    [N, 6] numpy array.  Divergences: the cloud is cast to float32 (the reference keeps the wire's float64 and
+    then fails in torch.searchsorted on mixed dtypes, util.py:93); 'ncut_partition' needs the fork's external
+    toolbox.pointcloud_segmentation package and is not provided."""
+    field_utils._cuda_device()
+    device = torch.device("cuda", torch.cuda.current_device())
+    input_pc = dnp_util.npxyz2tensor(np.asarray(xyz_data)).to(device)
+    estimate = getattr(util, "estimate_normals", dnp_util.estimate_normals)
+    input_pc = estimate(input_pc, max_nn=config['max_nn']).float()
+    input_pc, transform = util.Transform.trans(input_pc)
+    if config['divide_method'] == 'grid_partition':
+        G, index = dnp_util.divide_pc_to_graph(input_pc, n_part=config["n_part"], min_patch=config["min_patch"],
+                                               edge_calculator=field_utils.field_edge_calculator,
+                                               point_estimator=st_propagation_points_file)
+    elif config['divide_method'] == 'ncut_partition':
+        raise NotImplementedError("ncut_partition needs toolbox.pointcloud_segmentation (not part of the reference checkout)")
+    else:
+        print("Error: no such divide method")
+        return
+    input_pc = transform.inverse(input_pc)
+    A, B = G.to_matrix()
+    flip = MIQP(A, B)
+    for i in range(len(flip)):
+        if flip[i] == 1:
+            input_pc[index[i], 3:] *= -1
+    return input_pc.cpu().numpy()

@@ -539,9 +539,62 @@ def gen_graph(fu, util):
     save("graph", **out)
 
 
+def gen_patchgraph(fu, util):
+    """util.divide_pc_to_graph (util.py:160-212) with its grid partition
+    (_lzd_divide_pc, :85-108), merge (lzd_merge_nodes, :418-447), per-patch orientation and flip scores.
+    Shim outside the math: util.py:162 calls `util.timer_factory()` without importing itself (NameError at
+    HEAD) -> `util.util = util`.  The per-patch estimator is graph_dipole.st_propagation_points_file
+    (graph_dipole.py:27-36) restated here from the reference's own functions, because importing
+    graph_dipole.py creates directories (graph_dipole.py:9-25)."""
+    util.util = util
+
+    def st_points(pc, verbose=False):
+        pc, tr = util.Transform.trans(pc)
+        fu.strongest_field_propagation_points(pc, diffuse=True, starting_point=0, verbose=verbose)
+        if fu.measure_mean_potential(pc) < 0:
+            pc[:, 3:] *= -1
+        return tr.inverse(pc)
+    g = torch.Generator().manual_seed(31337)
+    out = {}
+    for tag, name, n_part, min_patch, estimator in (("hand", "hand.xyz", 10, 0, st_points),
+                                                    ("fandisk", "fandisk.xyz", 8, 60, None)):
+        pc, _ = util.Transform.trans(scramble(load_xyz(util, name), g))
+        out[f"{tag}_pc"] = pc.clone()
+        out[f"{tag}_n_part"], out[f"{tag}_min_patch"] = n_part, min_patch
+        idx, ijk = util._lzd_divide_pc(pc, n_part, min_patch=min_patch)
+        out[f"{tag}_cell_perm"], out[f"{tag}_cell_offsets"] = patch_csr([c[0] for c in idx])
+        out[f"{tag}_cell_ijk"] = torch.stack([c[0] for c in ijk]).numpy()
+        m_idx, m_ijk, m_src = util.lzd_merge_nodes(pc, idx, ijk, min_patch)
+        out[f"{tag}_merged_perm"], out[f"{tag}_merged_offsets"] = patch_csr(m_idx)
+        out[f"{tag}_merged_ijk"] = torch.stack(m_ijk).numpy()
+        out[f"{tag}_source_ijk"] = np.concatenate([torch.stack(c).numpy() for c in m_src])
+        out[f"{tag}_source_offsets"] = np.concatenate([[0], np.cumsum([len(c) for c in m_src])])
+        work = pc.clone()
+        t0 = time.time()
+        G, index = util.divide_pc_to_graph(work, n_part=n_part, min_patch=min_patch,
+                                           edge_calculator=fu.field_edge_calculator, point_estimator=estimator)
+        out[f"{tag}_graph_seconds"] = time.time() - t0
+        out[f"{tag}_graph_pc"] = work
+        out[f"{tag}_graph_perm"], out[f"{tag}_graph_offsets"] = patch_csr(index)
+        out[f"{tag}_graph_edges"] = np.array([[e.u, e.v] for e in G.E])
+        out[f"{tag}_graph_w"] = np.array([float(e.w) for e in G.E], dtype=np.float32)
+        out[f"{tag}_graph_invw"] = np.array([float(e.invw) for e in G.E], dtype=np.float32)
+        A, B = G.to_matrix()
+        out[f"{tag}_A"], out[f"{tag}_B"] = A, B
+        print(f"patchgraph {tag}: {len(index)} patches, {len(G.E)} edges, {out[f'{tag}_graph_seconds']:.1f}s")
+    import inspect
+    import json
+    sig = {n: [[p.name, None if p.default is inspect.Parameter.empty else repr(p.default)]
+               for p in inspect.signature(getattr(util, n)).parameters.values()]
+           for n in ("_lzd_divide_pc", "lzd_merge_nodes", "divide_pc_to_graph", "npxyz2tensor", "xyz2tensor", "export_pc",
+                     "estimate_normals", "estimate_normals_torch", "orient_center", "timer_factory")}
+    json.dump(sig, open(os.path.join(OUT, "util_signatures.json"), "w"), indent=1)
+    save("patchgraph", **out)
+
+
 GENERATORS = {"signatures": gen_signatures, "leaf": gen_leaf, "edge": gen_edge, "transfer": gen_transfer, "lattice": gen_lattice,
               "points": gen_points, "patches": gen_patches, "reps": gen_reps, "xie": gen_xie, "partition": gen_partition,
-              "graph": gen_graph}
+              "graph": gen_graph, "patchgraph": gen_patchgraph}
 
 if __name__ == "__main__":
     torch.manual_seed(0)

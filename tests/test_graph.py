@@ -107,3 +107,42 @@ def test_miqp_has_no_cpu_fallback():
     A = np.array([[0.0, 1.0], [1.0, 0.0]])
     with pytest.raises(dnp_native.DipoleError):
         graph.MIQP(A, -A)
+
+
+# ------------------------------------------------------------------ patch graph bookkeeping (util.py:85-108,160-212,418-447)
+def _csr(parts):
+    parts = [np.asarray(p) for p in parts]
+    return np.concatenate(parts), np.concatenate([[0], np.cumsum([len(p) for p in parts])])
+
+
+@pytest.mark.parametrize("tag", ["hand", "fandisk"])
+def test_lzd_partition_and_merge_match_reference(golden, tag):
+    """Index work: identical to the reference's own outputs (tests/golden/patchgraph.npz)."""
+    import dnp_util
+    g = golden("patchgraph")
+    pc = torch.from_numpy(g[f"{tag}_pc"])
+    n_part, min_patch = int(g[f"{tag}_n_part"]), int(g[f"{tag}_min_patch"])
+    idx, ijk = dnp_util._lzd_divide_pc(pc, n_part, min_patch=min_patch)
+    assert all(len(c) == 1 and c[0].dtype == torch.int64 for c in idx) and all(len(c) == 1 for c in ijk)
+    perm, off = _csr([c[0] for c in idx])
+    assert np.array_equal(perm, g[f"{tag}_cell_perm"]) and np.array_equal(off, g[f"{tag}_cell_offsets"])
+    assert np.array_equal(torch.stack([c[0] for c in ijk]).numpy(), g[f"{tag}_cell_ijk"])
+    m_idx, m_ijk, m_src = dnp_util.lzd_merge_nodes(pc, idx, ijk, min_patch)
+    perm, off = _csr(m_idx)
+    assert np.array_equal(perm, g[f"{tag}_merged_perm"]) and np.array_equal(off, g[f"{tag}_merged_offsets"])
+    assert np.array_equal(torch.stack(m_ijk).numpy(), g[f"{tag}_merged_ijk"])
+    assert np.array_equal(np.concatenate([torch.stack(c).numpy() for c in m_src]), g[f"{tag}_source_ijk"])
+    assert np.array_equal(np.concatenate([[0], np.cumsum([len(c) for c in m_src])]), g[f"{tag}_source_offsets"])
+    # the adjacent patch pairs, in the reference's (i, j) order
+    assert np.array_equal(np.array(dnp_util.graph_edges(m_src)), g[f"{tag}_graph_edges"])
+
+
+def test_util_signatures_match_the_reference():
+    import dnp_util
+    want = json.load(open(os.path.join(GOLDEN, "util_signatures.json")))
+    for name, params in want.items():
+        if not hasattr(dnp_util, name):
+            continue                                             # xyz2tensor / export_pc: see tests/test_io.py
+        got = [[p.name, None if p.default is inspect.Parameter.empty else repr(p.default)]
+               for p in inspect.signature(getattr(dnp_util, name)).parameters.values()]
+        assert got == params, name
