@@ -421,7 +421,48 @@ def extras(dn, field_utils, dev, src, tgt):
     out["flip_solve_36_patches_exhaustive_ms"] = ms
     out["flip_solve_exhaustive_states_per_s"] = 2.0 ** 35 / (ms * 1e-3)
     out["flip_solve_300_patches_anneal_ms"] = best_ms(lambda: dn.flip_solve(a300, -a300), 2)
+    # text IO of the 1M-point cloud (export -> parse), device time and end to end from host bytes
+    cloud = pc3[:, :6] if pc3.shape[1] >= 6 else torch.cat([pc3, torch.zeros_like(pc3)], 1)
+    rows = cloud.contiguous()
+    t0 = time.perf_counter()
+    text = dnp_util.export_text(rows.transpose(0, 1))
+    out["xyz_export_1M_pts_e2e_ms"] = (time.perf_counter() - t0) * 1e3
+    out["xyz_text_bytes"] = len(text)
+    out["xyz_format_1M_pts_ms"] = best_ms(lambda: _format_only(dn, rows), 2)
+    t0 = time.perf_counter()
+    back, mask, bad, lines = dn.xyz_parse(text)
+    torch.cuda.synchronize()
+    out["xyz_parse_1M_pts_e2e_ms"] = (time.perf_counter() - t0) * 1e3
+    txt_dev = torch.frombuffer(bytearray(text), dtype=torch.uint8).to(dev)
+    out["xyz_parse_1M_pts_ms"] = best_ms(lambda: _parse_only(dn, txt_dev, lines), 2)
+    out["xyz_parse_text_gbs"] = len(text) / out["xyz_parse_1M_pts_ms"] / 1e6
+    out["xyz_round_trip_bit_exact"] = bool(torch.equal(back.view(torch.int32), rows.view(torch.int32)))
+    out["xyz_reference_cpu"] = "util.xyz2tensor / export_pc are per-line Python loops: 1.2 us per value parsed, 1.5 us per value written on the build container (tools/io_probe.py), i.e. 7 s + 9 s for 1M points"
     return out
+
+
+def _format_only(dn, rows):
+    lib = dn.load()
+    n, c = rows.shape
+    cap = 25 * n * c
+    dev = rows.device
+    out = torch.empty(cap, dtype=torch.uint8, device=dev)
+    n_out = torch.zeros(1, dtype=torch.int64, device=dev)
+    nbytes = lib.dnp_xyz_format_workspace_bytes(n * c)
+    ws = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+    dn._check(lib.dnp_xyz_format_f32(dn._ptr(rows), n, c, rows.stride(0), rows.stride(1), dn._ptr(out), cap,
+                                     dn._ptr(n_out), dn._ptr(ws), nbytes, dn._stream(rows)))
+
+
+def _parse_only(dn, txt_dev, n_lines):
+    lib = dn.load()
+    dev = txt_dev.device
+    out = torch.empty(n_lines, 6, dtype=torch.float32, device=dev)
+    counts = torch.empty(4, dtype=torch.int64, device=dev)
+    nbytes = lib.dnp_xyz_parse_workspace_bytes(txt_dev.numel(), n_lines)
+    ws = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+    dn._check(lib.dnp_xyz_parse_f32(dn._ptr(txt_dev), txt_dev.numel(), n_lines, dn._ptr(out), n_lines, dn._ptr(counts),
+                                    dn._ptr(ws), nbytes, dn._stream(txt_dev)))
 
 
 def surface_cloud(n, seed):

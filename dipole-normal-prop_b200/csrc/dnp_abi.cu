@@ -421,6 +421,41 @@ int dnp_flip_solve_f64(const double* A, const double* B, int64_t n, int64_t ld, 
                           workspace_bytes, (cudaStream_t)stream);
 }
 
+// ------------------------------------------------------------------ text IO + wire format (dnp_textio.cu)
+size_t dnp_xyz_parse_workspace_bytes(int64_t n_bytes, int64_t max_lines) {
+    return xyz_parse_workspace_bytes(n_bytes, max_lines);
+}
+
+int dnp_xyz_parse_f32(const char* txt, int64_t n_bytes, int64_t max_lines, float* out, int64_t max_rows,
+                      int64_t* counts, void* workspace, size_t workspace_bytes, void* stream) {
+    DNP_REQUIRE(n_bytes >= 0 && max_lines >= 1 && max_rows >= 0, "bad size");
+    DNP_REQUIRE(counts && (n_bytes == 0 || txt) && (max_rows == 0 || out), "null pointer");
+    return run_xyz_parse(txt, n_bytes, max_lines, out, max_rows, counts, workspace, workspace_bytes,
+                         (cudaStream_t)stream);
+}
+
+size_t dnp_xyz_format_workspace_bytes(int64_t n_values) { return xyz_format_workspace_bytes(n_values); }
+
+int dnp_xyz_format_f32(const float* pts, int64_t n_rows, int cols, int64_t ld_row, int64_t ld_col, char* out,
+                       int64_t capacity, int64_t* n_bytes_out, void* workspace, size_t workspace_bytes, void* stream) {
+    DNP_REQUIRE(n_rows >= 0 && cols >= 1 && capacity >= 0, "bad size");
+    DNP_REQUIRE(n_bytes_out && (n_rows == 0 || (pts && out)), "null pointer");
+    return run_xyz_format(pts, n_rows, cols, ld_row, ld_col, out, capacity, n_bytes_out, workspace, workspace_bytes,
+                          (cudaStream_t)stream);
+}
+
+int dnp_wire_decode_f64(const double* xyz, int64_t n, float* out, int64_t ld, void* stream) {
+    DNP_REQUIRE(n >= 0 && ld >= 6, "bad size");
+    DNP_REQUIRE(n == 0 || (xyz && out), "null pointer");
+    return run_wire_decode(xyz, n, out, ld, (cudaStream_t)stream);
+}
+
+int dnp_wire_encode_f64(const float* pts, int64_t n, int64_t ld, double* out, void* stream) {
+    DNP_REQUIRE(n >= 0 && ld >= 6, "bad size");
+    DNP_REQUIRE(n == 0 || (pts && out), "null pointer");
+    return run_wire_encode(pts, n, ld, out, (cudaStream_t)stream);
+}
+
 int dnp_profile_begin(void) {
     profile_begin();
     return DNP_OK;

@@ -51,6 +51,16 @@ int run_flip_solve(const double* A, const double* B, int64_t n, int64_t ld, int 
                    uint64_t seed, uint8_t* x_out, double* obj_out, int32_t* status_out, void* workspace,
                    size_t workspace_bytes, cudaStream_t stream);
 
+// text IO + wire format (dnp_textio.cu)
+size_t xyz_parse_workspace_bytes(int64_t n_bytes, int64_t max_lines);
+int run_xyz_parse(const char* txt, int64_t n_bytes, int64_t max_lines, float* out, int64_t max_rows, int64_t* counts,
+                  void* workspace, size_t workspace_bytes, cudaStream_t stream);
+size_t xyz_format_workspace_bytes(int64_t n_values);
+int run_xyz_format(const float* pts, int64_t n_rows, int cols, int64_t ld_row, int64_t ld_col, char* out,
+                   int64_t capacity, int64_t* n_bytes_out, void* workspace, size_t workspace_bytes, cudaStream_t stream);
+int run_wire_decode(const double* xyz, int64_t n, float* out, int64_t ld, cudaStream_t stream);
+int run_wire_encode(const float* pts, int64_t n, int64_t ld, double* out, cudaStream_t stream);
+
 int run_microbench(int kind, int iters, float* ms_out, double* ops_out, cudaStream_t stream);
 
 }  // namespace dnp

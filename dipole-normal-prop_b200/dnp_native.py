@@ -49,6 +49,12 @@ SYMBOLS = [
     ("dnp_flip_solve_workspace_bytes", _sz, [_i64, _i32, _i32]),
     ("dnp_flip_solve_f64", _i32, [_vp, _vp, _i64, _i64, _i32, _i32, _i32, ctypes.c_uint64, _vp, _vp, _vp, _vp, _sz,
                                   _vp]),
+    ("dnp_xyz_parse_workspace_bytes", _sz, [_i64, _i64]),
+    ("dnp_xyz_parse_f32", _i32, [_vp, _i64, _i64, _vp, _i64, _vp, _vp, _sz, _vp]),
+    ("dnp_xyz_format_workspace_bytes", _sz, [_i64]),
+    ("dnp_xyz_format_f32", _i32, [_vp, _i64, _i32, _i64, _i64, _vp, _i64, _vp, _vp, _sz, _vp]),
+    ("dnp_wire_decode_f64", _i32, [_vp, _i64, _vp, _i64, _vp]),
+    ("dnp_wire_encode_f64", _i32, [_vp, _i64, _i64, _vp, _vp]),
     ("dnp_field_grad_host_f32", _i32, [_vp, _i64, _i64, _vp, _i64, _i64, _f32, _vp, _i32]),
     ("dnp_potential_host_f32", _i32, [_vp, _i64, _i64, _vp, _i64, _i64, _vp, _i32]),
     ("dnp_launch_count", _i64, []),
@@ -445,6 +451,83 @@ def flip_solve(A, B, exact_max_n=FLIP_EXACT_MAX, replicas=None, sweeps=None, see
                                       int(seed) & (2 ** 64 - 1), _ptr(x), _ptr(obj), _ptr(status), _ptr(ws), nbytes,
                                       _stream(A)))
     return x, obj, status
+
+
+# ------------------------------------------------------------------ text IO + wire format
+def xyz_parse(text_bytes, device=None):
+    """util.xyz2tensor's parse on the device.  text_bytes: bytes / bytearray / uint8 tensor with the file's content.
+    Returns (rows [n, 6] float32 CUDA tensor, column mask, first unparsable line or -1, number of lines)."""
+    lib = load()
+    require_cuda()
+    if isinstance(text_bytes, torch.Tensor):
+        host = text_bytes
+        n_lines = int((host == 10).sum().item()) + 1
+    else:
+        n_lines = text_bytes.count(b"\n") + 1
+        host = torch.frombuffer(bytearray(text_bytes), dtype=torch.uint8) if len(text_bytes) else \
+            torch.empty(0, dtype=torch.uint8)
+    dev = torch.device(device) if device is not None else torch.device("cuda", torch.cuda.current_device())
+    txt = host.to(dev, non_blocking=False)
+    n_bytes = txt.numel()
+    out = torch.empty(n_lines, 6, dtype=torch.float32, device=dev)
+    counts = torch.empty(4, dtype=torch.int64, device=dev)
+    with torch.cuda.device(dev):
+        nbytes = lib.dnp_xyz_parse_workspace_bytes(n_bytes, n_lines)
+        if nbytes == 0:
+            raise DipoleError("xyz parse: at most 2 GiB of text per call")
+        ws = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+        _check(lib.dnp_xyz_parse_f32(_ptr(txt), n_bytes, n_lines, _ptr(out), n_lines, _ptr(counts), _ptr(ws), nbytes,
+                                     _stream(txt)))
+    rows, mask, bad, lines = counts.tolist()
+    return out[:rows], mask, bad, lines
+
+
+def xyz_format(pc_rows):
+    """util.export_pc's text for a [N, C] float32 CUDA tensor (any strides): returns the bytes."""
+    lib = load()
+    if pc_rows.dtype != torch.float32 or not pc_rows.is_cuda or pc_rows.dim() != 2:
+        raise TypeError("xyz_format needs a 2-D float32 CUDA tensor")
+    n, c = pc_rows.shape
+    if n == 0 or c == 0:
+        return b""
+    dev = pc_rows.device
+    cap = 25 * n * c
+    out = torch.empty(cap, dtype=torch.uint8, device=dev)
+    n_out = torch.zeros(1, dtype=torch.int64, device=dev)
+    with torch.cuda.device(dev):
+        nbytes = lib.dnp_xyz_format_workspace_bytes(n * c)
+        if nbytes == 0:
+            raise DipoleError("xyz format: too many values for one call")
+        ws = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+        _check(lib.dnp_xyz_format_f32(_ptr(pc_rows), n, c, pc_rows.stride(0), pc_rows.stride(1), _ptr(out), cap,
+                                      _ptr(n_out), _ptr(ws), nbytes, _stream(pc_rows)))
+    return out[:int(n_out.item())].cpu().numpy().tobytes()
+
+
+def wire_decode(xyz_f64, device=None):
+    """N x 3 float64 request payload (numpy array, bytes or tensor) -> [N, 6] float32 CUDA rows, zero normals."""
+    import numpy as np
+    lib = load()
+    require_cuda()
+    if isinstance(xyz_f64, (bytes, bytearray, memoryview)):
+        xyz_f64 = np.frombuffer(xyz_f64, dtype=np.float64).copy()
+    t = torch.as_tensor(xyz_f64, dtype=torch.float64).reshape(-1, 3)
+    dev = torch.device(device) if device is not None else torch.device("cuda", torch.cuda.current_device())
+    t = t.to(dev).contiguous()
+    out = torch.empty(t.shape[0], 6, dtype=torch.float32, device=dev)
+    with torch.cuda.device(dev):
+        _check(lib.dnp_wire_decode_f64(_ptr(t), t.shape[0], _ptr(out), 6, _stream(t)))
+    return out
+
+
+def wire_encode(pc):
+    """[N, 6] float32 CUDA rows -> the reply payload: N x 6 float64 as bytes."""
+    lib = load()
+    p, ld = _rows(pc, 6, "pc")
+    out = torch.empty(p.shape[0], 6, dtype=torch.float64, device=p.device)
+    with torch.cuda.device(p.device):
+        _check(lib.dnp_wire_encode_f64(_ptr(p), p.shape[0], ld, _ptr(out), _stream(p)))
+    return out.cpu().numpy().tobytes()
 
 
 # ------------------------------------------------------------------ host-buffer calls (CPU tensors in, CPU tensors out)

@@ -344,3 +344,57 @@ def divide_pc_to_graph(pc_in: torch.Tensor, n_part: int, ranges=(-1.5, 1.5), min
                 w, invw = edge_calculator(pc_in[indices[i]], pc_in[indices[j]])
                 G.E.append(BiEdge(i, j, w, invw))
     return G, indices
+
+
+# ---------------------------------------------------------------------------- text IO + wire format
+def xyz2tensor_cuda(txt, append_normals=True, device=None):
+    """util.py:53-69 with the result left on the GPU.  `txt`: str or bytes.  Line splitting, the "nan" filter, the
+    single-space tokenisation, float() rounding and the float32 cast all happen in dnp_xyz_parse_f32."""
+    import dnp_native as _dn
+    raw = txt.encode("utf-8", errors="surrogateescape") if isinstance(txt, str) else bytes(txt)
+    rows, mask, bad, _ = _dn.xyz_parse(raw, device=device)
+    if bad >= 0:
+        line = raw.split(b"\n")[bad].strip()
+        raise ValueError(f"could not convert string to float in line {bad}: {line[:80]!r}")
+    if rows.shape[0] == 0:
+        raise RuntimeError("stack expects a non-empty TensorList")             # torch.stack([]) in the reference
+    if not append_normals:
+        if mask == 3:
+            raise RuntimeError("stack expects each tensor to be equal size (3- and 6-column lines mixed)")
+        if mask == 1:
+            return rows[:, :3].contiguous()
+    return rows
+
+
+def xyz2tensor(txt, append_normals=True):
+    """util.py:53-69: the parsed cloud as a CPU float32 tensor [n, 6] (or [n, 3]), like the reference returns it."""
+    return xyz2tensor_cuda(txt, append_normals).cpu()
+
+
+def export_text(pc):
+    """The text util.export_pc writes for pc [C, N] (it iterates pc.transpose(0, 1)): bytes, no trailing newline."""
+    import dnp_native as _dn
+    _dn.require_cuda()
+    if pc.dtype != torch.float32:
+        raise TypeError(f"export_pc formats float32 clouds (got {pc.dtype})")
+    dev = pc.device if pc.is_cuda else torch.device("cuda", torch.cuda.current_device())
+    return _dn.xyz_format(pc.detach().to(dev).transpose(0, 1))
+
+
+def export_pc(pc, dest):
+    """util.py:46-51."""
+    with open(dest, 'wb+') as file:
+        file.write(export_text(pc))
+
+
+def wire_decode(payload, device=None):
+    """socket_server_para.py:145-166: the request's N x 3 float64 payload -> [N, 6] float32 rows on the GPU."""
+    import dnp_native as _dn
+    return _dn.wire_decode(payload, device=device)
+
+
+def wire_encode(pc):
+    """socket_server_para.py:191: result.astype(np.float64).tobytes() for a [N, 6] float32 cloud."""
+    import dnp_native as _dn
+    dev = pc.device if pc.is_cuda else torch.device("cuda", torch.cuda.current_device())
+    return _dn.wire_encode(pc.to(dev))

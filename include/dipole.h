@@ -252,6 +252,33 @@ DNP_API int dnp_flip_solve_f64(const double* A, const double* B, int64_t n, int6
                        uint8_t* x_out, double* obj_out, int32_t* status_out,
                        void* workspace, size_t workspace_bytes, void* stream);
 
+/* ------------------------------------------------------------------ point-cloud text IO and wire format
+ * 
+ * dnp_xyz_parse_f32 replaces util.xyz2tensor (util.py:53-69): `txt` = the file's bytes on the device; lines are
+ * split on '\n' and stripped, lines containing "nan" are skipped, tokens are split on single spaces, lines with 3 or 6
+ * tokens become rows; each token is converted like Python's float() (correctly rounded to double) and then to
+ * float32.  out: [max_rows, 6] float32 (3-column lines get zero normals); max_lines >= number of '\n' + 1.
+ * counts (device int64[4]): rows written, column mask (bit 0: 3-column lines seen, bit 1: 6-column lines seen),
+ * index of the first line holding a literal the parser does not resolve (-1 = none; malformed, underscores, more
+ * than 38 significant digits on a rounding boundary, decimal exponent outside [-76, 60]), number of lines.
+ * dnp_xyz_format_f32 replaces util.export_pc (util.py:46-51): value (r, c) = pts[r * ld_row + c * ld_col]; every value
+ * is written as CPython's str(float(value)) (shortest round-trip repr of the widened double), ' ' between
+ * columns, '\n' between rows, no trailing newline.  out: device bytes (capacity >= 25 * n_rows * cols suffices),
+ * n_bytes_out: device int64.
+ * dnp_wire_decode_f64 / dnp_wire_encode_f64: the server payloads (socket_server_para.py:145-166,191):
+ * N x 3 float64 -> [N, 6] float32 rows with zero normals, and [N, 6] float32 rows -> N x 6 float64.
+ * All fully asynchronous.                                                                                       */
+DNP_API size_t dnp_xyz_parse_workspace_bytes(int64_t n_bytes, int64_t max_lines);
+DNP_API int dnp_xyz_parse_f32(const char* txt, int64_t n_bytes, int64_t max_lines,
+                      float* out, int64_t max_rows, int64_t* counts,
+                      void* workspace, size_t workspace_bytes, void* stream);
+DNP_API size_t dnp_xyz_format_workspace_bytes(int64_t n_values);
+DNP_API int dnp_xyz_format_f32(const float* pts, int64_t n_rows, int cols, int64_t ld_row, int64_t ld_col,
+                       char* out, int64_t capacity, int64_t* n_bytes_out,
+                       void* workspace, size_t workspace_bytes, void* stream);
+DNP_API int dnp_wire_decode_f64(const double* xyz, int64_t n, float* out, int64_t ld, void* stream);
+DNP_API int dnp_wire_encode_f64(const float* pts, int64_t n, int64_t ld, double* out, void* stream);
+
 /* ------------------------------------------------------------------ host-buffer entry points
  * Same math with HOST pointers: the call stages inputs to the device, runs the
  * kernels and copies the result back before returning (synchronous).  This is

@@ -592,9 +592,89 @@ def gen_patchgraph(fu, util):
     save("patchgraph", **out)
 
 
+def gen_textio(fu, util):
+    """util.xyz2tensor (util.py:53-69) and util.export_pc (util.py:46-51) on a text
+    with the cases the format allows: 3- and 6-column lines, blank / short / long lines, tabs and CR at the line
+    ends, 'nan' lines, exponents, 17-digit reprs, signed zeros, long literals, inf."""
+    import tempfile
+    rng = np.random.default_rng(4711)
+    lines = ["0.1 0.2 0.3 1 0 0", "  -1.5e-3 2.5E+2 .5 0. -0.0 +7  ", "1 2 3", "", "1 2", "1 2 3 4", "1 2 3 4 5 6 7",
+             "0.1 nan 0.3", "3 4 nan 0 0 1", "NaN 1 2", "1\t2\t3", "\t9 8 7\r", "0.30000001192092896 1e-5 1e22",
+             "123456789012345678901234567890 0.000000000000000000000123 1e-40", "inf -inf Infinity",
+             "4.9406564584124654e-40 3.4028234663852886e+38 1.1754943508222875e-38",
+             "16777217 16777219 0.100000001490116119384765625", "1e0 1E1 1e+2", "5e-46 7.006492321624085e-46 1e39",
+             "9007199254740993 9007199254740992.5 0.5000000298023224"]
+    vals = np.concatenate([rng.normal(size=300), rng.normal(size=300) * 1e-6, rng.normal(size=300) * 1e7,
+                           rng.integers(-50, 50, 300).astype(np.float64)]).astype(np.float32)
+    rng.shuffle(vals)
+    for i in range(0, 1200, 6):
+        lines.append(' '.join(repr(float(v)) for v in vals[i:i + 6]))
+    for i in range(0, 600, 3):
+        lines.append(' '.join(f"{float(v):.9g}" for v in vals[i:i + 3]))
+    txt = "\n".join(lines) + "\n"
+    out = {"text": np.frombuffer(txt.encode(), dtype=np.uint8)}
+    out["parsed_append"] = util.xyz2tensor(txt, append_normals=True)
+    six_only = "\n".join(l for l in lines if len(l.strip().split(' ')) != 3)
+    out["text_six"] = np.frombuffer(six_only.encode(), dtype=np.uint8)
+    out["parsed_six_noappend"] = util.xyz2tensor(six_only, append_normals=False)
+    three_only = "\n".join(l for l in lines if len(l.strip().split(' ')) != 6)
+    out["text_three"] = np.frombuffer(three_only.encode(), dtype=np.uint8)
+    out["parsed_three_noappend"] = util.xyz2tensor(three_only, append_normals=False)
+    # export: float32 values of every magnitude, special values, powers of two and ten
+    bits = rng.integers(0, 2 ** 32, 6 * 4000, dtype=np.uint64).astype(np.uint32)
+    ex = bits.view(np.float32).copy()
+    ex = ex[~np.isnan(ex)][:6 * 3000]
+    special = np.array([0.0, -0.0, 1.0, -1.0, 0.1, 0.5, 1e-5, 1e-4, 1e16, 1e15, 9.999999e15, 1.0000001e16, 123456.0,
+                        np.inf, -np.inf, 3.4028235e38, 1e-45, 1.1754944e-38, 2.0 ** -126, 2.0 ** 24, 2.0 ** 60,
+                        1e-3, 0.3, 16777216.0, 1e10, 1e22, 1e23, 5e-324 + 1e-40, 0.001, 1234.5], dtype=np.float32)
+    ex = np.concatenate([special, ex]).astype(np.float32)
+    ex = ex[:(len(ex) // 6) * 6].reshape(-1, 6)
+    pc = torch.from_numpy(ex)
+    with tempfile.TemporaryDirectory() as d:
+        dest = os.path.join(d, "out.xyz")
+        util.export_pc(pc.transpose(0, 1), dest)
+        written = open(dest, "rb").read()
+    out["export_pc"] = ex
+    out["export_text"] = np.frombuffer(written, dtype=np.uint8)
+    # the demo cloud round trip
+    ok_txt = open(os.path.join(REF, "data", "ok.xyz")).read()
+    ok = util.xyz2tensor(ok_txt)
+    out["ok_rows"] = ok[:2000]
+    out["ok_n"] = ok.shape[0]
+    save("textio", **out)
+
+
+def gen_parser(fu, util):
+    """dipole_api.get_parser (dipole_api.py:93-132) and options.get_parser (options.py:5-19): flags, types and
+    defaults.  dipole_api.py cannot be imported here (inference_utils -> torch_geometric), so its parser section
+    (module lines 89-132: imports, path constants, get_parser) is executed on its own."""
+    import json
+    src = open(os.path.join(REF, "dipole_api.py")).read().split("\n")
+    start = next(i for i, l in enumerate(src) if l.startswith("import argparse"))
+    end = next(i for i, l in enumerate(src) if l.startswith("if __name__"))
+    ns = {}
+    exec("\n".join(src[start:end]), ns)
+
+    def describe(parser):
+        rows = []
+        for a in parser._actions:
+            if a.dest == "help":
+                continue
+            rows.append({"flags": a.option_strings, "dest": a.dest, "type": getattr(a.type, "__name__", None),
+                         "default": repr(a.default), "nargs": a.nargs, "action": type(a).__name__,
+                         "required": a.required})
+        return rows
+    sys.path.insert(0, REF)
+    import options as ref_options
+    out = {"dipole_api.get_parser": describe(ns["get_parser"]()),
+           "options.get_parser": describe(ref_options.get_parser())}
+    json.dump(out, open(os.path.join(OUT, "parser_signatures.json"), "w"), indent=1)
+    print("wrote parser_signatures.json")
+
+
 GENERATORS = {"signatures": gen_signatures, "leaf": gen_leaf, "edge": gen_edge, "transfer": gen_transfer, "lattice": gen_lattice,
               "points": gen_points, "patches": gen_patches, "reps": gen_reps, "xie": gen_xie, "partition": gen_partition,
-              "graph": gen_graph, "patchgraph": gen_patchgraph}
+              "graph": gen_graph, "patchgraph": gen_patchgraph, "textio": gen_textio, "parser": gen_parser}
 
 if __name__ == "__main__":
     torch.manual_seed(0)
