@@ -117,13 +117,14 @@ def divide_pc(pc_in: torch.Tensor, n_part: int, ranges=(-1.5, 1.5), min_patch=0)
 
 
 def install(util_module=None):
-    """Point the reference's `util` module (the one its pipelines import) at the GPU partition:
-    util._divide_pc / util.merge_nodes / util.divide_pc.  Returns the module."""
+    """Point the reference's `util` module (the one its pipelines import) at the GPU path: the voxel partition
+    (_divide_pc / merge_nodes / divide_pc), the patch graph (_lzd_divide_pc / lzd_merge_nodes / divide_pc_to_graph)
+    and the text IO (xyz2tensor / export_pc).  Returns the module."""
     if util_module is None:
         import util as util_module
-    util_module._divide_pc = _divide_pc
-    util_module.merge_nodes = merge_nodes
-    util_module.divide_pc = divide_pc
+    for name in ("_divide_pc", "merge_nodes", "divide_pc", "_lzd_divide_pc", "lzd_merge_nodes", "divide_pc_to_graph",
+                 "xyz2tensor", "export_pc"):
+        setattr(util_module, name, globals()[name])
     return util_module
 
 
