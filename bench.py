@@ -421,6 +421,26 @@ def extras(dn, field_utils, dev, src, tgt):
     out["flip_solve_36_patches_exhaustive_ms"] = ms
     out["flip_solve_exhaustive_states_per_s"] = 2.0 ** 35 / (ms * 1e-3)
     out["flip_solve_300_patches_anneal_ms"] = best_ms(lambda: dn.flip_solve(a300, -a300), 2)
+    # the patch graph of a 100k-point cloud (grid 10, as graph_dipole.py:131-135):
+    # per-patch greedy orientation (one launch, a cluster per patch, vs one call per patch) + batched flip scores
+    import contextlib
+    import io
+    import graph_dipole
+    pcg = surface_cloud(100000, 12).to(dev)
+    pcg[:, :3] += 0.013                                             # off the cell faces
+
+    def run_graph(estimator):
+        with contextlib.redirect_stdout(io.StringIO()):
+            return dnp_util.divide_pc_to_graph(pcg.clone(), n_part=10, min_patch=50,
+                                               edge_calculator=field_utils.field_edge_calculator,
+                                               point_estimator=estimator)
+    G, index = run_graph(graph_dipole.st_propagation_points_file)
+    out["patch_graph_100k_pts_patches"] = len(index)
+    out["patch_graph_100k_pts_edges"] = len(G.E)
+    t0 = time.perf_counter(); run_graph(graph_dipole.st_propagation_points_file); torch.cuda.synchronize()
+    out["patch_graph_100k_pts_batched_ms"] = (time.perf_counter() - t0) * 1e3
+    t0 = time.perf_counter(); run_graph(lambda p: graph_dipole.st_propagation_points_file(p, verbose=False)); torch.cuda.synchronize()
+    out["patch_graph_100k_pts_per_patch_calls_ms"] = (time.perf_counter() - t0) * 1e3
     # text IO of the 1M-point cloud (export -> parse), device time and end to end from host bytes
     cloud = pc3[:, :6] if pc3.shape[1] >= 6 else torch.cat([pc3, torch.zeros_like(pc3)], 1)
     rows = cloud.contiguous()

@@ -355,6 +355,25 @@ int dnp_points_propagate_f32(float* pts, int64_t N, int64_t ld, int64_t starting
                                 workspace_bytes, (cudaStream_t)stream);
 }
 
+int64_t dnp_points_batched_max_n(void) { return points_batched_max_n(); }
+
+int dnp_points_propagate_batched_f32(float* pts, int64_t ld, const int64_t* offsets, int64_t P, int64_t max_patch,
+                                     float eps, int diffuse, void* stream) {
+    DNP_REQUIRE(P >= 0 && max_patch >= 0, "negative size");
+    DNP_REQUIRE(P == 0 || (pts && offsets), "null pointer");
+    DNP_REQUIRE(ld >= 6, "points need 6 columns");
+    DNP_REQUIRE(eps >= 0.f, "eps must be >= 0");
+    return run_points_propagate_batched(pts, ld, offsets, P, max_patch, eps, diffuse, (cudaStream_t)stream);
+}
+
+int dnp_patch_lattice_sign_f32(float* pts, int64_t ld, const int64_t* offsets, int64_t P, int n, float* mean_out,
+                               int flip, void* stream) {
+    DNP_REQUIRE(P >= 0, "negative size");
+    DNP_REQUIRE(P == 0 || (pts && offsets && mean_out), "null pointer");
+    DNP_REQUIRE(ld >= 6, "points need 6 columns");
+    return run_patch_lattice_sign(pts, ld, offsets, P, n, mean_out, flip, (cudaStream_t)stream);
+}
+
 // ------------------------------------------------------------------ "xie" interaction (dnp_xie.cu)
 static int xie_matrix_abi(bool field, const float* src, int64_t S, int64_t ld_s, const float* tgt, int64_t M,
                           int64_t ld_t, float C, const double* rad2, float* out, int64_t ld_o, void* stream) {

@@ -134,10 +134,11 @@ __device__ __forceinline__ void sweep_points(const PointSmem& sm, int n_local, i
     }
 }
 
-__global__ void __launch_bounds__(kPtThreads, 1)
-points_propagate_kernel(float* __restrict__ pts, int64_t N, int64_t ld, int cap, int64_t start, float eps,
-                        int diffuse, int32_t* __restrict__ order, uint8_t* __restrict__ flipped) {
-    extern __shared__ __align__(16) unsigned char smem_raw[];
+// The whole greedy loop for ONE cloud of N points on the calling thread-block cluster (every CTA of the cluster
+// calls it with the same arguments).  N == 0 is allowed (the barriers still pair up).
+__device__ __forceinline__ void propagate_on_cluster(unsigned char* smem_raw, float* __restrict__ pts, int64_t N,
+                                                     int64_t ld, int cap, int64_t start, float eps, int diffuse,
+                                                     int32_t* __restrict__ order, uint8_t* __restrict__ flipped) {
     const PointSmem sm = carve(smem_raw, cap);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const uint32_t rank = cluster_rank(), ncta = cluster_size();
@@ -153,12 +154,12 @@ points_propagate_kernel(float* __restrict__ pts, int64_t N, int64_t ld, int cap,
     }
     // current source (field_utils.py:358-362): the starting point, never flipped
     int64_t cur = start;
-    float px, py, pz, p3, p4, p5;
-    {
+    float px = 0.f, py = 0.f, pz = 0.f, p3 = 0.f, p4 = 0.f, p5 = 0.f;
+    if (N > 0) {
         const float* p = pts + start * ld;
         px = p[0]; py = p[1]; pz = p[2]; p3 = p[3]; p4 = p[4]; p5 = p[5];
     }
-    if (rank == 0 && tid == 0) {
+    if (rank == 0 && tid == 0 && N > 0) {
         if (order) order[0] = (int32_t)start;
         if (flipped) flipped[0] = 0;
     }
@@ -239,6 +240,94 @@ points_propagate_kernel(float* __restrict__ pts, int64_t N, int64_t ld, int cap,
         p[3] = nx; p[4] = ny; p[5] = nz;
     }
     cluster_barrier();   // no CTA may exit while a peer can still address its shared memory
+}
+
+__global__ void __launch_bounds__(kPtThreads, 1)
+points_propagate_kernel(float* __restrict__ pts, int64_t N, int64_t ld, int cap, int64_t start, float eps,
+                        int diffuse, int32_t* __restrict__ order, uint8_t* __restrict__ flipped) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    propagate_on_cluster(smem_raw, pts, N, ld, cap, start, eps, diffuse, order, flipped);
+}
+
+// Many independent clouds in ONE launch (the per-patch stage of the patch graph, util.py:185-196 with
+// graph_dipole.st_propagation_points_file): cluster c owns patch c = rows offsets[c] .. offsets[c+1] of `pts`
+// (patches stored contiguously), every patch starts at its first row.  Same code, hence the same bits, as the
+// single-cloud kernel; the clusters never talk to each other.
+__global__ void __launch_bounds__(kPtThreads, 1)
+points_propagate_batched_kernel(float* __restrict__ pts, int64_t ld, const int64_t* __restrict__ offsets, int cap,
+                                float eps, int diffuse) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const int64_t patch = blockIdx.x / cluster_size();
+    const int64_t o = offsets[patch];
+    propagate_on_cluster(smem_raw, pts + o * ld, offsets[patch + 1] - o, ld, cap, 0, eps, diffuse, nullptr, nullptr);
+}
+
+// Lattice sign test per patch (field_utils.py:7-9 + util.py:26-36 on every patch of a CSR): one CTA per patch,
+// thread t owns lattice nodes t, t + 512, ...; mean potential -> mean_out[patch]; with `flip`, the normals of a
+// patch whose mean is negative are negated in place (graph_dipole.py:30-31).
+__global__ void __launch_bounds__(kPtThreads)
+patch_lattice_sign_kernel(float* __restrict__ pts, int64_t ld, const int64_t* __restrict__ offsets, int n_lat,
+                          float* __restrict__ mean_out, int flip) {
+    constexpr int kTile = 256;
+    constexpr int kNodesPerThread = 4;                          // n_lat^3 <= 2048
+    __shared__ float s_src[kTile][6];
+    __shared__ float s_part[kWarps];
+    __shared__ float s_mean;
+    const int64_t o = offsets[blockIdx.x], N = offsets[blockIdx.x + 1] - o;
+    float* P = pts + o * ld;
+    const int M = n_lat * n_lat * n_lat;
+    float qx[kNodesPerThread], qy[kNodesPerThread], qz[kNodesPerThread], phi[kNodesPerThread];
+#pragma unroll
+    for (int k = 0; k < kNodesPerThread; ++k) {
+        const int node = threadIdx.x + k * kPtThreads;
+        const int iz = node % n_lat, ixy = node / n_lat, iy = ixy % n_lat, ix = ixy / n_lat;
+        qx[k] = __fmul_rn(__fsub_rn(__fdiv_rn((float)ix, (float)n_lat), 0.5f), 2.f);
+        qy[k] = __fmul_rn(__fsub_rn(__fdiv_rn((float)iy, (float)n_lat), 0.5f), 2.f);
+        qz[k] = __fmul_rn(__fsub_rn(__fdiv_rn((float)iz, (float)n_lat), 0.5f), 2.f);
+        phi[k] = 0.f;
+    }
+    for (int64_t t0 = 0; t0 < N; t0 += kTile) {
+        const int n_here = (int)min((int64_t)kTile, N - t0);
+        __syncthreads();
+        for (int i = threadIdx.x; i < n_here * 6; i += kPtThreads) s_src[i / 6][i % 6] = P[(t0 + i / 6) * ld + i % 6];
+        __syncthreads();
+#pragma unroll
+        for (int k = 0; k < kNodesPerThread; ++k) {
+            if (threadIdx.x + k * kPtThreads >= M) continue;
+            float acc = phi[k];
+            for (int i = 0; i < n_here; ++i) {
+                const float rx = s_src[i][0] - qx[k], ry = s_src[i][1] - qy[k], rz = s_src[i][2] - qz[k];
+                const float r2 = fmaf(rz, rz, fmaf(ry, ry, rx * rx));
+                const float r = sqrtf(r2);
+                const float dot = fmaf(s_src[i][5], rz, fmaf(s_src[i][4], ry, s_src[i][3] * rx));
+                acc += (r2 > 0.f) ? dot / (r2 * r) : 0.f;
+            }
+            phi[k] = acc;
+        }
+    }
+    float total = 0.f;
+#pragma unroll
+    for (int k = 0; k < kNodesPerThread; ++k) {
+        const bool live = threadIdx.x + k * kPtThreads < M;
+        const float v = phi[k];
+        total += (live && fabsf(v) <= 3.402823466e38f) ? v : 0.f;   // non-finite node totals -> 0 (field_utils.py:53-54)
+    }
+    total = warp_sum(total);
+    if ((threadIdx.x & 31) == 0) s_part[threadIdx.x >> 5] = total;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        float t = 0.f;
+        for (int w = 0; w < kWarps; ++w) t += s_part[w];
+        s_mean = t / (float)M;
+        mean_out[blockIdx.x] = s_mean;
+    }
+    __syncthreads();
+    if (flip && s_mean < 0.f) {
+        for (int64_t i = threadIdx.x; i < N; i += kPtThreads) {
+            float* q = P + i * ld;
+            q[3] = -q[3]; q[4] = -q[4]; q[5] = -q[5];
+        }
+    }
 }
 
 
@@ -438,6 +527,71 @@ static int run_points_propagate_grid(float* pts, int64_t N, int64_t ld, int64_t 
     DNP_CHECK_CUDA(cudaLaunchKernelEx(&cfg, points_propagate_grid_kernel, pts, N, ld, cap, start, eps, diffuse, order,
                                       flipped, slots, counter));
     count_launch(1);
+    return DNP_OK;
+}
+
+int64_t points_batched_max_n() { return points_max_n(); }
+
+int run_points_propagate_batched(float* pts, int64_t ld, const int64_t* offsets, int64_t P, int64_t max_patch,
+                                 float eps, int diffuse, cudaStream_t stream) {
+    if (P <= 0 || max_patch <= 0) return DNP_OK;
+    if (max_patch > points_max_n()) {
+        set_error("largest patch (%lld points) exceeds the single-cluster capacity (%lld)", (long long)max_patch,
+                  (long long)points_max_n());
+        return DNP_ERR_INVALID;
+    }
+    static std::atomic<int> attr_done{0};
+    if (!attr_done.load()) {
+        DNP_CHECK_CUDA(cudaFuncSetAttribute(points_propagate_batched_kernel,
+                                            cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+        DNP_CHECK_CUDA(cudaFuncSetAttribute(points_propagate_batched_kernel,
+                                            cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+        attr_done.store(1);
+    }
+    // <= 1024 points (2 per thread) per CTA; the cluster size is the same for every patch of the launch
+    int ncta = 1;
+    while (ncta < kMaxCluster && (int64_t)ncta * kPtThreads * 2 < max_patch) ncta *= 2;
+    while (point_smem_bytes((int)((max_patch + ncta - 1) / ncta)) > 227 * 1024 && ncta < kMaxCluster) ncta *= 2;
+    cudaLaunchConfig_t cfg = {};
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    cfg.blockDim = dim3(kPtThreads);
+    cfg.stream = stream;
+    int cap = 0;
+    for (;;) {
+        cap = (int)((max_patch + ncta - 1) / ncta);
+        cfg.gridDim = dim3((unsigned)(P * ncta));
+        cfg.dynamicSmemBytes = point_smem_bytes(cap);
+        attr[0].val.clusterDim.x = ncta;
+        attr[0].val.clusterDim.y = 1;
+        attr[0].val.clusterDim.z = 1;
+        int max_clusters = 0;
+        cudaError_t e = cudaOccupancyMaxActiveClusters(&max_clusters, points_propagate_batched_kernel, &cfg);
+        if (e == cudaSuccess && max_clusters >= 1) break;
+        (void)cudaGetLastError();
+        if (ncta == 1 || point_smem_bytes((int)((max_patch + ncta / 2 - 1) / (ncta / 2))) > 227 * 1024) {
+            set_error("cannot schedule a %d-CTA cluster for patches of %lld points", ncta, (long long)max_patch);
+            return DNP_ERR_CUDA;
+        }
+        ncta /= 2;
+    }
+    DNP_CHECK_CUDA(cudaLaunchKernelEx(&cfg, points_propagate_batched_kernel, pts, ld, offsets, cap, eps, diffuse));
+    count_launch(1);
+    return DNP_OK;
+}
+
+int run_patch_lattice_sign(float* pts, int64_t ld, const int64_t* offsets, int64_t P, int n_lat, float* mean_out,
+                           int flip, cudaStream_t stream) {
+    if (P <= 0) return DNP_OK;
+    if (n_lat < 1 || n_lat * n_lat * n_lat > 4 * kPtThreads) {
+        set_error("lattice size must satisfy n^3 <= %d (got n = %d)", 4 * kPtThreads, n_lat);
+        return DNP_ERR_INVALID;
+    }
+    patch_lattice_sign_kernel<<<(unsigned)P, kPtThreads, 0, stream>>>(pts, ld, offsets, n_lat, mean_out, flip);
+    count_launch(1);
+    DNP_CHECK_CUDA(cudaGetLastError());
     return DNP_OK;
 }
 

@@ -30,6 +30,12 @@ int run_points_propagate(float* pts, int64_t N, int64_t ld, int64_t start, float
                          int32_t* order, uint8_t* flipped, void* workspace, size_t workspace_bytes,
                          cudaStream_t stream);
 
+int64_t points_batched_max_n();
+int run_points_propagate_batched(float* pts, int64_t ld, const int64_t* offsets, int64_t P, int64_t max_patch,
+                                 float eps, int diffuse, cudaStream_t stream);
+int run_patch_lattice_sign(float* pts, int64_t ld, const int64_t* offsets, int64_t P, int n_lat, float* mean_out,
+                           int flip, cudaStream_t stream);
+
 // "xie" reflected-normal interaction (dnp_xie.cu)
 int run_xie_matrix(bool field, const float* src, int64_t S, int64_t ld_s, const float* tgt, int64_t M, int64_t ld_t,
                    float C, const double* rad2, float* out, int64_t ld_o, cudaStream_t stream);

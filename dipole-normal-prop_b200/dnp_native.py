@@ -38,6 +38,9 @@ SYMBOLS = [
     ("dnp_points_max_n", _i64, []),
     ("dnp_points_workspace_bytes", _sz, [_i64]),
     ("dnp_points_propagate_f32", _i32, [_vp, _i64, _i64, _i64, _f32, _i32, _vp, _vp, _vp, _sz, _vp]),
+    ("dnp_points_batched_max_n", _i64, []),
+    ("dnp_points_propagate_batched_f32", _i32, [_vp, _i64, _vp, _i64, _i64, _f32, _i32, _vp]),
+    ("dnp_patch_lattice_sign_f32", _i32, [_vp, _i64, _vp, _i64, _i32, _vp, _i32, _vp]),
     ("dnp_xie_interaction_f32", _i32, [_vp, _i64, _i64, _vp, _i64, _i64, _f32, _vp, _vp, _i64, _vp]),
     ("dnp_xie_field_f32", _i32, [_vp, _i64, _i64, _vp, _i64, _i64, _f32, _vp, _vp, _i64, _vp]),
     ("dnp_xie_max_n", _i64, [_i32]),
@@ -332,6 +335,35 @@ def points_propagate(pts, diffuse=False, starting_point=0, eps=1e-6, want_trace=
 
 
 # ------------------------------------------------------------------ "xie" interaction
+def points_propagate_batched(pts, offsets, max_patch, diffuse=False, eps=1e-6):
+    """strongest_field_propagation_points on every patch of a CSR in ONE launch (a cluster per patch), in place.
+    pts: [N, 6] float32 CUDA rows stored patch by patch; offsets: int64 [P + 1]."""
+    lib = load()
+    p, ld = _rows(pts, 6, "pts")
+    if p.data_ptr() != pts.data_ptr():
+        raise ValueError("pts must have unit column stride (the call works in place)")
+    off = _idx(offsets, p.device, "offsets")
+    with torch.cuda.device(p.device):
+        _check(lib.dnp_points_propagate_batched_f32(_ptr(p), ld, _ptr(off), off.numel() - 1, int(max_patch),
+                                                    float(eps), int(bool(diffuse)), _stream(p)))
+    return pts
+
+
+def patch_lattice_sign(pts, offsets, n=10, flip=True):
+    """Mean lattice potential of every patch (float32 [P]); with flip, patches with a negative mean are negated."""
+    lib = load()
+    p, ld = _rows(pts, 6, "pts")
+    if p.data_ptr() != pts.data_ptr():
+        raise ValueError("pts must have unit column stride (the call works in place)")
+    off = _idx(offsets, p.device, "offsets")
+    P = off.numel() - 1
+    mean = torch.zeros(P, dtype=torch.float32, device=p.device)
+    with torch.cuda.device(p.device):
+        _check(lib.dnp_patch_lattice_sign_f32(_ptr(p), ld, _ptr(off), P, int(n), _ptr(mean), int(bool(flip)),
+                                              _stream(p)))
+    return mean
+
+
 def knn_radius2(sources, targets, k, chunk=2048):
     """Squared distance (float64) from every source to its k-th nearest target: the kNN mask of
     field_utils.py:447-455 as one radius per source.  Plumbing in torch; exact differences of the float

@@ -329,8 +329,14 @@ def divide_pc_to_graph(pc_in: torch.Tensor, n_part: int, ranges=(-1.5, 1.5), min
         indices, ijk, ijk_source = lzd_merge_nodes(pc_in, indices, ijk, min_patch)
     with MyTimer('point estimator'):
         if point_estimator is not None:
-            for idx in indices:          # the reference starts one Python thread per patch; the device serialises them anyway
-                pc_in[idx] = point_estimator(pc_in[idx])
+            import dnp_native as _dn
+            batched = getattr(point_estimator, "batched", None)
+            if (batched is not None and pc_in.is_cuda and pc_in.dtype == torch.float32 and indices
+                    and max(len(i) for i in indices) <= _dn.load().dnp_points_batched_max_n()):
+                batched(pc_in, indices)  # every patch in one launch (graph_dipole.st_propagation_points_batched)
+            else:
+                for idx in indices:      # the reference starts one Python thread per patch; the device serialises them
+                    pc_in[idx] = point_estimator(pc_in[idx])
     with MyTimer('edge calculator'):
         G = BidGraph()
         G.V = [i for i in range(len(indices))]

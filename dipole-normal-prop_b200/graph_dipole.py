@@ -33,6 +33,38 @@ def st_propagation_points_file(input_pc, verbose=True):
                                  starting_point=0, verbose=verbose)
 
 
+def st_propagation_points_batched(pc_in, indices):
+    """st_propagation_points_file on every patch of `indices` at once, in place on pc_in [N, 6] float32 (CUDA):
+    the per-patch Transform (util.py:577-609) as segment reductions, ONE launch with a thread-block cluster per
+    patch for the greedy propagation (dnp_points_propagate_batched_f32), ONE launch for the per-patch lattice
+    sign test (dnp_patch_lattice_sign_f32), the inverse Transform, one scatter.  The reference runs this stage
+    as one Python thread per patch (util.py:185-196)."""
+    import dnp_native as _dn
+    dev = pc_in.device
+    sizes = [int(len(i)) for i in indices]
+    if not sizes:
+        return pc_in
+    counts = torch.tensor(sizes, dtype=torch.int64, device=dev)
+    offsets = torch.zeros(len(sizes) + 1, dtype=torch.int64, device=dev)
+    offsets[1:] = torch.cumsum(counts, 0)
+    perm = torch.cat([i.to(dev) for i in indices])
+    seg = torch.repeat_interleave(torch.arange(len(sizes), device=dev), counts)
+    work = pc_in[perm].contiguous()
+    xyz = work[:, :3].contiguous()
+    center = torch.segment_reduce(xyz, "mean", lengths=counts, axis=0)
+    extent = torch.segment_reduce(xyz, "max", lengths=counts, axis=0) - torch.segment_reduce(xyz, "min", lengths=counts, axis=0)
+    scale = extent.max(dim=1).values
+    work[:, :3] = (xyz - center[seg]) / scale[seg, None]
+    _dn.points_propagate_batched(work, offsets, max(sizes), diffuse=True, eps=field_utils._EPS_POINTS)
+    _dn.patch_lattice_sign(work, offsets, 10, flip=True)
+    work[:, :3] = work[:, :3] * scale[seg, None] + center[seg]
+    pc_in[perm] = work
+    return pc_in
+
+
+st_propagation_points_file.batched = st_propagation_points_batched
+
+
 def xie_tree_propagation_points_file(input_pc, eps=1e-2, verbose=True, times=1, use_pw=False):
     """graph_dipole.py:41-42."""
     return propagate_points_file(input_pc, field_utils.xie_propagation_points_onbfstree, eps=eps, diffuse=True,

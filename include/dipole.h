@@ -182,6 +182,21 @@ DNP_API int dnp_points_propagate_f32(float* pts, int64_t N, int64_t ld, int64_t 
                              int32_t* order_opt, uint8_t* flipped_opt,
                              void* workspace, size_t workspace_bytes, void* stream);
 
+/* ------------------------------------------------------------------ per-patch greedy orientation, batched
+ * The per-patch stage of the patch graph (util.py:185-196 calling graph_dipole.st_propagation_points_file,
+ * graph_dipole.py:27-36, once per patch from Python threads) as ONE launch: patch c = rows offsets[c] ..
+ * offsets[c+1] of `pts` (patches stored contiguously, offsets: device int64[P+1]); every patch runs
+ * strongest_field_propagation_points (field_utils.py:353-388) from its first row on its own thread-block
+ * cluster, in place.  max_patch = the largest patch size (<= dnp_points_batched_max_n()).
+ * dnp_patch_lattice_sign_f32: measure_mean_potential (field_utils.py:7-9) of every patch on the n^3 lattice
+ * (n^3 <= 2048) -> mean_out[P]; with flip != 0 the normals of patches with a negative mean are negated
+ * (graph_dipole.py:30-31).  Both fully asynchronous.                                                     */
+DNP_API int64_t dnp_points_batched_max_n(void);
+DNP_API int dnp_points_propagate_batched_f32(float* pts, int64_t ld, const int64_t* offsets, int64_t P,
+                                     int64_t max_patch, float eps, int diffuse, void* stream);
+DNP_API int dnp_patch_lattice_sign_f32(float* pts, int64_t ld, const int64_t* offsets, int64_t P, int n,
+                               float* mean_out, int flip, void* stream);
+
 /* ------------------------------------------------------------------ "xie" reflected-normal interaction
  * (the fork's N x N propagation variant.)
  * dnp_xie_field_f32 replaces field_utils.xie_field (field_utils.py:431-469):

@@ -14,16 +14,18 @@ def _csr(parts):
     return np.concatenate(parts), np.concatenate([[0], np.cumsum([len(p) for p in parts])])
 
 
-@pytest.mark.parametrize("tag", ["hand", "fandisk"])
-def test_divide_pc_to_graph_matches_reference(golden, dev, tag):
+@pytest.mark.parametrize("tag,batched", [("hand", True), ("hand", False), ("fandisk", False)])
+def test_divide_pc_to_graph_matches_reference(golden, dev, tag, batched):
+    """batched = every patch oriented in one launch (a cluster per patch); otherwise the per-patch calls the
+    reference makes.  Both must reproduce the reference's decisions."""
     import dnp_util
     import field_utils
     import graph_dipole
     g = golden("patchgraph")
     pc = torch.from_numpy(g[f"{tag}_pc"]).to(dev)
     estimator = graph_dipole.st_propagation_points_file if tag == "hand" else None
-    if estimator is not None:
-        estimator = lambda p, f=estimator: f(p, verbose=False)      # noqa: E731
+    if estimator is not None and not batched:
+        estimator = lambda p, f=estimator: f(p, verbose=False)      # noqa: E731  (a plain callable: per-patch path)
     G, index = dnp_util.divide_pc_to_graph(pc, n_part=int(g[f"{tag}_n_part"]), min_patch=int(g[f"{tag}_min_patch"]),
                                            edge_calculator=field_utils.field_edge_calculator,
                                            point_estimator=estimator)
@@ -35,6 +37,8 @@ def test_divide_pc_to_graph_matches_reference(golden, dev, tag):
     assert np.array_equal(np.isnan(got), np.isnan(want))
     assert np.array_equal(np.nan_to_num(got[:, 3:]), np.nan_to_num(want[:, 3:]))
     assert np.allclose(np.nan_to_num(got[:, :3]), np.nan_to_num(want[:, :3]), rtol=0, atol=1e-6)
+    if batched:
+        return
     # edges and scores
     assert G.V == list(range(len(index)))
     assert np.array_equal(np.array([[e.u, e.v] for e in G.E]), g[f"{tag}_graph_edges"])
@@ -93,3 +97,36 @@ def test_server_api_orients_a_sphere(dev):
     assert np.abs(np.abs(radial) - 1).max() < 0.05               # PCA normals of a sphere are radial
     assert abs(np.sign(radial).mean()) > 0.999                   # and all point the same way
     assert graph_dipole.graph_dipole_server_api(xyz, {"max_nn": 16, "divide_method": "nope"}) is None
+
+
+def test_batched_patch_orientation_equals_per_patch_calls(dev):
+    """dnp_points_propagate_batched_f32 / dnp_patch_lattice_sign_f32 against the single-cloud entry points on the
+    same patches: identical normals (same device code), lattice means within FP32 noise, same flips."""
+    import dnp_native
+    import field_utils
+    g = torch.Generator().manual_seed(77)
+    sizes = [1, 2, 37, 512, 1500, 3000, 64, 900]
+    parts = []
+    for k, n in enumerate(sizes):
+        d = torch.randn(n, 3, generator=g)
+        d = d / d.norm(dim=-1, keepdim=True)
+        pc = torch.cat([d * 0.4 + 0.01 * torch.randn(n, 3, generator=g), d], 1).float()
+        pc[torch.rand(n, generator=g) < 0.5, 3:] *= -1
+        parts.append(pc)
+    work = torch.cat(parts).to(dev)
+    offsets = torch.tensor(np.concatenate([[0], np.cumsum(sizes)]), dtype=torch.int64, device=dev)
+    single = [p.clone().to(dev) for p in parts]
+    for p in single:
+        field_utils.strongest_field_propagation_points(p, diffuse=True, starting_point=0)
+    dnp_native.points_propagate_batched(work, offsets, max(sizes), diffuse=True, eps=1e-6)
+    assert torch.equal(work, torch.cat(single))
+    means = dnp_native.patch_lattice_sign(work.clone(), offsets, 10, flip=False).cpu().numpy()
+    want = np.array([field_utils.measure_mean_potential(p).item() for p in single])
+    assert np.allclose(means, want, rtol=1e-4, atol=1e-5 * np.abs(want).max())
+    flipped = work.clone()
+    dnp_native.patch_lattice_sign(flipped, offsets, 10, flip=True)
+    for k in range(len(sizes)):
+        lo, hi = int(offsets[k]), int(offsets[k + 1])
+        sign = -1.0 if want[k] < 0 else 1.0
+        assert torch.equal(flipped[lo:hi, 3:], work[lo:hi, 3:] * sign)
+        assert torch.equal(flipped[lo:hi, :3], work[lo:hi, :3])
