@@ -52,17 +52,6 @@ __device__ __forceinline__ void big_mul_small(Big& a, uint32_t m) {
         carry = t >> 32;
     }
 }
-// a = floor(a / m), returns the remainder
-__device__ __forceinline__ uint32_t big_div_small(Big& a, uint32_t m) {
-    unsigned long long rem = 0;
-#pragma unroll
-    for (int i = kLimbs - 1; i >= 0; --i) {
-        const unsigned long long t = (rem << 32) | a.d[i];
-        a.d[i] = (uint32_t)(t / m);
-        rem = t % m;
-    }
-    return (uint32_t)rem;
-}
 __device__ __forceinline__ void big_mul_pow10(Big& a, int k) {
     for (; k >= 9; k -= 9) big_mul_small(a, 1000000000u);
     uint32_t m = 1;
@@ -96,14 +85,46 @@ __device__ __forceinline__ void big_add(Big& a, const Big& b) {
         carry = t >> 32;
     }
 }
-__device__ __forceinline__ void big_sub(Big& a, const Big& b) {   // a >= b
-    long long borrow = 0;
-#pragma unroll
-    for (int i = 0; i < kLimbs; ++i) {
-        long long t = (long long)a.d[i] - b.d[i] - borrow;
-        borrow = t < 0;
-        if (t < 0) t += (1ll << 32);
+// The same operations on the low `nl` limbs only (the callers know how wide their numbers are): the digit loops
+// run on 3-6 limbs for ordinary values instead of 16.
+__device__ __forceinline__ void big_mul_small_n(Big& a, uint32_t m, int nl) {
+    unsigned long long carry = 0;
+    for (int i = 0; i < nl; ++i) {
+        const unsigned long long t = (unsigned long long)a.d[i] * m + carry;
         a.d[i] = (uint32_t)t;
+        carry = t >> 32;
+    }
+}
+__device__ __forceinline__ bool big_div_1e9_n(Big& a, int nl) {    // a = floor(a / 10^9); true if a remainder is left
+    unsigned long long rem = 0;
+    for (int i = nl - 1; i >= 0; --i) {
+        const unsigned long long t = (rem << 32) | a.d[i];
+        const unsigned long long q = t / 1000000000ull;           // constant divisor: multiply-high, no division loop
+        a.d[i] = (uint32_t)q;
+        rem = t - q * 1000000000ull;
+    }
+    return rem != 0;
+}
+__device__ __forceinline__ int big_cmp_n(const Big& a, const Big& b, int nl) {
+    for (int i = nl - 1; i >= 0; --i) {
+        if (a.d[i] != b.d[i]) return a.d[i] > b.d[i] ? 1 : -1;
+    }
+    return 0;
+}
+__device__ __forceinline__ void big_add_n(Big& a, const Big& b, int nl) {
+    unsigned long long carry = 0;
+    for (int i = 0; i < nl; ++i) {
+        const unsigned long long t = (unsigned long long)a.d[i] + b.d[i] + carry;
+        a.d[i] = (uint32_t)t;
+        carry = t >> 32;
+    }
+}
+__device__ __forceinline__ void big_sub_n(Big& a, const Big& b, int nl) {   // a >= b
+    unsigned int borrow = 0;
+    for (int i = 0; i < nl; ++i) {
+        const unsigned long long t = (unsigned long long)a.d[i] - b.d[i] - borrow;
+        a.d[i] = (uint32_t)t;
+        borrow = (unsigned int)(t >> 63);
     }
 }
 __device__ __forceinline__ int big_top_bit(const Big& a) {        // index of the highest set bit, -1 for zero
@@ -149,21 +170,32 @@ __device__ double big_round_to_double(const Big& a, int exp2, bool sticky) {
 constexpr int kMaxPow10 = 60;      // w * 10^q, q in [-kMinPow10, kMaxPow10], w < 10^38 < 2^127: fits 512 bits
 constexpr int kMinPow10 = 76;
 
+__constant__ double kPow10[23] = {1e0,  1e1,  1e2,  1e3,  1e4,  1e5,  1e6,  1e7,  1e8,  1e9,  1e10, 1e11,
+                                  1e12, 1e13, 1e14, 1e15, 1e16, 1e17, 1e18, 1e19, 1e20, 1e21, 1e22};
+
 __device__ double dec_to_double(Big a, int q) {
     if (q >= 0) {
         big_mul_pow10(a, q);
         return big_round_to_double(a, 0, false);
     }
+    // w / 10^n = (w * 10^pad) / 10^(n + pad): every division is by the constant 10^9
     const int n = -q;
+    const int pad = (9 - n % 9) % 9;
+    big_mul_pow10(a, pad);
     const int s = 32 * ((57 + (n * 3402) / 1024 + 1 + 31) / 32);   // quotient keeps >= 56 significant bits
     big_shl(a, s);
+    const int nl = min(kLimbs, big_top_bit(a) / 32 + 1);
     bool sticky = false;
-    int k = n;
-    for (; k >= 9; k -= 9) sticky |= big_div_small(a, 1000000000u) != 0;
-    uint32_t m = 1;
-    for (int i = 0; i < k; ++i) m *= 10u;
-    if (m > 1) sticky |= big_div_small(a, m) != 0;
+    for (int k = n + pad; k > 0; k -= 9) sticky |= big_div_1e9_n(a, nl);
     return big_round_to_double(a, -s, sticky);
+}
+
+// w < 2^53 and |q| <= 22: both operands are exact doubles, one IEEE multiply / divide is correctly rounded
+__device__ __forceinline__ bool dec_fast_path(unsigned long long w, int q, double& out) {
+    if (w >> 53) return false;
+    if (q >= 0 && q <= 22) { out = __dmul_rn((double)w, kPow10[q]); return true; }
+    if (q < 0 && q >= -22) { out = __ddiv_rn((double)w, kPow10[-q]); return true; }
+    return false;
 }
 
 __device__ __forceinline__ bool is_py_space(unsigned char c) {     // str.strip() / float() whitespace, ASCII part
@@ -248,6 +280,11 @@ __device__ bool parse_float_token(const char* s, int len, double& out) {
     }
     const int q = ex + int_extra - frac_shift;
     if (q > kMaxPow10 || q < -kMinPow10) return false;
+    double fast;
+    if (nd <= 19 && !trunc && dec_fast_path(w, q, fast)) {
+        out = neg ? -fast : fast;
+        return true;
+    }
     Big a;
     big_set64(a, w);
     if (nd > 19) {
@@ -393,21 +430,23 @@ __device__ int shortest_digits(double v, unsigned char* digits, int& decpt) {
         }
     }
     decpt = k;
+    // from here on r < 10 s and m+, m- <= 10 s: everything fits in the limbs of s plus one
+    const int nl = min(kLimbs, big_top_bit(s) / 32 + 2);
     int nd = 0;
     while (true) {
         int d = 0;
-        while (big_cmp(r, s) >= 0) { big_sub(r, s); ++d; }      // quotient < 10
-        const int c1 = big_cmp(r, mm);
+        while (big_cmp_n(r, s, nl) >= 0) { big_sub_n(r, s, nl); ++d; }      // quotient < 10
+        const int c1 = big_cmp_n(r, mm, nl);
         const bool tc1 = even ? c1 <= 0 : c1 < 0;
         Big high = r;
-        big_add(high, mp);
-        const int c2 = big_cmp(high, s);
+        big_add_n(high, mp, nl);
+        const int c2 = big_cmp_n(high, s, nl);
         const bool tc2 = even ? c2 >= 0 : c2 > 0;
         if (!tc1 && !tc2 && nd < 24) {
             digits[nd++] = (unsigned char)d;
-            big_mul_small(r, 10u);
-            big_mul_small(mp, 10u);
-            big_mul_small(mm, 10u);
+            big_mul_small_n(r, 10u, nl);
+            big_mul_small_n(mp, 10u, nl);
+            big_mul_small_n(mm, 10u, nl);
             continue;
         }
         bool up;
@@ -415,8 +454,8 @@ __device__ int shortest_digits(double v, unsigned char* digits, int& decpt) {
         else if (!tc1 && tc2) up = true;
         else {                                                  // both: the digit closer to v, ties to even (dtoa)
             Big twice = r;
-            big_add(twice, r);
-            const int c = big_cmp(twice, s);
+            big_add_n(twice, r, nl);
+            const int c = big_cmp_n(twice, s, nl);
             up = c > 0 || (c == 0 && (d & 1));
         }
         digits[nd++] = (unsigned char)(d + (up ? 1 : 0));
