@@ -457,7 +457,7 @@ def extras(dn, field_utils, dev, src, tgt):
     out["xyz_parse_1M_pts_ms"] = best_ms(lambda: _parse_only(dn, txt_dev, lines), 2)
     out["xyz_parse_text_gbs"] = len(text) / out["xyz_parse_1M_pts_ms"] / 1e6
     out["xyz_round_trip_bit_exact"] = bool(torch.equal(back.view(torch.int32), rows.view(torch.int32)))
-    out["xyz_reference_cpu"] = "util.xyz2tensor / export_pc are per-line Python loops: 1.2 us per value parsed, 1.5 us per value written on the build container (tools/io_probe.py), i.e. 7 s + 9 s for 1M points"
+    out["xyz_reference_cpu"] = "util.xyz2tensor / export_pc are per-line Python loops: 1.2 us per value parsed, 1.5 us per value written on the build container (tests/test_io.py::test_reference_style_loops_rate), i.e. 7 s + 9 s for 1M points"
     return out
 
 

@@ -9,8 +9,10 @@
 //   * n <= exact_max_n (<= 40): exhaustive.  One spin is pinned (global flip symmetry); a thread owns one
 //     pattern of the high spins and walks the 2^10 states of the 10 low spins in Gray-code order, fully
 //     unrolled: the flipped bit, its new sign and the state of all lower bits at that moment are compile-time
-//     constants, so a state costs one FADD for the energy, ~1 amortised FADD for the local fields and three
-//     instructions to track the maximum.  FP32-pipe bound integer-free walk; 2^35 states in ~5 ms.
+//     constants, so a state costs one FADD for the energy, ~1 amortised FADD for the local fields and one FMNMX
+//     for the running maximum; the position of the maximum is recovered afterwards by walking the winning
+//     patterns once more (flip_resolve_kernel).  Runs of up to 64 high patterns are themselves visited in Gray
+//     order with incremental updates.  Issue-bound, memory-free walk.
 //   * larger n: simulated annealing, one warp per replica (spins and local fields in shared memory, exact
 //     sequential Metropolis order inside a warp: the 32 lanes test 32 spins at once and the first accepted
 //     one is applied before the rest are re-tested), then a zero-temperature descent.  Counter-based hash
@@ -96,8 +98,9 @@ __global__ void __launch_bounds__(1024) flip_prepare_kernel(const double* __rest
 
 // ------------------------------------------------------------------ exhaustive walk
 // One Gray-code step: T is a template parameter, so the flipped bit, its new sign and the loop bounds are
-// compile-time constants and D / J4 stay in registers.
-template <int T>
+// compile-time constants and D / J4 stay in registers.  kTrack = false keeps only the running maximum (one FMNMX
+// on the ALU pipe): the search pass; kTrack = true also remembers where it was: the resolve pass.
+template <int T, bool kTrack>
 __device__ __forceinline__ void gray_step(float& E, float (&D)[kLow], const float (&J4)[kLow][kLow], float& tb,
                                           int& tbest) {
     constexpr int b = ctz_const(T);
@@ -106,40 +109,38 @@ __device__ __forceinline__ void gray_step(float& E, float (&D)[kLow], const floa
     E = minus ? E - D[b] : E + D[b];
 #pragma unroll
     for (int c2 = 0; c2 < b; ++c2) D[c2] = minus ? D[c2] - J4[c2][b] : D[c2] + J4[c2][b];
-    if (E > tb) { tb = E; tbest = T; }
+    if (kTrack) {
+        if (E > tb) { tb = E; tbest = T; }
+    } else {
+        tb = fmaxf(tb, E);
+    }
 }
-template <int LO, int HI>
+template <int LO, int HI, bool kTrack>
 __device__ __forceinline__ void gray_walk(float& E, float (&D)[kLow], const float (&J4)[kLow][kLow], float& tb,
                                           int& tbest) {
     if constexpr (HI - LO == 1) {
-        gray_step<LO>(E, D, J4, tb, tbest);
+        gray_step<LO, kTrack>(E, D, J4, tb, tbest);
     } else {
         constexpr int MID = (LO + HI) / 2;
-        gray_walk<LO, MID>(E, D, J4, tb, tbest);
-        gray_walk<MID, HI>(E, D, J4, tb, tbest);
+        gray_walk<LO, MID, kTrack>(E, D, J4, tb, tbest);
+        gray_walk<MID, HI, kTrack>(E, D, J4, tb, tbest);
     }
 }
 
 // Spin layout: low bit b <-> spin b (b < kLow), high bit k <-> spin kLow + k, spin np-1 pinned to +1.
-// Candidate per CTA: (float energy without C0, 64-bit state, bit i = x_i).
-__global__ void __launch_bounds__(256) flip_exhaustive_kernel(const float* __restrict__ Jg, int np, int high_bits,
-                                                              float* __restrict__ cand_e,
-                                                              unsigned long long* __restrict__ cand_s) {
-    extern __shared__ float Js[];                            // [np][np]
-    for (int i = threadIdx.x; i < np * np; i += blockDim.x) Js[i] = Jg[i];
-    __syncthreads();
+struct LowTables {
+    float J4[kLow][kLow];      // 4 J among the low spins
+    float d_static[kLow];      // static part of the doubled local field of bit b at the moment it flips
+    float e_low;               // sum_{b<c} J_bc with every low spin +1
+};
 
-    // couplings among the low spins, pre-scaled: a flip changes the doubled local field of a lower bit by 4 J
-    float J4[kLow][kLow];
+__device__ __forceinline__ void low_tables(const float* Js, int np, LowTables& t) {
 #pragma unroll
     for (int a = 0; a < kLow; ++a)
 #pragma unroll
-        for (int b = 0; b < kLow; ++b) J4[a][b] = 4.f * Js[a * np + b];
-
-    // static part of the doubled local field of bit b at the moment it flips: all lower bits are +1
-    // except bit b-1 (Gray code), all higher low bits start at +1
-    float d_static[kLow];
-    float e_low = 0.f;
+        for (int b = 0; b < kLow; ++b) t.J4[a][b] = 4.f * Js[a * np + b];
+    // when bit b flips, all lower bits are +1 except bit b-1 (Gray code); all higher low bits start at +1
+    t.e_low = 0.f;
 #pragma unroll
     for (int b = 0; b < kLow; ++b) {
         float lo = 0.f, hi = 0.f;
@@ -148,62 +149,123 @@ __global__ void __launch_bounds__(256) flip_exhaustive_kernel(const float* __res
             if (c < b) lo += (c == b - 1) ? -Js[b * np + c] : Js[b * np + c];
             if (c > b) hi += Js[b * np + c];
         }
-        d_static[b] = 2.f * (lo + hi);
-        e_low += hi;                                          // sum_{b<c} J_bc with every low spin +1
+        t.d_static[b] = 2.f * (lo + hi);
+        t.e_low += hi;
     }
+}
+
+// energy among the high spins (+ the pinned one) and their field on every low spin, from scratch
+__device__ __forceinline__ void high_setup(const float* Js, int np, int high_bits, unsigned long long hp, float& c,
+                                           float (&g)[kLow]) {
+    c = 0.f;
+#pragma unroll
+    for (int b = 0; b < kLow; ++b) g[b] = Js[b * np + (np - 1)];
+    for (int k = 0; k < high_bits; ++k) {
+        const float sk = ((hp >> k) & 1ull) ? -1.f : 1.f;
+        const float* row = Js + (kLow + k) * np;
+        float acc = row[np - 1];                              // pinned spin
+        for (int m = k + 1; m < high_bits; ++m) acc += ((hp >> m) & 1ull) ? -row[kLow + m] : row[kLow + m];
+        c = fmaf(sk, acc, c);
+#pragma unroll
+        for (int b = 0; b < kLow; ++b) g[b] = fmaf(sk, row[b], g[b]);
+    }
+}
+
+// the 2^kLow states of the low spins under one high pattern: maximum (and, with kTrack, its Gray index)
+template <bool kTrack>
+__device__ __forceinline__ float walk_low(const LowTables& t, float c, const float (&g)[kLow], int& tbest) {
+    float D[kLow];
+    float E = c + t.e_low;
+#pragma unroll
+    for (int b = 0; b < kLow; ++b) {
+        E += g[b];
+        D[b] = fmaf(2.f, g[b], t.d_static[b]);
+    }
+    float tb = E;
+    tbest = 0;
+    gray_walk<1, kLowStates, kTrack>(E, D, t.J4, tb, tbest);
+    return tb;
+}
+
+// Search pass.  A thread takes runs of 2^mid_bits consecutive high patterns and walks them in Gray order too: one
+// high spin changes between neighbours, so c and g are updated in O(high_bits) instead of rebuilt in O(high_bits^2).
+// Per CTA: the best energy (without C0) and the HIGH pattern that reached it.
+__global__ void __launch_bounds__(256) flip_exhaustive_kernel(const float* __restrict__ Jg, int np, int high_bits,
+                                                              int mid_bits, float* __restrict__ cand_e,
+                                                              unsigned long long* __restrict__ cand_s) {
+    extern __shared__ float Js[];                            // [np][np]
+    for (int i = threadIdx.x; i < np * np; i += blockDim.x) Js[i] = Jg[i];
+    __syncthreads();
+    LowTables t;
+    low_tables(Js, np, t);
 
     float best = -INFINITY;
-    unsigned long long best_state = 0;
-    const unsigned long long patterns = 1ull << high_bits;
-    for (unsigned long long hp = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; hp < patterns;
-         hp += (unsigned long long)gridDim.x * blockDim.x) {
-        // energy among the high spins (+ the pinned one) and their field on every low spin
-        float c = 0.f;
-        float g[kLow];
+    unsigned long long best_hp = 0;
+    const unsigned long long runs = 1ull << (high_bits - mid_bits);
+    const int per_run = 1 << mid_bits;
+    for (unsigned long long run = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; run < runs;
+         run += (unsigned long long)gridDim.x * blockDim.x) {
+        unsigned long long hp = run << mid_bits;
+        float c, g[kLow];
+        high_setup(Js, np, high_bits, hp, c, g);
+#pragma unroll 1
+        for (int j = 0; j < per_run; ++j) {
+            if (j > 0) {
+                const int k = __ffs(j) - 1;                    // Gray code: bit k of the pattern flips
+                hp ^= 1ull << k;
+                const float two_s = ((hp >> k) & 1ull) ? -2.f : 2.f;
+                const float* row = Js + (kLow + k) * np;
+                float hh = row[np - 1];
+                for (int m = 0; m < high_bits; ++m)
+                    if (m != k) hh += ((hp >> m) & 1ull) ? -row[kLow + m] : row[kLow + m];
+                c = fmaf(two_s, hh, c);
 #pragma unroll
-        for (int b = 0; b < kLow; ++b) g[b] = Js[b * np + (np - 1)];
-        for (int k = 0; k < high_bits; ++k) {
-            const float sk = ((hp >> k) & 1ull) ? -1.f : 1.f;
-            const float* row = Js + (kLow + k) * np;
-            float acc = row[np - 1];                          // pinned spin
-            for (int m = k + 1; m < high_bits; ++m) acc += ((hp >> m) & 1ull) ? -row[kLow + m] : row[kLow + m];
-            c = fmaf(sk, acc, c);
-#pragma unroll
-            for (int b = 0; b < kLow; ++b) g[b] = fmaf(sk, row[b], g[b]);
-        }
-        float D[kLow];
-        float E = c + e_low;
-#pragma unroll
-        for (int b = 0; b < kLow; ++b) {
-            E += g[b];
-            D[b] = fmaf(2.f, g[b], d_static[b]);
-        }
-        float tb = E;
-        int tbest = 0;
-        gray_walk<1, kLowStates>(E, D, J4, tb, tbest);
-        if (tb > best) {
-            best = tb;
-            best_state = (hp << kLow) | (unsigned long long)(tbest ^ (tbest >> 1));
+                for (int b = 0; b < kLow; ++b) g[b] = fmaf(two_s, row[b], g[b]);
+            }
+            int tbest;
+            const float tb = walk_low<false>(t, c, g, tbest);
+            if (tb > best) { best = tb; best_hp = hp; }
         }
     }
-    // CTA maximum, ties -> smaller state code
+    // CTA maximum, ties -> smaller pattern
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
         const float oe = __shfl_xor_sync(0xffffffffu, best, o);
-        const unsigned long long os = __shfl_xor_sync(0xffffffffu, best_state, o);
-        if (oe > best || (oe == best && os < best_state)) { best = oe; best_state = os; }
+        const unsigned long long os = __shfl_xor_sync(0xffffffffu, best_hp, o);
+        if (oe > best || (oe == best && os < best_hp)) { best = oe; best_hp = os; }
     }
     __shared__ float sh_e[8];
     __shared__ unsigned long long sh_s[8];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    if (lane == 0) { sh_e[warp] = best; sh_s[warp] = best_state; }
+    if (lane == 0) { sh_e[warp] = best; sh_s[warp] = best_hp; }
     __syncthreads();
     if (threadIdx.x == 0) {
         for (int w = 1; w < (int)(blockDim.x >> 5); ++w)
-            if (sh_e[w] > best || (sh_e[w] == best && sh_s[w] < best_state)) { best = sh_e[w]; best_state = sh_s[w]; }
+            if (sh_e[w] > best || (sh_e[w] == best && sh_s[w] < best_hp)) { best = sh_e[w]; best_hp = sh_s[w]; }
         cand_e[blockIdx.x] = best;
-        cand_s[blockIdx.x] = best_state;
+        cand_s[blockIdx.x] = best_hp;
     }
+}
+
+// Resolve pass: one thread per CTA candidate walks its pattern again, this time remembering the best low state,
+// and replaces the pattern by the full 64-bit state (bit i = x_i).
+__global__ void __launch_bounds__(64) flip_resolve_kernel(const float* __restrict__ Jg, int np, int high_bits,
+                                                          int n_cand, float* __restrict__ cand_e,
+                                                          unsigned long long* __restrict__ cand_s) {
+    extern __shared__ float Js[];
+    for (int i = threadIdx.x; i < np * np; i += blockDim.x) Js[i] = Jg[i];
+    __syncthreads();
+    const int cnd = blockIdx.x * blockDim.x + threadIdx.x;
+    if (cnd >= n_cand) return;
+    LowTables t;
+    low_tables(Js, np, t);
+    const unsigned long long hp = cand_s[cnd];
+    float c, g[kLow];
+    high_setup(Js, np, high_bits, hp, c, g);
+    int tbest;
+    const float tb = walk_low<true>(t, c, g, tbest);
+    cand_e[cnd] = tb;
+    cand_s[cnd] = (hp << kLow) | (unsigned long long)(tbest ^ (tbest >> 1));
 }
 
 // ------------------------------------------------------------------ spanning-forest orientation
@@ -441,7 +503,7 @@ __global__ void __launch_bounds__(kTopK * 32) flip_select_kernel(const double* _
 inline size_t up256(size_t v) { return (v + 255) & ~(size_t)255; }
 
 struct FlipLayout {
-    int np, words, n_cand, blocks;
+    int np, words, n_cand, blocks, mid_bits;
     bool exhaustive;
     size_t J, info, scale, tree, cand_e, cand_s, total;
 };
@@ -453,7 +515,9 @@ FlipLayout flip_layout(int64_t n, int exact_max_n, int replicas) {
     if (L.exhaustive) {
         L.np = (int)(n < kExactMin ? kExactMin : n);
         const int high_bits = L.np - 1 - kLow;
-        const unsigned long long patterns = 1ull << high_bits;
+        // runs of 2^mid_bits patterns per thread visit, sized so that the grid still gets >= 2^22 runs to balance
+        L.mid_bits = high_bits - 22 < 0 ? 0 : (high_bits - 22 > 6 ? 6 : high_bits - 22);
+        const unsigned long long patterns = 1ull << (high_bits - L.mid_bits);
         unsigned long long blocks = (patterns + 255) / 256;
         if (blocks > 148ull * 8) blocks = 148ull * 8;
         L.blocks = (int)blocks;
@@ -508,8 +572,11 @@ int run_flip_solve(const double* A, const double* B, int64_t n, int64_t ld, int 
     flip_prepare_kernel<<<1, 1024, 0, stream>>>(A, B, (int)n, ld, L.np, J, info, scale);
     if (L.exhaustive) {
         const size_t smem = (size_t)L.np * L.np * sizeof(float);
-        flip_exhaustive_kernel<<<L.blocks, 256, smem, stream>>>(J, L.np, L.np - 1 - kLow, cand_e,
-                                                                reinterpret_cast<unsigned long long*>(cand_s));
+        unsigned long long* cand_s64 = reinterpret_cast<unsigned long long*>(cand_s);
+        flip_exhaustive_kernel<<<L.blocks, 256, smem, stream>>>(J, L.np, L.np - 1 - kLow, L.mid_bits, cand_e, cand_s64);
+        flip_resolve_kernel<<<(L.n_cand + 63) / 64, 64, smem, stream>>>(J, L.np, L.np - 1 - kLow, L.n_cand, cand_e,
+                                                                        cand_s64);
+        count_launch(1);
     } else {
         signed char* s_tree = reinterpret_cast<signed char*>(ws + L.tree);
         flip_tree_kernel<<<1, 1024, (size_t)L.np * 5, stream>>>(J, (int)n, L.np, s_tree);

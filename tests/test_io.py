@@ -28,3 +28,20 @@ def test_export_then_parse_round_trips(golden, orc):
     keep = np.isfinite(pc).all(axis=1)
     back = orc.xyz2tensor(orc.export_text(pc[keep]))
     assert np.array_equal(back.view(np.uint32), pc[keep].view(np.uint32))
+
+
+def test_reference_style_loops_rate(orc, capsys):
+    """Not a speed assertion: records what the reference's per-line Python loops cost on this host (the figure
+    DESIGN.md section 3.11 quotes next to the kernels)."""
+    import time
+    rng = np.random.default_rng(0)
+    pc = rng.normal(size=(20000, 6)).astype(np.float32)
+    t0 = time.perf_counter()
+    txt = orc.export_text(pc)
+    t1 = time.perf_counter()
+    back = orc.xyz2tensor(txt)
+    t2 = time.perf_counter()
+    assert np.array_equal(back, pc)
+    with capsys.disabled():
+        print(f"\n[reference-style text IO on this host] export {1e6 * (t1 - t0) / pc.size:.2f} us/value, "
+              f"parse {1e6 * (t2 - t1) / pc.size:.2f} us/value, {len(txt) / pc.size:.1f} bytes/value")

@@ -14,3 +14,16 @@ ncu --set full --clock-control none --import-source on -k regex:cpairs_kernel -s
     python bench.py --steps 1 --warmup 3 --no-cpu-baseline --no-extras > $OUT/ncu_full.log 2>&1
 echo "full capture rc=$?"
 ls -la $OUT
+# ---- this round's additional kernels: flip solve (exhaustive walk at 36 patches), text IO (parse / format at 1M points)
+python tools/flip_probe.py > $OUT/flip_probe.json 2> $OUT/flip_probe.err || { echo "flip probe failed"; tail -5 $OUT/flip_probe.err; }
+ncu --set full --clock-control none --import-source on -k regex:flip_exhaustive_kernel -s 18 -c 1 -o $OUT/flip_full -f \
+    python tools/flip_probe.py > $OUT/ncu_flip.log 2>&1
+echo "flip capture rc=$?"
+python tools/io_gpu_probe.py > $OUT/io_probe.json 2> $OUT/io_probe.err || { echo "io probe failed"; tail -5 $OUT/io_probe.err; }
+ncu --set full --clock-control none --import-source on -k regex:parse_lines_kernel -s 2 -c 1 -o $OUT/parse_full -f \
+    python tools/io_gpu_probe.py > $OUT/ncu_parse.log 2>&1
+echo "parse capture rc=$?"
+ncu --set full --clock-control none --import-source on -k regex:format_values_kernel -s 2 -c 1 -o $OUT/format_full -f \
+    python tools/io_gpu_probe.py > $OUT/ncu_format.log 2>&1
+echo "format capture rc=$?"
+ls -la $OUT

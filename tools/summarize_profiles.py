@@ -79,6 +79,25 @@ def full():
     return got
 
 
+def extra(rep_name, out_name, note):
+    """Selected raw-page metrics of one additional `--set full` capture (same metric list)."""
+    rep = os.path.join(OUT, rep_name)
+    if not os.path.exists(rep):
+        print("missing", rep)
+        return
+    txt = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+    rows = list(csv.reader(txt.splitlines()))
+    hdr, units, val = rows[0], rows[1], rows[2]
+    path = os.path.join(PROF, f"{tag}_{out_name}_ncu_full.txt")
+    with open(path, "w") as f:
+        f.write(f"# {note}   (raw page, selected metrics)\n")
+        f.write(f"kernel\t\t{val[hdr.index('Kernel Name')]}\n")
+        for h, u, v in sorted(zip(hdr, units, val)):
+            if KEEP.match(h) or h.startswith("smsp__inst_executed_op") or h in ("l1tex__t_bytes.sum", "lts__t_bytes.sum"):
+                f.write(f"{h}\t{u}\t{v}\n")
+    print("wrote", path)
+
+
 def to_bytes(u, v):
     return float(v.replace(",", "")) * {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}[u]
 
@@ -98,3 +117,14 @@ if __name__ == "__main__":
         "source": f"profiles/{tag}_cpairs_kernel_ncu_full.txt (ncu --set full, one launch = 896 sources x {pts} targets)"}
     json.dump(t, open(tpath, "w"), indent=1)
     print("wrote", tpath)
+    extra("flip_full.ncu-rep", "flip_exhaustive_kernel",
+          "ncu --set full --clock-control none --import-source on -k regex:flip_exhaustive_kernel -s 18 -c 1 python tools/flip_probe.py  (36 patches, 2^35 states)")
+    extra("parse_full.ncu-rep", "parse_lines_kernel",
+          "ncu --set full --clock-control none --import-source on -k regex:parse_lines_kernel -s 2 -c 1 python tools/io_gpu_probe.py  (1M points, 124 MB of text)")
+    extra("format_full.ncu-rep", "format_values_kernel",
+          "ncu --set full --clock-control none --import-source on -k regex:format_values_kernel -s 2 -c 1 python tools/io_gpu_probe.py  (1M points x 6 values)")
+    for name in ("bench.json", "flip_probe.json", "io_probe.json"):
+        src = os.path.join(OUT, name)
+        if os.path.exists(src):
+            open(os.path.join(PROF, f"{tag}_{name}"), "w").write(open(src).read())
+            print("copied", name)
