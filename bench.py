@@ -93,7 +93,7 @@ class ClockSampler:
         if not mhz:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
         mhz.sort()
-        return {"sm_mhz": mhz[len(mhz) // 2], "sm_max_mhz": max(mx), "reasons": sorted(reasons),
+        return {"sm_mhz": mhz[len(mhz) // 2], "sm_min_mhz": mhz[0], "sm_max_mhz": max(mx), "reasons": sorted(reasons),
                 "samples": len(mhz), "power_w_max": max(power)}
 
 
@@ -247,14 +247,15 @@ def main():
 
     e2e_step()
     barrier()
-    t0 = time.perf_counter()
-    e2e_calls = []
-    for _ in range(args.steps):
-        t1 = time.perf_counter()
-        out_host = e2e_step()
-        e2e_calls.append((time.perf_counter() - t1) * 1e3)
-    barrier()
-    e2e_s = time.perf_counter() - t0
+    with ClockSampler(local_rank) as e2e_clocks:
+        t0 = time.perf_counter()
+        e2e_calls = []
+        for _ in range(args.steps):
+            t1 = time.perf_counter()
+            out_host = e2e_step()
+            e2e_calls.append((time.perf_counter() - t1) * 1e3)
+        barrier()
+        e2e_s = time.perf_counter() - t0
     if os.environ.get("DNP_BENCH_DEBUG"):
         print("e2e per call ms:", ["%.1f" % v for v in e2e_calls], file=sys.stderr)
     assert not out_host.is_cuda and out_host.shape == (P, 3)
@@ -279,6 +280,7 @@ def main():
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": workload_config(args, world),
             "e2e": {"value": world * pairs_per_step * args.steps / (e2e_ms * 1e-3), "unit": UNIT,
+                    "ms_per_call": [round(v, 1) for v in e2e_calls], "clocks": e2e_clocks.summary(),
                     "h2d_bytes_per_step": int(src_host.numel() * 4 + tgt_host.numel() * 4),
                     "d2h_bytes_per_step": int(P * 3 * 4),
                     "api": "field_utils.field_grad(host float32 tensors) -> dnp_field_grad_host_f32"},

@@ -195,6 +195,49 @@ struct DeviceGuard {
     }
 };
 
+// Per-host-thread scratch of the host-buffer entry points (released when the thread exits).
+struct HostScratch {
+    int device = -1;
+    cudaStream_t stream = nullptr;
+    unsigned char* dev = nullptr;
+    size_t dev_cap = 0;
+    unsigned char* pin = nullptr;
+    size_t pin_cap = 0;
+
+    void release() {
+        if (dev) cudaFree(dev);
+        if (pin) cudaFreeHost(pin);
+        if (stream) cudaStreamDestroy(stream);
+        dev = nullptr; pin = nullptr; stream = nullptr;
+        dev_cap = pin_cap = 0;
+        device = -1;
+    }
+    ~HostScratch() { release(); }
+
+    cudaError_t prepare(int d, size_t dev_bytes, size_t pin_bytes) {
+        cudaError_t e;
+        if (device != d) {
+            release();
+            if ((e = cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking)) != cudaSuccess) return e;
+            device = d;
+        }
+        if (dev_bytes > dev_cap) {
+            if (dev) cudaFree(dev);
+            dev = nullptr; dev_cap = 0;
+            if ((e = cudaMalloc(reinterpret_cast<void**>(&dev), dev_bytes)) != cudaSuccess) return e;
+            dev_cap = dev_bytes;
+        }
+        if (pin_bytes > pin_cap) {
+            if (pin) cudaFreeHost(pin);
+            pin = nullptr; pin_cap = 0;
+            if ((e = cudaMallocHost(reinterpret_cast<void**>(&pin), pin_bytes)) != cudaSuccess) return e;
+            pin_cap = pin_bytes;
+        }
+        return cudaSuccess;
+    }
+};
+thread_local HostScratch t_host;
+
 // copies a strided [rows, cols] host matrix into a dense device matrix
 cudaError_t upload_rows(float* dst, const float* src_host, int64_t rows, int64_t cols, int64_t ld,
                         cudaStream_t stream) {
@@ -225,14 +268,16 @@ int host_pairs(bool potential, const float* src_host, int64_t S, int64_t ld_s, c
     const bool trace = getenv("DNP_HOST_TRACE") != nullptr;
     auto now = [] { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
     const double t_0 = now();
-    cudaStream_t stream;
-    DNP_CHECK_CUDA(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
-    unsigned char* base = nullptr;
+    // per-thread stream, device arena and pinned result buffer, kept between calls: a call then consists of
+    // copies and launches only (no allocation, no stream creation -- both take driver-wide locks and made the
+    // end-to-end time sensitive to anything else that talks to the driver, e.g. a monitoring nvidia-smi)
     const size_t a256 = 256;
     auto up = [&](size_t v) { return (v + a256 - 1) / a256 * a256; };
     const size_t total = up(src_bytes) + up(tgt_bytes) + up(out_bytes) + ws_bytes;
-    cudaError_t e = cudaMallocAsync(reinterpret_cast<void**>(&base), total, stream);
-    if (e != cudaSuccess) { cudaStreamDestroy(stream); return cuda_fail(e, "cudaMallocAsync"); }
+    cudaError_t e = t_host.prepare(device, total, out_bytes);
+    if (e != cudaSuccess) return cuda_fail(e, "host scratch");
+    cudaStream_t stream = t_host.stream;
+    unsigned char* base = t_host.dev;
     const double t_alloc = now();
     double t_up = 0, t_launch = 0, t_dl = 0;
     float* d_src = reinterpret_cast<float*>(base);
@@ -254,15 +299,15 @@ int host_pairs(bool potential, const float* src_host, int64_t S, int64_t ld_s, c
                        by_value ? src_host : nullptr);
         t_launch = now();
         if (rc != DNP_OK) break;
-        if ((e = cudaMemcpyAsync(out_host, d_out, out_bytes, cudaMemcpyDeviceToHost, stream)) != cudaSuccess) { rc = cuda_fail(e, "download"); break; }
+        // result -> pinned buffer (asynchronous), then one host memcpy into the caller's (pageable) array
+        if ((e = cudaMemcpyAsync(t_host.pin, d_out, out_bytes, cudaMemcpyDeviceToHost, stream)) != cudaSuccess) { rc = cuda_fail(e, "download"); break; }
     } while (0);
     t_dl = now();
-    cudaFreeAsync(base, stream);
     e = cudaStreamSynchronize(stream);
     const double t_sync = now();
-    cudaStreamDestroy(stream);
+    if (rc == DNP_OK && e == cudaSuccess) memcpy(out_host, t_host.pin, out_bytes);
     if (trace)
-        fprintf(stderr, "[dnp host] alloc %.2f upload %.2f enqueue %.2f download-enqueue %.2f sync %.2f destroy %.2f ms\n",
+        fprintf(stderr, "[dnp host] scratch %.2f upload %.2f enqueue %.2f download-enqueue %.2f sync %.2f copy-out %.2f ms\n",
                 t_alloc - t_0, t_up - t_alloc, t_launch - t_up, t_dl - t_launch, t_sync - t_dl, now() - t_sync);
     if (rc == DNP_OK && e != cudaSuccess) rc = cuda_fail(e, "cudaStreamSynchronize");
     return rc;
@@ -353,6 +398,26 @@ int dnp_points_propagate_f32(float* pts, int64_t N, int64_t ld, int64_t starting
     DNP_REQUIRE(eps >= 0.f, "eps must be >= 0");
     return run_points_propagate(pts, N, ld, starting_point, eps, diffuse, order_opt, flipped_opt, workspace,
                                 workspace_bytes, (cudaStream_t)stream);
+}
+
+size_t dnp_patch_propagate_workspace_bytes(int64_t N, int64_t P, int64_t max_patch, int64_t n_tgt) {
+    return patch_propagate_workspace_bytes(N, P, max_patch, n_tgt);
+}
+
+int dnp_patch_propagate_f32(float* pts, int64_t N, int64_t ld, const int64_t* perm, const int64_t* offsets_dev,
+                            const int64_t* offsets_host, int64_t P, const int64_t* rest_perm,
+                            const int64_t* rest_offsets_host, const int64_t* tgt_idx, int64_t n_tgt,
+                            int64_t start_patch, float eps, int diffuse, float* E, int64_t ld_e, int32_t* order_host,
+                            float* value_host, void* workspace, size_t workspace_bytes, void* stream) {
+    DNP_REQUIRE(N >= 0 && P >= 0 && n_tgt >= 0, "negative size");
+    if (P == 0) return DNP_OK;
+    DNP_REQUIRE(pts && perm && offsets_dev && offsets_host && E, "null pointer");
+    DNP_REQUIRE(ld >= 6 && ld_e >= 3, "row stride too small");
+    DNP_REQUIRE((rest_perm == nullptr) == (rest_offsets_host == nullptr), "rest_perm and rest_offsets_host go together");
+    DNP_REQUIRE(eps >= 0.f, "eps must be >= 0");
+    return run_patch_propagate(pts, N, ld, perm, offsets_dev, offsets_host, P, rest_perm, rest_offsets_host, tgt_idx,
+                               n_tgt, start_patch, eps, diffuse, E, ld_e, order_host, value_host, workspace,
+                               workspace_bytes, (cudaStream_t)stream);
 }
 
 int64_t dnp_points_batched_max_n(void) { return points_batched_max_n(); }

@@ -1,0 +1,169 @@
+// dnp_drivers.cu -- the greedy patch-propagation loop as ONE native call.
+//
+// field_utils.strongest_field_propagation (field_utils.py:286-348) and strongest_field_propagation_reps
+// (:207-282) run P - 1 dependent steps; the reference spends each of them in Python: a list comprehension over
+// the remaining patches (:244,316), P host synchronisations, boolean-mask indexing.  The first version of this
+// library kept the loop in Python with one call per kernel (about ten launches, several torch index ops and one
+// 8-byte read per step, ~100 us of host work).  Here the whole loop lives behind the C ABI: per step
+//   commit   flip the chosen patch (and the rows that follow it) if its interaction was negative, mark its rows
+//   field    E += field of the chosen patch on the target rows (the all-pairs kernel, sources through src_idx)
+//   score    I_p = sum_{t in p} E_t . n_t for the remaining patches + first abs-arg-max (K4)
+// and ONE 8-byte device->host read, which the next step's launch shapes (the patch size) depend on.
+// Decisions are the kernels' (identical to the per-call path); nothing here does arithmetic on the host.
+#include "dnp_common.cuh"
+#include "dnp_pairs.h"
+#include "dnp_scores.h"
+#include "dipole.h"
+
+namespace dnp {
+namespace {
+
+// rows[0..n): negate normals if flip, set settled / scratch; rest[0..n_rest): negate normals if flip
+__global__ void patch_commit_kernel(float* __restrict__ normals, int64_t ld, const int64_t* __restrict__ rows,
+                                    int64_t n, const int64_t* __restrict__ rest, int64_t n_rest, int flip,
+                                    uint8_t* __restrict__ settled, uint8_t* __restrict__ scratch,
+                                    uint8_t* __restrict__ active, int64_t patch) {
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n + n_rest; i += stride) {
+        const bool own = i < n;
+        const int64_t r = own ? rows[i] : rest[i - n];
+        if (flip) {
+            float* q = normals + r * ld;
+            q[0] = -q[0]; q[1] = -q[1]; q[2] = -q[2];
+        }
+        if (own) {
+            settled[r] = 1;
+            if (scratch) scratch[r] = 1;
+        }
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) active[patch] = 0;
+}
+
+__global__ void mask_clear_kernel(uint8_t* __restrict__ mask, const int64_t* __restrict__ rows, int64_t n) {
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) mask[rows[i]] = 0;
+}
+
+inline size_t up256(size_t v) { return (v + 255) & ~(size_t)255; }
+
+struct DriverLayout {
+    size_t settled, scratch, active, inter, best, pairs, pairs_bytes, total;
+};
+
+DriverLayout driver_layout(int64_t N, int64_t P, int64_t max_patch, int64_t M) {
+    DriverLayout L{};
+    size_t off = 0;
+    L.settled = off; off += up256((size_t)N);
+    L.scratch = off; off += up256((size_t)N);
+    L.active = off; off += up256((size_t)P);
+    L.inter = off; off += up256((size_t)P * sizeof(float));
+    L.best = off; off += 256;
+    L.pairs_bytes = pairs_workspace_bytes(max_patch, M);
+    L.pairs = off; off += up256(L.pairs_bytes);
+    L.total = off;
+    return L;
+}
+
+}  // namespace
+
+size_t patch_propagate_workspace_bytes(int64_t N, int64_t P, int64_t max_patch, int64_t n_tgt) {
+    if (N < 0 || P < 0 || max_patch < 0) return 0;
+    return driver_layout(N, P, max_patch, n_tgt > 0 ? n_tgt : N).total;
+}
+
+int run_patch_propagate(float* pts, int64_t N, int64_t ld, const int64_t* perm, const int64_t* offsets_dev,
+                        const int64_t* offsets_host, int64_t P, const int64_t* rest_perm,
+                        const int64_t* rest_offsets_host, const int64_t* tgt_idx, int64_t n_tgt, int64_t start_patch,
+                        float eps, int diffuse, float* E, int64_t ld_e, int32_t* order_host, float* value_host,
+                        void* workspace, size_t workspace_bytes, cudaStream_t stream) {
+    if (P <= 0) return DNP_OK;
+    if (start_patch < 0 || start_patch >= P) {
+        set_error("start patch %lld out of range [0, %lld)", (long long)start_patch, (long long)P);
+        return DNP_ERR_INVALID;
+    }
+    int64_t max_patch = 0;
+    for (int64_t p = 0; p < P; ++p) {
+        const int64_t n = offsets_host[p + 1] - offsets_host[p];
+        if (n < 0) {
+            set_error("offsets must be non-decreasing");
+            return DNP_ERR_INVALID;
+        }
+        if (n > max_patch) max_patch = n;
+    }
+    const int64_t M = tgt_idx ? n_tgt : N;
+    const DriverLayout L = driver_layout(N, P, max_patch, M);
+    if (!workspace || workspace_bytes < L.total) {
+        set_error("workspace too small: need %zu bytes (dnp_patch_propagate_workspace_bytes), got %zu", L.total,
+                  workspace_bytes);
+        return DNP_ERR_WORKSPACE;
+    }
+    unsigned char* ws = reinterpret_cast<unsigned char*>(workspace);
+    uint8_t* settled = ws + L.settled;
+    uint8_t* scratch = ws + L.scratch;
+    uint8_t* active = ws + L.active;
+    float* inter = reinterpret_cast<float*>(ws + L.inter);
+    int32_t* best_idx = reinterpret_cast<int32_t*>(ws + L.best);
+    float* best_val = reinterpret_cast<float*>(ws + L.best + 4);
+    void* pairs_ws = ws + L.pairs;
+    float* normals = pts + 3;
+
+    DNP_CHECK_CUDA(cudaMemsetAsync(settled, 0, (size_t)N, stream));
+    if (diffuse) DNP_CHECK_CUDA(cudaMemsetAsync(scratch, 0, (size_t)N, stream));
+    DNP_CHECK_CUDA(cudaMemsetAsync(active, 1, (size_t)P, stream));
+
+    PairEpilogue ep;
+    ep.out = E;
+    ep.ld_out = ld_e;
+    ep.tgt_idx = tgt_idx;
+    ep.tgt_skip = diffuse ? scratch : settled;       // diffuse: only the source patch itself is skipped (:256-261)
+
+    int64_t j = start_patch, prev = -1;
+    int flip = 0;
+    for (int64_t step = 0; step < P; ++step) {
+        const int64_t o = offsets_host[j], n = offsets_host[j + 1] - o;
+        const int64_t ro = rest_perm ? rest_offsets_host[j] : 0;
+        const int64_t rn = rest_perm ? rest_offsets_host[j + 1] - ro : 0;
+        if (diffuse && prev >= 0) {
+            const int64_t po = offsets_host[prev], pn = offsets_host[prev + 1] - po;
+            if (pn > 0) {
+                mask_clear_kernel<<<(unsigned)((pn + 255) / 256), 256, 0, stream>>>(scratch, perm + po, pn);
+                count_launch(1);
+            }
+        }
+        {
+            const int64_t work = n + rn > 0 ? n + rn : 1;
+            const int64_t blocks = (work + 255) / 256;
+            patch_commit_kernel<<<(unsigned)(blocks < 1184 ? blocks : 1184), 256, 0, stream>>>(
+                normals, ld, perm + o, n, rest_perm ? rest_perm + ro : nullptr, rn, flip, settled,
+                diffuse ? scratch : nullptr, active, j);
+            count_launch(1);
+        }
+        if (order_host) order_host[step] = (int32_t)j;
+        ep.mode = step == 0 ? DNP_EPI_STORE : DNP_EPI_ACCUM;                     // :239,311 then :261,265,330,335
+        if (n > 0 && M > 0) {
+            const int rc = run_pairs(false, pts, n, ld, perm + o, pts, M, ld, 0, eps, ep, pairs_ws, L.pairs_bytes,
+                                     stream);
+            if (rc != DNP_OK) return rc;
+        }
+        if (step == P - 1) break;
+        const int rc = run_patch_interactions(E, ld_e, normals, ld, perm, offsets_dev, P, active, inter, best_idx,
+                                              best_val, stream);                 // :244-247,316-319
+        if (rc != DNP_OK) return rc;
+        struct { int32_t idx; float val; } best;
+        DNP_CHECK_CUDA(cudaMemcpyAsync(&best, best_idx, sizeof(best), cudaMemcpyDeviceToHost, stream));
+        DNP_CHECK_CUDA(cudaStreamSynchronize(stream));
+        if (best.idx < 0 || best.idx >= P) {
+            set_error("no remaining patch at step %lld", (long long)step);
+            return DNP_ERR_INVALID;
+        }
+        prev = j;
+        j = best.idx;
+        flip = best.val < 0.f;                                                    // :250,322
+        if (value_host) value_host[step + 1] = best.val;
+    }
+    if (value_host) value_host[0] = 0.f;
+    DNP_CHECK_CUDA(cudaGetLastError());
+    return DNP_OK;
+}
+
+}  // namespace dnp

@@ -30,6 +30,14 @@ int run_points_propagate(float* pts, int64_t N, int64_t ld, int64_t start, float
                          int32_t* order, uint8_t* flipped, void* workspace, size_t workspace_bytes,
                          cudaStream_t stream);
 
+// greedy patch propagation loop (dnp_drivers.cu)
+size_t patch_propagate_workspace_bytes(int64_t N, int64_t P, int64_t max_patch, int64_t n_tgt);
+int run_patch_propagate(float* pts, int64_t N, int64_t ld, const int64_t* perm, const int64_t* offsets_dev,
+                        const int64_t* offsets_host, int64_t P, const int64_t* rest_perm,
+                        const int64_t* rest_offsets_host, const int64_t* tgt_idx, int64_t n_tgt, int64_t start_patch,
+                        float eps, int diffuse, float* E, int64_t ld_e, int32_t* order_host, float* value_host,
+                        void* workspace, size_t workspace_bytes, cudaStream_t stream);
+
 int64_t points_batched_max_n();
 int run_points_propagate_batched(float* pts, int64_t ld, const int64_t* offsets, int64_t P, int64_t max_patch,
                                  float eps, int diffuse, cudaStream_t stream);

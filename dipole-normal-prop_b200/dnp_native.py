@@ -38,6 +38,9 @@ SYMBOLS = [
     ("dnp_points_max_n", _i64, []),
     ("dnp_points_workspace_bytes", _sz, [_i64]),
     ("dnp_points_propagate_f32", _i32, [_vp, _i64, _i64, _i64, _f32, _i32, _vp, _vp, _vp, _sz, _vp]),
+    ("dnp_patch_propagate_workspace_bytes", _sz, [_i64, _i64, _i64, _i64]),
+    ("dnp_patch_propagate_f32", _i32, [_vp, _i64, _i64, _vp, _vp, _vp, _i64, _vp, _vp, _vp, _i64, _i64, _f32, _i32,
+                                       _vp, _i64, _vp, _vp, _vp, _sz, _vp]),
     ("dnp_points_batched_max_n", _i64, []),
     ("dnp_points_propagate_batched_f32", _i32, [_vp, _i64, _vp, _i64, _i64, _f32, _i32, _vp]),
     ("dnp_patch_lattice_sign_f32", _i32, [_vp, _i64, _vp, _i64, _i32, _vp, _i32, _vp]),
@@ -335,6 +338,47 @@ def points_propagate(pts, diffuse=False, starting_point=0, eps=1e-6, want_trace=
 
 
 # ------------------------------------------------------------------ "xie" interaction
+def patch_propagate(pts, perm, offsets, start_patch, E, diffuse=False, eps=1e-5, rest_perm=None, rest_offsets=None,
+                    tgt_idx=None, want_trace=False):
+    """The whole greedy patch loop of strongest_field_propagation{,_reps} in one native call
+    (dnp_patch_propagate_f32), in place on pts [N, 6]; E [N, 3] must be zero and receives the final field.
+    offsets / rest_offsets may be tensors on any device (a host copy is made: the launch shapes need the sizes).
+    Returns (order, values) as numpy arrays when want_trace."""
+    import numpy as np
+    lib = load()
+    p, ld = _rows(pts, 6, "pts")
+    if p.data_ptr() != pts.data_ptr():
+        raise ValueError("pts must have unit column stride (the call works in place)")
+    e, ld_e = _rows(E, 3, "E")
+    if e.data_ptr() != E.data_ptr():
+        raise ValueError("E must have unit column stride")
+    dev = p.device
+    perm = _idx(perm, dev, "perm")
+    off_dev = _idx(offsets, dev, "offsets")
+    off_host = np.ascontiguousarray(offsets.cpu().numpy(), dtype=np.int64)
+    P = off_host.size - 1
+    rest_perm = _idx(rest_perm, dev, "rest_perm")
+    rest_host = None if rest_offsets is None else np.ascontiguousarray(rest_offsets.cpu().numpy(), dtype=np.int64)
+    if (rest_perm is None) != (rest_host is None):
+        raise ValueError("rest_perm and rest_offsets go together")
+    tgt_idx = _idx(tgt_idx, dev, "tgt_idx")
+    n_tgt = 0 if tgt_idx is None else tgt_idx.numel()
+    order = np.zeros(max(P, 1), dtype=np.int32) if want_trace else None
+    values = np.zeros(max(P, 1), dtype=np.float32) if want_trace else None
+    max_patch = int((off_host[1:] - off_host[:-1]).max()) if P > 0 else 0
+    N = p.shape[0]
+    with torch.cuda.device(dev):
+        nbytes = lib.dnp_patch_propagate_workspace_bytes(N, P, max_patch, n_tgt)
+        ws = torch.empty(max(nbytes, 1), dtype=torch.uint8, device=dev)
+        _check(lib.dnp_patch_propagate_f32(
+            _ptr(p), N, ld, _ptr(perm), _ptr(off_dev), ctypes.c_void_p(off_host.ctypes.data), P, _ptr(rest_perm),
+            ctypes.c_void_p(rest_host.ctypes.data if rest_host is not None else 0), _ptr(tgt_idx), n_tgt,
+            int(start_patch), float(eps), int(bool(diffuse)), _ptr(e), ld_e,
+            ctypes.c_void_p(order.ctypes.data if want_trace else 0),
+            ctypes.c_void_p(values.ctypes.data if want_trace else 0), _ptr(ws), nbytes, _stream(p)))
+    return (order[:P], values[:P]) if want_trace else None
+
+
 def points_propagate_batched(pts, offsets, max_patch, diffuse=False, eps=1e-6):
     """strongest_field_propagation_points on every patch of a CSR in ONE launch (a cluster per patch), in place.
     pts: [N, 6] float32 CUDA rows stored patch by patch; offsets: int64 [P + 1]."""

@@ -35,6 +35,7 @@ except Exception:  # reference checkout (or its open3d dependency) not importabl
 import dnp_native as _dn
 
 ALLOW_FLOAT64_CAST = False
+NATIVE_PATCH_LOOP = True      # greedy patch loops behind one native call (dnp_patch_propagate_f32)
 
 _EPS_DEFAULT = 1e-5
 _EPS_POINTS = 1e-6      # field_utils.py:362,380
@@ -370,6 +371,66 @@ def xie_propagation_points_onbfstree(pts: torch.Tensor, eps, diffuse=False, star
         pts[(cnts > times / 2).to(pts.device), 3:] *= -1
 
 
+def _reps_loop_per_call(pts, rep_idx, rest_idx, perm, offsets, start, E, diffuse):
+    """The loop of field_utils.py:239-265 with one library call per kernel (the first version of this driver;
+    kept as the reference for the native loop, tests/test_gpu_drivers.py)."""
+    dev = pts.device
+    N, P = pts.shape[0], len(rep_idx)
+    settled = torch.ones(N, dtype=torch.uint8, device=dev)     # NOT non_oriented_pts_mask (:223-227)
+    settled.index_fill_(0, perm, 0)
+    scratch_mask = torch.zeros(N, dtype=torch.uint8, device=dev)
+    active = torch.ones(P, dtype=torch.uint8, device=dev)
+    patch = rep_idx[start]
+    _clear(active, start)
+    settled.index_fill_(0, patch, 1)
+    _dn.field_apply(pts, pts, _EPS_DEFAULT, _dn.EPI_STORE, out=E, src_idx=patch,          # :239
+                    tgt_idx=perm, tgt_skip=settled)
+    for _ in range(P - 1):
+        _, best = _dn.patch_interactions(E, pts, perm, offsets, active)                   # :244-247
+        j, value = _dn.best_to_host(best)
+        patch = rep_idx[j]
+        if value < 0:                                                                     # :250-252
+            pts[patch, 3:] *= -1
+            pts[rest_idx[j], 3:] *= -1
+        _clear(active, j)
+        settled.index_fill_(0, patch, 1)
+        if diffuse:                                                                       # :256-261
+            scratch_mask.index_fill_(0, patch, 1)
+            _dn.field_apply(pts, pts, _EPS_DEFAULT, _dn.EPI_ACCUM, out=E, src_idx=patch,
+                            tgt_idx=perm, tgt_skip=scratch_mask)
+            scratch_mask.index_fill_(0, patch, 0)
+        else:                                                                             # :264-265
+            _dn.field_apply(pts, pts, _EPS_DEFAULT, _dn.EPI_ACCUM, out=E, src_idx=patch,
+                            tgt_idx=perm, tgt_skip=settled)
+
+
+def _patch_loop_per_call(p, idx, perm, offsets, start, E, diffuse):
+    """The loop of field_utils.py:311-335 with one library call per kernel (see _reps_loop_per_call)."""
+    dev = p.device
+    N, P = p.shape[0], len(idx)
+    oriented = torch.zeros(N, dtype=torch.uint8, device=dev)      # pts_mask (:296)
+    scratch_mask = torch.zeros(N, dtype=torch.uint8, device=dev)
+    active = torch.ones(P, dtype=torch.uint8, device=dev)
+    patch = idx[start]
+    _clear(active, start)
+    oriented.index_fill_(0, patch, 1)
+    _dn.field_apply(p, p, _EPS_DEFAULT, _dn.EPI_STORE, out=E, src_idx=patch, tgt_skip=oriented)   # :311
+    for _ in range(P - 1):
+        _, best = _dn.patch_interactions(E, p, perm, offsets, active)                     # :316-319
+        j, value = _dn.best_to_host(best)
+        patch = idx[j]
+        if value < 0:                                                                     # :322-323
+            p[patch, 3:] *= -1
+        _clear(active, j)
+        oriented.index_fill_(0, patch, 1)
+        if diffuse:                                                                       # :326-331
+            scratch_mask.index_fill_(0, patch, 1)
+            _dn.field_apply(p, p, _EPS_DEFAULT, _dn.EPI_ACCUM, out=E, src_idx=patch, tgt_skip=scratch_mask)
+            scratch_mask.index_fill_(0, patch, 0)
+        else:                                                                             # :333-335
+            _dn.field_apply(p, p, _EPS_DEFAULT, _dn.EPI_ACCUM, out=E, src_idx=patch, tgt_skip=oriented)
+
+
 # ---------------------------------------------------------------------------- a8: patch propagation on representatives
 def strongest_field_propagation_reps(input_pc, reps, diffuse=False, weights=None):
     """field_utils.py:207-282.  reps = [(rep_idx, rest_idx)] per patch.  Mutates input_pc[:, 3:]; returns None."""
@@ -387,39 +448,19 @@ def strongest_field_propagation_reps(input_pc, reps, diffuse=False, weights=None
         rest_idx = _index_list([rest for rep, rest in reps], dev)
         P = len(rep_idx)
         perm, offsets = _csr(rep_idx, dev)            # perm = every representative row
+        rest_perm, rest_offsets = _csr(rest_idx, dev)
         E = torch.zeros(N, 3, dtype=torch.float32, device=dev)
         oriented = torch.zeros(N, dtype=torch.uint8, device=dev)
-        settled = torch.ones(N, dtype=torch.uint8, device=dev)     # NOT non_oriented_pts_mask (:223-227)
-        settled.index_fill_(0, perm, 0)
-        scratch_mask = torch.zeros(N, dtype=torch.uint8, device=dev)
-        active = torch.ones(P, dtype=torch.uint8, device=dev)
+        oriented.index_fill_(0, perm, 1)              # after the loop every representative is oriented
 
-        start = _flattest_patch(pts, perm, offsets)                                       # :230-233
-        patch = rep_idx[start]
-        _clear(active, start)
-        oriented.index_fill_(0, patch, 1)
-        settled.index_fill_(0, patch, 1)
-        _dn.field_apply(pts, pts, _EPS_DEFAULT, _dn.EPI_STORE, out=E, src_idx=patch,      # :239
-                        tgt_idx=perm, tgt_skip=settled)
-
-        for _ in range(P - 1):
-            _, best = _dn.patch_interactions(E, pts, perm, offsets, active)               # :244-247
-            j, value = _dn.best_to_host(best)
-            patch = rep_idx[j]
-            if value < 0:                                                                 # :250-252
-                pts[patch, 3:] *= -1
-                pts[rest_idx[j], 3:] *= -1
-            _clear(active, j)
-            oriented.index_fill_(0, patch, 1)
-            settled.index_fill_(0, patch, 1)
-            if diffuse:                                                                   # :256-261
-                scratch_mask.index_fill_(0, patch, 1)
-                _dn.field_apply(pts, pts, _EPS_DEFAULT, _dn.EPI_ACCUM, out=E, src_idx=patch,
-                                tgt_idx=perm, tgt_skip=scratch_mask)
-                scratch_mask.index_fill_(0, patch, 0)
-            else:                                                                         # :264-265
-                _dn.field_apply(pts, pts, _EPS_DEFAULT, _dn.EPI_ACCUM, out=E, src_idx=patch,
-                                tgt_idx=perm, tgt_skip=settled)
+        if P > 0:
+            start = _flattest_patch(pts, perm, offsets)                                   # :230-233
+            if NATIVE_PATCH_LOOP:
+                # :239-265 in one native call: interactions, arg-max, flips (reps + the rest of the patch), field
+                _dn.patch_propagate(pts, perm, offsets, start, E, diffuse=diffuse, eps=_EPS_DEFAULT,
+                                    rest_perm=rest_perm, rest_offsets=rest_offsets, tgt_idx=perm)
+            else:
+                _reps_loop_per_call(pts, rep_idx, rest_idx, perm, offsets, start, E, diffuse)
 
         if diffuse:                                                                       # :267-271
             _dn.field_sign(E, pts, idx=perm, strict=True)
@@ -451,30 +492,12 @@ def strongest_field_propagation(pts, patches, all_patches, diffuse=False, weight
         P = len(idx)
         perm, offsets = _csr(idx, dev)
         E = torch.zeros(N, 3, dtype=torch.float32, device=dev)
-        oriented = torch.zeros(N, dtype=torch.uint8, device=dev)      # pts_mask (:296)
-        scratch_mask = torch.zeros(N, dtype=torch.uint8, device=dev)
-        active = torch.ones(P, dtype=torch.uint8, device=dev)
-
-        start = _flattest_patch(p, perm, offsets)                                         # :303-306
-        patch = idx[start]
-        _clear(active, start)
-        oriented.index_fill_(0, patch, 1)
-        _dn.field_apply(p, p, _EPS_DEFAULT, _dn.EPI_STORE, out=E, src_idx=patch, tgt_skip=oriented)   # :311
-
-        for _ in range(P - 1):
-            _, best = _dn.patch_interactions(E, p, perm, offsets, active)                 # :316-319
-            j, value = _dn.best_to_host(best)
-            patch = idx[j]
-            if value < 0:                                                                 # :322-323
-                p[patch, 3:] *= -1
-            _clear(active, j)
-            oriented.index_fill_(0, patch, 1)
-            if diffuse:                                                                   # :326-331
-                scratch_mask.index_fill_(0, patch, 1)
-                _dn.field_apply(p, p, _EPS_DEFAULT, _dn.EPI_ACCUM, out=E, src_idx=patch, tgt_skip=scratch_mask)
-                scratch_mask.index_fill_(0, patch, 0)
-            else:                                                                         # :333-335
-                _dn.field_apply(p, p, _EPS_DEFAULT, _dn.EPI_ACCUM, out=E, src_idx=patch, tgt_skip=oriented)
+        if P > 0:
+            start = _flattest_patch(p, perm, offsets)                                     # :303-306
+            if NATIVE_PATCH_LOOP:
+                _dn.patch_propagate(p, perm, offsets, start, E, diffuse=diffuse, eps=_EPS_DEFAULT)   # :311-335
+            else:
+                _patch_loop_per_call(p, idx, perm, offsets, start, E, diffuse)
 
         if diffuse:                                                                       # :337-342
             kept = _index_list([entry[1] for entry in patches], dev)

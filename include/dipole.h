@@ -182,6 +182,29 @@ DNP_API int dnp_points_propagate_f32(float* pts, int64_t N, int64_t ld, int64_t 
                              int32_t* order_opt, uint8_t* flipped_opt,
                              void* workspace, size_t workspace_bytes, void* stream);
 
+/* ------------------------------------------------------------------ greedy patch propagation, whole loop
+ * replaces the loops of field_utils.strongest_field_propagation (field_utils.py:311-335) and
+ * strongest_field_propagation_reps (:239-265): starting from `start_patch`, P - 1 times: per-patch interactions
+ * sum E.n over the remaining patches, first abs-arg-max, flip the chosen patch if its interaction is negative,
+ * add its field to the running field E.  Patches are a CSR: perm (device int64) with offsets given BOTH on the
+ * device (offsets_dev) and on the host (offsets_host, the launch shapes depend on the patch sizes).
+ * rest_perm / rest_offsets_host (optional): rows that are flipped together with patch p but are neither sources nor
+ * targets (the non-representative points of a patch, field_utils.py:250-252).
+ * tgt_idx (optional, device, n_tgt rows): the target rows (all representatives, :239); NULL = all N rows.
+ * diffuse != 0: only the source patch is skipped as a target (:256-261,326-331), else every visited patch.
+ * E: [N, ld_e >= 3] running field, ZEROED by the caller, holds the final field on return.
+ * order_host / value_host (optional, host, P entries): visit order and the signed interaction that chose each
+ * patch.  The call synchronises `stream` once per step (an 8-byte read) and returns after the last launch
+ * has been enqueued.                                                                                       */
+DNP_API size_t dnp_patch_propagate_workspace_bytes(int64_t N, int64_t P, int64_t max_patch, int64_t n_tgt);
+DNP_API int dnp_patch_propagate_f32(float* pts, int64_t N, int64_t ld,
+                            const int64_t* perm, const int64_t* offsets_dev, const int64_t* offsets_host, int64_t P,
+                            const int64_t* rest_perm, const int64_t* rest_offsets_host,
+                            const int64_t* tgt_idx, int64_t n_tgt,
+                            int64_t start_patch, float eps, int diffuse,
+                            float* E, int64_t ld_e, int32_t* order_host, float* value_host,
+                            void* workspace, size_t workspace_bytes, void* stream);
+
 /* ------------------------------------------------------------------ per-patch greedy orientation, batched
  * The per-patch stage of the patch graph (util.py:185-196 calling graph_dipole.st_propagation_points_file,
  * graph_dipole.py:27-36, once per patch from Python threads) as ONE launch: patch c = rows offsets[c] ..

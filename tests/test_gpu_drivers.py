@@ -19,6 +19,32 @@ def _patches(perm, off):
     return [torch.from_numpy(perm[off[i]:off[i + 1]].copy()) for i in range(len(off) - 1)]
 
 
+def _spy_order(fu, monkeypatch, native):
+    """Greedy visit order (after the start patch) as the product decides it: from the trace of the native loop
+    (dnp_patch_propagate_f32) or, with the per-call loop, from every 8-byte read of the arg-max."""
+    import dnp_native
+    order = []
+    monkeypatch.setattr(fu, "NATIVE_PATCH_LOOP", native)
+    if native:
+        real = dnp_native.patch_propagate
+
+        def spy(*a, **k):
+            k["want_trace"] = True
+            o, v = real(*a, **k)
+            order.extend(int(x) for x in o[1:])
+            assert all((v[1:] < 0) | (v[1:] >= 0))
+        monkeypatch.setattr(dnp_native, "patch_propagate", spy)
+    else:
+        real = dnp_native.best_to_host
+
+        def spy(best):
+            j, v = real(best)
+            order.append(j)
+            return j, v
+        monkeypatch.setattr(dnp_native, "best_to_host", spy)
+    return order
+
+
 # ------------------------------------------------------------------ a6: per-point propagation (cfg1, data/ok.xyz)
 @pytest.mark.parametrize("tag", ["n512", "n2000", "full"])
 def test_points_propagation_bit_exact(fu, golden, dev, tag):
@@ -212,21 +238,14 @@ def test_field_sign_streamed(dev):
 
 
 # ------------------------------------------------------------------ a7: patch propagation (cfg2, data/fandisk.xyz)
+@pytest.mark.parametrize("native", [True, False])
 @pytest.mark.parametrize("tag,diffuse,use_w", [("plain", False, False), ("diffuse_w", True, True)])
-def test_patch_propagation_golden(fu, golden, dev, tag, diffuse, use_w, monkeypatch):
-    import dnp_native
+def test_patch_propagation_golden(fu, golden, dev, tag, diffuse, use_w, native, monkeypatch):
     g = golden("patch_prop")
     patches = _patches(g["perm"], g["offsets"])
     kept = [(int(i), patches[int(i)]) for i in g["kept_ids"]]
     # record the greedy order through the product's own call into the ABI
-    order = []
-    real = dnp_native.best_to_host
-
-    def spy(best):
-        j, v = real(best)
-        order.append(j)
-        return j, v
-    monkeypatch.setattr(dnp_native, "best_to_host", spy)
+    order = _spy_order(fu, monkeypatch, native)
     pts = torch.from_numpy(g["pc_in"].copy()).to(dev)
     weights = torch.from_numpy(g["weights"].copy()).to(dev) if use_w else None
     ret = fu.strongest_field_propagation(pts, kept, patches, diffuse=diffuse, weights=weights)
@@ -249,14 +268,12 @@ def test_patch_propagation_cpu_tensor(fu, golden):
 
 
 # ------------------------------------------------------------------ a8: representative-point propagation (cfg3 stand-in)
+@pytest.mark.parametrize("native", [True, False])
 @pytest.mark.parametrize("tag,diffuse", [("plain", False), ("diffuse", True)])
-def test_reps_propagation_golden(fu, golden, dev, tag, diffuse, monkeypatch):
-    import dnp_native
+def test_reps_propagation_golden(fu, golden, dev, tag, diffuse, native, monkeypatch):
     g = golden("reps_prop")
     reps = list(zip(_patches(g["rep_perm"], g["rep_off"]), _patches(g["rest_perm"], g["rest_off"])))
-    order = []
-    real = dnp_native.best_to_host
-    monkeypatch.setattr(dnp_native, "best_to_host", lambda b: (order.append(real(b)[0]), real(b))[1])
+    order = _spy_order(fu, monkeypatch, native)
     pts = torch.from_numpy(g["pc_in"].copy()).to(dev)
     assert fu.strongest_field_propagation_reps(pts, reps, diffuse=diffuse) is None
     assert order == list(g[f"{tag}_order"][1:])
@@ -276,6 +293,36 @@ def test_reps_propagation_weights_vs_oracle(fu, golden, orc, dev):
     got = pts[:, 3:].cpu().numpy()
     assert np.array_equal(np.sign(got), np.sign(want[:, 3:]))
     assert np.abs(got - want[:, 3:]).max() < 1e-6
+
+
+@pytest.mark.parametrize("diffuse", [False, True])
+def test_native_patch_loop_equals_per_call_loop(fu, dev, diffuse, monkeypatch):
+    """dnp_patch_propagate_f32 against the per-kernel-call loop on a synthetic cloud with ragged patches (sizes
+    1 .. 700, an empty remainder, representatives + rest): same kernels in the same order, so the normals must be
+    bit-identical."""
+    g = torch.Generator().manual_seed(123)
+    n = 12000
+    d = torch.randn(n, 3, generator=g)
+    d = d / d.norm(dim=-1, keepdim=True)
+    pc = torch.cat([d * 0.45 + 0.004 * torch.randn(n, 3, generator=g), d], 1).float()
+    key = ((pc[:, :3] + 0.6) * 5).long().clamp(0, 5)
+    cell = key[:, 0] * 36 + key[:, 1] * 6 + key[:, 2]
+    patches = [torch.nonzero(cell == c).flatten() for c in cell.unique()]
+    for pt in patches[::3]:
+        pc[pt, 3:] *= -1
+    reps = [(pt[:200], pt[200:]) for pt in patches]
+    out = {}
+    for native in (True, False):
+        monkeypatch.setattr(fu, "NATIVE_PATCH_LOOP", native)
+        a = pc.clone().to(dev)
+        fu.strongest_field_propagation(a, [(i, pt) for i, pt in enumerate(patches)], patches, diffuse=diffuse)
+        b = pc.clone().to(dev)
+        fu.strongest_field_propagation_reps(b, reps, diffuse=diffuse)
+        out[native] = (a.cpu(), b.cpu())
+    assert torch.equal(out[True][0], out[False][0])
+    assert torch.equal(out[True][1], out[False][1])
+    radial = (out[True][0][:, 3:] * d).sum(-1)
+    assert abs(torch.sign(radial).mean()) > 0.99
 
 
 # ------------------------------------------------------------------ a10: thin callers
