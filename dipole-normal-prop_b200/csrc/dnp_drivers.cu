@@ -8,8 +8,17 @@
 //   commit   flip the chosen patch (and the rows that follow it) if its interaction was negative, mark its rows
 //   field    E += field of the chosen patch on the target rows (the all-pairs kernel, sources through src_idx)
 //   score    I_p = sum_{t in p} E_t . n_t for the remaining patches + first abs-arg-max (K4)
-// and ONE 8-byte device->host read, which the next step's launch shapes (the patch size) depend on.
+// Two schedules of the same kernels:
+//   * device-driven (patches below the by-value kernel's threshold, i.e. nearly always): the winner of a step
+//     stays on the device -- the arg-max kernel advances cur = {patch, flip, previous patch}, the commit / pack /
+//     all-pairs kernels read their row range from it (launches are shaped for the LARGEST patch; the all-pairs
+//     kernel walks only the chosen patch's source tiles).  No host read inside the loop: all P steps are
+//     enqueued at once and the GPU runs them back to back.
+//   * host-driven (a patch large enough for the by-value kernel, whose sources are kernel parameters): one
+//     8-byte device->host read per step.
 // Decisions are the kernels' (identical to the per-call path); nothing here does arithmetic on the host.
+#include <stdlib.h>
+
 #include "dnp_common.cuh"
 #include "dnp_pairs.h"
 #include "dnp_scores.h"
@@ -44,10 +53,52 @@ __global__ void mask_clear_kernel(uint8_t* __restrict__ mask, const int64_t* __r
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) mask[rows[i]] = 0;
 }
 
+// ---- device-driven schedule: the same two kernels with the row ranges read from cur = {patch, flip, previous}
+__global__ void patch_commit_selected_kernel(float* __restrict__ normals, int64_t ld, const int64_t* __restrict__ perm,
+                                             const int64_t* __restrict__ offsets,
+                                             const int64_t* __restrict__ rest_perm,
+                                             const int64_t* __restrict__ rest_offsets, const int32_t* __restrict__ cur,
+                                             uint8_t* __restrict__ settled, uint8_t* __restrict__ scratch,
+                                             uint8_t* __restrict__ active) {
+    const int patch = cur[0], flip = cur[1];
+    if (patch < 0) return;
+    const int64_t o = offsets[patch], n = offsets[patch + 1] - o;
+    const int64_t ro = rest_perm ? rest_offsets[patch] : 0, rn = rest_perm ? rest_offsets[patch + 1] - ro : 0;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n + rn; i += stride) {
+        const bool own = i < n;
+        const int64_t r = own ? perm[o + i] : rest_perm[ro + i - n];
+        if (flip) {
+            float* q = normals + r * ld;
+            q[0] = -q[0]; q[1] = -q[1]; q[2] = -q[2];
+        }
+        if (own) {
+            settled[r] = 1;
+            if (scratch) scratch[r] = 1;
+        }
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) active[patch] = 0;
+}
+
+__global__ void mask_clear_selected_kernel(uint8_t* __restrict__ mask, const int64_t* __restrict__ perm,
+                                           const int64_t* __restrict__ offsets, const int32_t* __restrict__ cur) {
+    const int prev = cur[2];
+    if (prev < 0) return;
+    const int64_t o = offsets[prev], n = offsets[prev + 1] - o;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) mask[perm[o + i]] = 0;
+}
+
+__global__ void cur_init_kernel(int32_t* cur, int32_t start, int32_t* order, float* value) {
+    cur[0] = start; cur[1] = 0; cur[2] = -1; cur[3] = 0;
+    if (order) order[0] = start;
+    if (value) value[0] = 0.f;
+}
+
 inline size_t up256(size_t v) { return (v + 255) & ~(size_t)255; }
 
 struct DriverLayout {
-    size_t settled, scratch, active, inter, best, pairs, pairs_bytes, total;
+    size_t settled, scratch, active, inter, best, cur, rest_off, order, value, pairs, pairs_bytes, total;
 };
 
 DriverLayout driver_layout(int64_t N, int64_t P, int64_t max_patch, int64_t M) {
@@ -58,6 +109,10 @@ DriverLayout driver_layout(int64_t N, int64_t P, int64_t max_patch, int64_t M) {
     L.active = off; off += up256((size_t)P);
     L.inter = off; off += up256((size_t)P * sizeof(float));
     L.best = off; off += 256;
+    L.cur = off; off += 256;
+    L.rest_off = off; off += up256((size_t)(P + 1) * sizeof(int64_t));
+    L.order = off; off += up256((size_t)P * sizeof(int32_t));
+    L.value = off; off += up256((size_t)P * sizeof(float));
     L.pairs_bytes = pairs_workspace_bytes(max_patch, M);
     L.pairs = off; off += up256(L.pairs_bytes);
     L.total = off;
@@ -116,6 +171,74 @@ int run_patch_propagate(float* pts, int64_t N, int64_t ld, const int64_t* perm, 
     ep.ld_out = ld_e;
     ep.tgt_idx = tgt_idx;
     ep.tgt_skip = diffuse ? scratch : settled;       // diffuse: only the source patch itself is skipped (:256-261)
+
+    // DNP_PATCH_LOOP=host|device overrides the schedule (tests run both and compare)
+    const char* forced = getenv("DNP_PATCH_LOOP");
+    bool device_driven = !use_const_path(max_patch, M, 0);
+    if (forced && forced[0] == 'h') device_driven = false;
+    if (forced && forced[0] == 'd') device_driven = true;
+    if (device_driven) {
+        int32_t* cur = reinterpret_cast<int32_t*>(ws + L.cur);
+        int64_t* rest_off_dev = reinterpret_cast<int64_t*>(ws + L.rest_off);
+        int32_t* order_dev = order_host ? reinterpret_cast<int32_t*>(ws + L.order) : nullptr;
+        float* value_dev = value_host ? reinterpret_cast<float*>(ws + L.value) : nullptr;
+        int64_t max_rest = 0;
+        if (rest_perm) {
+            for (int64_t p = 0; p < P; ++p) {
+                const int64_t n = rest_offsets_host[p + 1] - rest_offsets_host[p];
+                if (n < 0) {
+                    set_error("rest offsets must be non-decreasing");
+                    return DNP_ERR_INVALID;
+                }
+                if (n > max_rest) max_rest = n;
+            }
+            DNP_CHECK_CUDA(cudaMemcpyAsync(rest_off_dev, rest_offsets_host, (size_t)(P + 1) * sizeof(int64_t),
+                                           cudaMemcpyHostToDevice, stream));
+        }
+        cur_init_kernel<<<1, 1, 0, stream>>>(cur, (int32_t)start_patch, order_dev, value_dev);
+        count_launch(1);
+        const int64_t commit_work = max_patch + max_rest > 0 ? max_patch + max_rest : 1;
+        const int64_t commit_want = (commit_work + 255) / 256, clear_want = (max_patch + 255) / 256;
+        const unsigned commit_blocks = (unsigned)(commit_want < 1184 ? commit_want : 1184);
+        const unsigned clear_blocks = (unsigned)(clear_want < 1184 ? clear_want : 1184);
+        SourceSelect sel;
+        sel.patch = cur;
+        sel.offsets = offsets_dev;
+        for (int64_t step = 0; step < P; ++step) {
+            if (diffuse && step > 0 && max_patch > 0) {
+                mask_clear_selected_kernel<<<clear_blocks, 256, 0, stream>>>(scratch, perm, offsets_dev, cur);
+                count_launch(1);
+            }
+            patch_commit_selected_kernel<<<commit_blocks, 256, 0, stream>>>(
+                normals, ld, perm, offsets_dev, rest_perm, rest_perm ? rest_off_dev : nullptr, cur, settled,
+                diffuse ? scratch : nullptr, active);
+            count_launch(1);
+            ep.mode = step == 0 ? DNP_EPI_STORE : DNP_EPI_ACCUM;
+            if (max_patch > 0 && M > 0) {
+                const int rc = run_pairs(false, pts, max_patch, ld, perm, pts, M, ld, 0, eps, ep, pairs_ws,
+                                         L.pairs_bytes, stream, 0, 0, nullptr, sel);
+                if (rc != DNP_OK) return rc;
+            }
+            if (step == P - 1) break;
+            PatchAdvance adv;
+            adv.cur = cur;
+            adv.order = order_dev;
+            adv.value = value_dev;
+            adv.step = (int)(step + 1);
+            const int rc = run_patch_interactions(E, ld_e, normals, ld, perm, offsets_dev, P, active, inter, best_idx,
+                                                  best_val, stream, adv);
+            if (rc != DNP_OK) return rc;
+        }
+        if (order_host)
+            DNP_CHECK_CUDA(cudaMemcpyAsync(order_host, order_dev, (size_t)P * sizeof(int32_t), cudaMemcpyDeviceToHost,
+                                           stream));
+        if (value_host)
+            DNP_CHECK_CUDA(cudaMemcpyAsync(value_host, value_dev, (size_t)P * sizeof(float), cudaMemcpyDeviceToHost,
+                                           stream));
+        if (order_host || value_host) DNP_CHECK_CUDA(cudaStreamSynchronize(stream));
+        DNP_CHECK_CUDA(cudaGetLastError());
+        return DNP_OK;
+    }
 
     int64_t j = start_patch, prev = -1;
     int flip = 0;

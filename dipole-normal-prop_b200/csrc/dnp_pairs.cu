@@ -60,6 +60,24 @@ __global__ void pack_sources_kernel(const float* __restrict__ src, int64_t S, in
     packed[3 * s + 2] = make_float4(v[5] * -3.f, 0.f, 0.f, 0.f);
 }
 
+// the same for a source range chosen on the device: rows idx[o .. o + n) of patch *sel.patch, null dipoles up to S_pad
+__global__ void pack_selected_kernel(const float* __restrict__ src, int64_t ld_s, const int64_t* __restrict__ idx,
+                                     SourceSelect sel, int64_t S_pad, float4* __restrict__ packed) {
+    const int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= S_pad) return;
+    const int pj = *sel.patch;
+    const int64_t o = pj < 0 ? 0 : sel.offsets[pj], n = pj < 0 ? 0 : sel.offsets[pj + 1] - o;
+    float v[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    if (s < n) {
+        const float* p = src + idx[o + s] * ld_s;
+#pragma unroll
+        for (int c = 0; c < 6; ++c) v[c] = __ldg(p + c);
+    }
+    packed[3 * s + 0] = make_float4(v[0], v[1], v[2], v[3]);
+    packed[3 * s + 1] = make_float4(v[4], v[5], v[3] * -3.f, v[4] * -3.f);
+    packed[3 * s + 2] = make_float4(v[5] * -3.f, 0.f, 0.f, 0.f);
+}
+
 // ------------------------------------------------------------------ epilogue (K7)
 __device__ __forceinline__ float zero_nonfinite(float v, int& bad) {
     // (v - v) is NaN for both Inf and NaN
@@ -173,8 +191,13 @@ template <int TP, bool kPotential>
 __global__ void __launch_bounds__(kBlock, (TP >= 4 ? 3 : (TP == 2 ? 5 : 8)))
 pairs_kernel(const float4* __restrict__ packed, int tiles_total, int nsplit,
              const float* __restrict__ tgt, int64_t M, int64_t ld_t, int lattice_n,
-             float eps, float* __restrict__ partial, PairEpilogue ep) {
+             float eps, float* __restrict__ partial, PairEpilogue ep, SourceSelect sel) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
+    if (sel.patch) {                                 // device-chosen source range: only its tiles are walked
+        const int pj = *sel.patch;
+        const int64_t n = pj < 0 ? 0 : sel.offsets[pj + 1] - sel.offsets[pj];
+        tiles_total = (int)((n + kTileSrc - 1) / kTileSrc);
+    }
     float4* stage_buf = reinterpret_cast<float4*>(smem_raw);
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem_raw + size_t(kStages) * kTileBytes);
 
@@ -432,31 +455,51 @@ PairPlan make_pair_plan(int64_t S, int64_t M, int sm_count, int force_tp, int fo
     p.tiles_total = (int)((S + kTileSrc - 1) / kTileSrc);
     if (p.tiles_total < 1) p.tiles_total = 1;
     p.S_pad = (int64_t)p.tiles_total * kTileSrc;
-    // targets per thread: enough CTAs to cover the machine, then as many registers-resident targets as possible
-    const int64_t full_tp4 = (int64_t)sm_count * 3 * kBlock * 8;
-    const int64_t full_tp2 = (int64_t)sm_count * 5 * kBlock * 4;
-    p.tp = (M >= full_tp4) ? 4 : (M >= full_tp2 / 2 ? 2 : 1);
+    // (targets per thread, source splits) by a small cost model of the grid, in units of one full wave of the
+    // candidate (resident CTAs on every SM): full waves cost 1 each; the last, partial wave costs the deepest
+    // SM's share of it, but never less than what ONE CTA needs when it has an SM to itself (few warps cannot
+    // hide the MUFU / shared-memory latency); a split adds the reduction pass over its partial sums.  The
+    // constants are from tools/plan_probe.py on B200 (profiles/README.md): before this the S = 500, M = 524288
+    // step of the representatives loop ran 512 TP4 CTAs on 444 slots, 1.15 waves at 1.13e12 pairs/s, where
+    // TP2 reaches 1.33e12.
     if (force_tp <= 0) force_tp = env_int("DNP_FORCE_TP");
     if (force_nsplit <= 0) force_nsplit = env_int("DNP_FORCE_NSPLIT");
-    if (force_tp == 1 || force_tp == 2 || force_tp == 4) p.tp = force_tp;
-    const int resident = p.tp >= 4 ? 3 : (p.tp == 2 ? 5 : 8);
-    p.m_tiles = (int)((M + (int64_t)kBlock * 2 * p.tp - 1) / ((int64_t)kBlock * 2 * p.tp));
-    if (p.m_tiles < 1) p.m_tiles = 1;
-    // source splits: pick the split count whose CTA count fills whole waves best
-    const int64_t wave = (int64_t)sm_count * resident;
-    int best = 1;
-    double best_eff = -1.0;
+    if (force_tp != 1 && force_tp != 2 && force_tp != 4) force_tp = 0;
+    if (force_nsplit > p.tiles_total) force_nsplit = p.tiles_total;
     const int max_split = (int)((p.tiles_total < 64) ? p.tiles_total : 64);
-    for (int k = 1; k <= max_split; ++k) {
-        if (k > 1 && p.tiles_total / k < 2) break;
-        const int64_t ctas = (int64_t)p.m_tiles * k;
-        const int64_t waves = (ctas + wave - 1) / wave;
-        double eff = (double)ctas / (double)(waves * wave);
-        if (ctas >= 6 * wave) eff = 1.0 - 1e-9 * k;                // deep enough: stop splitting
-        if (eff > best_eff + 0.01) { best_eff = eff; best = k; }
+    double best_cost = 0.0;
+    p.tp = 0;
+    for (int tp = 4; tp >= 1; tp >>= 1) {
+        if (force_tp && tp != force_tp) continue;
+        const int resident = tp >= 4 ? 3 : (tp == 2 ? 5 : 8);
+        const double alone = tp >= 4 ? 0.55 : (tp == 2 ? 0.40 : 0.30);    // one CTA alone on an SM / a full wave
+        const double rate = tp == 2 ? 1.0 : 0.97;                          // measured steady-state rate vs TP2
+        const int64_t tile_tgts = (int64_t)kBlock * 2 * tp;
+        int64_t m_tiles = (M + tile_tgts - 1) / tile_tgts;
+        if (m_tiles < 1) m_tiles = 1;
+        const int64_t wave = (int64_t)sm_count * resident;
+        for (int k = 1; k <= max_split; ++k) {
+            if (force_nsplit > 0 && k != force_nsplit) continue;
+            const int64_t ctas = m_tiles * k;
+            const int64_t full = ctas / wave, tail = ctas - full * wave;
+            double waves = (double)full;
+            if (tail > 0) {
+                const double deepest = (double)((tail + sm_count - 1) / sm_count) / resident;
+                waves += deepest > alone ? deepest : alone;
+            }
+            // sources one CTA walks (the longest split) + its prologue / epilogue, in source iterations
+            const double cta_src = (double)((p.tiles_total + k - 1) / k) * kTileSrc + 32.0;
+            double cost = waves * (double)wave * (double)tile_tgts * cta_src / rate;
+            if (k > 1) cost += 3.5 * (double)(k + 1) * (double)M;          // partial sums written, read, reduced
+            if (p.tp == 0 || cost < best_cost * 0.99) {                     // ties: fewer splits, more targets per thread
+                best_cost = cost;
+                p.tp = tp;
+                p.nsplit = k;
+                p.m_tiles = (int)m_tiles;
+            }
+            if (ctas >= 8 * wave) break;                                    // deep enough: stop splitting
+        }
     }
-    p.nsplit = best;
-    if (force_nsplit > 0) p.nsplit = force_nsplit > p.tiles_total ? p.tiles_total : force_nsplit;
     p.packed_bytes = (size_t)round_up(p.S_pad * kSrcBytes, 256);
     p.partial_bytes = p.nsplit > 1 ? (size_t)round_up((int64_t)p.nsplit * M * 3 * sizeof(float), 256) : 0;
     return p;
@@ -468,7 +511,15 @@ size_t pairs_workspace_bytes(int64_t S, int64_t M) {
     if (S < 1) S = 1;
     if (M < 1) M = 1;
     const PairPlan p = make_pair_plan(S, M, sm_count_cached(), 0, 0);
-    size_t core = p.packed_bytes + p.partial_bytes;
+    // callers size one workspace for their LARGEST source set and reuse it for smaller ones (the greedy drivers),
+    // and a smaller set may want more splits: cover the plans of the smaller tile counts too (run_pairs clamps
+    // the split count to what fits in any case)
+    size_t partial = p.partial_bytes;
+    for (int64_t t = 1; t < p.tiles_total; t += (t < 8 ? 1 : t / 4)) {
+        const PairPlan q = make_pair_plan(t * kTileSrc, M, sm_count_cached(), 0, 0);
+        if (q.partial_bytes > partial) partial = q.partial_bytes;
+    }
+    size_t core = p.packed_bytes + partial;
     if (use_const_path(S, M, 0)) {
         const size_t c = cpairs_workspace_bytes(S, M);
         if (c > core) core = c;
@@ -480,11 +531,11 @@ size_t pairs_workspace_bytes(int64_t S, int64_t M) {
 template <int TP, bool kPot>
 static int launch_pairs_tp(const PairPlan& plan, const float4* packed, const float* tgt, int64_t M,
                            int64_t ld_t, int lattice_n, float eps, float* partial, const PairEpilogue& ep,
-                           cudaStream_t stream) {
+                           const SourceSelect& sel, cudaStream_t stream) {
     dim3 grid((unsigned)plan.m_tiles, (unsigned)plan.nsplit);
     timer_mark(stream);
     pairs_kernel<TP, kPot><<<grid, kBlock, kSmemBytes, stream>>>(packed, plan.tiles_total, plan.nsplit, tgt, M,
-                                                                 ld_t, lattice_n, eps, partial, ep);
+                                                                 ld_t, lattice_n, eps, partial, ep, sel);
     timer_mark(stream);
     count_launch(1);
     return DNP_OK;
@@ -493,13 +544,25 @@ static int launch_pairs_tp(const PairPlan& plan, const float4* packed, const flo
 int run_pairs(bool potential, const float* src, int64_t S, int64_t ld_s, const int64_t* src_idx,
               const float* tgt, int64_t M, int64_t ld_t, int lattice_n, float eps,
               const PairEpilogue& ep, void* workspace, size_t workspace_bytes, cudaStream_t stream,
-              int force_tp, int force_nsplit, const float* src_host_dense) {
+              int force_tp, int force_nsplit, const float* src_host_dense, SourceSelect sel) {
     if (M <= 0) return DNP_OK;
-    if (force_tp <= 0 && force_nsplit <= 0 && use_const_path(S, M, lattice_n) &&
+    if (sel.patch && (!src_idx || !sel.offsets)) {
+        set_error("device-selected sources need src_idx and offsets");
+        return DNP_ERR_INVALID;
+    }
+    if (!sel.patch && force_tp <= 0 && force_nsplit <= 0 && use_const_path(S, M, lattice_n) &&
         (src_host_dense || !stream_is_capturing(stream)))     // the by-value path synchronises once: never under capture
         return run_cpairs(potential, src, S, ld_s, src_idx, src_host_dense, tgt, M, ld_t, eps, ep, workspace,
                           workspace_bytes, stream);
-    const PairPlan plan = make_pair_plan(S, M, sm_count_cached(), force_tp, force_nsplit);
+    PairPlan plan = make_pair_plan(S, M, sm_count_cached(), force_tp, force_nsplit);
+    if (workspace && plan.nsplit > 1 && workspace_bytes < plan.packed_bytes + plan.partial_bytes) {
+        // a workspace sized for another source count: keep the splits that fit
+        const size_t per_split = (size_t)M * 3 * sizeof(float);
+        const size_t room = workspace_bytes > plan.packed_bytes ? workspace_bytes - plan.packed_bytes : 0;
+        const int fit = (int)(room / per_split < 64 ? room / per_split : 64);
+        plan.nsplit = fit >= 2 ? (fit < plan.nsplit ? fit : plan.nsplit) : 1;
+        plan.partial_bytes = plan.nsplit > 1 ? (size_t)plan.nsplit * per_split : 0;
+    }
     if (!workspace || workspace_bytes < plan.packed_bytes + plan.partial_bytes) {
         set_error("workspace too small: need %zu bytes, got %zu", plan.packed_bytes + plan.partial_bytes,
                   workspace_bytes);
@@ -512,14 +575,15 @@ int run_pairs(bool potential, const float* src, int64_t S, int64_t ld_s, const i
     {
         const int threads = 256;
         const unsigned blocks = (unsigned)((plan.S_pad + threads - 1) / threads);
-        pack_sources_kernel<<<blocks, threads, 0, stream>>>(src, S < 0 ? 0 : S, ld_s, src_idx, plan.S_pad, packed);
+        if (sel.patch) pack_selected_kernel<<<blocks, threads, 0, stream>>>(src, ld_s, src_idx, sel, plan.S_pad, packed);
+        else pack_sources_kernel<<<blocks, threads, 0, stream>>>(src, S < 0 ? 0 : S, ld_s, src_idx, plan.S_pad, packed);
         count_launch(1);
     }
     const float4* pk = packed;
     int rc;
 #define DNP_LAUNCH(TP)                                                                                       \
-    rc = potential ? launch_pairs_tp<TP, true>(plan, pk, tgt, M, ld_t, lattice_n, eps, partial, ep, stream)  \
-                   : launch_pairs_tp<TP, false>(plan, pk, tgt, M, ld_t, lattice_n, eps, partial, ep, stream)
+    rc = potential ? launch_pairs_tp<TP, true>(plan, pk, tgt, M, ld_t, lattice_n, eps, partial, ep, sel, stream)  \
+                   : launch_pairs_tp<TP, false>(plan, pk, tgt, M, ld_t, lattice_n, eps, partial, ep, sel, stream)
     switch (plan.tp) {
         case 4: DNP_LAUNCH(4); break;
         case 2: DNP_LAUNCH(2); break;

@@ -22,6 +22,14 @@ struct PairEpilogue {
     int32_t* nonfinite = nullptr;
 };
 
+// Sources chosen on the device (the device-driven greedy loop, dnp_drivers.cu): the source rows are
+// src_idx[offsets[*patch] .. offsets[*patch + 1]); the S given to run_pairs is then only the upper bound the launch
+// is planned for.  *patch < 0: no sources.
+struct SourceSelect {
+    const int32_t* patch = nullptr;
+    const int64_t* offsets = nullptr;
+};
+
 struct PairPlan {
     int tp = 2;            // target pairs per thread (2*tp targets)
     int nsplit = 1;        // source splits (grid.y)
@@ -51,7 +59,8 @@ size_t pairs_workspace_bytes(int64_t S, int64_t M);
 int run_pairs(bool potential, const float* src, int64_t S, int64_t ld_s, const int64_t* src_idx,
               const float* tgt, int64_t M, int64_t ld_t, int lattice_n, float eps,
               const PairEpilogue& ep, void* workspace, size_t workspace_bytes, cudaStream_t stream,
-              int force_tp = 0, int force_nsplit = 0, const float* src_host_dense = nullptr);
+              int force_tp = 0, int force_nsplit = 0, const float* src_host_dense = nullptr,
+              SourceSelect sel = SourceSelect());
 
 // Large calls: sources passed by value through the kernel-parameter constant bank (dnp_cpairs.cu).
 bool use_const_path(int64_t S, int64_t M, int lattice_n);

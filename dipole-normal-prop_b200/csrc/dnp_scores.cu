@@ -122,7 +122,7 @@ patch_interactions_kernel(const float* __restrict__ E, int64_t ld_e, const float
 // first maximal |out[p]| among active patches (torch abs().argmax() on the remaining list)
 __global__ void __launch_bounds__(1024)
 patch_argmax_kernel(const float* __restrict__ vals, const uint8_t* __restrict__ active, int64_t P,
-                    int32_t* __restrict__ best_idx, float* __restrict__ best_val) {
+                    int32_t* __restrict__ best_idx, float* __restrict__ best_val, PatchAdvance adv) {
     __shared__ unsigned long long warp_best[32];
     unsigned long long best = 0ull;
     for (int64_t p = threadIdx.x; p < P; p += blockDim.x) {
@@ -146,11 +146,20 @@ patch_argmax_kernel(const float* __restrict__ vals, const uint8_t* __restrict__ 
             if (other > best) best = other;
         }
         if (threadIdx.x == 0) {
-            if (best == 0ull) { *best_idx = -1; *best_val = 0.f; }
-            else {
-                const int32_t idx = (int32_t)(0xffffffffu - (uint32_t)best);
-                *best_idx = idx;
-                *best_val = vals[idx];
+            int32_t idx = -1;
+            float val = 0.f;
+            if (best != 0ull) {
+                idx = (int32_t)(0xffffffffu - (uint32_t)best);
+                val = vals[idx];
+            }
+            *best_idx = idx;
+            *best_val = val;
+            if (adv.cur) {                       // device-driven loop: the winner becomes the next step's patch
+                adv.cur[2] = adv.cur[0];
+                adv.cur[0] = idx;
+                adv.cur[1] = val < 0.f;          // field_utils.py:250,322
+                if (adv.order) adv.order[adv.step] = idx;
+                if (adv.value) adv.value[adv.step] = val;
             }
         }
     }
@@ -235,13 +244,13 @@ int run_edge_interactions_batched(const float* pts, int64_t ld, const int64_t* p
 
 int run_patch_interactions(const float* E, int64_t ld_e, const float* normals, int64_t ld_n, const int64_t* perm,
                            const int64_t* offsets, int64_t P, const uint8_t* active, float* out,
-                           int32_t* best_idx, float* best_val, cudaStream_t stream) {
+                           int32_t* best_idx, float* best_val, cudaStream_t stream, PatchAdvance adv) {
     if (P <= 0) return DNP_OK;
     patch_interactions_kernel<<<(unsigned)P, kEdgeThreads, 0, stream>>>(E, ld_e, normals, ld_n, perm, offsets, active,
                                                                        out);
     count_launch(1);
     if (best_idx && best_val) {
-        patch_argmax_kernel<<<1, 1024, 0, stream>>>(out, active, P, best_idx, best_val);
+        patch_argmax_kernel<<<1, 1024, 0, stream>>>(out, active, P, best_idx, best_val, adv);
         count_launch(1);
     }
     DNP_CHECK_CUDA(cudaGetLastError());

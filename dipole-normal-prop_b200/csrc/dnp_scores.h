@@ -13,9 +13,18 @@ int run_edge_interactions_batched(const float* pts, int64_t ld, const int64_t* p
                                   const int64_t* edges, int64_t n_edges, float eps, float* out,
                                   cudaStream_t stream);
 
+// Optional tail of the arg-max for the device-driven greedy loop (dnp_drivers.cu): cur = {patch, flip, previous
+// patch} is advanced to the winner on the device, order / value (device, optional) record the trace at `step`.
+struct PatchAdvance {
+    int32_t* cur = nullptr;
+    int32_t* order = nullptr;
+    float* value = nullptr;
+    int step = 0;
+};
+
 int run_patch_interactions(const float* E, int64_t ld_e, const float* normals, int64_t ld_n, const int64_t* perm,
                            const int64_t* offsets, int64_t P, const uint8_t* active, float* out,
-                           int32_t* best_idx, float* best_val, cudaStream_t stream);
+                           int32_t* best_idx, float* best_val, cudaStream_t stream, PatchAdvance adv = PatchAdvance());
 
 int run_patch_covariance(const float* pts, int64_t ld, const int64_t* perm, const int64_t* offsets, int64_t P,
                          double* cov, cudaStream_t stream);

@@ -19,13 +19,19 @@ def _patches(perm, off):
     return [torch.from_numpy(perm[off[i]:off[i + 1]].copy()) for i in range(len(off) - 1)]
 
 
-def _spy_order(fu, monkeypatch, native):
+LOOPS = ["device", "host", "per_call"]
+
+
+def _spy_order(fu, monkeypatch, loop):
     """Greedy visit order (after the start patch) as the product decides it: from the trace of the native loop
-    (dnp_patch_propagate_f32) or, with the per-call loop, from every 8-byte read of the arg-max."""
+    (dnp_patch_propagate_f32, device-driven or host-driven schedule) or, with the per-call loop, from every 8-byte
+    read of the arg-max."""
     import dnp_native
     order = []
+    native = loop != "per_call"
     monkeypatch.setattr(fu, "NATIVE_PATCH_LOOP", native)
     if native:
+        monkeypatch.setenv("DNP_PATCH_LOOP", loop)
         real = dnp_native.patch_propagate
 
         def spy(*a, **k):
@@ -238,14 +244,14 @@ def test_field_sign_streamed(dev):
 
 
 # ------------------------------------------------------------------ a7: patch propagation (cfg2, data/fandisk.xyz)
-@pytest.mark.parametrize("native", [True, False])
+@pytest.mark.parametrize("loop", LOOPS)
 @pytest.mark.parametrize("tag,diffuse,use_w", [("plain", False, False), ("diffuse_w", True, True)])
-def test_patch_propagation_golden(fu, golden, dev, tag, diffuse, use_w, native, monkeypatch):
+def test_patch_propagation_golden(fu, golden, dev, tag, diffuse, use_w, loop, monkeypatch):
     g = golden("patch_prop")
     patches = _patches(g["perm"], g["offsets"])
     kept = [(int(i), patches[int(i)]) for i in g["kept_ids"]]
     # record the greedy order through the product's own call into the ABI
-    order = _spy_order(fu, monkeypatch, native)
+    order = _spy_order(fu, monkeypatch, loop)
     pts = torch.from_numpy(g["pc_in"].copy()).to(dev)
     weights = torch.from_numpy(g["weights"].copy()).to(dev) if use_w else None
     ret = fu.strongest_field_propagation(pts, kept, patches, diffuse=diffuse, weights=weights)
@@ -268,12 +274,12 @@ def test_patch_propagation_cpu_tensor(fu, golden):
 
 
 # ------------------------------------------------------------------ a8: representative-point propagation (cfg3 stand-in)
-@pytest.mark.parametrize("native", [True, False])
+@pytest.mark.parametrize("loop", LOOPS)
 @pytest.mark.parametrize("tag,diffuse", [("plain", False), ("diffuse", True)])
-def test_reps_propagation_golden(fu, golden, dev, tag, diffuse, native, monkeypatch):
+def test_reps_propagation_golden(fu, golden, dev, tag, diffuse, loop, monkeypatch):
     g = golden("reps_prop")
     reps = list(zip(_patches(g["rep_perm"], g["rep_off"]), _patches(g["rest_perm"], g["rest_off"])))
-    order = _spy_order(fu, monkeypatch, native)
+    order = _spy_order(fu, monkeypatch, loop)
     pts = torch.from_numpy(g["pc_in"].copy()).to(dev)
     assert fu.strongest_field_propagation_reps(pts, reps, diffuse=diffuse) is None
     assert order == list(g[f"{tag}_order"][1:])
@@ -297,9 +303,13 @@ def test_reps_propagation_weights_vs_oracle(fu, golden, orc, dev):
 
 @pytest.mark.parametrize("diffuse", [False, True])
 def test_native_patch_loop_equals_per_call_loop(fu, dev, diffuse, monkeypatch):
-    """dnp_patch_propagate_f32 against the per-kernel-call loop on a synthetic cloud with ragged patches (sizes
-    1 .. 700, an empty remainder, representatives + rest): same kernels in the same order, so the normals must be
-    bit-identical."""
+    """dnp_patch_propagate_f32 (both schedules) against the per-kernel-call loop on a synthetic cloud with ragged
+    patches (sizes 1 .. 700, an empty remainder, representatives + rest).  The host-driven schedule launches the
+    same kernels with the same shapes as the per-call loop: bit-identical normals.  The device-driven schedule
+    shapes every launch for the largest patch (a different source split, so a different float32 summation order
+    of the running field): same decisions -- every normal's sign and the visit order -- and the same values where
+    the normals are only flipped."""
+    import dnp_native
     g = torch.Generator().manual_seed(123)
     n = 12000
     d = torch.randn(n, 3, generator=g)
@@ -311,17 +321,21 @@ def test_native_patch_loop_equals_per_call_loop(fu, dev, diffuse, monkeypatch):
     for pt in patches[::3]:
         pc[pt, 3:] *= -1
     reps = [(pt[:200], pt[200:]) for pt in patches]
-    out = {}
-    for native in (True, False):
-        monkeypatch.setattr(fu, "NATIVE_PATCH_LOOP", native)
+    out, orders = {}, {}
+    for loop in LOOPS:
+        monkeypatch.undo()
+        orders[loop] = _spy_order(fu, monkeypatch, loop)
         a = pc.clone().to(dev)
         fu.strongest_field_propagation(a, [(i, pt) for i, pt in enumerate(patches)], patches, diffuse=diffuse)
         b = pc.clone().to(dev)
         fu.strongest_field_propagation_reps(b, reps, diffuse=diffuse)
-        out[native] = (a.cpu(), b.cpu())
-    assert torch.equal(out[True][0], out[False][0])
-    assert torch.equal(out[True][1], out[False][1])
-    radial = (out[True][0][:, 3:] * d).sum(-1)
+        out[loop] = (a.cpu(), b.cpu())
+    assert torch.equal(out["host"][0], out["per_call"][0])
+    assert torch.equal(out["host"][1], out["per_call"][1])
+    assert orders["device"] == orders["host"] == orders["per_call"]
+    assert torch.equal(out["device"][0], out["host"][0])                  # pure sign flips either way
+    assert torch.equal(out["device"][1], out["host"][1])
+    radial = (out["device"][0][:, 3:] * d).sum(-1)
     assert abs(torch.sign(radial).mean()) > 0.99
 
 

@@ -153,6 +153,38 @@ def test_kernel_variants(fu, orc, dev, force, tp, nsplit):
     check_phi(phi, orc.potential(src.numpy(), tgt.numpy()), f"tp={tp} nsplit={nsplit}")
 
 
+@pytest.mark.parametrize("S,M", [(1000, 250000), (2000, 65536), (500, 300000)])
+def test_planned_splits_match_the_single_pass(fu, dev, force, S, M):
+    """Mid-size calls (a patch against every representative): the plan's (targets per thread, splits) choice is a
+    scheduling decision only -- same field as the unsplit TP4 kernel up to float32 summation order."""
+    src, tgt = cloud(S, 11).to(dev), cloud(M, 12).to(dev)
+    force(None, None)
+    E = fu.field_grad(src, tgt)
+    force(4, 1)
+    E_ref = fu.field_grad(src, tgt)
+    scale = E_ref.abs().max().item()
+    assert (E - E_ref).abs().max().item() <= 2e-5 * scale
+
+
+def test_workspace_sized_for_another_source_count(fu, dev, monkeypatch):
+    """The greedy drivers size one workspace for their largest patch: a call whose plan wants more splits than the
+    workspace has room for keeps the splits that fit instead of failing."""
+    import dnp_native as dn
+    S, M = 2000, 65536                                            # plan: 4 splits
+    src, tgt = cloud(S, 13).to(dev), cloud(M, 14).to(dev)
+    E_ref = fu.field_grad(src, tgt)
+    packed = 2048 * 48                                            # 3 float4 per packed source
+    for room_splits in (0, 2.5):
+        nbytes = packed + int(room_splits * M * 12)
+        monkeypatch.setattr(dn, "_workspace",
+                            lambda s, m, d, nb=nbytes: (torch.empty(nb, dtype=torch.uint8, device=d), nb))
+        E = fu.field_grad(src, tgt)
+        assert (E - E_ref).abs().max().item() <= 2e-5 * E_ref.abs().max().item()
+    monkeypatch.setattr(dn, "_workspace", lambda s, m, d: (torch.empty(1024, dtype=torch.uint8, device=d), 1024))
+    with pytest.raises(Exception, match="workspace too small"):
+        fu.field_grad(src, tgt)
+
+
 def test_surface_cloud_with_near_pairs(fu, orc, dev):
     """Noisy-sphere cloud evaluated on itself shifted by 1e-4: near-singular pairs, eps matters."""
     g = torch.Generator().manual_seed(77)
