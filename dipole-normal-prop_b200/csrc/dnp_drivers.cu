@@ -89,6 +89,79 @@ __global__ void mask_clear_selected_kernel(uint8_t* __restrict__ mask, const int
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) mask[perm[o + i]] = 0;
 }
 
+// ---- the device-driven step head as ONE single-CTA kernel (patches + rest rows up to kFusedRows): first
+// abs-arg-max over the interactions of the previous step -> cur, un-mark the previous patch (diffuse), flip + mark
+// the winner's rows, and write them in the all-pairs kernel's packed source layout (null dipoles up to pad_rows).
+// Four dependent launches (arg-max, un-mark, commit, pack) become one; at fandisk size a launch costs as much as
+// the field kernel itself.
+constexpr int64_t kFusedRows = 32768;
+
+__global__ void __launch_bounds__(1024)
+patch_step_kernel(const float* __restrict__ inter, int64_t P, int do_argmax, int32_t start, int step,
+                  int32_t* __restrict__ cur, int32_t* __restrict__ order, float* __restrict__ value,
+                  float* __restrict__ pts, int64_t ld, const int64_t* __restrict__ perm,
+                  const int64_t* __restrict__ offsets, const int64_t* __restrict__ rest_perm,
+                  const int64_t* __restrict__ rest_offsets, uint8_t* __restrict__ settled,
+                  uint8_t* __restrict__ scratch, uint8_t* __restrict__ active, float4* __restrict__ packed,
+                  int64_t pad_rows) {
+    __shared__ unsigned long long warp_best[32];
+    __shared__ int32_t sh[3];
+    if (do_argmax) {
+        const unsigned long long best = block_first_absmax(inter, active, P, warp_best);
+        if (threadIdx.x == 0) {
+            int32_t idx = -1;
+            float val = 0.f;
+            if (best != 0ull) {
+                idx = (int32_t)(0xffffffffu - (uint32_t)best);
+                val = inter[idx];
+            }
+            sh[2] = cur[0];
+            sh[0] = idx;
+            sh[1] = val < 0.f;                                                    // field_utils.py:250,322
+            if (value) value[step] = val;
+        }
+    } else if (threadIdx.x == 0) {
+        sh[0] = start; sh[1] = 0; sh[2] = -1;
+        if (value) value[step] = 0.f;
+    }
+    __syncthreads();
+    const int patch = sh[0], flip = sh[1], prev = sh[2];
+    if (threadIdx.x == 0) {
+        cur[0] = patch; cur[1] = flip; cur[2] = prev;
+        if (order) order[step] = patch;
+    }
+    if (scratch && prev >= 0) {                                                   // :256-261: only the source patch is skipped
+        const int64_t po = offsets[prev], pn = offsets[prev + 1] - po;
+        for (int64_t i = threadIdx.x; i < pn; i += blockDim.x) scratch[perm[po + i]] = 0;
+        __syncthreads();
+    }
+    const int64_t o = patch < 0 ? 0 : offsets[patch], n = patch < 0 ? 0 : offsets[patch + 1] - o;
+    const int64_t ro = (rest_perm && patch >= 0) ? rest_offsets[patch] : 0;
+    const int64_t rn = (rest_perm && patch >= 0) ? rest_offsets[patch + 1] - ro : 0;
+    for (int64_t i = threadIdx.x; i < n; i += blockDim.x) {
+        const int64_t r = perm[o + i];
+        float* q = pts + r * ld;
+        float v[6];
+#pragma unroll
+        for (int c = 0; c < 6; ++c) v[c] = q[c];
+        if (flip) {
+            v[3] = -v[3]; v[4] = -v[4]; v[5] = -v[5];
+            q[3] = v[3]; q[4] = v[4]; q[5] = v[5];
+        }
+        settled[r] = 1;
+        if (scratch) scratch[r] = 1;
+        pack_source_row(v, packed + 3 * i);
+    }
+    if (flip)
+        for (int64_t i = threadIdx.x; i < rn; i += blockDim.x) {
+            float* q = pts + rest_perm[ro + i] * ld + 3;
+            q[0] = -q[0]; q[1] = -q[1]; q[2] = -q[2];
+        }
+    const float zero[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    for (int64_t i = n + threadIdx.x; i < pad_rows; i += blockDim.x) pack_source_row(zero, packed + 3 * i);
+    if (threadIdx.x == 0 && patch >= 0) active[patch] = 0;
+}
+
 __global__ void cur_init_kernel(int32_t* cur, int32_t start, int32_t* order, float* value) {
     cur[0] = start; cur[1] = 0; cur[2] = -1; cur[3] = 0;
     if (order) order[0] = start;
@@ -195,15 +268,38 @@ int run_patch_propagate(float* pts, int64_t N, int64_t ld, const int64_t* perm, 
             DNP_CHECK_CUDA(cudaMemcpyAsync(rest_off_dev, rest_offsets_host, (size_t)(P + 1) * sizeof(int64_t),
                                            cudaMemcpyHostToDevice, stream));
         }
+        SourceSelect sel;
+        sel.patch = cur;
+        sel.offsets = offsets_dev;
+        // single-CTA step head when the rows one step touches are few (always, short of 32k-row patches)
+        const bool fused = max_patch + max_rest <= kFusedRows && !getenv("DNP_PATCH_LOOP_UNFUSED");
+        if (fused) {
+            const PairPlan plan = make_pair_plan(max_patch > 0 ? max_patch : 1, M > 0 ? M : 1, sm_count_cached(), 0, 0);
+            sel.prepacked = true;
+            for (int64_t step = 0; step < P; ++step) {
+                patch_step_kernel<<<1, 1024, 0, stream>>>(
+                    inter, P, step > 0, (int32_t)start_patch, (int)step, cur, order_dev, value_dev, pts, ld, perm,
+                    offsets_dev, rest_perm, rest_perm ? rest_off_dev : nullptr, settled, diffuse ? scratch : nullptr,
+                    active, reinterpret_cast<float4*>(pairs_ws), plan.S_pad);
+                count_launch(1);
+                ep.mode = step == 0 ? DNP_EPI_STORE : DNP_EPI_ACCUM;
+                if (max_patch > 0 && M > 0) {
+                    const int rc = run_pairs(false, pts, max_patch, ld, perm, pts, M, ld, 0, eps, ep, pairs_ws,
+                                             L.pairs_bytes, stream, 0, 0, nullptr, sel);
+                    if (rc != DNP_OK) return rc;
+                }
+                if (step == P - 1) break;
+                const int rc = run_patch_interactions(E, ld_e, normals, ld, perm, offsets_dev, P, active, inter,
+                                                      nullptr, nullptr, stream);
+                if (rc != DNP_OK) return rc;
+            }
+        } else {
         cur_init_kernel<<<1, 1, 0, stream>>>(cur, (int32_t)start_patch, order_dev, value_dev);
         count_launch(1);
         const int64_t commit_work = max_patch + max_rest > 0 ? max_patch + max_rest : 1;
         const int64_t commit_want = (commit_work + 255) / 256, clear_want = (max_patch + 255) / 256;
         const unsigned commit_blocks = (unsigned)(commit_want < 1184 ? commit_want : 1184);
         const unsigned clear_blocks = (unsigned)(clear_want < 1184 ? clear_want : 1184);
-        SourceSelect sel;
-        sel.patch = cur;
-        sel.offsets = offsets_dev;
         for (int64_t step = 0; step < P; ++step) {
             if (diffuse && step > 0 && max_patch > 0) {
                 mask_clear_selected_kernel<<<clear_blocks, 256, 0, stream>>>(scratch, perm, offsets_dev, cur);
@@ -228,6 +324,7 @@ int run_patch_propagate(float* pts, int64_t N, int64_t ld, const int64_t* perm, 
             const int rc = run_patch_interactions(E, ld_e, normals, ld, perm, offsets_dev, P, active, inter, best_idx,
                                                   best_val, stream, adv);
             if (rc != DNP_OK) return rc;
+        }
         }
         if (order_host)
             DNP_CHECK_CUDA(cudaMemcpyAsync(order_host, order_dev, (size_t)P * sizeof(int32_t), cudaMemcpyDeviceToHost,

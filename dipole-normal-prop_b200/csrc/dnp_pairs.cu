@@ -36,10 +36,10 @@ namespace {
 
 constexpr int kBlock = 128;                      // threads per CTA
 constexpr int kTileSrc = 256;                    // sources per shared-memory stage
+constexpr int kTileSmall = 64;                   // ... for calls too small to fill the machine with 256-source tiles
 constexpr int kStages = 3;                       // TMA ring depth
 constexpr int kSrcBytes = 48;                    // packed bytes per source
-constexpr uint32_t kTileBytes = kTileSrc * kSrcBytes;
-constexpr size_t kSmemBytes = size_t(kStages) * kTileBytes + kStages * sizeof(uint64_t);
+constexpr size_t smem_bytes(int tile_src) { return size_t(kStages) * tile_src * kSrcBytes + kStages * sizeof(uint64_t); }
 constexpr float kRsqrtClamp = 1.152921504606847e18f;   // 2^60: clamp^2 is finite (field: c = d w u^2)
 constexpr float kRsqrtClampPhi = 1.099511627776e12f;   // 2^40: clamp^3 is finite (potential: d u^3)
 
@@ -55,9 +55,7 @@ __global__ void pack_sources_kernel(const float* __restrict__ src, int64_t S, in
 #pragma unroll
         for (int c = 0; c < 6; ++c) v[c] = __ldg(p + c);
     }
-    packed[3 * s + 0] = make_float4(v[0], v[1], v[2], v[3]);
-    packed[3 * s + 1] = make_float4(v[4], v[5], v[3] * -3.f, v[4] * -3.f);
-    packed[3 * s + 2] = make_float4(v[5] * -3.f, 0.f, 0.f, 0.f);
+    pack_source_row(v, packed + 3 * s);
 }
 
 // the same for a source range chosen on the device: rows idx[o .. o + n) of patch *sel.patch, null dipoles up to S_pad
@@ -73,9 +71,7 @@ __global__ void pack_selected_kernel(const float* __restrict__ src, int64_t ld_s
 #pragma unroll
         for (int c = 0; c < 6; ++c) v[c] = __ldg(p + c);
     }
-    packed[3 * s + 0] = make_float4(v[0], v[1], v[2], v[3]);
-    packed[3 * s + 1] = make_float4(v[4], v[5], v[3] * -3.f, v[4] * -3.f);
-    packed[3 * s + 2] = make_float4(v[5] * -3.f, 0.f, 0.f, 0.f);
+    pack_source_row(v, packed + 3 * s);
 }
 
 // ------------------------------------------------------------------ epilogue (K7)
@@ -187,7 +183,7 @@ __device__ __forceinline__ void pair_potential_x2(const SrcX2& s, f32x2 qx, f32x
 
 // ------------------------------------------------------------------ the all-pairs kernel
 // grid.x = target tiles of kBlock*2*TP targets, grid.y = source splits.
-template <int TP, bool kPotential>
+template <int TP, bool kPotential, int TS>
 __global__ void __launch_bounds__(kBlock, (TP >= 4 ? 3 : (TP == 2 ? 5 : 8)))
 pairs_kernel(const float4* __restrict__ packed, int tiles_total, int nsplit,
              const float* __restrict__ tgt, int64_t M, int64_t ld_t, int lattice_n,
@@ -196,10 +192,10 @@ pairs_kernel(const float4* __restrict__ packed, int tiles_total, int nsplit,
     if (sel.patch) {                                 // device-chosen source range: only its tiles are walked
         const int pj = *sel.patch;
         const int64_t n = pj < 0 ? 0 : sel.offsets[pj + 1] - sel.offsets[pj];
-        tiles_total = (int)((n + kTileSrc - 1) / kTileSrc);
+        tiles_total = (int)((n + TS - 1) / TS);
     }
     float4* stage_buf = reinterpret_cast<float4*>(smem_raw);
-    uint64_t* bars = reinterpret_cast<uint64_t*>(smem_raw + size_t(kStages) * kTileBytes);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem_raw + size_t(kStages) * (uint32_t)(TS * kSrcBytes));
 
     const int tid = threadIdx.x;
     const int64_t tile_base = (int64_t)blockIdx.x * (kBlock * 2 * TP);
@@ -216,9 +212,9 @@ pairs_kernel(const float4* __restrict__ packed, int tiles_total, int nsplit,
     __syncthreads();
     if (tid == 0) {
         for (int i = 0; i < kStages && i < n_tiles; ++i) {
-            mbar_arrive_expect_tx(&bars[i], kTileBytes);
-            tma_bulk_g2s(stage_buf + size_t(i) * kTileSrc * 3,
-                         packed + size_t(t_begin + i) * kTileSrc * 3, kTileBytes, &bars[i]);
+            mbar_arrive_expect_tx(&bars[i], (uint32_t)(TS * kSrcBytes));
+            tma_bulk_g2s(stage_buf + size_t(i) * TS * 3,
+                         packed + size_t(t_begin + i) * TS * 3, (uint32_t)(TS * kSrcBytes), &bars[i]);
         }
     }
 
@@ -258,14 +254,14 @@ pairs_kernel(const float4* __restrict__ packed, int tiles_total, int nsplit,
     for (int it = 0; it < n_tiles; ++it) {
         const int st = it % kStages;
         mbar_wait(&bars[st], (uint32_t)((it / kStages) & 1));
-        const float4* sp = stage_buf + size_t(st) * kTileSrc * 3;
+        const float4* sp = stage_buf + size_t(st) * TS * 3;
 
         if (kPotential) {
             f32x2 phi[TP];
 #pragma unroll
             for (int j = 0; j < TP; ++j) phi[j] = zero2;
 #pragma unroll 2
-            for (int s = 0; s < kTileSrc; ++s) {
+            for (int s = 0; s < TS; ++s) {
                 const SrcX2 src(sp[3 * s], sp[3 * s + 1], sp[3 * s + 2]);
 #pragma unroll
                 for (int j = 0; j < TP; ++j) pair_potential_x2(src, qx[j], qy[j], qz[j], phi[j]);
@@ -277,7 +273,7 @@ pairs_kernel(const float4* __restrict__ packed, int tiles_total, int nsplit,
 #pragma unroll
             for (int j = 0; j < TP; ++j) { ax[j] = ay[j] = az[j] = zero2; }
 #pragma unroll 2
-            for (int s = 0; s < kTileSrc; ++s) {
+            for (int s = 0; s < TS; ++s) {
                 const SrcX2 src(sp[3 * s], sp[3 * s + 1], sp[3 * s + 2]);
 #pragma unroll
                 for (int j = 0; j < TP; ++j)
@@ -293,9 +289,9 @@ pairs_kernel(const float4* __restrict__ packed, int tiles_total, int nsplit,
 
         __syncthreads();                                  // every warp is done with stage `st`
         if (tid == 0 && it + kStages < n_tiles) {
-            mbar_arrive_expect_tx(&bars[st], kTileBytes);
-            tma_bulk_g2s(stage_buf + size_t(st) * kTileSrc * 3,
-                         packed + size_t(t_begin + it + kStages) * kTileSrc * 3, kTileBytes, &bars[st]);
+            mbar_arrive_expect_tx(&bars[st], (uint32_t)(TS * kSrcBytes));
+            tma_bulk_g2s(stage_buf + size_t(st) * TS * 3,
+                         packed + size_t(t_begin + it + kStages) * TS * 3, (uint32_t)(TS * kSrcBytes), &bars[st]);
         }
     }
 
@@ -452,25 +448,29 @@ int sm_count_cached() {
 
 PairPlan make_pair_plan(int64_t S, int64_t M, int sm_count, int force_tp, int force_nsplit) {
     PairPlan p;
-    p.tiles_total = (int)((S + kTileSrc - 1) / kTileSrc);
-    if (p.tiles_total < 1) p.tiles_total = 1;
-    p.S_pad = (int64_t)p.tiles_total * kTileSrc;
-    // (targets per thread, source splits) by a small cost model of the grid, in units of one full wave of the
-    // candidate (resident CTAs on every SM): full waves cost 1 each; the last, partial wave costs the deepest
-    // SM's share of it, but never less than what ONE CTA needs when it has an SM to itself (few warps cannot
-    // hide the MUFU / shared-memory latency); a split adds the reduction pass over its partial sums.  The
-    // constants are from tools/plan_probe.py on B200 (profiles/README.md): before this the S = 500, M = 524288
-    // step of the representatives loop ran 512 TP4 CTAs on 444 slots, 1.15 waves at 1.13e12 pairs/s, where
-    // TP2 reaches 1.33e12.
+    // (targets per thread, source tile, source splits) by a small cost model of the grid, in units of one full
+    // wave of the candidate (resident CTAs on every SM): full waves cost 1 each; the last, partial wave costs the
+    // deepest SM's share of it, but never less than what ONE CTA needs when it has an SM to itself (few warps
+    // cannot hide the MUFU / shared-memory latency); a split adds the reduction pass over its partial sums.
+    // Calls too small to fill the machine with 256-source tiles (a 150-row patch against 11 000 points is one
+    // tile x 44 CTAs) take 64-source tiles, so that the sources can be split over more CTAs.  The constants are
+    // from tools/plan_probe.py on B200 (profiles/README.md): before this the S = 500, M = 524288 step of the
+    // representatives loop ran 512 TP4 CTAs on 444 slots, 1.15 waves at 1.13e12 pairs/s, where TP2 reaches 1.33e12.
     if (force_tp <= 0) force_tp = env_int("DNP_FORCE_TP");
     if (force_nsplit <= 0) force_nsplit = env_int("DNP_FORCE_NSPLIT");
     if (force_tp != 1 && force_tp != 2 && force_tp != 4) force_tp = 0;
-    if (force_nsplit > p.tiles_total) force_nsplit = p.tiles_total;
-    const int max_split = (int)((p.tiles_total < 64) ? p.tiles_total : 64);
+    const int force_tile = env_int("DNP_FORCE_TILE");
     double best_cost = 0.0;
     p.tp = 0;
-    for (int tp = 4; tp >= 1; tp >>= 1) {
+    for (int cand = 0; cand < 4; ++cand) {
+        const int tp = cand == 0 ? 4 : (cand == 1 ? 2 : 1);
+        const int tile = cand == 3 ? kTileSmall : kTileSrc;               // small tiles: TP1 only
         if (force_tp && tp != force_tp) continue;
+        if (force_tile > 0 ? tile != force_tile : (force_tp && tile != kTileSrc)) continue;
+        int tiles = (int)((S + tile - 1) / tile);
+        if (tiles < 1) tiles = 1;
+        const int max_split = tiles < 64 ? tiles : 64;
+        const int want_split = force_nsplit > max_split ? max_split : force_nsplit;
         const int resident = tp >= 4 ? 3 : (tp == 2 ? 5 : 8);
         const double alone = tp >= 4 ? 0.55 : (tp == 2 ? 0.40 : 0.30);    // one CTA alone on an SM / a full wave
         const double rate = tp == 2 ? 1.0 : 0.97;                          // measured steady-state rate vs TP2
@@ -479,7 +479,7 @@ PairPlan make_pair_plan(int64_t S, int64_t M, int sm_count, int force_tp, int fo
         if (m_tiles < 1) m_tiles = 1;
         const int64_t wave = (int64_t)sm_count * resident;
         for (int k = 1; k <= max_split; ++k) {
-            if (force_nsplit > 0 && k != force_nsplit) continue;
+            if (want_split > 0 && k != want_split) continue;
             const int64_t ctas = m_tiles * k;
             const int64_t full = ctas / wave, tail = ctas - full * wave;
             double waves = (double)full;
@@ -487,19 +487,24 @@ PairPlan make_pair_plan(int64_t S, int64_t M, int sm_count, int force_tp, int fo
                 const double deepest = (double)((tail + sm_count - 1) / sm_count) / resident;
                 waves += deepest > alone ? deepest : alone;
             }
-            // sources one CTA walks (the longest split) + its prologue / epilogue, in source iterations
-            const double cta_src = (double)((p.tiles_total + k - 1) / k) * kTileSrc + 32.0;
+            // sources one CTA walks (the longest split; 8 iterations' worth of barrier + fold per tile) + its
+            // prologue / epilogue, in source iterations
+            const double cta_src = (double)((tiles + k - 1) / k) * (tile + 8.0) + 32.0;
             double cost = waves * (double)wave * (double)tile_tgts * cta_src / rate;
             if (k > 1) cost += 3.5 * (double)(k + 1) * (double)M;          // partial sums written, read, reduced
+            if (k > 1) cost += 3.0e6;                                       // ... by one more launch (~2 us of pairs)
             if (p.tp == 0 || cost < best_cost * 0.99) {                     // ties: fewer splits, more targets per thread
                 best_cost = cost;
                 p.tp = tp;
+                p.tile_src = tile;
+                p.tiles_total = tiles;
                 p.nsplit = k;
                 p.m_tiles = (int)m_tiles;
             }
             if (ctas >= 8 * wave) break;                                    // deep enough: stop splitting
         }
     }
+    p.S_pad = (int64_t)p.tiles_total * p.tile_src;
     p.packed_bytes = (size_t)round_up(p.S_pad * kSrcBytes, 256);
     p.partial_bytes = p.nsplit > 1 ? (size_t)round_up((int64_t)p.nsplit * M * 3 * sizeof(float), 256) : 0;
     return p;
@@ -515,11 +520,13 @@ size_t pairs_workspace_bytes(int64_t S, int64_t M) {
     // and a smaller set may want more splits: cover the plans of the smaller tile counts too (run_pairs clamps
     // the split count to what fits in any case)
     size_t partial = p.partial_bytes;
-    for (int64_t t = 1; t < p.tiles_total; t += (t < 8 ? 1 : t / 4)) {
-        const PairPlan q = make_pair_plan(t * kTileSrc, M, sm_count_cached(), 0, 0);
+    const int64_t tiles_small = (S + kTileSmall - 1) / kTileSmall;
+    for (int64_t t = 1; t < tiles_small; t += (t < 16 ? 1 : t / 8)) {
+        const PairPlan q = make_pair_plan(t * kTileSmall, M, sm_count_cached(), 0, 0);
         if (q.partial_bytes > partial) partial = q.partial_bytes;
     }
-    size_t core = p.packed_bytes + partial;
+    const size_t packed = (size_t)round_up(round_up(S, kTileSrc) * kSrcBytes, 256);   // either tile's padding
+    size_t core = packed + partial;
     if (use_const_path(S, M, 0)) {
         const size_t c = cpairs_workspace_bytes(S, M);
         if (c > core) core = c;
@@ -528,14 +535,14 @@ size_t pairs_workspace_bytes(int64_t S, int64_t M) {
 }
 
 // ------------------------------------------------------------------ launchers
-template <int TP, bool kPot>
+template <int TP, bool kPot, int TS = kTileSrc>
 static int launch_pairs_tp(const PairPlan& plan, const float4* packed, const float* tgt, int64_t M,
                            int64_t ld_t, int lattice_n, float eps, float* partial, const PairEpilogue& ep,
                            const SourceSelect& sel, cudaStream_t stream) {
     dim3 grid((unsigned)plan.m_tiles, (unsigned)plan.nsplit);
     timer_mark(stream);
-    pairs_kernel<TP, kPot><<<grid, kBlock, kSmemBytes, stream>>>(packed, plan.tiles_total, plan.nsplit, tgt, M,
-                                                                 ld_t, lattice_n, eps, partial, ep, sel);
+    pairs_kernel<TP, kPot, TS><<<grid, kBlock, smem_bytes(TS), stream>>>(packed, plan.tiles_total, plan.nsplit, tgt,
+                                                                         M, ld_t, lattice_n, eps, partial, ep, sel);
     timer_mark(stream);
     count_launch(1);
     return DNP_OK;
@@ -575,16 +582,28 @@ int run_pairs(bool potential, const float* src, int64_t S, int64_t ld_s, const i
     {
         const int threads = 256;
         const unsigned blocks = (unsigned)((plan.S_pad + threads - 1) / threads);
-        if (sel.patch) pack_selected_kernel<<<blocks, threads, 0, stream>>>(src, ld_s, src_idx, sel, plan.S_pad, packed);
-        else pack_sources_kernel<<<blocks, threads, 0, stream>>>(src, S < 0 ? 0 : S, ld_s, src_idx, plan.S_pad, packed);
-        count_launch(1);
+        if (sel.patch && sel.prepacked) {
+            // packed by the caller's own kernel (dnp_drivers.cu)
+        } else {
+            if (sel.patch)
+                pack_selected_kernel<<<blocks, threads, 0, stream>>>(src, ld_s, src_idx, sel, plan.S_pad, packed);
+            else
+                pack_sources_kernel<<<blocks, threads, 0, stream>>>(src, S < 0 ? 0 : S, ld_s, src_idx, plan.S_pad,
+                                                                    packed);
+            count_launch(1);
+        }
     }
     const float4* pk = packed;
     int rc;
 #define DNP_LAUNCH(TP)                                                                                       \
     rc = potential ? launch_pairs_tp<TP, true>(plan, pk, tgt, M, ld_t, lattice_n, eps, partial, ep, sel, stream)  \
                    : launch_pairs_tp<TP, false>(plan, pk, tgt, M, ld_t, lattice_n, eps, partial, ep, sel, stream)
-    switch (plan.tp) {
+    if (plan.tile_src == kTileSmall) {
+        rc = potential ? launch_pairs_tp<1, true, kTileSmall>(plan, pk, tgt, M, ld_t, lattice_n, eps, partial, ep, sel,
+                                                              stream)
+                       : launch_pairs_tp<1, false, kTileSmall>(plan, pk, tgt, M, ld_t, lattice_n, eps, partial, ep,
+                                                               sel, stream);
+    } else switch (plan.tp) {
         case 4: DNP_LAUNCH(4); break;
         case 2: DNP_LAUNCH(2); break;
         default: DNP_LAUNCH(1); break;

@@ -28,12 +28,26 @@ struct PairEpilogue {
 struct SourceSelect {
     const int32_t* patch = nullptr;
     const int64_t* offsets = nullptr;
+    // the caller has already written the packed rows [0, plan.S_pad) at the start of the workspace
+    // (pack_source_row below; null dipoles beyond the patch): run_pairs launches no pack kernel
+    bool prepacked = false;
 };
+
+#ifdef __CUDACC__
+// One source in the layout the all-pairs kernel streams through shared memory: 48 bytes,
+// [x y z nx | ny nz -3nx -3ny | -3nz 0 0 0].
+__device__ __forceinline__ void pack_source_row(const float v[6], float4* __restrict__ dst) {
+    dst[0] = make_float4(v[0], v[1], v[2], v[3]);
+    dst[1] = make_float4(v[4], v[5], v[3] * -3.f, v[4] * -3.f);
+    dst[2] = make_float4(v[5] * -3.f, 0.f, 0.f, 0.f);
+}
+#endif
 
 struct PairPlan {
     int tp = 2;            // target pairs per thread (2*tp targets)
     int nsplit = 1;        // source splits (grid.y)
-    int tiles_total = 1;   // 256-source tiles
+    int tile_src = 256;    // sources per shared-memory tile (256, or 64 for calls too small to fill the machine)
+    int tiles_total = 1;   // source tiles
     int m_tiles = 1;       // target tiles (grid.x)
     int64_t S_pad = 0;
     size_t packed_bytes = 0;

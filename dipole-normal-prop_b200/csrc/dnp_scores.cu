@@ -124,43 +124,22 @@ __global__ void __launch_bounds__(1024)
 patch_argmax_kernel(const float* __restrict__ vals, const uint8_t* __restrict__ active, int64_t P,
                     int32_t* __restrict__ best_idx, float* __restrict__ best_val, PatchAdvance adv) {
     __shared__ unsigned long long warp_best[32];
-    unsigned long long best = 0ull;
-    for (int64_t p = threadIdx.x; p < P; p += blockDim.x) {
-        if (active && !active[p]) continue;
-        const unsigned long long k =
-            ((unsigned long long)__float_as_uint(fabsf(vals[p])) << 32) | (0xffffffffu - (uint32_t)p);
-        if (k > best) best = k;
-    }
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-        const unsigned long long other = __shfl_xor_sync(0xffffffffu, best, o);
-        if (other > best) best = other;
-    }
-    if ((threadIdx.x & 31) == 0) warp_best[threadIdx.x >> 5] = best;
-    __syncthreads();
-    if (threadIdx.x < 32) {
-        best = threadIdx.x < (blockDim.x >> 5) ? warp_best[threadIdx.x] : 0ull;
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) {
-            const unsigned long long other = __shfl_xor_sync(0xffffffffu, best, o);
-            if (other > best) best = other;
+    const unsigned long long best = block_first_absmax(vals, active, P, warp_best);
+    if (threadIdx.x == 0) {
+        int32_t idx = -1;
+        float val = 0.f;
+        if (best != 0ull) {
+            idx = (int32_t)(0xffffffffu - (uint32_t)best);
+            val = vals[idx];
         }
-        if (threadIdx.x == 0) {
-            int32_t idx = -1;
-            float val = 0.f;
-            if (best != 0ull) {
-                idx = (int32_t)(0xffffffffu - (uint32_t)best);
-                val = vals[idx];
-            }
-            *best_idx = idx;
-            *best_val = val;
-            if (adv.cur) {                       // device-driven loop: the winner becomes the next step's patch
-                adv.cur[2] = adv.cur[0];
-                adv.cur[0] = idx;
-                adv.cur[1] = val < 0.f;          // field_utils.py:250,322
-                if (adv.order) adv.order[adv.step] = idx;
-                if (adv.value) adv.value[adv.step] = val;
-            }
+        *best_idx = idx;
+        *best_val = val;
+        if (adv.cur) {                           // device-driven loop: the winner becomes the next step's patch
+            adv.cur[2] = adv.cur[0];
+            adv.cur[0] = idx;
+            adv.cur[1] = val < 0.f;              // field_utils.py:250,322
+            if (adv.order) adv.order[adv.step] = idx;
+            if (adv.value) adv.value[adv.step] = val;
         }
     }
 }

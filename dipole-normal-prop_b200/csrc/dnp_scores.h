@@ -22,6 +22,39 @@ struct PatchAdvance {
     int step = 0;
 };
 
+#ifdef __CUDACC__
+// Block-wide first maximum of |vals[p]| over the active patches, as ONE unsigned key per candidate:
+// (|v| bits << 32) | inverted index, so that the larger key is the larger |v| and, among equals, the smaller
+// index (torch's abs().argmax()).  Returned to thread 0 (0 = nothing active); warp_best: 32 shared slots.
+__device__ __forceinline__ unsigned long long block_first_absmax(const float* __restrict__ vals,
+                                                                 const uint8_t* __restrict__ active, int64_t P,
+                                                                 unsigned long long* warp_best) {
+    unsigned long long best = 0ull;
+    for (int64_t p = threadIdx.x; p < P; p += blockDim.x) {
+        if (active && !active[p]) continue;
+        const unsigned long long k =
+            ((unsigned long long)__float_as_uint(fabsf(vals[p])) << 32) | (0xffffffffu - (uint32_t)p);
+        if (k > best) best = k;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const unsigned long long other = __shfl_xor_sync(0xffffffffu, best, o);
+        if (other > best) best = other;
+    }
+    if ((threadIdx.x & 31) == 0) warp_best[threadIdx.x >> 5] = best;
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        best = threadIdx.x < (blockDim.x >> 5) ? warp_best[threadIdx.x] : 0ull;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const unsigned long long other = __shfl_xor_sync(0xffffffffu, best, o);
+            if (other > best) best = other;
+        }
+    }
+    return best;
+}
+#endif
+
 int run_patch_interactions(const float* E, int64_t ld_e, const float* normals, int64_t ld_n, const int64_t* perm,
                            const int64_t* offsets, int64_t P, const uint8_t* active, float* out,
                            int32_t* best_idx, float* best_val, cudaStream_t stream, PatchAdvance adv = PatchAdvance());

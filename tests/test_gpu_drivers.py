@@ -19,7 +19,7 @@ def _patches(perm, off):
     return [torch.from_numpy(perm[off[i]:off[i + 1]].copy()) for i in range(len(off) - 1)]
 
 
-LOOPS = ["device", "host", "per_call"]
+LOOPS = ["device", "device_unfused", "host", "per_call"]
 
 
 def _spy_order(fu, monkeypatch, loop):
@@ -31,7 +31,11 @@ def _spy_order(fu, monkeypatch, loop):
     native = loop != "per_call"
     monkeypatch.setattr(fu, "NATIVE_PATCH_LOOP", native)
     if native:
-        monkeypatch.setenv("DNP_PATCH_LOOP", loop)
+        monkeypatch.setenv("DNP_PATCH_LOOP", "host" if loop == "host" else "device")
+        if loop == "device_unfused":                      # separate arg-max / commit / pack launches per step
+            monkeypatch.setenv("DNP_PATCH_LOOP_UNFUSED", "1")
+        else:
+            monkeypatch.delenv("DNP_PATCH_LOOP_UNFUSED", raising=False)
         real = dnp_native.patch_propagate
 
         def spy(*a, **k):
@@ -332,9 +336,10 @@ def test_native_patch_loop_equals_per_call_loop(fu, dev, diffuse, monkeypatch):
         out[loop] = (a.cpu(), b.cpu())
     assert torch.equal(out["host"][0], out["per_call"][0])
     assert torch.equal(out["host"][1], out["per_call"][1])
-    assert orders["device"] == orders["host"] == orders["per_call"]
-    assert torch.equal(out["device"][0], out["host"][0])                  # pure sign flips either way
-    assert torch.equal(out["device"][1], out["host"][1])
+    assert orders["device"] == orders["device_unfused"] == orders["host"] == orders["per_call"]
+    for loop in ("device", "device_unfused"):
+        assert torch.equal(out[loop][0], out["host"][0])                  # pure sign flips either way
+        assert torch.equal(out[loop][1], out["host"][1])
     radial = (out["device"][0][:, 3:] * d).sum(-1)
     assert abs(torch.sign(radial).mean()) > 0.99
 

@@ -153,7 +153,20 @@ def test_kernel_variants(fu, orc, dev, force, tp, nsplit):
     check_phi(phi, orc.potential(src.numpy(), tgt.numpy()), f"tp={tp} nsplit={nsplit}")
 
 
-@pytest.mark.parametrize("S,M", [(1000, 250000), (2000, 65536), (500, 300000)])
+@pytest.mark.parametrize("nsplit", [None, 1, 3, 7])
+@pytest.mark.parametrize("S,M", [(5000, 3001), (150, 11031), (63, 64), (64, 1), (65, 700)])
+def test_small_source_tiles(fu, orc, dev, force, monkeypatch, S, M, nsplit):
+    """The 64-source-tile variant small calls take (a patch against a small cloud), forced at every size."""
+    monkeypatch.setenv("DNP_FORCE_TILE", "64")
+    force(None, nsplit)
+    src, tgt = cloud(S, 21), cloud(M, 22)
+    E = fu.field_grad(src.to(dev), tgt.to(dev)).cpu().numpy()
+    phi = fu.potential(src.to(dev), tgt.to(dev)).cpu().numpy()
+    check_E(E, orc.field_grad(src.numpy(), tgt.numpy()), f"tile 64 nsplit={nsplit}")
+    check_phi(phi, orc.potential(src.numpy(), tgt.numpy()), f"tile 64 nsplit={nsplit}")
+
+
+@pytest.mark.parametrize("S,M", [(1000, 250000), (2000, 65536), (500, 300000), (150, 11031)])
 def test_planned_splits_match_the_single_pass(fu, dev, force, S, M):
     """Mid-size calls (a patch against every representative): the plan's (targets per thread, splits) choice is a
     scheduling decision only -- same field as the unsplit TP4 kernel up to float32 summation order."""

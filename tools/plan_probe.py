@@ -23,6 +23,21 @@ if len(sys.argv) > 1 and sys.argv[1] == "child":
         best = min(best, a.elapsed_time(b) / 10)
     print(json.dumps({"ms": best, "pairs_per_s": S * M / best / 1e-3}))
     sys.exit(0)
+SMALL = ((150, 11031), (268, 11031), (300, 300000), (200, 100000), (700, 12000), (1000, 250000), (100, 2000))
+if os.environ.get("PLAN_SMALL") == "1":
+    for S, M in SMALL:
+        for tile, tp, ns in ((0, 0, 0), (256, 1, 1), (256, 2, 1), (64, 0, 1), (64, 0, 2), (64, 0, 3), (64, 0, 5), (64, 0, 8)):
+            env = dict(os.environ)
+            if tile: env["DNP_FORCE_TILE"] = str(tile)
+            if tp: env["DNP_FORCE_TP"] = str(tp)
+            if ns: env["DNP_FORCE_NSPLIT"] = str(ns)
+            r = subprocess.run([sys.executable, __file__, "child", str(S), str(M)], env=env, capture_output=True, text=True)
+            try:
+                d = json.loads(r.stdout.strip().splitlines()[-1])
+                print(f"S={S} M={M} tile={tile or 'auto'} tp={tp or 'auto'} nsplit={ns or 'auto'}: {d['ms']*1e3:.1f} us  {d['pairs_per_s']:.3e} pairs/s", flush=True)
+            except Exception:
+                print(f"S={S} M={M} tile={tile} nsplit={ns}: failed {r.stderr[-300:]}", flush=True)
+    sys.exit(0)
 SHAPES = ((500, 524288), (500, 1 << 20), (200, 100000), (1000, 250000), (150, 11031), (5000, 524288), (2000, 65536),
           (300, 300000), (20000, 200000))
 AUTO_ONLY = os.environ.get("PLAN_AUTO_ONLY") == "1"
