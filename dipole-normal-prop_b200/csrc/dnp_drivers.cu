@@ -171,7 +171,7 @@ __global__ void cur_init_kernel(int32_t* cur, int32_t start, int32_t* order, flo
 inline size_t up256(size_t v) { return (v + 255) & ~(size_t)255; }
 
 struct DriverLayout {
-    size_t settled, scratch, active, inter, best, cur, rest_off, order, value, pairs, pairs_bytes, total;
+    size_t settled, scratch, active, inter, best, cur, rest_off, order, value, loop, loop_bytes, pairs, pairs_bytes, total;
 };
 
 DriverLayout driver_layout(int64_t N, int64_t P, int64_t max_patch, int64_t M) {
@@ -186,6 +186,8 @@ DriverLayout driver_layout(int64_t N, int64_t P, int64_t max_patch, int64_t M) {
     L.rest_off = off; off += up256((size_t)(P + 1) * sizeof(int64_t));
     L.order = off; off += up256((size_t)P * sizeof(int32_t));
     L.value = off; off += up256((size_t)P * sizeof(float));
+    L.loop_bytes = patch_loop_workspace_bytes(N, P);
+    L.loop = off; off += up256(L.loop_bytes);
     L.pairs_bytes = pairs_workspace_bytes(max_patch, M);
     L.pairs = off; off += up256(L.pairs_bytes);
     L.total = off;
@@ -245,8 +247,21 @@ int run_patch_propagate(float* pts, int64_t N, int64_t ld, const int64_t* perm, 
     ep.tgt_idx = tgt_idx;
     ep.tgt_skip = diffuse ? scratch : settled;       // diffuse: only the source patch itself is skipped (:256-261)
 
-    // DNP_PATCH_LOOP=host|device overrides the schedule (tests run both and compare)
+    // DNP_PATCH_LOOP=persistent|device|host overrides the schedule (tests run all of them and compare)
     const char* forced = getenv("DNP_PATCH_LOOP");
+    if (!forced || forced[0] == 'p') {
+        // small cloud, disjoint patches covering the targets: the whole loop in one cooperative launch (dnp_loop.cu)
+        int taken = 0;
+        const int rc = run_patch_loop_persistent(pts, N, ld, perm, offsets_dev, offsets_host, P, rest_perm,
+                                                 rest_offsets_host, tgt_idx, n_tgt, start_patch, eps, diffuse, E, ld_e,
+                                                 order_host, value_host, ws + L.loop, L.loop_bytes, stream, &taken);
+        if (rc != DNP_OK) return rc;
+        if (taken) return DNP_OK;
+        if (forced) {
+            set_error("DNP_PATCH_LOOP=persistent: the preconditions of the persistent loop do not hold");
+            return DNP_ERR_INVALID;
+        }
+    }
     bool device_driven = !use_const_path(max_patch, M, 0);
     if (forced && forced[0] == 'h') device_driven = false;
     if (forced && forced[0] == 'd') device_driven = true;

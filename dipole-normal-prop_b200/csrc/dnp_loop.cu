@@ -1,0 +1,438 @@
+// dnp_loop.cu -- the greedy patch-propagation loop of a SMALL cloud as one persistent cooperative kernel
+// (field_utils.py:239-265, :311-335).
+//
+// At fandisk size (72 patches of 100-268 rows, 11 031 points) one step of the loop is 3e6 pair interactions,
+// two microseconds of arithmetic, and the multi-launch schedule of dnp_drivers.cu spends 27 us on it: three or
+// four dependent launches of ~7 us each.  Here the whole loop is ONE launch of up to one CTA per SM:
+//   * the rows of the patch CSR are dealt to the CTAs in equal contiguous shares (a patch may straddle CTAs); a
+//     CTA keeps its rows' positions, normals and running field E in shared memory for the whole loop (nothing of
+//     the loop state lives in HBM),
+//   * per step every CTA stages the chosen patch's rows (flipped if its interaction was negative) as packed sources
+//     in shared memory, adds their field to its own rows (L lanes per target row walk the sources two at a time
+//     through the packed f32x2 pair arithmetic of the all-pairs kernel, fixed-order reduction), and sums E.n over
+//     its rows of every unvisited patch it holds a part of (one warp per patch, fixed order),
+//   * ONE grid-wide barrier per step (a monotonically increasing arrival counter in L2), after which every CTA
+//     adds up the partial interactions of every patch in CTA order and takes the first abs-arg-max itself -- no
+//     winner broadcast.
+// Preconditions (checked by the launcher, otherwise the multi-launch schedule runs): the patches are disjoint and
+// cover the target rows, the largest patch has <= 1024 rows, <= 2048 rows per CTA (303 000 rows), P <= 8192.
+// Deterministic: no float atomics, every sum in a fixed order.  The running field is summed in a different order
+// than the all-pairs kernel's, so E differs from the multi-launch schedule in the last bits; the decisions
+// (visit order, flips) are pinned by the reference's golden fixtures for both.
+#include <stdio.h>
+#include <stdlib.h>
+
+#include <atomic>
+
+#include "dnp_common.cuh"
+#include "dnp_pairmath.cuh"
+#include "dnp_pairs.h"
+#include "dnp_scores.h"
+#include "dipole.h"
+
+namespace dnp {
+namespace {
+
+constexpr int kLoopThreads = 1024;
+constexpr int kLoopWarps = kLoopThreads / 32;
+constexpr int64_t kLoopMaxRows = 2048;      // target rows of one CTA
+constexpr int64_t kLoopMaxSrc = 1024;       // rows of the largest patch
+constexpr int64_t kLoopMaxPatches = 8192;
+constexpr double kLoopMaxPairsPerStep = 3.0e7;   // beyond this the all-pairs kernel's throughput wins
+
+__device__ __forceinline__ unsigned int loop_ld_acquire(const unsigned int* p) {
+    unsigned int v;
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+
+__device__ __forceinline__ float finite_or_zero(float v) { return fabsf(v) <= 3.402823466e38f ? v : 0.f; }
+
+// every CTA arrives once per step; `target` = arrivals expected so far
+__device__ __forceinline__ void grid_arrive_wait(unsigned int* counter, unsigned int target) {
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        atomicAdd(counter, 1u);
+        while (loop_ld_acquire(counter) < target) { }
+    }
+    __syncthreads();
+}
+
+struct LoopArgs {
+    float* pts;                     // [N, ld] xyz + normals; normals of flipped patches are negated in place
+    int64_t ld;
+    const int64_t* perm;            // CSR rows of the patches
+    const int64_t* offsets;         // device, P + 1
+    int P;
+    const int64_t* rest_perm;       // optional: rows flipped together with a patch
+    const int64_t* rest_offsets;    // device
+    int rows_per;                   // CTA c owns rows [c * rows_per, (c + 1) * rows_per) of the CSR
+    int start;
+    float eps;
+    int diffuse;
+    float* E;                       // [N, ld_e] final field of the patch rows
+    int64_t ld_e;
+    float* inter;                   // device, 2 * (P + G): partial interactions (slot p + c), double-buffered by step parity
+    unsigned int* counter;          // zeroed by the launcher
+    int32_t* order;                 // optional device traces, P entries
+    float* value;
+    int cap_rows, cap_src;          // shared-memory capacities this launch was sized for
+    int lanes;                      // > 0: forced threads per target row (DNP_LOOP_LANES)
+    long long* prof;                // optional device array of 8 cycle counters (DNP_LOOP_DEBUG & 4), CTA 0
+    int debug;                      // DNP_LOOP_DEBUG=4: print CTA 0's cycles per phase to stderr
+};
+
+// sum of the partial interactions of patch p over the CTAs [c0, c1] that hold rows of it, in CTA order (slot =
+// p + c: patches and CTAs are both contiguous row ranges, so p + c is unique along the staircase of overlaps)
+__device__ __forceinline__ float patch_interaction(const float* __restrict__ part_inter, int p, int c0, int c1) {
+    float v = 0.f;
+    for (int c = c0; c <= c1; ++c) v += __ldcg(part_inter + p + c);
+    return v;
+}
+
+__global__ void __launch_bounds__(kLoopThreads, 1) patch_loop_kernel(LoopArgs a) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    float4* src = reinterpret_cast<float4*>(smem_raw);                               // cap_src * 3
+    float* tq = reinterpret_cast<float*>(src + (size_t)a.cap_src * 3);               // cap_rows * 3 each
+    float* tn = tq + (size_t)a.cap_rows * 3;
+    float* tE = tn + (size_t)a.cap_rows * 3;
+    float* dots = tE + (size_t)a.cap_rows * 3;                                       // cap_rows
+    int32_t* tpatch = reinterpret_cast<int32_t*>(dots + a.cap_rows);                 // cap_rows
+    uint8_t* tstate = reinterpret_cast<uint8_t*>(tpatch + a.cap_rows);               // cap_rows: 1 = visited
+    uint8_t* visited = tstate + a.cap_rows;                                          // P
+    uint8_t* span = visited + a.P;                                                   // 2 * P: first / last CTA of a patch
+    __shared__ float part[kLoopThreads * 6];                                          // per-thread partial fields (a row pair)
+    __shared__ unsigned long long warp_best[32];
+    __shared__ float warp_val[32];
+    __shared__ int32_t sh_next[2];
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const unsigned int G = gridDim.x;
+    const int64_t* __restrict__ off = a.offsets;
+    const int64_t T = off[a.P];
+    const int64_t rb = (int64_t)blockIdx.x * a.rows_per;                             // my rows of the CSR: [rb, re)
+    const int64_t re = rb + a.rows_per < T ? rb + a.rows_per : T;
+    const int R = (int)(re - rb);
+
+    for (int i = tid; i < R; i += kLoopThreads) {
+        const float* q = a.pts + a.perm[rb + i] * a.ld;
+        tq[3 * i] = q[0]; tq[3 * i + 1] = q[1]; tq[3 * i + 2] = q[2];
+        tn[3 * i] = q[3]; tn[3 * i + 1] = q[4]; tn[3 * i + 2] = q[5];
+        tE[3 * i] = 0.f; tE[3 * i + 1] = 0.f; tE[3 * i + 2] = 0.f;
+        tstate[i] = 0;
+        int lo = 0, hi = a.P;                                                        // the patch of row rb + i:
+        while (hi - lo > 1) {                                                        // last p with off[p] <= row
+            const int mid = (lo + hi) >> 1;
+            if (off[mid] <= rb + i) lo = mid; else hi = mid;
+        }
+        tpatch[i] = lo;
+    }
+    for (int p = tid; p < a.P; p += kLoopThreads) {
+        visited[p] = 0;
+        const int64_t b = off[p], e = off[p + 1];
+        span[2 * p] = (uint8_t)(e > b ? b / a.rows_per : 1);                         // empty patch: empty span
+        span[2 * p + 1] = (uint8_t)(e > b ? (e - 1) / a.rows_per : 0);
+    }
+    __syncthreads();
+    const int pfirst = R > 0 ? tpatch[0] : 0, plast = R > 0 ? tpatch[R - 1] : -1;
+
+    const f32x2 eps2 = pack2(a.eps, a.eps);
+    const f32x2 zero2 = pack2(0.f, 0.f);
+    int j = a.start, flip = 0;
+    const bool prof = a.prof && blockIdx.x == 0 && tid == 0;
+    long long t0 = prof ? clock64() : 0, acc[6] = {0, 0, 0, 0, 0, 0};
+#define LOOP_MARK(k) if (prof) { const long long t1 = clock64(); acc[k] += t1 - t0; t0 = t1; }
+    for (int step = 0; step < a.P; ++step) {
+        if (blockIdx.x == 0 && tid == 0) {
+            if (a.order) a.order[step] = j;
+            if (step == 0 && a.value) a.value[0] = 0.f;
+        }
+        if (tid == 0) visited[j] = 1;
+        // ---- the chosen patch as packed sources (its commit: flipped if the interaction was negative, :250,322)
+        const int64_t so = off[j];
+        const int n = (int)(off[j + 1] - so), n_pad = (n + 1) & ~1;
+        for (int i = tid; i < n_pad; i += kLoopThreads) {
+            float v[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+            if (i < n) {
+                const float* q = a.pts + a.perm[so + i] * a.ld;
+#pragma unroll
+                for (int c = 0; c < 6; ++c) v[c] = q[c];
+                if (flip) { v[3] = -v[3]; v[4] = -v[4]; v[5] = -v[5]; }
+            }
+            pack_source_row(v, src + 3 * i);
+        }
+        // my rows of the chosen patch
+        const int mb = (int)((so > rb ? so : rb) - rb), me = (int)((so + n < re ? so + n : re) - rb);
+        for (int i = mb + tid; i < me; i += kLoopThreads) tstate[i] = 1;
+        if (flip && a.rest_perm && so >= rb && so < re) {                         // :250-252: the rest of the patch follows
+            const int64_t ro = a.rest_offsets[j], rn = a.rest_offsets[j + 1] - ro;
+            for (int64_t i = tid; i < rn; i += kLoopThreads) {
+                float* q = a.pts + a.rest_perm[ro + i] * a.ld + 3;
+                q[0] = -q[0]; q[1] = -q[1]; q[2] = -q[2];
+            }
+        }
+        __syncthreads();
+        LOOP_MARK(0)
+        // ---- E += field of the patch on my rows (:261,265,330,335); visited rows are skipped, or, when diffuse,
+        // only the source patch itself (:256-261,326-331).  A thread owns a PAIR of rows (the two halves of the
+        // packed arithmetic) and every L-th source; consecutive threads are consecutive row pairs, so a warp reads
+        // one or two sources at a time (broadcast shared-memory loads).  The L partial fields of a row are then
+        // summed in lane order.
+        const int pairs = (R + 1) >> 1;
+        int L = pairs > 0 ? kLoopThreads / pairs : 1;
+        const int l_cap = (n + 3) >> 2;
+        L = L > l_cap ? l_cap : L;
+        L = L < 1 ? 1 : L;
+        if (a.lanes > 0 && a.lanes * pairs <= kLoopThreads) L = a.lanes;
+        {
+            const int tp = pairs > 0 ? tid % pairs : 0, l = pairs > 0 ? tid / pairs : L;
+            const int t0 = 2 * tp, t1 = t0 + 1;
+            bool live0 = l < L && t0 < R, live1 = l < L && t1 < R;
+            if (live0) live0 = a.diffuse ? (tpatch[t0] != j) : !tstate[t0];
+            if (live1) live1 = a.diffuse ? (tpatch[t1] != j) : !tstate[t1];
+            f32x2 ax = zero2, ay = zero2, az = zero2;
+            if (live0 || live1) {
+                const int u1 = t1 < R ? t1 : t0;
+                const f32x2 qx = pack2(tq[3 * t0], tq[3 * u1]), qy = pack2(tq[3 * t0 + 1], tq[3 * u1 + 1]),
+                            qz = pack2(tq[3 * t0 + 2], tq[3 * u1 + 2]);
+#pragma unroll 2
+                for (int s = l; s < n; s += L) {
+                    const SrcX2 one(src[3 * s], src[3 * s + 1], src[3 * s + 2]);
+                    pair_field_x2(one, qx, qy, qz, eps2, ax, ay, az);
+                }
+            }
+            if (l < L) {
+                float* o = part + 6 * tid;
+                unpack2(ax, o[0], o[1]); unpack2(ay, o[2], o[3]); unpack2(az, o[4], o[5]);
+            }
+        }
+        __syncthreads();
+        for (int idx = tid; idx < 3 * R; idx += kLoopThreads) {
+            const int t = idx / 3, c = idx - 3 * t;
+            if (a.diffuse ? (tpatch[t] == j) : (tstate[t] != 0)) continue;
+            const float* o = part + 6 * (t >> 1) + 2 * c + (t & 1);
+            float e = 0.f;
+            for (int l = 0; l < L; ++l) e += o[(size_t)6 * pairs * l];
+            tE[idx] += finite_or_zero(e);                                         // field_utils.py:114-115
+        }
+        __syncthreads();
+        LOOP_MARK(1)
+        // ---- my share of sum E.n of every unvisited patch I hold rows of (:244-247,316-319), into this step's buffer
+        float* part_inter = a.inter + (size_t)(step & 1) * (a.P + G);
+        if (step + 1 < a.P) {
+            for (int t = tid; t < R; t += kLoopThreads)
+                dots[t] = __fadd_rn(__fadd_rn(__fmul_rn(tE[3 * t], tn[3 * t]), __fmul_rn(tE[3 * t + 1], tn[3 * t + 1])),
+                                    __fmul_rn(tE[3 * t + 2], tn[3 * t + 2]));
+            __syncthreads();
+            for (int p = pfirst + warp; p <= plast; p += kLoopWarps) {
+                if (visited[p]) continue;
+                const int64_t pb = off[p], pe = off[p + 1];
+                const int b = (int)((pb > rb ? pb : rb) - rb), e = (int)((pe < re ? pe : re) - rb);
+                if (e <= b) continue;                                             // an empty patch inside my range
+                float acc = 0.f;
+                for (int i = b + lane; i < e; i += 32) acc += dots[i];
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+                if (lane == 0) __stcg(part_inter + p + blockIdx.x, acc);
+            }
+        }
+        LOOP_MARK(2)
+        grid_arrive_wait(a.counter, (unsigned int)(step + 1) * G);
+        LOOP_MARK(3)
+        // every CTA is done reading the sources: commit the flip of my rows of the patch to the cloud
+        if (flip) {
+            for (int i = mb + tid; i < me; i += kLoopThreads) {
+                float* q = a.pts + a.perm[rb + i] * a.ld + 3;
+                q[0] = -q[0]; q[1] = -q[1]; q[2] = -q[2];
+            }
+        }
+        if (step + 1 == a.P) break;
+        // ---- first abs-arg-max over the unvisited patches, by every CTA for itself
+        unsigned long long best = 0ull;
+        float best_v = 0.f;
+        for (int p = tid; p < a.P; p += kLoopThreads) {
+            if (visited[p]) continue;
+            const float v = patch_interaction(part_inter, p, span[2 * p], span[2 * p + 1]);
+            const unsigned long long k =
+                ((unsigned long long)__float_as_uint(fabsf(v)) << 32) | (0xffffffffu - (uint32_t)p);
+            if (k > best) { best = k; best_v = v; }
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const unsigned long long other = __shfl_xor_sync(0xffffffffu, best, o);
+            const float other_v = __shfl_xor_sync(0xffffffffu, best_v, o);
+            if (other > best) { best = other; best_v = other_v; }
+        }
+        if (lane == 0) { warp_best[warp] = best; warp_val[warp] = best_v; }
+        __syncthreads();
+        if (warp == 0) {
+            best = lane < kLoopWarps ? warp_best[lane] : 0ull;
+            best_v = lane < kLoopWarps ? warp_val[lane] : 0.f;
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                const unsigned long long other = __shfl_xor_sync(0xffffffffu, best, o);
+                const float other_v = __shfl_xor_sync(0xffffffffu, best_v, o);
+                if (other > best) { best = other; best_v = other_v; }
+            }
+            if (lane == 0) {
+                sh_next[0] = (int32_t)(0xffffffffu - (uint32_t)best);             // best != 0: a patch is left
+                sh_next[1] = best_v < 0.f;
+                if (blockIdx.x == 0 && a.value) a.value[step + 1] = best_v;
+            }
+        }
+        __syncthreads();
+        j = sh_next[0];
+        flip = sh_next[1];
+        LOOP_MARK(4)
+    }
+#undef LOOP_MARK
+    if (prof)
+        for (int k = 0; k < 6; ++k) a.prof[k] = acc[k];
+    // ---- the final field of my rows
+    for (int t = tid; t < R; t += kLoopThreads) {
+        float* o = a.E + a.perm[rb + t] * a.ld_e;
+        o[0] = tE[3 * t]; o[1] = tE[3 * t + 1]; o[2] = tE[3 * t + 2];
+    }
+}
+
+// distinct rows named by the CSR (disjoint patches <=> distinct == T) and rows out of range
+__global__ void loop_cover_kernel(const int64_t* __restrict__ perm, int64_t T, int64_t N, int* __restrict__ flags,
+                                  int* __restrict__ counts) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= T) return;
+    const int64_t r = perm[i];
+    if (r < 0 || r >= N) { atomicAdd(counts + 1, 1); return; }
+    if (atomicExch(flags + r, 1) == 0) atomicAdd(counts, 1);
+}
+
+inline size_t up256(size_t v) { return (v + 255) & ~(size_t)255; }
+
+size_t loop_smem_bytes(int cap_rows, int cap_src, int P) {
+    return (size_t)cap_src * 48 + (size_t)cap_rows * (10 * 4 + 4 + 1) + (size_t)3 * P + 64;
+}
+
+}  // namespace
+
+size_t patch_loop_workspace_bytes(int64_t N, int64_t P) {
+    return up256((size_t)N * 4) + 256 + up256((size_t)2 * (P + sm_count_cached()) * 4 + 64) + up256((size_t)P * 4) * 2;
+}
+
+// Returns DNP_OK and sets *taken = 1 when the loop ran here; *taken = 0 (nothing launched that matters) when the
+// preconditions do not hold and the caller has to run the multi-launch schedule.
+int run_patch_loop_persistent(float* pts, int64_t N, int64_t ld, const int64_t* perm, const int64_t* offsets_dev,
+                              const int64_t* offsets_host, int64_t P, const int64_t* rest_perm,
+                              const int64_t* rest_offsets_host, const int64_t* tgt_idx, int64_t n_tgt,
+                              int64_t start_patch, float eps, int diffuse, float* E, int64_t ld_e, int32_t* order_host,
+                              float* value_host, void* workspace, size_t workspace_bytes, cudaStream_t stream,
+                              int* taken) {
+    *taken = 0;
+    const int64_t T = offsets_host[P] - offsets_host[0];
+    if (P < 1 || P > kLoopMaxPatches || offsets_host[0] != 0 || T < 1) return DNP_OK;
+    if (tgt_idx ? (tgt_idx != perm || n_tgt != T) : T != N) return DNP_OK;       // the patches must be the targets
+    int64_t max_patch = 0;
+    for (int64_t p = 0; p < P; ++p) {
+        const int64_t n = offsets_host[p + 1] - offsets_host[p];
+        if (n > max_patch) max_patch = n;
+    }
+    if (max_patch > kLoopMaxSrc || (double)max_patch * (double)T > kLoopMaxPairsPerStep) return DNP_OK;
+    if (workspace_bytes < patch_loop_workspace_bytes(N, P)) return DNP_OK;
+    // an equal share of the CSR rows for every CTA (at least 32: fewer CTAs make the barrier cheaper)
+    const int sms = sm_count_cached();
+    int64_t rows_per = (T + sms - 1) / sms;
+    if (rows_per < 32) rows_per = 32;
+    const int G = (int)((T + rows_per - 1) / rows_per);
+    const int64_t max_rows = rows_per;
+    if (max_rows > kLoopMaxRows || G > 255) return DNP_OK;                       // (a patch's CTA span is stored in bytes)
+
+    unsigned char* ws = reinterpret_cast<unsigned char*>(workspace);
+    size_t off = 0;
+    int* flags = reinterpret_cast<int*>(ws + off); off += up256((size_t)N * 4);
+    int* counts = reinterpret_cast<int*>(ws + off);                                   // [0] distinct, [1] out of range
+    unsigned int* counter = reinterpret_cast<unsigned int*>(ws + off + 128); off += 256;
+    float* inter = reinterpret_cast<float*>(ws + off); off += up256((size_t)2 * (P + sms) * 4 + 64);
+    int32_t* order_dev = reinterpret_cast<int32_t*>(ws + off); off += up256((size_t)P * 4);
+    float* value_dev = reinterpret_cast<float*>(ws + off); off += up256((size_t)P * 4);
+
+    // disjoint patches covering the targets?  (one 8-byte read per CALL)
+    DNP_CHECK_CUDA(cudaMemsetAsync(flags, 0, (size_t)N * 4, stream));
+    DNP_CHECK_CUDA(cudaMemsetAsync(counts, 0, 256, stream));
+    loop_cover_kernel<<<(unsigned)((T + 255) / 256), 256, 0, stream>>>(perm, T, N, flags, counts);
+    count_launch(1);
+    int host_counts[2] = {0, 0};
+    DNP_CHECK_CUDA(cudaMemcpyAsync(host_counts, counts, sizeof(host_counts), cudaMemcpyDeviceToHost, stream));
+    DNP_CHECK_CUDA(cudaStreamSynchronize(stream));
+    if (host_counts[1] != 0) {
+        set_error("patch rows out of range [0, %lld)", (long long)N);
+        return DNP_ERR_INVALID;
+    }
+    if (host_counts[0] != T) return DNP_OK;                                           // overlapping patches
+
+    // rest offsets on the device (they arrive on the host): reuse the flags area, no longer needed
+    int64_t* rest_off_dev = nullptr;
+    if (rest_perm) {
+        if ((size_t)(P + 1) * 8 > up256((size_t)N * 4)) return DNP_OK;
+        rest_off_dev = reinterpret_cast<int64_t*>(flags);
+        DNP_CHECK_CUDA(cudaMemcpyAsync(rest_off_dev, rest_offsets_host, (size_t)(P + 1) * 8, cudaMemcpyHostToDevice,
+                                       stream));
+    }
+
+    LoopArgs a;
+    a.pts = pts; a.ld = ld; a.perm = perm; a.offsets = offsets_dev; a.P = (int)P;
+    a.rest_perm = rest_perm; a.rest_offsets = rest_off_dev; a.rows_per = (int)rows_per;
+    a.start = (int)start_patch; a.eps = eps; a.diffuse = diffuse; a.E = E; a.ld_e = ld_e;
+    a.inter = inter; a.counter = counter;
+    a.order = order_host ? order_dev : nullptr;
+    a.value = value_host ? value_dev : nullptr;
+    a.cap_rows = (int)((max_rows + 3) & ~(int64_t)3);
+    a.cap_src = (int)((max_patch + 1) & ~(int64_t)1);
+    if (a.cap_src < 2) a.cap_src = 2;
+    a.lanes = 0;
+    a.debug = getenv("DNP_LOOP_DEBUG") ? atoi(getenv("DNP_LOOP_DEBUG")) : 0;
+    a.prof = (a.debug & 4) ? reinterpret_cast<long long*>(reinterpret_cast<unsigned char*>(inter) +
+                                                           (((size_t)2 * (P + sms) * 4 + 7) & ~(size_t)7))
+                           : nullptr;
+    if (getenv("DNP_LOOP_LANES")) a.lanes = atoi(getenv("DNP_LOOP_LANES"));
+    const size_t smem = loop_smem_bytes(a.cap_rows, a.cap_src, (int)P);
+    static std::atomic<int> smem_opted[64];
+    int dev = 0;
+    DNP_CHECK_CUDA(cudaGetDevice(&dev));
+    if (dev >= 0 && dev < 64 && !smem_opted[dev].load()) {
+        DNP_CHECK_CUDA(cudaFuncSetAttribute(patch_loop_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        smem_opted[dev].store(1);
+    }
+    if (smem > 200 * 1024) return DNP_OK;
+    int per_sm = 0;
+    DNP_CHECK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, patch_loop_kernel, kLoopThreads, smem));
+    if (per_sm < 1 || (int64_t)per_sm * sms < G) return DNP_OK;
+
+    cudaLaunchConfig_t cfg = {};
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeCooperative;
+    attr[0].val.cooperative = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    cfg.gridDim = dim3((unsigned)G);
+    cfg.blockDim = dim3(kLoopThreads);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = stream;
+    DNP_CHECK_CUDA(cudaLaunchKernelEx(&cfg, patch_loop_kernel, a));
+    count_launch(1);
+    *taken = 1;
+    if (a.prof) {
+        long long h[6];
+        DNP_CHECK_CUDA(cudaMemcpyAsync(h, a.prof, sizeof(h), cudaMemcpyDeviceToHost, stream));
+        DNP_CHECK_CUDA(cudaStreamSynchronize(stream));
+        fprintf(stderr, "[patch_loop] cycles per step, CTA 0: stage %.0f field %.0f interactions %.0f barrier %.0f argmax %.0f (P=%lld G=%d rows_per=%lld)\n",
+                h[0] / (double)P, h[1] / (double)P, h[2] / (double)P, h[3] / (double)P, h[4] / (double)P, (long long)P, G, (long long)rows_per);
+    }
+    if (order_host)
+        DNP_CHECK_CUDA(cudaMemcpyAsync(order_host, order_dev, (size_t)P * 4, cudaMemcpyDeviceToHost, stream));
+    if (value_host)
+        DNP_CHECK_CUDA(cudaMemcpyAsync(value_host, value_dev, (size_t)P * 4, cudaMemcpyDeviceToHost, stream));
+    if (order_host || value_host) DNP_CHECK_CUDA(cudaStreamSynchronize(stream));
+    DNP_CHECK_CUDA(cudaGetLastError());
+    return DNP_OK;
+}
+
+}  // namespace dnp

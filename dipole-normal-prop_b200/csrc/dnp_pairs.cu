@@ -28,6 +28,7 @@
 #include <vector>
 
 #include "dnp_common.cuh"
+#include "dnp_pairmath.cuh"
 #include "dnp_pairs.h"
 
 namespace dnp {
@@ -40,8 +41,6 @@ constexpr int kTileSmall = 64;                   // ... for calls too small to f
 constexpr int kStages = 3;                       // TMA ring depth
 constexpr int kSrcBytes = 48;                    // packed bytes per source
 constexpr size_t smem_bytes(int tile_src) { return size_t(kStages) * tile_src * kSrcBytes + kStages * sizeof(uint64_t); }
-constexpr float kRsqrtClamp = 1.152921504606847e18f;   // 2^60: clamp^2 is finite (field: c = d w u^2)
-constexpr float kRsqrtClampPhi = 1.099511627776e12f;   // 2^40: clamp^3 is finite (potential: d u^3)
 
 // ------------------------------------------------------------------ source packing
 __global__ void pack_sources_kernel(const float* __restrict__ src, int64_t S, int64_t ld_s,
@@ -137,48 +136,6 @@ __device__ __forceinline__ void lattice_node(int64_t i, int n, float& x, float& 
     x = __fmul_rn(__fsub_rn(__fdiv_rn((float)xi, fn), 0.5f), 2.f);
     y = __fmul_rn(__fsub_rn(__fdiv_rn((float)yi, fn), 0.5f), 2.f);
     z = __fmul_rn(__fsub_rn(__fdiv_rn((float)zi, fn), 0.5f), 2.f);
-}
-
-// ------------------------------------------------------------------ per-pair arithmetic, packed
-// one source, broadcast to both halves of every packed operation (ptxas emits the `R.F32` operand form)
-struct SrcX2 {
-    f32x2 px, py, pz, nx, ny, nz, mx, my, mz;
-    __device__ __forceinline__ SrcX2(const float4& A, const float4& B, const float4& C)
-        : px(pack2(A.x, A.x)), py(pack2(A.y, A.y)), pz(pack2(A.z, A.z)), nx(pack2(A.w, A.w)),
-          ny(pack2(B.x, B.x)), nz(pack2(B.y, B.y)), mx(pack2(B.z, B.z)), my(pack2(B.w, B.w)),
-          mz(pack2(C.x, C.x)) {}
-};
-
-// field: E += w (n + t R) with w = 1/(r^3+eps), t = (m.R) / r^2, m = -3 n            (19 packed FP32 ops)
-__device__ __forceinline__ void pair_field_x2(const SrcX2& s, f32x2 qx, f32x2 qy, f32x2 qz, f32x2 eps2,
-                                              f32x2& ax, f32x2& ay, f32x2& az) {
-    const f32x2 rx = sub2(s.px, qx), ry = sub2(s.py, qy), rz = sub2(s.pz, qz);
-    const f32x2 r2 = fma2(rz, rz, fma2(ry, ry, mul2(rx, rx)));
-    float r2a, r2b;
-    unpack2(r2, r2a, r2b);
-    const float ua = rsqrt_sfu(r2a), ub = rsqrt_sfu(r2b);                 // +inf on a coincident pair
-    const f32x2 u = pack2(ua, ub);
-    const f32x2 uc = pack2(fminf(ua, kRsqrtClamp), fminf(ub, kRsqrtClamp));
-    const f32x2 den = fma2(mul2(r2, r2), u, eps2);                        // |R|^3 + eps; 0*inf = NaN if R = 0
-    float da, db;
-    unpack2(den, da, db);
-    const f32x2 w = pack2(fmaxf(rcp_sfu(da), 0.f), fmaxf(rcp_sfu(db), 0.f));   // NaN -> 0
-    const f32x2 d = fma2(s.mz, rz, fma2(s.my, ry, mul2(s.mx, rx)));       // -3 n.R (exactly 0 when R = 0)
-    const f32x2 t = mul2(d, mul2(uc, uc));
-    const f32x2 vx = fma2(t, rx, s.nx), vy = fma2(t, ry, s.ny), vz = fma2(t, rz, s.nz);
-    ax = fma2(w, vx, ax); ay = fma2(w, vy, ay); az = fma2(w, vz, az);
-}
-
-// potential: phi += (n.R) / r^3                                         (12 packed FP32 ops)
-__device__ __forceinline__ void pair_potential_x2(const SrcX2& s, f32x2 qx, f32x2 qy, f32x2 qz, f32x2& phi) {
-    const f32x2 rx = sub2(s.px, qx), ry = sub2(s.py, qy), rz = sub2(s.pz, qz);
-    const f32x2 r2 = fma2(rz, rz, fma2(ry, ry, mul2(rx, rx)));
-    float r2a, r2b;
-    unpack2(r2, r2a, r2b);
-    // coincident pair: n.R is exactly 0 and the clamped rsqrt^3 stays finite, so the pair adds 0
-    const f32x2 uc = pack2(fminf(rsqrt_sfu(r2a), kRsqrtClampPhi), fminf(rsqrt_sfu(r2b), kRsqrtClampPhi));
-    const f32x2 d = fma2(s.nz, rz, fma2(s.ny, ry, mul2(s.nx, rx)));
-    phi = fma2(d, mul2(mul2(uc, uc), uc), phi);
 }
 
 // ------------------------------------------------------------------ the all-pairs kernel

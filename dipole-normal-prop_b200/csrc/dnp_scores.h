@@ -59,6 +59,16 @@ int run_patch_interactions(const float* E, int64_t ld_e, const float* normals, i
                            const int64_t* offsets, int64_t P, const uint8_t* active, float* out,
                            int32_t* best_idx, float* best_val, cudaStream_t stream, PatchAdvance adv = PatchAdvance());
 
+// The whole greedy patch loop as one persistent cooperative kernel (dnp_loop.cu), for small clouds with disjoint
+// patches covering the targets; *taken = 0 when the preconditions do not hold (the caller runs its own schedule).
+size_t patch_loop_workspace_bytes(int64_t N, int64_t P);
+int run_patch_loop_persistent(float* pts, int64_t N, int64_t ld, const int64_t* perm, const int64_t* offsets_dev,
+                              const int64_t* offsets_host, int64_t P, const int64_t* rest_perm,
+                              const int64_t* rest_offsets_host, const int64_t* tgt_idx, int64_t n_tgt,
+                              int64_t start_patch, float eps, int diffuse, float* E, int64_t ld_e, int32_t* order_host,
+                              float* value_host, void* workspace, size_t workspace_bytes, cudaStream_t stream,
+                              int* taken);
+
 int run_patch_covariance(const float* pts, int64_t ld, const int64_t* perm, const int64_t* offsets, int64_t P,
                          double* cov, cudaStream_t stream);
 

@@ -19,19 +19,19 @@ def _patches(perm, off):
     return [torch.from_numpy(perm[off[i]:off[i + 1]].copy()) for i in range(len(off) - 1)]
 
 
-LOOPS = ["device", "device_unfused", "host", "per_call"]
+LOOPS = ["persistent", "device", "device_unfused", "host", "per_call"]
 
 
 def _spy_order(fu, monkeypatch, loop):
     """Greedy visit order (after the start patch) as the product decides it: from the trace of the native loop
-    (dnp_patch_propagate_f32, device-driven or host-driven schedule) or, with the per-call loop, from every 8-byte
-    read of the arg-max."""
+    (dnp_patch_propagate_f32: persistent cooperative kernel, device-driven or host-driven launches) or, with the
+    per-call loop, from every 8-byte read of the arg-max."""
     import dnp_native
     order = []
     native = loop != "per_call"
     monkeypatch.setattr(fu, "NATIVE_PATCH_LOOP", native)
     if native:
-        monkeypatch.setenv("DNP_PATCH_LOOP", "host" if loop == "host" else "device")
+        monkeypatch.setenv("DNP_PATCH_LOOP", loop if loop in ("host", "persistent") else "device")
         if loop == "device_unfused":                      # separate arg-max / commit / pack launches per step
             monkeypatch.setenv("DNP_PATCH_LOOP_UNFUSED", "1")
         else:
@@ -337,7 +337,8 @@ def test_native_patch_loop_equals_per_call_loop(fu, dev, diffuse, monkeypatch):
     assert torch.equal(out["host"][0], out["per_call"][0])
     assert torch.equal(out["host"][1], out["per_call"][1])
     assert orders["device"] == orders["device_unfused"] == orders["host"] == orders["per_call"]
-    for loop in ("device", "device_unfused"):
+    assert orders["persistent"] == orders["host"]
+    for loop in ("persistent", "device", "device_unfused"):
         assert torch.equal(out[loop][0], out["host"][0])                  # pure sign flips either way
         assert torch.equal(out[loop][1], out["host"][1])
     radial = (out["device"][0][:, 3:] * d).sum(-1)
