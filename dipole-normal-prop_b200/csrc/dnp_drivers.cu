@@ -188,7 +188,7 @@ DriverLayout driver_layout(int64_t N, int64_t P, int64_t max_patch, int64_t M) {
     L.value = off; off += up256((size_t)P * sizeof(float));
     L.loop_bytes = patch_loop_workspace_bytes(N, P);
     L.loop = off; off += up256(L.loop_bytes);
-    L.pairs_bytes = pairs_workspace_bytes(max_patch, M);
+    L.pairs_bytes = pairs_workspace_bytes_upper(max_patch, M);
     L.pairs = off; off += up256(L.pairs_bytes);
     L.total = off;
     return L;

@@ -473,22 +473,38 @@ size_t pairs_workspace_bytes(int64_t S, int64_t M) {
     if (S < 1) S = 1;
     if (M < 1) M = 1;
     const PairPlan p = make_pair_plan(S, M, sm_count_cached(), 0, 0);
-    // callers size one workspace for their LARGEST source set and reuse it for smaller ones (the greedy drivers),
-    // and a smaller set may want more splits: cover the plans of the smaller tile counts too (run_pairs clamps
-    // the split count to what fits in any case)
-    size_t partial = p.partial_bytes;
-    const int64_t tiles_small = (S + kTileSmall - 1) / kTileSmall;
-    for (int64_t t = 1; t < tiles_small; t += (t < 16 ? 1 : t / 8)) {
-        const PairPlan q = make_pair_plan(t * kTileSmall, M, sm_count_cached(), 0, 0);
-        if (q.partial_bytes > partial) partial = q.partial_bytes;
-    }
     const size_t packed = (size_t)round_up(round_up(S, kTileSrc) * kSrcBytes, 256);   // either tile's padding
-    size_t core = packed + partial;
+    size_t core = packed + p.partial_bytes;
     if (use_const_path(S, M, 0)) {
         const size_t c = cpairs_workspace_bytes(S, M);
         if (c > core) core = c;
     }
     return core + (size_t)round_up(M * 4, 256) + 1024;
+}
+
+// For callers that size ONE workspace for their largest source set and reuse it for smaller ones (the greedy
+// drivers): a smaller set may want more source splits, so bound the split count of ANY plan with <= S sources
+// instead of planning every size (the plan stops splitting at 8 waves of CTAs; run_pairs clamps in any case).
+size_t pairs_workspace_bytes_upper(int64_t S, int64_t M) {
+    if (S < 1) S = 1;
+    if (M < 1) M = 1;
+    const int sm = sm_count_cached();
+    int64_t kmax = 1;
+    for (int tp = 4; tp >= 1; tp >>= 1) {
+        const int resident = tp >= 4 ? 3 : (tp == 2 ? 5 : 8);
+        const int64_t tile_tgts = (int64_t)kBlock * 2 * tp;
+        const int64_t m_tiles = (M + tile_tgts - 1) / tile_tgts;
+        const int64_t k = (8 * (int64_t)sm * resident + m_tiles - 1) / m_tiles;
+        if (k > kmax) kmax = k;
+    }
+    const int64_t tiles_small = (S + kTileSmall - 1) / kTileSmall;
+    if (kmax > tiles_small) kmax = tiles_small;
+    if (kmax > 64) kmax = 64;
+    const size_t partial = kmax > 1 ? (size_t)round_up(kmax * M * 3 * (int64_t)sizeof(float), 256) : 0;
+    const size_t exact = pairs_workspace_bytes(S, M);
+    const size_t upper = (size_t)round_up(round_up(S, kTileSrc) * kSrcBytes, 256) + partial +
+                         (size_t)round_up(M * 4, 256) + 1024;
+    return upper > exact ? upper : exact;
 }
 
 // ------------------------------------------------------------------ launchers

@@ -67,6 +67,7 @@ struct CPairPlan {
 int sm_count_cached();
 PairPlan make_pair_plan(int64_t S, int64_t M, int sm_count, int force_tp, int force_nsplit);
 size_t pairs_workspace_bytes(int64_t S, int64_t M);
+size_t pairs_workspace_bytes_upper(int64_t S, int64_t M);   // covers every source count <= S
 
 // potential == true: phi epilogue (STORE/ACCUM on a scalar per row).
 // lattice_n > 0: targets are the nodes of the n^3 lattice (tgt ignored).

@@ -345,6 +345,54 @@ def test_native_patch_loop_equals_per_call_loop(fu, dev, diffuse, monkeypatch):
     assert abs(torch.sign(radial).mean()) > 0.99
 
 
+def _surface(n, seed):
+    g = torch.Generator().manual_seed(seed)
+    d = torch.randn(n, 3, generator=g)
+    d = d / d.norm(dim=-1, keepdim=True)
+    return torch.cat([d * 0.45 + 0.004 * torch.randn(n, 3, generator=g), d], 1).float(), d
+
+
+def test_persistent_loop_edge_cases(fu, dev, monkeypatch):
+    """The cooperative-kernel schedule on the shapes its bookkeeping can get wrong: an empty patch in the middle of
+    the CSR, one-row patches, a single patch, patches that straddle CTA boundaries many times over (2 patches on
+    ~60 CTAs); overlapping patches and patches that do not cover the cloud must fall back to the launches."""
+    import dnp_native
+    pc, d = _surface(3000, 5)
+    order = torch.randperm(3000, generator=torch.Generator().manual_seed(6))
+    cuts = [0, 1, 2, 2, 300, 301, 1100, 1900, 1900, 2900, 3000]                  # empty patches, one-row patches
+    ragged = [order[a:b] for a, b in zip(cuts[:-1], cuts[1:])]
+    small, _ = _surface(800, 7)
+    two, _ = _surface(2000, 8)
+    for cloud_, patches in ((pc, ragged), (small, [torch.arange(800)]),
+                            (two, [torch.arange(1000), torch.arange(1000, 2000)])):
+        flipped = cloud_.clone()
+        for pt in patches[::2]:
+            flipped[pt, 3:] *= -1
+        res = {}
+        for loop in ("persistent", "host"):
+            monkeypatch.undo()
+            res[loop] = (_spy_order(fu, monkeypatch, loop), flipped.clone().to(dev))
+            fu.strongest_field_propagation(res[loop][1], [], patches)
+        assert res["persistent"][0] == res["host"][0]
+        assert torch.equal(res["persistent"][1], res["host"][1])
+    # not applicable: forced -> a clear error; by default -> the multi-launch schedule, same result
+    monkeypatch.undo()
+    overlapping = [order[:1600], order[1400:]]
+    partial = [order[:1000], order[1000:2000]]
+    for patches in (overlapping, partial):
+        monkeypatch.setenv("DNP_PATCH_LOOP", "persistent")
+        with pytest.raises(dnp_native.DipoleError, match="persistent"):
+            fu.strongest_field_propagation(pc.clone().to(dev), [], patches)
+        monkeypatch.delenv("DNP_PATCH_LOOP")
+        a = pc.clone().to(dev)
+        fu.strongest_field_propagation(a, [], patches)
+        monkeypatch.setenv("DNP_PATCH_LOOP", "host")
+        b = pc.clone().to(dev)
+        fu.strongest_field_propagation(b, [], patches)
+        monkeypatch.delenv("DNP_PATCH_LOOP")
+        assert torch.equal(a, b)
+
+
 # ------------------------------------------------------------------ a10: thin callers
 def test_st_propagation_points_file(golden, orc, dev):
     """graph_dipole.py:27-36: Transform -> propagate (diffuse) -> lattice test -> inverse transform."""
