@@ -327,6 +327,11 @@ int run_patch_loop_persistent(float* pts, int64_t N, int64_t ld, const int64_t* 
                               float* value_host, void* workspace, size_t workspace_bytes, cudaStream_t stream,
                               int* taken) {
     *taken = 0;
+    {   // the precondition check reads 8 bytes back: not on a capturing stream (the device-driven launches capture)
+        cudaStreamCaptureStatus st = cudaStreamCaptureStatusNone;
+        if (cudaStreamIsCapturing(stream, &st) != cudaSuccess) { cudaGetLastError(); return DNP_OK; }
+        if (st != cudaStreamCaptureStatusNone) return DNP_OK;
+    }
     const int64_t T = offsets_host[P] - offsets_host[0];
     if (P < 1 || P > kLoopMaxPatches || offsets_host[0] != 0 || T < 1) return DNP_OK;
     if (tgt_idx ? (tgt_idx != perm || n_tgt != T) : T != N) return DNP_OK;       // the patches must be the targets

@@ -194,11 +194,14 @@ DNP_API int dnp_points_propagate_f32(float* pts, int64_t N, int64_t ld, int64_t 
  * diffuse != 0: only the source patch is skipped as a target (:256-261,326-331), else every visited patch.
  * E: [N, ld_e >= 3] running field, ZEROED by the caller, holds the final field on return.
  * order_host / value_host (optional, host, P entries): visit order and the signed interaction that chose each
- * patch.  Schedule: the step winner stays on the device and every launch reads its row range from it, so all
- * P steps are enqueued without a host read and the call returns after the last launch has been enqueued (it
- * synchronises `stream` once, at the end, only when a trace is requested).  Only when a patch is large enough
- * for the by-value all-pairs kernel (>= 16 384 rows, sources are kernel parameters) does the loop read the
- * winner back once per step (8 bytes).  DNP_PATCH_LOOP=host|device forces either schedule.                  */
+ * patch.  Schedule: the step winner stays on the device.  Small clouds (largest patch <= 1024 rows, disjoint patches
+ * that are exactly the target rows -- checked with one 8-byte read per call) run all P steps inside ONE persistent
+ * cooperative kernel (loop state in shared memory, one grid barrier per step).  Otherwise every launch reads its row
+ * range from the device-resident winner, all P steps are enqueued without a host read and the call returns after the
+ * last launch has been enqueued.  Only when a patch is large enough for the by-value all-pairs kernel (>= 16 384
+ * rows, sources are kernel parameters) does the loop read the winner back once per step (8 bytes).  With a trace
+ * requested the call synchronises `stream` once at the end.  DNP_PATCH_LOOP=persistent|device|host forces a
+ * schedule.                                                                                                  */
 DNP_API size_t dnp_patch_propagate_workspace_bytes(int64_t N, int64_t P, int64_t max_patch, int64_t n_tgt);
 DNP_API int dnp_patch_propagate_f32(float* pts, int64_t N, int64_t ld,
                             const int64_t* perm, const int64_t* offsets_dev, const int64_t* offsets_host, int64_t P,
