@@ -339,11 +339,12 @@ def points_propagate(pts, diffuse=False, starting_point=0, eps=1e-6, want_trace=
 
 # ------------------------------------------------------------------ "xie" interaction
 def patch_propagate(pts, perm, offsets, start_patch, E, diffuse=False, eps=1e-5, rest_perm=None, rest_offsets=None,
-                    tgt_idx=None, want_trace=False):
+                    tgt_idx=None, want_trace=False, offsets_host=None):
     """The whole greedy patch loop of strongest_field_propagation{,_reps} in one native call
     (dnp_patch_propagate_f32), in place on pts [N, 6]; E [N, 3] must be zero and receives the final field.
-    offsets / rest_offsets may be tensors on any device (a host copy is made: the launch shapes need the sizes).
-    Returns (order, values) as numpy arrays when want_trace."""
+    offsets / rest_offsets may be tensors on any device (a host copy is made: the launch shapes need the sizes);
+    pass the device tensor as `offsets` AND its host copy as `offsets_host` to avoid any copy inside the call (needed
+    to record the call into a CUDA graph).  Returns (order, values) as numpy arrays when want_trace."""
     import numpy as np
     lib = load()
     p, ld = _rows(pts, 6, "pts")
@@ -355,7 +356,8 @@ def patch_propagate(pts, perm, offsets, start_patch, E, diffuse=False, eps=1e-5,
     dev = p.device
     perm = _idx(perm, dev, "perm")
     off_dev = _idx(offsets, dev, "offsets")
-    off_host = np.ascontiguousarray(offsets.cpu().numpy(), dtype=np.int64)
+    src_host = offsets if offsets_host is None else offsets_host
+    off_host = np.ascontiguousarray(src_host.cpu().numpy() if torch.is_tensor(src_host) else src_host, dtype=np.int64)
     P = off_host.size - 1
     rest_perm = _idx(rest_perm, dev, "rest_perm")
     rest_host = None if rest_offsets is None else np.ascontiguousarray(rest_offsets.cpu().numpy(), dtype=np.int64)
