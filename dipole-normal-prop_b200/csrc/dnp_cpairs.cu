@@ -267,7 +267,9 @@ bool use_const_path(int64_t S, int64_t M, int lattice_n) {
     const int mode = env_int("DNP_CONST_PATH", 1);
     if (mode == 0 || lattice_n > 0) return false;
     if (mode == 2) return S >= 1 && M >= 1;
-    return S >= 16384 && M >= 131072;
+    // tools/plan_probe.py: 65 536 x 65 536 runs 1.56e12 pairs/s here vs 1.39e12 in the shared-memory kernel, 32 768 x
+    // 100 000 1.54e12 vs 1.36e12; at 16 384 x 65 536 they tie and at M = 32 768 this path loses
+    return (S >= 16384 && M >= 131072) || (S >= 32768 && M >= 65536);
 }
 
 CPairPlan make_cpair_plan(bool potential, int64_t S, int64_t M, int sm_count) {

@@ -16,7 +16,7 @@
  *   - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream).
  *     Work is enqueued asynchronously; nothing synchronises unless stated.
  *     Stated exception: potential / field calls with >= 16384 sources and
- *     >= 131072 targets hand their sources to the kernels by value (kernel
+ *     >= 131072 targets (or >= 32768 sources and >= 65536 targets) hand their sources to the kernels by value (kernel
  *     parameters -> uniform registers), which needs them on the host: the call
  *     synchronises `stream` once before its launches.  Never under stream
  *     capture; DNP_CONST_PATH=0 in the environment disables that path.

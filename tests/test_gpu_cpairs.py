@@ -81,6 +81,14 @@ def test_threshold_selects_the_path_and_matches_the_shared_memory_kernel(fu, dev
     n0 = dn.launch_count()
     fu.field_grad(src[:8192], tgt)
     assert dn.launch_count() - n0 <= 3
+    # second branch of the rule: >= 32 768 sources x >= 65 536 targets (37 blocks of 896 sources)
+    big_src = cloud(32768, 53).to(dev)
+    n0 = dn.launch_count()
+    fu.field_grad(big_src, tgt[:65536])
+    assert dn.launch_count() - n0 == 1 + 37 + 1
+    n0 = dn.launch_count()
+    fu.field_grad(big_src, tgt[:65535])
+    assert dn.launch_count() - n0 <= 3
 
 
 def test_epilogues_gathers_and_masks(fu, orc, dev, path):
