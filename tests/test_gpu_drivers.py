@@ -2,6 +2,8 @@
 decision sequences recorded from the unmodified reference (tests/golden/make_golden.py) and against the
 oracle.  The bar for decisions is IDENTITY: visit order, flip booleans, final normal signs, lattice sign.
 """
+import os
+
 import numpy as np
 import pytest
 import torch
@@ -391,6 +393,18 @@ def test_persistent_loop_edge_cases(fu, dev, monkeypatch):
         fu.strongest_field_propagation(b, [], patches)
         monkeypatch.delenv("DNP_PATCH_LOOP")
         assert torch.equal(a, b)
+
+
+def test_schedules_agree_on_random_clouds():
+    """tools/loop_stress.py: 16 random clouds (40 .. 60 000 points; coherent, ragged, tiny and 1000-row patches; P up to
+    several thousand; empty patches; diffuse on / off; with and without rest rows) through the persistent kernel and
+    the device-driven launches: same visit order, same final normals."""
+    import importlib.util
+    spec = importlib.util.spec_from_file_location(
+        "loop_stress", os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tools", "loop_stress.py"))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    assert mod.run(16, verbose=False) == 0
 
 
 def test_patch_loop_captures_into_a_cuda_graph(dev, golden, monkeypatch):
