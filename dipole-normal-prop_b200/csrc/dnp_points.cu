@@ -610,9 +610,16 @@ int run_points_propagate(float* pts, int64_t N, int64_t ld, int64_t start, float
         DNP_CHECK_CUDA(cudaFuncSetAttribute(points_propagate_kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
         attr_done.store(1);
     }
-    // smallest power-of-two cluster that gives every thread <= 2 points, capped by what the device can co-schedule
+    // smallest power-of-two cluster that gives every thread <= 1 point, capped by what the device can co-schedule
+    // (tools/points_probe.py, us per step: N = 2000: 2 CTAs 1.76, 4 CTAs 1.38, 8 CTAs 1.53; N = 5000: 8 CTAs 1.97,
+    // 16 CTAs 1.85; N = 10 000: 8 CTAs 2.46, 16 CTAs 2.27 -- a second point per thread costs more than a wider
+    // cluster exchange; 1024-thread CTAs were slower still, 2.85 at N = 10 000)
     int ncta = 1;
-    while (ncta < kMaxCluster && (int64_t)ncta * kPtThreads * 2 < N) ncta *= 2;
+    while (ncta < kMaxCluster && (int64_t)ncta * kPtThreads < N) ncta *= 2;
+    if (const char* forced = getenv("DNP_POINTS_CTAS")) {                       // tuning override (power of two)
+        const int f = atoi(forced);
+        if (f == 1 || f == 2 || f == 4 || f == 8 || f == 16) ncta = f;
+    }
     for (;; ncta *= 2) {
         const int cap = (int)((N + ncta - 1) / ncta);
         if (point_smem_bytes(cap) <= 227 * 1024) break;
