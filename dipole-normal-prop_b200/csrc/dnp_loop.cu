@@ -111,7 +111,7 @@ __global__ void __launch_bounds__(kLoopThreads, 1) patch_loop_kernel(LoopArgs a)
     __shared__ unsigned long long warp_best[32];
     __shared__ float warp_val[32];
     __shared__ int32_t sh_next[2];
-    __shared__ int sh_nseg, sh_nlive;
+    __shared__ int sh_nseg, sh_nlive[2];
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int G = (int)gridDim.x, c = (int)blockIdx.x;
@@ -123,7 +123,7 @@ __global__ void __launch_bounds__(kLoopThreads, 1) patch_loop_kernel(LoopArgs a)
     if (nk > 0 && (NQ - 1) % G == c) R -= (int)(NQ * kChunk - T);                    // CSR row ((li/8) G + c) 8 + li%8
 #define LOOP_GLOBAL_ROW(li) ((((int64_t)((li) / kChunk) * G + c) * kChunk) + ((li) % kChunk))
 
-    if (tid == 0) sh_nseg = 0;
+    if (tid == 0) { sh_nseg = 0; sh_nlive[0] = 0; sh_nlive[1] = 0; }
     for (int li = tid; li < R; li += kLoopThreads) {
         const int64_t i = LOOP_GLOBAL_ROW(li);
         const float* q = a.pts + a.perm[i] * a.ld;
@@ -198,6 +198,17 @@ __global__ void __launch_bounds__(kLoopThreads, 1) patch_loop_kernel(LoopArgs a)
                 q[0] = -q[0]; q[1] = -q[1]; q[2] = -q[2];
             }
         }
+        // the rows alive this step, compacted (so that dead rows cost nothing and free their lanes): not of the
+        // chosen patch and, unless diffuse, not of a patch visited before
+        for (int base = 0; base < R; base += kLoopThreads) {
+            const int t = base + tid;
+            const bool f = t < R && tpatch[t] != j && (a.diffuse || !tstate[t]);
+            const unsigned m = __ballot_sync(0xffffffffu, f);
+            int wbase = 0;
+            if (lane == 0 && m) wbase = atomicAdd(&sh_nlive[step & 1], __popc(m));
+            wbase = __shfl_sync(0xffffffffu, wbase, 0);
+            if (f) live[wbase + __popc(m & ((1u << lane) - 1u))] = (uint16_t)t;
+        }
         __syncthreads();
         LOOP_MARK(0)
         // ---- E += field of the patch on my rows (:261,265,330,335); visited rows are skipped, or, when diffuse,
@@ -205,20 +216,8 @@ __global__ void __launch_bounds__(kLoopThreads, 1) patch_loop_kernel(LoopArgs a)
         // packed arithmetic) and every L-th source; consecutive threads are consecutive row pairs, so a warp reads
         // one or two sources at a time (broadcast shared-memory loads).  The L partial fields of a row are then
         // summed in lane order.
-        // The live rows are compacted first, so that dead rows cost nothing and the lanes they free go to the rest.
-        if (tid == 0) sh_nlive = 0;
-        __syncthreads();
-        for (int base = 0; base < R; base += kLoopThreads) {
-            const int t = base + tid;
-            const bool f = t < R && (a.diffuse ? (tpatch[t] != j) : !tstate[t]);
-            const unsigned m = __ballot_sync(0xffffffffu, f);
-            int wbase = 0;
-            if (lane == 0 && m) wbase = atomicAdd(&sh_nlive, __popc(m));
-            wbase = __shfl_sync(0xffffffffu, wbase, 0);
-            if (f) live[wbase + __popc(m & ((1u << lane) - 1u))] = (uint16_t)t;
-        }
-        __syncthreads();
-        const int nlive = sh_nlive;
+        const int nlive = sh_nlive[step & 1];
+        if (tid == 0) sh_nlive[(step + 1) & 1] = 0;                               // next step's counter
         const int pairs = (nlive + 1) >> 1;
         int L = pairs > 0 ? kLoopThreads / pairs : 1;
         const int l_cap = (n + 3) >> 2;
@@ -245,12 +244,20 @@ __global__ void __launch_bounds__(kLoopThreads, 1) patch_loop_kernel(LoopArgs a)
             }
             __syncthreads();
             const int rows_here = (2 * (pbase + span) < nlive ? 2 * (pbase + span) : nlive) - 2 * pbase;
-            for (int idx = tid; idx < 3 * rows_here; idx += kLoopThreads) {
-                const int m = idx / 3, k = idx - 3 * m;                           // m: position among this pass's live rows
-                const float* o = part + 6 * (m >> 1) + 2 * k + (m & 1);
-                float e = 0.f;
-                for (int l2 = 0; l2 < L; ++l2) e += o[(size_t)6 * span * l2];
-                tE[3 * live[2 * pbase + m] + k] += finite_or_zero(e);             // field_utils.py:114-115
+            for (int m = tid; m < rows_here; m += kLoopThreads) {                 // m: position among this pass's live rows
+                const float* o = part + 6 * (m >> 1) + (m & 1);
+                float ex = 0.f, ey = 0.f, ez = 0.f;
+                for (int l2 = 0; l2 < L; ++l2) {                                  // the row's lanes, in lane order
+                    const float* ol = o + (size_t)6 * span * l2;
+                    ex += ol[0]; ey += ol[2]; ez += ol[4];
+                }
+                const int t = live[2 * pbase + m];
+                const float Ex = tE[3 * t] + finite_or_zero(ex), Ey = tE[3 * t + 1] + finite_or_zero(ey),
+                            Ez = tE[3 * t + 2] + finite_or_zero(ez);              // field_utils.py:114-115
+                tE[3 * t] = Ex; tE[3 * t + 1] = Ey; tE[3 * t + 2] = Ez;
+                // E.n of the row for the interactions below (only live rows belong to unvisited patches)
+                dots[t] = __fadd_rn(__fadd_rn(__fmul_rn(Ex, tn[3 * t]), __fmul_rn(Ey, tn[3 * t + 1])),
+                                    __fmul_rn(Ez, tn[3 * t + 2]));
             }
             __syncthreads();
         }
@@ -259,10 +266,6 @@ __global__ void __launch_bounds__(kLoopThreads, 1) patch_loop_kernel(LoopArgs a)
         // step's buffer
         float* part_inter = a.inter + (size_t)(step & 1) * a.P * G;
         if (step + 1 < a.P) {
-            for (int t = tid; t < R; t += kLoopThreads)
-                dots[t] = __fadd_rn(__fadd_rn(__fmul_rn(tE[3 * t], tn[3 * t]), __fmul_rn(tE[3 * t + 1], tn[3 * t + 1])),
-                                    __fmul_rn(tE[3 * t + 2], tn[3 * t + 2]));
-            __syncthreads();
             for (int s = warp; s < nseg; s += kLoopWarps) {
                 const int b = seg_lb[s], e = seg_le[s], p = tpatch[b];
                 if (visited[p]) continue;
