@@ -96,6 +96,9 @@ def _clear(mask, j):
 def _index_list(idx_list, dev):
     out = []
     for idx in idx_list:
+        if torch.is_tensor(idx) and idx.dtype == torch.int64 and idx.device == dev and idx.dim() == 1:
+            out.append(idx)                       # the common case, without the per-tensor dispatch overhead
+            continue
         idx = torch.as_tensor(idx)
         if idx.dtype == torch.bool:
             idx = torch.nonzero(idx).flatten()
