@@ -116,9 +116,264 @@ def cpu_baseline_block(n):
     m = 2 * n                                          # > max_pts = 15000 at the default n: the chunking runs too
     sec = time_cpu_port(n, m)
     return {"value": n * m / sec, "unit": UNIT, "cores": torch.get_num_threads(), "kind": "port",
-            "host_cpus": os.cpu_count(),
+            "host_cpus": os.cpu_count(), "drivers": cpu_driver_seconds(full=False),
             "sample": f"oracle/torch_port.field_grad (the reference's op chain and chunking, field_utils.py:61-116), "
                       f"float32, {n} sources x {m} targets = {n * m:.3e} pairs, one run of {sec:.1f} s"}
+
+
+def _golden(name):
+    import numpy as np
+    return np.load(os.path.join(ROOT, "tests", "golden", name + ".npz"))
+
+
+def _csr_patches(perm, off, dev=None):
+    out = [torch.from_numpy(perm[off[i]:off[i + 1]].copy()) for i in range(len(off) - 1)]
+    return [p.to(dev) for p in out] if dev is not None else out
+
+
+def cpu_driver_seconds(full):
+    """Wall seconds of the reference's DRIVERS on this box's host cores (BASELINE.json metric "e2e orient sec";
+    BASELINE.md section 4 item 4): oracle/torch_drivers.py = the reference's op sequence (bit-equal outputs, pinned
+    in tests/test_oracle_drivers.py), stage names as in the reference's MyTimer blocks ('propagating field' /
+    'fix global orientation' / 'calculating field').  full=False: the two cheap configurations only."""
+    from oracle import torch_drivers as td
+    torch.set_num_threads(os.cpu_count() or 1)
+    out, stages = {}, {}
+
+    def timed(key, fn):
+        t0 = time.perf_counter()
+        fn()
+        out[key] = time.perf_counter() - t0
+
+    def pipeline(key, propagate, pts):
+        t0 = time.perf_counter()
+        propagate()
+        t1 = time.perf_counter()
+        flip = bool(td.lattice_mean_potential(pts) < 0)
+        if flip:
+            pts[:, 3:] *= -1
+        t2 = time.perf_counter()
+        out[key] = t2 - t0
+        stages[key] = {"propagating field": t1 - t0, "fix global orientation": t2 - t1}
+
+    g = _golden("points_prop")
+    pts = torch.from_numpy(g["pc_in"][:2000].copy())
+    pipeline("cfg1_ok_xyz_first_2000_pts_e2e_s", lambda: td.propagate_points(pts, diffuse=True), pts)
+    g2 = _golden("patch_prop")
+    groups = _csr_patches(g2["perm"], g2["offsets"])
+    pts2 = torch.from_numpy(g2["pc_in"].copy())
+    pipeline("cfg2_fandisk_72_patches_e2e_s", lambda: td.propagate_patches(pts2, [], groups), pts2)
+    if full:
+        pts1 = torch.from_numpy(g["pc_in"].copy())
+        pipeline("cfg1_ok_xyz_10000_pts_e2e_s", lambda: td.propagate_points(pts1), pts1)
+        pc3, reps = cfg3_standin()
+        st = {}
+        pipeline("cfg3_reps_60000_pts_48_patches_e2e_s",
+                 lambda: td.propagate_representatives(pc3, reps, diffuse=True, stage_seconds=st), pc3)
+        stages["cfg3_reps_60000_pts_48_patches_e2e_s"].update({"propagation (greedy loop)": st.get("propagation"),
+                                                               "final field reps -> rest": st.get("final_field")})
+        ref, tgt = cfg4_standin()
+        timed("cfg4_transfer_20000_x_40000_e2e_s", lambda: td.transfer_orientation(ref, tgt))
+        stages["cfg4_transfer_20000_x_40000_e2e_s"] = {"calculating field": out["cfg4_transfer_20000_x_40000_e2e_s"]}
+    out["stages"] = stages
+    out["cores"] = torch.get_num_threads()
+    return out
+
+
+# ---------------------------------------------------------------------------------------------- multi-GPU product path
+def dist_parity(dn, dist, dnp_dist, dev, rank, world):
+    """The assertions of tests/test_gpu_dist.py on this run's ranks, before anything is timed: every sharded call
+    of dnp_dist against the same call on one GPU (each rank computes the unsharded answer itself)."""
+    src, tgt = cloud(20001, 1).to(dev), cloud(150003, 2).to(dev)          # uneven shards
+    checks = {}
+    E = dn.field_grad(src, tgt)
+    mag = E.norm(dim=-1)
+    E_full = dnp_dist.field_grad_sharded(src, tgt, gather=True)
+    checks["field_grad_gathered_within_tolerance"] = bool(((E_full - E).norm(dim=-1) <= 1e-4 * mag + 1e-6 * mag.max()).all())
+    a, b = dnp_dist.shard_range(tgt.shape[0], rank, world)
+    checks["local_block_is_the_gathered_slice"] = bool(torch.equal(dnp_dist.field_grad_sharded(src, tgt), E_full[a:b]))
+    phi = dn.potential(src, tgt)
+    phi_full = dnp_dist.potential_sharded(src, tgt, gather=True)
+    checks["potential_gathered_within_tolerance"] = bool(((phi_full - phi).abs() <= 1e-4 * phi.abs() + 1e-5 * phi.abs().max()).all())
+    mean = dnp_dist.measure_mean_potential_sharded(src)
+    want = dn.lattice_mean_potential(src)
+    checks["lattice_mean_sources_sharded"] = bool((mean - want).abs() <= 1e-4 * want.abs())
+    perm = torch.randperm(20001, generator=torch.Generator().manual_seed(3)).to(dev)
+    offsets = torch.tensor([0, 400, 401, 1200, 2500, 3010, 20001])
+    edges = torch.tensor([[0, 1], [1, 0], [2, 3], [3, 2], [4, 0], [1, 1], [5, 4]])
+    inter = dnp_dist.edge_interactions_sharded(src, perm, offsets, edges)
+    one = dn.edge_interactions_batched(src, perm, offsets.to(dev), edges.to(dev))
+    checks["edge_interactions_allreduced_within_tolerance"] = bool(((inter - one).abs() <= 2e-4 * one.abs() + 1e-3).all())
+    # identical on every rank (all_gather / all_reduce results): compare bit patterns through a MAX and a MIN reduce
+    sig = torch.stack([E_full.view(torch.int32).sum(dtype=torch.int64), inter.view(torch.int32).sum(dtype=torch.int64)])
+    hi, lo = sig.clone(), sig.clone()
+    dist.all_reduce(hi, op=dist.ReduceOp.MAX)
+    dist.all_reduce(lo, op=dist.ReduceOp.MIN)
+    checks["results_identical_on_all_ranks"] = bool(torch.equal(hi, lo))
+    ok = torch.tensor([int(all(checks.values()))], device=dev)
+    dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+    return {"ok": bool(ok.item()), "world": world, "rank0_checks": checks}
+
+
+def multi_gpu_blocks(args, dn, dist, dev, rank, world):
+    """Strong scaling of the product's multi-GPU layer (dnp_dist.py): a FIXED global problem split over the ranks,
+    starting from rank 0's pinned host buffers and ending with the full result in rank 0's host memory.
+      field: G sources x G targets; broadcast of the sources (24 B each) and the targets (12 B each), each rank's
+             target shard through field_grad, all_gather of E (12 B per target), device -> host on rank 0
+      edges: flip scores of a 1000-patch graph of the 1M-point cloud (field_utils.py:145-160); each rank sums over
+             its slice of every target patch, ONE all_reduce(SUM) over the edge vector combines them."""
+    import dnp_dist
+
+    def sync_all():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(ms):
+        t = torch.tensor([ms], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def ev_ms(fn):
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        sync_all()
+        a.record()
+        r = fn()
+        b.record()
+        sync_all()
+        return max_over_ranks(a.elapsed_time(b)), r
+
+    G = args.strong_points
+    out = {}
+    src_host = cloud(G, 11, pin=True) if rank == 0 else None
+    tgt_host = cloud(G, 12, cols=3, pin=True) if rank == 0 else None
+    E_host = torch.empty(G, 3).pin_memory() if rank == 0 else None
+    src = torch.empty(G, 6, device=dev)
+    tgt = torch.empty(G, 3, device=dev)
+
+    def field_step():
+        if rank == 0:
+            src.copy_(src_host, non_blocking=True)
+            tgt.copy_(tgt_host, non_blocking=True)
+        if world > 1:
+            dist.broadcast(src, 0)
+            dist.broadcast(tgt, 0)
+        E = dnp_dist.field_grad_sharded(src, tgt, eps=EPS, gather=True)
+        if rank == 0:
+            E_host.copy_(E, non_blocking=True)
+        return E
+
+    field_step()
+    times = [ev_ms(field_step)[0] for _ in range(2)]
+    ms = min(times)
+    compute_ms, _ = ev_ms(lambda: dnp_dist.field_grad_sharded(src, tgt, eps=EPS))
+    bcast_ms = ev_ms(lambda: (dist.broadcast(src, 0), dist.broadcast(tgt, 0)))[0] if world > 1 else 0.0
+    a, b = dnp_dist.shard_range(G, rank, world)
+    local = torch.empty(b - a, 3, device=dev)
+    gather_ms = ev_ms(lambda: dnp_dist._gather_rows(local, G, None))[0] if world > 1 else 0.0
+    out["field"] = {
+        "sources": G, "targets": G, "ms_per_step": ms, "pairs_per_s": float(G) * G / (ms * 1e-3),
+        "shard_compute_ms": compute_ms, "broadcast_ms": bcast_ms, "all_gather_ms": gather_ms,
+        "broadcast_bytes": G * 36, "all_gather_bytes": G * 12, "h2d_bytes": G * 36, "d2h_bytes": G * 12,
+        "bound_by": "shard compute" if compute_ms >= max(bcast_ms, gather_ms) else "collective",
+        "api": "dnp_dist.field_grad_sharded(gather=True): targets block-sharded, sources replicated by broadcast"}
+    del src, tgt, local
+
+    # ---- flip scores of a patch graph, one all_reduce
+    pc = surface_cloud(1 << 20, 10)
+    key = ((pc[:, :3] + 0.6) * 8).long().clamp(0, 15)
+    order = torch.argsort(key[:, 0] * 256 + key[:, 1] * 16 + key[:, 2], stable=True)
+    chunks = torch.chunk(order, 1000)
+    perm = torch.cat(chunks).to(dev)
+    offsets = torch.zeros(1001, dtype=torch.int64)
+    offsets[1:] = torch.tensor([c.numel() for c in chunks]).cumsum(0)
+    e = [(i, (i + d) % 1000) for i in range(1000) for d in (1, 2, 3)]
+    edges = torch.tensor(e + [(j, i) for i, j in e])
+    pcd = pc.to(dev)
+    dnp_dist.edge_scores_sharded(pcd, perm, offsets, edges)
+    ms_e, (w, _) = ev_ms(lambda: dnp_dist.edge_scores_sharded(pcd, perm, offsets, edges))
+    vec = torch.zeros(edges.shape[0], device=dev)
+    ar_ms = ev_ms(lambda: dist.all_reduce(vec))[0] if world > 1 else 0.0
+    pairs = float(sum(chunks[i].numel() * chunks[j].numel() for i, j in edges.tolist()))
+    out["edge_scores"] = {"patches": 1000, "edges": int(edges.shape[0]), "pairs": pairs, "ms": ms_e,
+                          "pairs_per_s": pairs / (ms_e * 1e-3), "all_reduce_ms": ar_ms,
+                          "all_reduce_bytes": int(edges.shape[0]) * 4, "checksum": float(w.double().abs().sum().item()),
+                          "api": "dnp_dist.edge_scores_sharded: per-patch target slices + one all_reduce(SUM)"}
+    return out
+
+
+def gpu_driver_seconds(field_utils, dev):
+    """The same five driver workloads as cpu_driver_seconds through the drop-in API, HOST tensors in and out
+    (device copies inside the timed region), wall clock, best of 2; each result is compared with the reference's
+    recorded decisions (tests/golden, generated by the unmodified reference)."""
+    import numpy as np
+    out, parity = {}, {}
+
+    def best(fn, reps=2):
+        b = float("inf")
+        for _ in range(reps):
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            r = fn()
+            torch.cuda.synchronize()
+            b = min(b, time.perf_counter() - t0)
+        return b, r
+
+    def pipeline(propagate, pts):
+        propagate(pts)
+        if bool(field_utils.measure_mean_potential(pts) < 0):
+            pts[:, 3:] *= -1
+        return pts
+
+    def flips_of(pts, pc_in):
+        return np.packbits(((pts[:, 3:] * pc_in[:, 3:]).sum(-1) < 0).numpy())
+
+    g = _golden("points_prop")
+    pc = torch.from_numpy(g["pc_in"].copy())
+    for key, n, diffuse, tag in (("cfg1_ok_xyz_first_2000_pts_e2e_s", 2000, True, "n2000"),
+                                 ("cfg1_ok_xyz_10000_pts_e2e_s", 10000, False, "full")):
+        sec, res = best(lambda: pipeline(lambda p: field_utils.strongest_field_propagation_points(p, diffuse=diffuse),
+                                         pc[:n].clone()))
+        out[key] = sec
+        want = torch.from_numpy(g[f"{tag}_normals"].copy())
+        if float(g[f"{tag}_mean_potential"]) < 0:
+            want = -want
+        parity[key] = bool(torch.equal(res[:, 3:], want))
+    g2 = _golden("patch_prop")
+    groups = _csr_patches(g2["perm"], g2["offsets"])
+    pc2 = torch.from_numpy(g2["pc_in"].copy())
+    sec, res = best(lambda: pipeline(lambda p: field_utils.strongest_field_propagation(p, [], groups), pc2.clone()))
+    out["cfg2_fandisk_72_patches_e2e_s"] = sec
+    want = torch.from_numpy(g2["plain_normals"].copy())
+    if float(g2["plain_mean_potential"]) < 0:
+        want = -want
+    parity["cfg2_fandisk_72_patches_e2e_s"] = bool(torch.equal(res[:, 3:], want))
+    try:
+        gl = _golden("large")
+    except OSError:
+        gl = None
+    pc3, reps = cfg3_standin()
+    sec, res = best(lambda: pipeline(lambda p: field_utils.strongest_field_propagation_reps(p, reps, diffuse=True),
+                                     pc3.clone()))
+    out["cfg3_reps_60000_pts_48_patches_e2e_s"] = sec
+    if gl is not None and abs(pc3.double().sum().item() - float(gl["cfg3_input_checksum"])) < 1e-9:
+        got = flips_of(res, pc3)
+        want = gl["cfg3_diffuse_flip_bits"]
+        if float(gl["cfg3_diffuse_mean_potential"]) < 0:
+            want = np.packbits(1 - np.unpackbits(want)[:pc3.shape[0]])
+        parity["cfg3_reps_60000_pts_48_patches_e2e_s"] = {
+            "points_differing_from_reference": int(np.unpackbits(got ^ want)[:pc3.shape[0]].sum()), "points": pc3.shape[0]}
+    ref, tgt = cfg4_standin()
+    sec, res = best(lambda: field_utils.reference_field(ref, tgt.clone()))
+    out["cfg4_transfer_20000_x_40000_e2e_s"] = sec
+    if gl is not None and abs(ref.double().sum().item() + tgt.double().sum().item() - float(gl["cfg4_input_checksum"])) < 1e-9:
+        diff = np.unpackbits(flips_of(res, tgt) ^ gl["cfg4_flip_bits"])[:tgt.shape[0]].astype(bool)
+        parity["cfg4_transfer_20000_x_40000_e2e_s"] = {
+            "points_differing_from_reference": int(diff.sum()), "points": tgt.shape[0],
+            "largest_margin_among_them": float(gl["cfg4_margin"][diff].max()) if diff.any() else 0.0}
+    out["parity_vs_reference_decisions"] = parity
+    return out
 
 
 def run_reference_arm(args, rank, world):
@@ -129,15 +384,17 @@ def run_reference_arm(args, rank, world):
     torch.set_num_threads(os.cpu_count() or 1)
     n = args.cpu_points
     for _ in range(args.warmup):
-        time_cpu_port(n, n, 1)
+        time_cpu_port(n, 2 * n, 1)
     t0 = time.perf_counter()
     for _ in range(args.steps):
-        time_cpu_port(n, n, 1)
+        time_cpu_port(n, 2 * n, 1)
     sec = time.perf_counter() - t0
-    value = args.steps * n * n / sec
-    sample = (f"each step = oracle/torch_port.field_grad on {n} x {n} float32 points ({n * n:.3e} pairs), a bounded "
-              f"sample of the {args.points} x {args.points} per-GPU workload; the reference is pure Python/torch and "
-              f"does not travel to this box, so its op chain is ported (bit-exact vs tests/golden/leaf.npz)")
+    value = args.steps * n * 2 * n / sec
+    sample = (f"each step = oracle/torch_port.field_grad on {n} x {2 * n} float32 points ({2 * n * n:.3e} pairs, the "
+              f"targets above max_pts = 15000 so that the reference's recursive chunking runs), a bounded sample of "
+              f"the {args.points} x {args.points} per-GPU workload; the reference is pure Python/torch and does not "
+              f"travel to this box, so its op chain is ported (bit-exact vs tests/golden/leaf.npz)")
+    extras = {} if args.no_extras else cpu_driver_seconds(full=True)
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": sec / args.steps * 1e3,
@@ -146,7 +403,7 @@ def run_reference_arm(args, rank, world):
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": torch.get_num_threads(), "kind": "port",
                          "host_cpus": os.cpu_count(), "sample": sample},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-        "gpu_launches": 0}), flush=True)
+        "extras": extras, "gpu_launches": 0}), flush=True)
 
 
 def ncu_traffic(points):
@@ -177,6 +434,9 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--points", type=int, default=1 << 20, help="sources (replicated) and targets per GPU")
     ap.add_argument("--cpu-points", type=int, default=8192, help="side of the CPU sample (reference arm / baseline)")
+    ap.add_argument("--strong-points", type=int, default=1 << 21,
+                    help="side of the fixed global problem of the strong-scaling block (dnp_dist)")
+    ap.add_argument("--no-strong", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-extras", action="store_true")
     args = ap.parse_args()
@@ -205,6 +465,11 @@ def main():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
+
+    parity = None
+    if world > 1:
+        import dnp_dist
+        parity = dist_parity(dn, dist, dnp_dist, dev, rank, world)
 
     P = args.points
     src_host = cloud(P, 1, pin=True)                                    # replicated sources
@@ -265,6 +530,11 @@ def main():
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms_total, e2e_ms = t.tolist()
 
+    strong = None
+    if not args.no_strong:
+        del E, flush
+        strong = multi_gpu_blocks(args, dn, dist, dev, rank, world)
+
     if rank == 0:
         value = world * pairs_per_step * args.steps / (ms_total * 1e-3)
         # one timed region per step: the fork->join span of the step's chunk launches (dnp_cpairs.cu runs them on
@@ -304,6 +574,14 @@ def main():
                 "hbm_algorithmic_gbs": chunk_launches * (P * 12 + 2 * P * 12) / (k_ms * 1e-3) / 1e9,
                 "traffic": ncu_traffic(P)},
         }
+        if parity is not None:
+            line["dist_parity"] = parity
+        if strong is not None:
+            one_gpu_rate = value / world                     # this run's own per-GPU rate on the weak workload
+            f = strong["field"]
+            f["speedup_vs_one_gpu_rate"] = f["pairs_per_s"] / one_gpu_rate
+            f["efficiency_vs_one_gpu_rate"] = f["pairs_per_s"] / one_gpu_rate / world
+            line["strong"] = dict(strong, scaling="strong", n_gpus=world)
         if not args.no_extras:
             line["extras"] = extras(dn, field_utils, dev, src, tgt)
         if world == 1 and not args.no_cpu_baseline:
@@ -332,7 +610,7 @@ def extras(dn, field_utils, dev, src, tgt):
         return best
 
     P = src.shape[0]
-    out = {}
+    out = gpu_driver_seconds(field_utils, dev)
     phi = torch.empty(P, device=dev)
     ms = best_ms(lambda: dn.potential(src, tgt, out=phi), 2)
     out["potential_pairs_per_s"] = P * P / ms * 1e3
@@ -495,6 +773,31 @@ def surface_cloud(n, seed):
     pc = torch.cat([d * 0.45 + torch.randn(n, 3, generator=g) * 0.002, d], 1).float()
     pc[torch.rand(n, generator=g) < 0.5, 3:] *= -1
     return pc.contiguous()
+
+
+def cfg3_standin(n=60000, n_patches=48, max_rep=500, seed=10):
+    """BASELINE config 3 stand-in at the size BASELINE.md section 2 timed the reference (data/lion.xyz is not shipped):
+    a scrambled noisy sphere, `n_patches` spatially coherent patches (points sorted by a coarse voxel key, equal
+    chunks), `max_rep` seeded random representatives per patch (orient_large.py:48-52).  CPU tensors."""
+    pc = surface_cloud(n, seed)
+    key = ((pc[:, :3] + 0.6) * 8).long().clamp(0, 15)
+    order = torch.argsort(key[:, 0] * 256 + key[:, 1] * 16 + key[:, 2], stable=True)
+    g = torch.Generator().manual_seed(seed + 1)
+    reps = []
+    for c in torch.chunk(order, n_patches):
+        pm = c[torch.randperm(c.shape[0], generator=g)]
+        reps.append((pm[:max_rep].clone(), pm[max_rep:].clone()))
+    return pc, reps
+
+
+def cfg4_standin(n_ref=20000, n_tgt=40000, seed=8):
+    """BASELINE config 4 stand-in (data/interpolate/*.xyz are not shipped), the size BASELINE.md section 2 timed:
+    an oriented reference sampling of the sphere and a scrambled, independently sampled target.  CPU tensors."""
+    g = torch.Generator().manual_seed(seed)
+    d = torch.randn(n_ref, 3, generator=g)
+    d = d / d.norm(dim=-1, keepdim=True)
+    ref = torch.cat([d * 0.45 + torch.randn(n_ref, 3, generator=g) * 0.002, d], 1).float().contiguous()
+    return ref, surface_cloud(n_tgt, seed + 1)
 
 
 if __name__ == "__main__":

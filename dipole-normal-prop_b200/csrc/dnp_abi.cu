@@ -287,7 +287,7 @@ int host_pairs(bool potential, const float* src_host, int64_t S, int64_t ld_s, c
     int rc = DNP_OK;
     do {
         // large calls pass the sources by value from the host (dnp_cpairs.cu): dense host rows need no upload
-        const bool by_value = ld_s == 6 && use_const_path(S, M, 0);
+        const bool by_value = ld_s == 6 && !use_ring_path(S, M, 0) && use_const_path(S, M, 0);
         if (!by_value && (e = upload_rows(d_src, src_host, S, 6, ld_s, stream)) != cudaSuccess) { rc = cuda_fail(e, "upload sources"); break; }
         if ((e = upload_rows(d_tgt, tgt_host, M, 3, ld_t, stream)) != cudaSuccess) { rc = cuda_fail(e, "upload targets"); break; }
         t_up = now();

@@ -23,6 +23,21 @@ int cuda_fail(cudaError_t err, const char* what);
         if (_e != cudaSuccess) return ::dnp::cuda_fail(_e, #expr); \
     } while (0)
 
+// ---------------------------------------------------------------- per-device one-time setup
+// cudaFuncSetAttribute applies to the CURRENT device only: a process that calls on cuda:0 and then on cuda:1 has
+// to opt in on both.  `flags` is a function-local `static std::atomic<int> flags[kMaxDevices]`.
+constexpr int kMaxDevices = 64;
+#define DNP_ONCE_PER_DEVICE(flags, body)                                             \
+    do {                                                                             \
+        int _dev = 0;                                                                \
+        DNP_CHECK_CUDA(cudaGetDevice(&_dev));                                        \
+        const bool _tracked = _dev >= 0 && _dev < ::dnp::kMaxDevices;                \
+        if (!_tracked || !(flags)[_dev].load()) {                                    \
+            body;                                                                    \
+            if (_tracked) (flags)[_dev].store(1);                                    \
+        }                                                                            \
+    } while (0)
+
 // ---------------------------------------------------------------- packed f32x2 arithmetic
 // Blackwell executes two independent FP32 operations per lane with one
 // FFMA2/FADD2/FMUL2 instruction on a 64-bit register pair.  The hot loops keep

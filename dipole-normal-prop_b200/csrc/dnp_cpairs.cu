@@ -75,11 +75,15 @@ __global__ void pack_sources24_kernel(const float* __restrict__ src, int64_t S, 
     for (int c = 0; c < 6; ++c) packed[6 * s + c] = v[c];
 }
 
-template <bool kPotential>
+__constant__ float c_bank3_probe[8064];   // experiment (DNP_CONST_BANK3=1): same kernel, sources from bank 3
+
+template <bool kPotential, bool kBank3 = false>
 __global__ void __launch_bounds__(kCBlock, 3)
-cpairs_kernel(const __grid_constant__ SrcBlock<kPotential> blk, int n_src, CTargets T, float eps,
+cpairs_kernel(const __grid_constant__ SrcBlock<kPotential> blk_param, int n_src, CTargets T, float eps,
               float* __restrict__ part, int first) {
     constexpr int TP = kCTP;
+    struct View { const float* v; };
+    const View blk{kBank3 ? c_bank3_probe : blk_param.v};
     const int tid = threadIdx.x;
     const int64_t tile_base = (int64_t)blockIdx.x * (kCBlock * 2 * TP);
 
@@ -336,6 +340,10 @@ int launch_chunks(const CPairPlan& plan, const float* host_rows, int64_t host_va
         if (n_have > n_src) n_have = n_src;
         fill_block<kPotential>(blk, host_rows + s_begin * 6, n_have, n_src);
         float* part = partial + (size_t)l * T.M * ncomp;
+        if (!kPotential && env_int("DNP_CONST_BANK3", 0))
+            cpairs_kernel<kPotential, true><<<plan.m_tiles, kCBlock, 0, t_lanes.lane[l]>>>(blk, n_src, T, eps, part,
+                                                                                            k < plan.lanes);
+        else
         cpairs_kernel<kPotential><<<plan.m_tiles, kCBlock, 0, t_lanes.lane[l]>>>(blk, n_src, T, eps, part,
                                                                                   k < plan.lanes);
     }

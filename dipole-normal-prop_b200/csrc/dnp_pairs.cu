@@ -281,19 +281,20 @@ pairs_kernel(const float4* __restrict__ packed, int tiles_total, int nsplit,
 
 // ------------------------------------------------------------------ fixed-order reduction over source splits
 template <bool kPotential>
-__global__ void split_reduce_kernel(const float* __restrict__ partial, int nsplit, int64_t M, PairEpilogue ep) {
+__global__ void split_reduce_kernel(const float* __restrict__ partial, int nsplit, int64_t M, int64_t set_stride,
+                                    PairEpilogue ep) {
     const int64_t m = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (m >= M) return;
     const int64_t r = ep.tgt_idx ? ep.tgt_idx[m] : m;
     if (ep.tgt_skip && ep.tgt_skip[r]) return;
     if (kPotential) {
         float acc = 0.f;
-        for (int k = 0; k < nsplit; ++k) acc += partial[(int64_t)k * M + m];
+        for (int k = 0; k < nsplit; ++k) acc += partial[(int64_t)k * set_stride + m];
         apply_potential_epilogue(ep, r, acc);
     } else {
         float ex = 0.f, ey = 0.f, ez = 0.f;
         for (int k = 0; k < nsplit; ++k) {
-            const float* p = partial + ((int64_t)k * M + m) * 3;
+            const float* p = partial + (int64_t)k * set_stride + m * 3;
             ex += p[0]; ey += p[1]; ez += p[2];
         }
         apply_field_epilogue(ep, r, ex, ey, ez);
@@ -355,11 +356,12 @@ int64_t launch_count() { return g_launches.load(); }
 void timer_mark(cudaStream_t stream) { timer_mark_impl(stream); }
 
 int run_split_reduce(bool potential, const float* partial, int nsplit, int64_t M, const PairEpilogue& ep,
-                     cudaStream_t stream) {
+                     cudaStream_t stream, int64_t set_stride) {
     const int threads = 256;
     const unsigned blocks = (unsigned)((M + threads - 1) / threads);
-    if (potential) split_reduce_kernel<true><<<blocks, threads, 0, stream>>>(partial, nsplit, M, ep);
-    else split_reduce_kernel<false><<<blocks, threads, 0, stream>>>(partial, nsplit, M, ep);
+    if (set_stride <= 0) set_stride = M * (potential ? 1 : 3);
+    if (potential) split_reduce_kernel<true><<<blocks, threads, 0, stream>>>(partial, nsplit, M, set_stride, ep);
+    else split_reduce_kernel<false><<<blocks, threads, 0, stream>>>(partial, nsplit, M, set_stride, ep);
     count_launch(1);
     DNP_CHECK_CUDA(cudaGetLastError());
     return DNP_OK;
@@ -479,6 +481,10 @@ size_t pairs_workspace_bytes(int64_t S, int64_t M) {
         const size_t c = cpairs_workspace_bytes(S, M);
         if (c > core) core = c;
     }
+    if (use_ring_path(S, M, 0)) {
+        const size_t c = upairs_workspace_bytes(S, M);
+        if (c > core) core = c;
+    }
     return core + (size_t)round_up(M * 4, 256) + 1024;
 }
 
@@ -530,6 +536,8 @@ int run_pairs(bool potential, const float* src, int64_t S, int64_t ld_s, const i
         set_error("device-selected sources need src_idx and offsets");
         return DNP_ERR_INVALID;
     }
+    if (!sel.patch && force_tp <= 0 && force_nsplit <= 0 && use_ring_path(S, M, lattice_n))
+        return run_upairs(potential, src, S, ld_s, src_idx, tgt, M, ld_t, eps, ep, workspace, workspace_bytes, stream);
     if (!sel.patch && force_tp <= 0 && force_nsplit <= 0 && use_const_path(S, M, lattice_n) &&
         (src_host_dense || !stream_is_capturing(stream)))     // the by-value path synchronises once: never under capture
         return run_cpairs(potential, src, S, ld_s, src_idx, src_host_dense, tgt, M, ld_t, eps, ep, workspace,

@@ -64,6 +64,24 @@ struct CPairPlan {
     size_t partial_bytes = 0;
 };
 
+// plan of the constant-window path (dnp_upairs.cu)
+struct UPairPlan {
+    int tp = 4;            // target pairs per thread (1024- or 256-target tiles)
+    int lanes = 1;         // 1: everything on the caller's stream; 2 / 4: chunks rotate over that many lane streams
+    int n_chunks = 1;      // launches
+    int chunk = 4;         // sources per launch (multiple of 4, <= one window slot)
+    int m_tiles = 1;       // target tiles
+    int grid = 1;          // CTAs per launch
+    int per = 4;           // (tile, source) iterations per CTA (multiple of 4)
+    int ways = 2;          // partial row sets per lane
+    bool whole_tiles = false;  // one target tile per CTA over the whole slot (many chunks x many tiles)
+    int slot_floats = 8064;    // window floats per lane's slot (half or a quarter of the window)
+    int64_t way_stride = 0;    // floats between row sets
+    int64_t S_pad = 0;
+    size_t packed_bytes = 0;
+    size_t partial_bytes = 0;
+};
+
 int sm_count_cached();
 PairPlan make_pair_plan(int64_t S, int64_t M, int sm_count, int force_tp, int force_nsplit);
 size_t pairs_workspace_bytes(int64_t S, int64_t M);
@@ -84,9 +102,17 @@ size_t cpairs_workspace_bytes(int64_t S, int64_t M);
 int run_cpairs(bool potential, const float* src, int64_t S, int64_t ld_s, const int64_t* src_idx,
                const float* src_host_dense, const float* tgt, int64_t M, int64_t ld_t, float eps,
                const PairEpilogue& ep, void* workspace, size_t workspace_bytes, cudaStream_t stream);
-// fixed-order sum of `nsplit` partial row sets + the fused epilogue
+// Sources through the device-resident constant window (dnp_upairs.cu): asynchronous, capturable.
+bool use_ring_path(int64_t S, int64_t M, int lattice_n);
+UPairPlan make_upair_plan(bool potential, int64_t S, int64_t M, int sm_count);
+size_t upairs_workspace_bytes(int64_t S, int64_t M);
+int run_upairs(bool potential, const float* src, int64_t S, int64_t ld_s, const int64_t* src_idx, const float* tgt,
+               int64_t M, int64_t ld_t, float eps, const PairEpilogue& ep, void* workspace, size_t workspace_bytes,
+               cudaStream_t stream);
+// fixed-order sum of `nsplit` partial row sets + the fused epilogue; set_stride = floats between row sets
+// (0: M rows of 1 / 3 floats)
 int run_split_reduce(bool potential, const float* partial, int nsplit, int64_t M, const PairEpilogue& ep,
-                     cudaStream_t stream);
+                     cudaStream_t stream, int64_t set_stride = 0);
 // records one event of the armed per-thread kernel timer (no-op otherwise)
 void timer_mark(cudaStream_t stream);
 

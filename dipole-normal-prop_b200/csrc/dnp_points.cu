@@ -492,12 +492,9 @@ static int run_points_propagate_grid(float* pts, int64_t N, int64_t ld, int64_t 
         set_error("workspace too small: need %zu bytes (dnp_points_workspace_bytes), got %zu", need, workspace_bytes);
         return DNP_ERR_WORKSPACE;
     }
-    static std::atomic<int> attr_done{0};
-    if (!attr_done.load()) {
-        DNP_CHECK_CUDA(cudaFuncSetAttribute(points_propagate_grid_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                            227 * 1024));
-        attr_done.store(1);
-    }
+    static std::atomic<int> attr_done[kMaxDevices];
+    DNP_ONCE_PER_DEVICE(attr_done, DNP_CHECK_CUDA(cudaFuncSetAttribute(
+        points_propagate_grid_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024)));
     // about 2048 points per CTA (4 per thread) until every SM has one: fewer CTAs make the per-step exchange cheaper
     const int sms = sm_count_cached();
     int ncta = (int)((N + 2047) / 2048);
@@ -540,14 +537,13 @@ int run_points_propagate_batched(float* pts, int64_t ld, const int64_t* offsets,
                   (long long)points_max_n());
         return DNP_ERR_INVALID;
     }
-    static std::atomic<int> attr_done{0};
-    if (!attr_done.load()) {
+    static std::atomic<int> attr_done[kMaxDevices];
+    DNP_ONCE_PER_DEVICE(attr_done, {
         DNP_CHECK_CUDA(cudaFuncSetAttribute(points_propagate_batched_kernel,
                                             cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
         DNP_CHECK_CUDA(cudaFuncSetAttribute(points_propagate_batched_kernel,
                                             cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
-        attr_done.store(1);
-    }
+    });
     // <= 1024 points (2 per thread) per CTA; the cluster size is the same for every patch of the launch
     int ncta = 1;
     while (ncta < kMaxCluster && (int64_t)ncta * kPtThreads * 2 < max_patch) ncta *= 2;
@@ -603,13 +599,12 @@ int run_points_propagate(float* pts, int64_t N, int64_t ld, int64_t start, float
     if (N > points_max_n() || (force_grid && workspace))
         return run_points_propagate_grid(pts, N, ld, start, eps, diffuse, order, flipped, workspace, workspace_bytes,
                                          stream);
-    static std::atomic<int> attr_done{0};
-    if (!attr_done.load()) {
+    static std::atomic<int> attr_done[kMaxDevices];
+    DNP_ONCE_PER_DEVICE(attr_done, {
         DNP_CHECK_CUDA(cudaFuncSetAttribute(points_propagate_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                             227 * 1024));
         DNP_CHECK_CUDA(cudaFuncSetAttribute(points_propagate_kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
-        attr_done.store(1);
-    }
+    });
     // smallest power-of-two cluster that gives every thread <= 1 point, capped by what the device can co-schedule
     // (tools/points_probe.py, us per step: N = 2000: 2 CTAs 1.76, 4 CTAs 1.38, 8 CTAs 1.53; N = 5000: 8 CTAs 1.97,
     // 16 CTAs 1.85; N = 10 000: 8 CTAs 2.46, 16 CTAs 2.27 -- a second point per thread costs more than a wider

@@ -1,0 +1,657 @@
+// dnp_upairs.cu -- all-pairs field / potential with the sources in UNIFORM registers, fed from a
+// device-resident constant window.  field_utils.py:96-116 (field leaf) / :46-55 (potential leaf) and the
+// recursive chunking around them (:23-44, :73-94).
+//
+// Why the constant bank (profiles/README.md, round 1): a packed FFMA2 issues every 2 cycles only if it reads
+// at most two fresh 64-bit register pairs; a source is the same for all 32 lanes, so it belongs in a uniform
+// register (`FFMA2 R, R.pair, UR.F32, R.pair` costs no register-file read), and ptxas fills uniform registers
+// at speed only from a constant bank (LDCU) -- values produced by LDS / LDG / REDUX are moved back into vector
+// registers.  Round 1 used the kernel-PARAMETER bank (sources by value): that needs the sources on the host,
+// i.e. a device->host copy and a stream synchronisation per call.  This file uses the module's own constant
+// bank instead:
+//
+//   * `c_window[2][8064]`: two 32 256-byte slots (896 field sources x 36 B or 1344 potential sources x 24 B).
+//     A slot is filled ON THE DEVICE by an asynchronous device-to-device copy from the packed source array
+//     (cudaMemcpyToSymbolAsync), ordered before the launch that reads it by the stream.  Nothing touches the
+//     host: the call is asynchronous and capturable into a CUDA graph.
+//   * one launch = one slot (chunk of sources) x all targets.  The (target tile, source) iteration space of a
+//     launch is cut into EQUAL contiguous shares, one per resident CTA (stream-K style): a CTA walks up to a
+//     few (tile, source range) segments, so a single launch is exactly one full wave whatever M is -- the
+//     500 x 524 288 step of the representatives loop no longer runs 1.15 or 1.38 waves.  A tile cut between
+//     CTAs lands in different partial row sets ("ways"); partial rows are accumulated by read-modify-write
+//     in L2 (launches that share a row set are serialised by their stream) and summed in a fixed order by
+//     split_reduce_kernel together with the fused epilogue: deterministic, no float atomics.
+//   * calls with more than one chunk alternate over two lanes (streams), one slot each, so the copy into one
+//     slot and the ramp of its launch overlap the other lane's launch.
+//   * the window is a per-device resource: calls are queued on it in submission order (a mutex held while
+//     enqueueing + an event the next user's stream waits for).  Large calls fill the machine anyway.
+//
+// Arithmetic per (2 targets x 1 source): 19 packed FP32 operations + 2 MUFU.RSQ + 2 MUFU.RCP (field),
+// 12 + 2 MUFU.RSQ (potential); coincident pairs contribute exactly 0 (see dnp_pairs.cu).
+#include <stdlib.h>
+#include <string.h>
+
+#include <mutex>
+
+#include "dnp_common.cuh"
+#include "dnp_pairs.h"
+
+namespace dnp {
+
+namespace {
+
+constexpr int kUBlock = 128;                       // threads per CTA
+constexpr int kWindowFloats = 16128;               // 64 512 B of the 64 KB constant bank
+constexpr int kSlotFloats = 8064;                  // two slots of 32 256 B ...
+constexpr int kQuarterFloats = 4032;               // ... or four of 16 128 B (more launches in flight for fewer targets)
+constexpr int kMaxSlots = 4;
+constexpr float kRsqrtClampU = 1.152921504606847e18f;   // 2^60
+constexpr float kRsqrtClampPhiU = 1.099511627776e12f;   // 2^40
+
+__constant__ float c_window[kWindowFloats];
+
+template <bool kPotential>
+struct Win {
+    static constexpr int kStride = kPotential ? 6 : 9;            // floats per source in the window
+    static constexpr int kFold = kPotential ? 336 : 224;          // sources per first-level sum
+};
+
+struct UTargets {
+    const float* tgt;
+    int64_t M;
+    int64_t ld_t;
+    const int64_t* tgt_idx;
+    const uint8_t* tgt_skip;
+};
+
+// sources -> dense window rows: field [x y z | nx ny nz | -3nx -3ny -3nz], potential [x y z | nx ny nz];
+// rows >= S are null dipoles.  n_dev (optional): the live row count is read on the device.
+template <bool kPotential>
+__global__ void pack_window_kernel(const float* __restrict__ src, int64_t S, int64_t ld_s,
+                                   const int64_t* __restrict__ idx, int64_t S_pad, float* __restrict__ packed) {
+    constexpr int ST = Win<kPotential>::kStride;
+    const int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= S_pad) return;
+    float v[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    if (s < S) {
+        const float* p = src + (idx ? idx[s] : s) * ld_s;
+#pragma unroll
+        for (int c = 0; c < 6; ++c) v[c] = __ldg(p + c);
+    }
+    float* o = packed + ST * s;
+#pragma unroll
+    for (int c = 0; c < 6; ++c) o[c] = v[c];
+    if (!kPotential) { o[6] = v[3] * -3.f; o[7] = v[4] * -3.f; o[8] = v[5] * -3.f; }
+}
+
+// fill of a slot by a kernel writing through the window's global address (DNP_RING_FILL=2, experiment)
+__global__ void fill_window_kernel(const float4* __restrict__ from, float4* __restrict__ to, int n4) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n4) to[i] = from[i];
+}
+
+// Where each CTA's share of the (tile, source) space starts.  Computed on the host and passed by value so that
+// the kernel reads it with LDCU: everything the source index depends on has to stay in the uniform datapath
+// (an in-kernel division would land in vector registers and turn every LDCU of the window into an LDC).
+constexpr int kMaxGrid = 148 * 8 + 16;
+struct ShareTable {
+    int tile[kMaxGrid];          // first tile of CTA c
+    unsigned q_way[kMaxGrid];    // first source QUAD inside that tile | (partial row set of that first segment << 16)
+};
+
+// One launch: the window slot at float offset win_off (4 n_q sources) x all target tiles.  CTA c owns per_q quads of the flattened
+// (tile, source) space, starting where the table says.
+//
+// NOTE for maintainers: the share LENGTH is a plain kernel parameter on purpose.  Whenever the trip count of the
+// segment loop depended on a value loaded from the table (per-CTA lengths, an end position, bits of q_way), ptxas
+// 12.9 moved the whole index chain -- blockIdx included -- into vector registers and every LDCU.64 of the window
+// became an LDC.64 (tests/test_abi.py::test_window_kernel_reads_sources_through_uniform_registers guards this).
+template <bool kPotential, int TP>
+__global__ void __launch_bounds__(kUBlock, (TP >= 4 ? 3 : (TP == 2 ? 5 : 8)))
+upairs_kernel(const __grid_constant__ ShareTable tab, int win_q, int n_q, int m_tiles, int per_q, UTargets T, float eps, float* __restrict__ part, int64_t way_stride) {
+    constexpr int ST = Win<kPotential>::kStride;
+    constexpr int kFold = Win<kPotential>::kFold;
+    constexpr int NC = kPotential ? 1 : 3;
+    const int tid = threadIdx.x;
+    const float* __restrict__ win = c_window + 4 * win_q;     // slot offsets in units of 4 floats: 16-byte aligned reads
+    const f32x2 zero2 = pack2(0.f, 0.f);
+    const f32x2 eps2 = pack2(eps, eps);
+
+    // all source positions in QUADS (4 sources; n_q and the table): lets ptxas prove the alignment of the
+    // LDCU.64 window reads, and keeps shifts / divisions out of the kernel
+    int tile = tab.tile[blockIdx.x];
+    int q_first = (int)(tab.q_way[blockIdx.x] & 0xffffu);
+    // which partial row set: the number of CTA boundaries between the start of the tile and the segment; later
+    // segments of this CTA start their tile, i.e. way 0
+    int way = (int)(tab.q_way[blockIdx.x] >> 16);
+    int left = per_q;                                 // quads this CTA still owns
+
+    while (left > 0 && tile < m_tiles) {
+        int q_last = q_first + left;
+        if (q_last > n_q) q_last = n_q;
+        const int64_t tile_base = (int64_t)tile * (kUBlock * 2 * TP);
+
+        f32x2 qx[TP], qy[TP], qz[TP];
+#pragma unroll
+        for (int j = 0; j < TP; ++j) {
+            float x[2] = {0.f, 0.f}, y[2] = {0.f, 0.f}, z[2] = {0.f, 0.f};
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                const int64_t m = tile_base + (int64_t)(2 * j + h) * kUBlock + tid;
+                if (m < T.M) {
+                    const int64_t r = T.tgt_idx ? T.tgt_idx[m] : m;
+                    if (!(T.tgt_skip && T.tgt_skip[r])) {
+                        const float* q = T.tgt + r * T.ld_t;
+                        x[h] = __ldg(q); y[h] = __ldg(q + 1); z[h] = __ldg(q + 2);
+                    }
+                }
+            }
+            qx[j] = pack2(x[0], x[1]); qy[j] = pack2(y[0], y[1]); qz[j] = pack2(z[0], z[1]);
+        }
+
+        f32x2 tx[TP], ty[TP], tz[TP];
+#pragma unroll
+        for (int j = 0; j < TP; ++j) { tx[j] = zero2; ty[j] = zero2; tz[j] = zero2; }
+
+        for (int f0 = q_first; f0 < q_last; f0 += kFold / 4) {
+            const int f1 = (f0 + kFold / 4 < q_last) ? f0 + kFold / 4 : q_last;
+            if (kPotential) {
+                f32x2 phi[TP];
+#pragma unroll
+                for (int j = 0; j < TP; ++j) phi[j] = zero2;
+                for (int s4 = 4 * f0; s4 < 4 * f1; s4 += 4) {
+                    __builtin_assume((s4 & 3) == 0);
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) {
+                        const int s = s4 + k;
+                        const float px = win[ST * s], py = win[ST * s + 1], pz = win[ST * s + 2];
+                        const float nx = win[ST * s + 3], ny = win[ST * s + 4], nz = win[ST * s + 5];
+                        const f32x2 px2 = pack2(px, px), py2 = pack2(py, py), pz2 = pack2(pz, pz);
+                        const f32x2 nx2 = pack2(nx, nx), ny2 = pack2(ny, ny), nz2 = pack2(nz, nz);
+#pragma unroll
+                        for (int j = 0; j < TP; ++j) {
+                            const f32x2 rx = sub2(px2, qx[j]), ry = sub2(py2, qy[j]), rz = sub2(pz2, qz[j]);
+                            const f32x2 r2 = fma2(rz, rz, fma2(ry, ry, mul2(rx, rx)));
+                            float r2a, r2b;
+                            unpack2(r2, r2a, r2b);
+                            const f32x2 uc = pack2(fminf(rsqrt_sfu(r2a), kRsqrtClampPhiU),
+                                                   fminf(rsqrt_sfu(r2b), kRsqrtClampPhiU));
+                            const f32x2 d = fma2(nz2, rz, fma2(ny2, ry, mul2(nx2, rx)));
+                            phi[j] = fma2(d, mul2(mul2(uc, uc), uc), phi[j]);
+                        }
+                    }
+                }
+#pragma unroll
+                for (int j = 0; j < TP; ++j) tx[j] = add2(tx[j], phi[j]);
+            } else {
+                // E += w (n + t R),  t = (m.R) u^2,  m = -3 n,  u = rsqrt(r2),  w = 1 / (r2^2 u + eps)
+                f32x2 ax[TP], ay[TP], az[TP];
+#pragma unroll
+                for (int j = 0; j < TP; ++j) { ax[j] = ay[j] = az[j] = zero2; }
+                for (int s4 = 4 * f0; s4 < 4 * f1; s4 += 4) {
+                    __builtin_assume((s4 & 3) == 0);
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) {
+                        const int s = s4 + k;
+                        const float px = win[ST * s], py = win[ST * s + 1], pz = win[ST * s + 2];
+                        const float nx = win[ST * s + 3], ny = win[ST * s + 4], nz = win[ST * s + 5];
+                        const float mx = win[ST * s + 6], my = win[ST * s + 7], mz = win[ST * s + 8];
+                        const f32x2 px2 = pack2(px, px), py2 = pack2(py, py), pz2 = pack2(pz, pz);
+                        const f32x2 nx2 = pack2(nx, nx), ny2 = pack2(ny, ny), nz2 = pack2(nz, nz);
+                        const f32x2 mx2 = pack2(mx, mx), my2 = pack2(my, my), mz2 = pack2(mz, mz);
+#pragma unroll
+                        for (int j = 0; j < TP; ++j) {
+                            const f32x2 rx = sub2(px2, qx[j]), ry = sub2(py2, qy[j]), rz = sub2(pz2, qz[j]);
+                            const f32x2 r2 = fma2(rz, rz, fma2(ry, ry, mul2(rx, rx)));
+                            float r2a, r2b;
+                            unpack2(r2, r2a, r2b);
+                            const float ua = rsqrt_sfu(r2a), ub = rsqrt_sfu(r2b);      // +inf on a coincident pair
+                            const f32x2 u = pack2(ua, ub);
+                            const f32x2 uc = pack2(fminf(ua, kRsqrtClampU), fminf(ub, kRsqrtClampU));
+                            const f32x2 den = fma2(mul2(r2, r2), u, eps2);             // |R|^3 + eps; NaN if R = 0
+                            float da, db;
+                            unpack2(den, da, db);
+                            const f32x2 w = pack2(fmaxf(rcp_sfu(da), 0.f), fmaxf(rcp_sfu(db), 0.f));   // NaN -> 0
+                            const f32x2 d = fma2(mz2, rz, fma2(my2, ry, mul2(mx2, rx)));   // -3 n.R
+                            const f32x2 t = mul2(d, mul2(uc, uc));
+                            const f32x2 vx = fma2(t, rx, nx2), vy = fma2(t, ry, ny2), vz = fma2(t, rz, nz2);
+                            ax[j] = fma2(w, vx, ax[j]); ay[j] = fma2(w, vy, ay[j]); az[j] = fma2(w, vz, az[j]);
+                        }
+                    }
+                }
+#pragma unroll
+                for (int j = 0; j < TP; ++j) {
+                    tx[j] = add2(tx[j], ax[j]);
+                    ty[j] = add2(ty[j], ay[j]);
+                    tz[j] = add2(tz[j], az[j]);
+                }
+            }
+        }
+
+        // accumulate into this segment's partial row set (zeroed at the start of the call)
+        float* rows = part + (int64_t)way * way_stride;
+#pragma unroll
+        for (int j = 0; j < TP; ++j) {
+            float ex[2], ey[2], ez[2];
+            unpack2(tx[j], ex[0], ex[1]);
+            unpack2(ty[j], ey[0], ey[1]);
+            unpack2(tz[j], ez[0], ez[1]);
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                const int64_t m = tile_base + (int64_t)(2 * j + h) * kUBlock + tid;
+                if (m >= T.M) continue;
+                float* o = rows + m * NC;
+                if (kPotential) {
+                    o[0] += ex[h];
+                } else {
+                    o[0] += ex[h]; o[1] += ey[h]; o[2] += ez[h];
+                }
+            }
+        }
+        left -= q_last - q_first;
+        ++tile;
+        q_first = 0;
+        way = 0;
+    }
+}
+
+
+// The same arithmetic with ONE target tile per CTA and the whole slot per CTA (no share table, no cut tiles): the
+// launch shape of calls with many chunks and >= 256 target tiles, where 2 or 4 launches in flight (one per lane)
+// keep every SM supplied with CTAs that start and end at different times.  `first`: this lane's first launch
+// stores its partial rows, later launches accumulate (launches of a lane are serialised by its stream).
+// n_src is a multiple of the fold (224 field / 336 potential sources).
+template <bool kPotential>
+__global__ void __launch_bounds__(kUBlock, 3)
+upairs_tile_kernel(int win_q, int n_src, UTargets T, float eps, float* __restrict__ part, int first) {
+    constexpr int TP = 4;
+    constexpr int kFold = Win<kPotential>::kFold;
+    const float* __restrict__ win = c_window + 4 * win_q;     // slot offsets in units of 4 floats: 16-byte aligned reads
+    const int tid = threadIdx.x;
+    const int64_t tile_base = (int64_t)blockIdx.x * (kUBlock * 2 * TP);
+
+    f32x2 qx[TP], qy[TP], qz[TP];
+#pragma unroll
+    for (int j = 0; j < TP; ++j) {
+        float x[2] = {0.f, 0.f}, y[2] = {0.f, 0.f}, z[2] = {0.f, 0.f};
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            const int64_t m = tile_base + (int64_t)(2 * j + h) * kUBlock + tid;
+            if (m < T.M) {
+                const int64_t r = T.tgt_idx ? T.tgt_idx[m] : m;
+                if (!(T.tgt_skip && T.tgt_skip[r])) {
+                    const float* q = T.tgt + r * T.ld_t;
+                    x[h] = __ldg(q); y[h] = __ldg(q + 1); z[h] = __ldg(q + 2);
+                }
+            }
+        }
+        qx[j] = pack2(x[0], x[1]); qy[j] = pack2(y[0], y[1]); qz[j] = pack2(z[0], z[1]);
+    }
+
+    const f32x2 zero2 = pack2(0.f, 0.f);
+    const f32x2 eps2 = pack2(eps, eps);
+    f32x2 tx[TP], ty[TP], tz[TP];
+#pragma unroll
+    for (int j = 0; j < TP; ++j) { tx[j] = zero2; ty[j] = zero2; tz[j] = zero2; }
+
+    for (int s0 = 0; s0 < n_src; s0 += kFold) {
+        if (kPotential) {
+            f32x2 phi[TP];
+#pragma unroll
+            for (int j = 0; j < TP; ++j) phi[j] = zero2;
+#pragma unroll 2
+            for (int s = s0; s < s0 + kFold; ++s) {
+                const float px = win[6 * s], py = win[6 * s + 1], pz = win[6 * s + 2];
+                const float nx = win[6 * s + 3], ny = win[6 * s + 4], nz = win[6 * s + 5];
+                const f32x2 px2 = pack2(px, px), py2 = pack2(py, py), pz2 = pack2(pz, pz);
+                const f32x2 nx2 = pack2(nx, nx), ny2 = pack2(ny, ny), nz2 = pack2(nz, nz);
+#pragma unroll
+                for (int j = 0; j < TP; ++j) {
+                    const f32x2 rx = sub2(px2, qx[j]), ry = sub2(py2, qy[j]), rz = sub2(pz2, qz[j]);
+                    const f32x2 r2 = fma2(rz, rz, fma2(ry, ry, mul2(rx, rx)));
+                    float r2a, r2b;
+                    unpack2(r2, r2a, r2b);
+                    const f32x2 uc = pack2(fminf(rsqrt_sfu(r2a), kRsqrtClampPhiU), fminf(rsqrt_sfu(r2b), kRsqrtClampPhiU));
+                    const f32x2 d = fma2(nz2, rz, fma2(ny2, ry, mul2(nx2, rx)));
+                    phi[j] = fma2(d, mul2(mul2(uc, uc), uc), phi[j]);
+                }
+            }
+#pragma unroll
+            for (int j = 0; j < TP; ++j) tx[j] = add2(tx[j], phi[j]);
+        } else {
+            f32x2 ax[TP], ay[TP], az[TP];
+#pragma unroll
+            for (int j = 0; j < TP; ++j) { ax[j] = ay[j] = az[j] = zero2; }
+#pragma unroll 4
+            for (int s = s0; s < s0 + kFold; ++s) {
+                const float px = win[9 * s], py = win[9 * s + 1], pz = win[9 * s + 2];
+                const float nx = win[9 * s + 3], ny = win[9 * s + 4], nz = win[9 * s + 5];
+                const float mx = win[9 * s + 6], my = win[9 * s + 7], mz = win[9 * s + 8];
+                const f32x2 px2 = pack2(px, px), py2 = pack2(py, py), pz2 = pack2(pz, pz);
+                const f32x2 nx2 = pack2(nx, nx), ny2 = pack2(ny, ny), nz2 = pack2(nz, nz);
+                const f32x2 mx2 = pack2(mx, mx), my2 = pack2(my, my), mz2 = pack2(mz, mz);
+#pragma unroll
+                for (int j = 0; j < TP; ++j) {
+                    const f32x2 rx = sub2(px2, qx[j]), ry = sub2(py2, qy[j]), rz = sub2(pz2, qz[j]);
+                    const f32x2 r2 = fma2(rz, rz, fma2(ry, ry, mul2(rx, rx)));
+                    float r2a, r2b;
+                    unpack2(r2, r2a, r2b);
+                    const float ua = rsqrt_sfu(r2a), ub = rsqrt_sfu(r2b);
+                    const f32x2 u = pack2(ua, ub);
+                    const f32x2 uc = pack2(fminf(ua, kRsqrtClampU), fminf(ub, kRsqrtClampU));
+                    const f32x2 den = fma2(mul2(r2, r2), u, eps2);
+                    float da, db;
+                    unpack2(den, da, db);
+                    const f32x2 w = pack2(fmaxf(rcp_sfu(da), 0.f), fmaxf(rcp_sfu(db), 0.f));
+                    const f32x2 d = fma2(mz2, rz, fma2(my2, ry, mul2(mx2, rx)));
+                    const f32x2 t = mul2(d, mul2(uc, uc));
+                    const f32x2 vx = fma2(t, rx, nx2), vy = fma2(t, ry, ny2), vz = fma2(t, rz, nz2);
+                    ax[j] = fma2(w, vx, ax[j]); ay[j] = fma2(w, vy, ay[j]); az[j] = fma2(w, vz, az[j]);
+                }
+            }
+#pragma unroll
+            for (int j = 0; j < TP; ++j) {
+                tx[j] = add2(tx[j], ax[j]);
+                ty[j] = add2(ty[j], ay[j]);
+                tz[j] = add2(tz[j], az[j]);
+            }
+        }
+    }
+
+#pragma unroll
+    for (int j = 0; j < TP; ++j) {
+        float ex[2], ey[2], ez[2];
+        unpack2(tx[j], ex[0], ex[1]);
+        unpack2(ty[j], ey[0], ey[1]);
+        unpack2(tz[j], ez[0], ez[1]);
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            const int64_t m = tile_base + (int64_t)(2 * j + h) * kUBlock + tid;
+            if (m >= T.M) continue;
+            if (kPotential) {
+                float* o = part + m;
+                *o = first ? ex[h] : *o + ex[h];
+            } else {
+                float* o = part + m * 3;
+                if (first) { o[0] = ex[h]; o[1] = ey[h]; o[2] = ez[h]; }
+                else { o[0] += ex[h]; o[1] += ey[h]; o[2] += ez[h]; }
+            }
+        }
+    }
+}
+
+// ---------------------------------------------------------------- the per-device window
+struct DeviceRing {
+    std::mutex mu;
+    bool ready = false;
+    cudaStream_t lane[kMaxSlots] = {};
+    cudaEvent_t lane_done[kMaxSlots] = {};
+    cudaEvent_t fork = nullptr;
+    cudaEvent_t last_done = nullptr;       // end of the previous user's window accesses
+    bool has_last = false;
+    cudaStream_t last_stream = nullptr;
+    float* window = nullptr;               // global address of c_window on this device
+
+    cudaError_t prepare() {
+        if (ready) return cudaSuccess;
+        cudaError_t e;
+        for (int i = 0; i < kMaxSlots; ++i) {
+            if ((e = cudaStreamCreateWithFlags(&lane[i], cudaStreamNonBlocking)) != cudaSuccess) return e;
+            if ((e = cudaEventCreateWithFlags(&lane_done[i], cudaEventDisableTiming)) != cudaSuccess) return e;
+        }
+        if ((e = cudaEventCreateWithFlags(&fork, cudaEventDisableTiming)) != cudaSuccess) return e;
+        if ((e = cudaEventCreateWithFlags(&last_done, cudaEventDisableTiming)) != cudaSuccess) return e;
+        if ((e = cudaGetSymbolAddress(reinterpret_cast<void**>(&window), c_window)) != cudaSuccess) return e;
+        ready = true;
+        return cudaSuccess;
+    }
+};
+DeviceRing g_ring[kMaxDevices];
+
+int env_int_u(const char* name, int dflt) {
+    const char* v = getenv(name);
+    return v ? atoi(v) : dflt;
+}
+
+inline int64_t round_up_u(int64_t a, int64_t b) { return (a + b - 1) / b * b; }
+
+bool capturing(cudaStream_t stream) {
+    cudaStreamCaptureStatus st = cudaStreamCaptureStatusNone;
+    if (cudaStreamIsCapturing(stream, &st) != cudaSuccess) { cudaGetLastError(); return false; }
+    return st != cudaStreamCaptureStatusNone;
+}
+
+// DNP_RING_FILL: 0 cudaMemcpyToSymbolAsync (default), 1 plain device-to-device copy to the window's global address,
+// 2 a copy kernel writing through that address -- all three are seen by the next launch (tests/test_gpu_upairs.py)
+cudaError_t fill_slot(DeviceRing& ring, int win_off, const float* from, size_t bytes, cudaStream_t stream) {
+    const int mode = env_int_u("DNP_RING_FILL", 0);
+    if (mode == 3) return cudaSuccess;          // timing experiment only: stale window, wrong results
+    if (mode == 1)
+        return cudaMemcpyAsync(ring.window + win_off, from, bytes, cudaMemcpyDeviceToDevice, stream);
+    if (mode == 2) {
+        const int n4 = (int)(bytes / 16);
+        fill_window_kernel<<<(n4 + 255) / 256, 256, 0, stream>>>(
+            reinterpret_cast<const float4*>(from), reinterpret_cast<float4*>(ring.window + win_off), n4);
+        return cudaGetLastError();
+    }
+    return cudaMemcpyToSymbolAsync(c_window, from, bytes, (size_t)win_off * sizeof(float), cudaMemcpyDeviceToDevice,
+                                   stream);
+}
+
+// Cuts the m_tiles x n_src iteration space of one launch into `grid` equal contiguous shares of `per` sources
+// (a multiple of 4) and returns the number of partial row sets the cut needs (tab may be null).
+int build_shares(int m_tiles, int n_src, int grid, int per, ShareTable* tab) {
+    const int n_q = n_src >> 2, per_q = per >> 2;
+    const int64_t total_q = (int64_t)m_tiles * n_q;
+    int max_way = 0;
+    int owner = 0;        // the CTA whose share contains the START of the tile that `begin` lies in
+    for (int c = 0; c < grid; ++c) {
+        const int64_t begin = (int64_t)c * per_q;
+        int64_t end = begin + per_q;
+        if (end > total_q) end = total_q;
+        const int64_t tile = begin < total_q ? begin / n_q : m_tiles;
+        // a share that starts inside a tile continues it: its way is its distance from the tile's owner
+        const int way = (end > begin && begin != tile * n_q) ? c - owner : 0;
+        if (way > max_way) max_way = way;
+        if (tab) {
+            tab->tile[c] = (int)tile;
+            tab->q_way[c] = (unsigned)(begin - tile * n_q) | ((unsigned)way << 16);
+        }
+        if (end < total_q && end % n_q != 0 && (end / n_q) * n_q >= begin) owner = c;   // c opened the tile `end` is in
+    }
+    return max_way + 1;
+}
+
+template <bool kPotential, int TP>
+void launch_shares(const UPairPlan& plan, int win_off, const UTargets& T, float eps, float* part, cudaStream_t stream) {
+    ShareTable tab;
+    build_shares(plan.m_tiles, plan.chunk, plan.grid, plan.per, &tab);
+    upairs_kernel<kPotential, TP><<<plan.grid, kUBlock, 0, stream>>>(tab, win_off >> 2, plan.chunk >> 2, plan.m_tiles,
+                                                                      plan.per >> 2, T, eps, part, plan.way_stride);
+}
+
+// one launch over the slot at win_off: whole tiles (plan.whole_tiles) or equal shares
+void launch_chunk(bool potential, const UPairPlan& plan, int win_off, const UTargets& T, float eps, float* part,
+                  int first, cudaStream_t stream) {
+    if (plan.whole_tiles) {
+        if (potential) upairs_tile_kernel<true><<<plan.m_tiles, kUBlock, 0, stream>>>(win_off >> 2, plan.chunk, T, eps, part, first);
+        else upairs_tile_kernel<false><<<plan.m_tiles, kUBlock, 0, stream>>>(win_off >> 2, plan.chunk, T, eps, part, first);
+        return;
+    }
+    if (potential) {
+        if (plan.tp == 4) launch_shares<true, 4>(plan, win_off, T, eps, part, stream);
+        else launch_shares<true, 1>(plan, win_off, T, eps, part, stream);
+    } else {
+        if (plan.tp == 4) launch_shares<false, 4>(plan, win_off, T, eps, part, stream);
+        else launch_shares<false, 1>(plan, win_off, T, eps, part, stream);
+    }
+}
+
+}  // namespace
+
+// DNP_RING: 0 = never, 1 = by the size rule (default), 2 = always (tests).
+bool use_ring_path(int64_t S, int64_t M, int lattice_n) {
+    const int mode = env_int_u("DNP_RING", 1);
+    if (mode == 0 || lattice_n > 0) return false;
+    if (mode == 2) return S >= 1 && M >= 1;
+    // tools/ring_probe.py (profiles/README.md, r02): a call pays ~25 us for the window copy, the zeroing of the
+    // partial rows and the reduction pass; below ~2e8 pairs, or with target sets too small to amortise one launch
+    // per 896 sources, the shared-memory kernel is faster
+    const int64_t min_pairs = (int64_t)env_int_u("DNP_RING_MIN_MPAIRS", 200) * 1000000;
+    return S >= 64 && M >= 32768 && S * M >= min_pairs;
+}
+
+UPairPlan make_upair_plan(bool potential, int64_t S, int64_t M, int sm_count) {
+    UPairPlan p;
+    const int stride = potential ? 6 : 9;
+    const int fold = potential ? Win<true>::kFold : Win<false>::kFold;
+    if (S < 1) S = 1;
+    if (M < 1) M = 1;
+    const int64_t S4 = round_up_u(S, 4);
+    const int64_t tiles4 = (M + (int64_t)kUBlock * 8 - 1) / ((int64_t)kUBlock * 8);
+    const int slots3 = sm_count * 3;                         // resident CTAs of the 8-targets-per-thread kernels
+
+    // ---- whole tiles: many chunks x many tiles.  2 lanes when one launch alone is >= ~1.15 waves of CTAs, else 4
+    // lanes on quarter slots, so that >= ~2.3 waves are in flight and wave tails overlap the next launch's head.
+    int mode = env_int_u("DNP_RING_MODE", 0);                // 1: force shares, 2: force whole tiles (tests)
+    const int cap2 = kSlotFloats / stride / fold * fold;     // 896 / 1344
+    const int cap4 = kQuarterFloats / stride / fold * fold;  // 448 / 672
+    const bool tiles_ok = tiles4 * 4 >= (int64_t)slots3 * 23 / 10 && S4 >= 4 * (int64_t)cap4;
+    if (mode == 2 || (mode == 0 && tiles_ok)) {
+        p.whole_tiles = true;
+        p.tp = 4;
+        p.m_tiles = (int)tiles4;
+        p.lanes = tiles4 * 2 >= (int64_t)slots3 * 23 / 10 ? 2 : 4;
+        { const int forced = env_int_u("DNP_RING_LANES", 0); if (forced == 2 || forced == 4) p.lanes = forced; }
+        const int cap = p.lanes == 2 ? cap2 : cap4;
+        p.slot_floats = p.lanes == 2 ? kSlotFloats : kQuarterFloats;
+        p.n_chunks = (int)((S4 + cap - 1) / cap);
+        p.chunk = (int)round_up_u((S4 + p.n_chunks - 1) / p.n_chunks, fold);
+        if (p.lanes > p.n_chunks) p.lanes = p.n_chunks;
+        p.S_pad = (int64_t)p.n_chunks * p.chunk;
+        p.grid = p.m_tiles;
+        p.per = p.chunk;
+        p.ways = 1;
+    } else {
+        // ---- equal shares: targets per thread 8 (1024-target tiles) unless that pads a small set by more than ~6 %
+        p.tp = 4;
+        if ((double)(tiles4 * kUBlock * 8 - M) > 0.06 * (double)M) p.tp = 1;
+        { const int forced = env_int_u("DNP_RING_TP", 0); if (forced == 4 || forced == 1) p.tp = forced; }
+        const int resident = p.tp == 4 ? 3 : 8;
+        const int64_t tile_tgts = (int64_t)kUBlock * 2 * p.tp;
+        p.m_tiles = (int)((M + tile_tgts - 1) / tile_tgts);
+        const int cap = kSlotFloats / stride;                // 896 / 1344 sources per slot
+        p.slot_floats = kSlotFloats;
+        p.n_chunks = (int)((S4 + cap - 1) / cap);
+        p.chunk = (int)round_up_u((S4 + p.n_chunks - 1) / p.n_chunks, 4);
+        p.S_pad = (int64_t)p.n_chunks * p.chunk;
+        p.lanes = p.n_chunks > 1 ? 2 : 1;
+        // one full wave of shares; shares shorter than ~48 sources are not worth their prologue
+        const int64_t total = (int64_t)p.m_tiles * p.chunk;
+        int64_t grid = (int64_t)sm_count * resident;
+        { const int forced = env_int_u("DNP_RING_GRID", 0); if (forced > 0) grid = forced; }
+        if (grid > kMaxGrid) grid = kMaxGrid;
+        const int64_t min_share = 48;
+        if (grid * min_share > total) grid = total / min_share;
+        if (grid < 1) grid = 1;
+        p.per = (int)round_up_u((total + grid - 1) / grid, 4);
+        p.grid = (int)((total + p.per - 1) / p.per);
+        p.ways = build_shares(p.m_tiles, p.chunk, p.grid, p.per, nullptr);
+    }
+    const int ncomp = potential ? 1 : 3;
+    p.way_stride = round_up_u(M * ncomp, 64);
+    p.packed_bytes = (size_t)round_up_u(p.S_pad * stride * (int64_t)sizeof(float), 256);
+    p.partial_bytes = (size_t)round_up_u((int64_t)p.lanes * p.ways * p.way_stride * (int64_t)sizeof(float), 256);
+    return p;
+}
+
+size_t upairs_workspace_bytes(int64_t S, int64_t M) {
+    const UPairPlan f = make_upair_plan(false, S, M, sm_count_cached());
+    const UPairPlan p = make_upair_plan(true, S, M, sm_count_cached());
+    const size_t a = f.packed_bytes + f.partial_bytes, b = p.packed_bytes + p.partial_bytes;
+    return a > b ? a : b;
+}
+
+int run_upairs(bool potential, const float* src, int64_t S, int64_t ld_s, const int64_t* src_idx, const float* tgt,
+               int64_t M, int64_t ld_t, float eps, const PairEpilogue& ep, void* workspace, size_t workspace_bytes,
+               cudaStream_t stream) {
+    if (M <= 0) return DNP_OK;
+    const UPairPlan plan = make_upair_plan(potential, S, M, sm_count_cached());
+    if (!workspace || workspace_bytes < plan.packed_bytes + plan.partial_bytes) {
+        set_error("workspace too small: need %zu bytes, got %zu", plan.packed_bytes + plan.partial_bytes,
+                  workspace_bytes);
+        return DNP_ERR_WORKSPACE;
+    }
+    int dev = 0;
+    DNP_CHECK_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= kMaxDevices) {
+        set_error("device index %d out of range", dev);
+        return DNP_ERR_INVALID;
+    }
+    float* packed = reinterpret_cast<float*>(workspace);
+    float* partial = reinterpret_cast<float*>(reinterpret_cast<unsigned char*>(workspace) + plan.packed_bytes);
+    const int stride = potential ? 6 : 9;
+
+    {
+        const int threads = 256;
+        const unsigned blocks = (unsigned)((plan.S_pad + threads - 1) / threads);
+        if (potential)
+            pack_window_kernel<true><<<blocks, threads, 0, stream>>>(src, S < 0 ? 0 : S, ld_s, src_idx, plan.S_pad, packed);
+        else
+            pack_window_kernel<false><<<blocks, threads, 0, stream>>>(src, S < 0 ? 0 : S, ld_s, src_idx, plan.S_pad, packed);
+        count_launch(1);
+        DNP_CHECK_CUDA(cudaGetLastError());
+        // cut tiles accumulate into zeroed row sets; whole-tile launches store on a lane's first launch instead
+        if (!plan.whole_tiles) DNP_CHECK_CUDA(cudaMemsetAsync(partial, 0, plan.partial_bytes, stream));
+    }
+
+    const UTargets T{tgt, M, ld_t, ep.tgt_idx, ep.tgt_skip};
+    const size_t chunk_bytes = (size_t)plan.chunk * stride * sizeof(float);
+    const int64_t lane_stride = (int64_t)plan.ways * plan.way_stride;
+    DeviceRing& ring = g_ring[dev];
+    int rc = DNP_OK;
+    {
+        std::lock_guard<std::mutex> lock(ring.mu);
+        DNP_CHECK_CUDA(ring.prepare());
+        const bool cap = capturing(stream);
+        // queue behind the previous user of the window (same stream: already ordered)
+        if (!cap && ring.has_last && ring.last_stream != stream) DNP_CHECK_CUDA(cudaStreamWaitEvent(stream, ring.last_done, 0));
+        timer_mark(stream);
+        if (plan.lanes == 1) {
+            cudaError_t e = fill_slot(ring, 0, packed, chunk_bytes, stream);
+            if (e != cudaSuccess) rc = cuda_fail(e, "window fill");
+            else launch_chunk(potential, plan, 0, T, eps, partial, 1, stream);
+            count_launch(1);
+        } else {
+            DNP_CHECK_CUDA(cudaEventRecord(ring.fork, stream));
+            for (int l = 0; l < plan.lanes; ++l) DNP_CHECK_CUDA(cudaStreamWaitEvent(ring.lane[l], ring.fork, 0));
+            for (int k = 0; k < plan.n_chunks && rc == DNP_OK; ++k) {
+                const int l = k % plan.lanes;
+                const int win_off = l * plan.slot_floats;
+                cudaError_t e = fill_slot(ring, win_off, packed + (size_t)k * plan.chunk * stride, chunk_bytes, ring.lane[l]);
+                if (e != cudaSuccess) { rc = cuda_fail(e, "window fill"); break; }
+                launch_chunk(potential, plan, win_off, T, eps, partial + (int64_t)l * lane_stride, k < plan.lanes,
+                             ring.lane[l]);
+            }
+            count_launch(plan.n_chunks);
+            for (int l = 0; l < plan.lanes; ++l) {       // always re-join
+                cudaEventRecord(ring.lane_done[l], ring.lane[l]);
+                cudaStreamWaitEvent(stream, ring.lane_done[l], 0);
+            }
+        }
+        timer_mark(stream);
+        if (rc == DNP_OK) {
+            cudaError_t e = cudaGetLastError();
+            if (e != cudaSuccess) rc = cuda_fail(e, "upairs launch");
+        }
+        if (!cap) {
+            cudaEventRecord(ring.last_done, stream);
+            ring.has_last = true;
+            ring.last_stream = stream;
+        }
+    }
+    if (rc != DNP_OK) return rc;
+    return run_split_reduce(potential, partial, plan.lanes * plan.ways, M, ep, stream, plan.way_stride);
+}
+
+}  // namespace dnp

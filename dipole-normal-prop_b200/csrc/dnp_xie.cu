@@ -302,12 +302,11 @@ int run_xie_propagate(const float* pts, int64_t N, int64_t ld, const int64_t* or
                   workspace_bytes);
         return DNP_ERR_WORKSPACE;
     }
-    static std::atomic<int> attr_done{0};
-    if (!attr_done.load()) {
+    static std::atomic<int> attr_done[kMaxDevices];
+    DNP_ONCE_PER_DEVICE(attr_done, {
         DNP_CHECK_CUDA(cudaFuncSetAttribute(xie_chain_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
         DNP_CHECK_CUDA(cudaFuncSetAttribute(xie_chain_kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
-        attr_done.store(1);
-    }
+    });
     // smallest power-of-two cluster that gives every thread <= 4 points and fits the shared memory
     int ncta = 1;
     while (ncta < kXMaxCluster && (int64_t)ncta * kXThreads * 4 < N) ncta *= 2;

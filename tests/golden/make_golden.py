@@ -205,9 +205,17 @@ class Recorder:
         self.calls = []
 
     def __enter__(self):
+        self.depth = 0
+
         def wrapped(sources, means, *a, **k):
-            self.calls.append((sources[0].clone(), int(sources.shape[0]), int(means.shape[0])))
-            return self.orig(sources, means, *a, **k)
+            # field_grad recurses through the module attribute when a side exceeds max_pts: log top-level calls only
+            if self.depth == 0:
+                self.calls.append((sources[0].clone(), int(sources.shape[0]), int(means.shape[0])))
+            self.depth += 1
+            try:
+                return self.orig(sources, means, *a, **k)
+            finally:
+                self.depth -= 1
         self.fu.field_grad = wrapped
         return self
 
@@ -353,6 +361,51 @@ def gen_reps(fu, util):
         out[f"{tag}_ref_seconds"] = dt
         print(f"reps {tag}: N={pts.shape[0]} P={P} ref CPU {dt:.1f}s")
     save("reps_prop", **out)
+
+
+def _sign_bits(normals, pc_in):
+    """one bit per point: the output normal is the input normal negated"""
+    return np.packbits(((normals * pc_in[:, 3:]).sum(-1) < 0).numpy())
+
+
+def gen_large(fu, util):
+    """cfg3 / cfg4 at the sizes BASELINE.md section 2 timed the reference (N = 60 000 / P = 48 representatives
+    propagation, field_utils.py:207-282; 20 000 x 40 000 orientation transfer, :188-201).  The inputs are the
+    seeded stand-ins of bench.py (regenerated by the tests; a checksum guards the generator); only decisions are
+    stored: visit order, one flip bit per point, and the reference's wall times."""
+    sys.path.insert(0, os.path.dirname(os.path.dirname(OUT)))
+    import bench
+    out = {}
+    pc, reps = bench.cfg3_standin()
+    out["cfg3_input_checksum"] = pc.double().sum().item()
+    first_pt = {int(r[0]): i for i, (r, _) in enumerate(reps)}
+    for tag, diffuse in (("plain", False), ("diffuse", True)):
+        pts = pc.clone()
+        t0 = time.time()
+        with Recorder(fu) as rec:
+            fu.strongest_field_propagation_reps(pts, [(r.clone(), q.clone()) for r, q in reps], diffuse=diffuse)
+        dt = time.time() - t0
+        order = []
+        for k, c in enumerate(rec.calls[:len(reps)]):
+            row = match_rows(pc[:, :3], [c[0]])[0]
+            pid = [i for i, (r, _) in enumerate(reps) if int(r.min()) == row][0] if k == 0 else first_pt[int(row)]
+            order.append(pid)
+        out[f"cfg3_{tag}_order"] = np.array(order, dtype=np.int32)
+        out[f"cfg3_{tag}_flip_bits"] = _sign_bits(pts[:, 3:], pc)
+        out[f"cfg3_{tag}_ref_seconds"] = dt
+        out[f"cfg3_{tag}_mean_potential"] = fu.measure_mean_potential(pts)
+        print(f"large reps {tag}: N={pts.shape[0]} P={len(reps)} ref CPU {dt:.1f}s")
+    ref, tgt = bench.cfg4_standin()
+    out["cfg4_input_checksum"] = ref.double().sum().item() + tgt.double().sum().item()
+    t0 = time.time()
+    res6 = fu.reference_field(ref.clone(), tgt.clone())
+    out["cfg4_ref_seconds"] = time.time() - t0
+    out["cfg4_flip_bits"] = _sign_bits(res6[:, 3:], tgt)
+    E = fu.field_grad(ref, tgt[:, :3])
+    dots = (E * tgt[:, 3:]).sum(-1)
+    out["cfg4_margin"] = (dots.abs() / (E.norm(dim=-1) + 1e-30)).numpy().astype(np.float32)   # |cos| of E vs n
+    print(f"large transfer: {ref.shape[0]} x {tgt.shape[0]} ref CPU {out['cfg4_ref_seconds']:.1f}s")
+    save("large", **out)
 
 
 def gen_signatures(fu, util):
@@ -674,7 +727,8 @@ def gen_parser(fu, util):
 
 GENERATORS = {"signatures": gen_signatures, "leaf": gen_leaf, "edge": gen_edge, "transfer": gen_transfer, "lattice": gen_lattice,
               "points": gen_points, "patches": gen_patches, "reps": gen_reps, "xie": gen_xie, "partition": gen_partition,
-              "graph": gen_graph, "patchgraph": gen_patchgraph, "textio": gen_textio, "parser": gen_parser}
+              "graph": gen_graph, "patchgraph": gen_patchgraph, "textio": gen_textio, "parser": gen_parser,
+              "large": gen_large}
 
 if __name__ == "__main__":
     torch.manual_seed(0)

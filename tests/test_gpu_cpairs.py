@@ -21,6 +21,7 @@ def fu():
 @pytest.fixture()
 def path(monkeypatch):
     def _set(mode, lanes=None):
+        monkeypatch.setenv("DNP_RING", "0")                 # these tests are about the by-value kernel
         monkeypatch.setenv("DNP_CONST_PATH", str(mode))
         if lanes is None:
             monkeypatch.delenv("DNP_CONST_LANES", raising=False)

@@ -89,3 +89,29 @@ def test_world_size_2_nccl(tmp_path, dev):
         got = res[0]["w"][e].item()
         assert abs(got - float(want)) <= 2e-4 * abs(float(want)) + 1e-3, (e, got, float(want))
     np.save(os.path.join(tmp_path, "ok.npy"), np.zeros(1))
+
+
+def test_second_device_in_one_process(dev):
+    """cudaFuncSetAttribute opt-ins (227 KB dynamic shared memory, non-portable cluster sizes) are per device: the
+    cluster / cooperative kernels must work on cuda:1 after cuda:0 in the SAME process."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs (gpurun --gpus 2)")
+    import dnp_native as dn
+    import field_utils
+    results = []
+    for d in (0, 1):
+        device = torch.device("cuda", d)
+        pts = _cloud(20000, 5).to(device)                              # 16-CTA cluster, > 48 KB shared memory
+        out = field_utils.strongest_field_propagation_points(pts.clone())
+        big = _cloud(120000, 6).to(device)                             # cooperative-grid kernel
+        field_utils.strongest_field_propagation_points(big)
+        g = torch.Generator().manual_seed(9)
+        orders = torch.stack([torch.randperm(20000, generator=g) for _ in range(2)]).to(device)
+        flips = field_utils.xie_propagation_points_in_order(pts.clone(), 1e-2, orders)
+        offsets = torch.tensor([0, 3000, 9000, 20000], device=device)
+        batched = pts.clone()
+        dn.points_propagate_batched(batched, offsets, 11000)
+        torch.cuda.synchronize(device)
+        results.append((out.cpu(), flips.cpu() if torch.is_tensor(flips) else flips, batched.cpu()))
+    assert torch.equal(results[0][0], results[1][0])
+    assert torch.equal(results[0][2], results[1][2])
