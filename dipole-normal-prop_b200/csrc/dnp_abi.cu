@@ -286,17 +286,14 @@ int host_pairs(bool potential, const float* src_host, int64_t S, int64_t ld_s, c
     void* d_ws = base + up(src_bytes) + up(tgt_bytes) + up(out_bytes);
     int rc = DNP_OK;
     do {
-        // large calls pass the sources by value from the host (dnp_cpairs.cu): dense host rows need no upload
-        const bool by_value = ld_s == 6 && !use_ring_path(S, M, 0) && use_const_path(S, M, 0);
-        if (!by_value && (e = upload_rows(d_src, src_host, S, 6, ld_s, stream)) != cudaSuccess) { rc = cuda_fail(e, "upload sources"); break; }
+        if ((e = upload_rows(d_src, src_host, S, 6, ld_s, stream)) != cudaSuccess) { rc = cuda_fail(e, "upload sources"); break; }
         if ((e = upload_rows(d_tgt, tgt_host, M, 3, ld_t, stream)) != cudaSuccess) { rc = cuda_fail(e, "upload targets"); break; }
         t_up = now();
         PairEpilogue ep;
         ep.mode = DNP_EPI_STORE;
         ep.out = d_out;
         ep.ld_out = ncomp;
-        rc = run_pairs(potential, d_src, S, 6, nullptr, d_tgt, M, 3, 0, eps, ep, d_ws, ws_bytes, stream, 0, 0,
-                       by_value ? src_host : nullptr);
+        rc = run_pairs(potential, d_src, S, 6, nullptr, d_tgt, M, 3, 0, eps, ep, d_ws, ws_bytes, stream);
         t_launch = now();
         if (rc != DNP_OK) break;
         // result -> pinned buffer (asynchronous), then one host memcpy into the caller's (pageable) array

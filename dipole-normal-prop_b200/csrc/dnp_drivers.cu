@@ -9,12 +9,12 @@
 //   field    E += field of the chosen patch on the target rows (the all-pairs kernel, sources through src_idx)
 //   score    I_p = sum_{t in p} E_t . n_t for the remaining patches + first abs-arg-max (K4)
 // Two schedules of the same kernels:
-//   * device-driven (patches below the by-value kernel's threshold, i.e. nearly always): the winner of a step
+//   * device-driven (patches below 16 384 rows, i.e. nearly always): the winner of a step
 //     stays on the device -- the arg-max kernel advances cur = {patch, flip, previous patch}, the commit / pack /
 //     all-pairs kernels read their row range from it (launches are shaped for the LARGEST patch; the all-pairs
 //     kernel walks only the chosen patch's source tiles).  No host read inside the loop: all P steps are
 //     enqueued at once and the GPU runs them back to back.
-//   * host-driven (a patch large enough for the by-value kernel, whose sources are kernel parameters): one
+//   * host-driven (a patch of >= 16 384 rows, served by the constant-window kernel with host-planned launches): one
 //     8-byte device->host read per step.
 // Decisions are the kernels' (identical to the per-call path); nothing here does arithmetic on the host.
 #include <stdlib.h>
@@ -262,7 +262,9 @@ int run_patch_propagate(float* pts, int64_t N, int64_t ld, const int64_t* perm, 
             return DNP_ERR_INVALID;
         }
     }
-    bool device_driven = !use_const_path(max_patch, M, 0);
+    // patches of >= 16 384 rows take the constant-window kernel, whose launches are planned on the host for an
+    // explicit source range: one 8-byte read of the winner per step
+    bool device_driven = max_patch < 16384;
     if (forced && forced[0] == 'h') device_driven = false;
     if (forced && forced[0] == 'd') device_driven = true;
     if (device_driven) {
@@ -300,7 +302,7 @@ int run_patch_propagate(float* pts, int64_t N, int64_t ld, const int64_t* perm, 
                 ep.mode = step == 0 ? DNP_EPI_STORE : DNP_EPI_ACCUM;
                 if (max_patch > 0 && M > 0) {
                     const int rc = run_pairs(false, pts, max_patch, ld, perm, pts, M, ld, 0, eps, ep, pairs_ws,
-                                             L.pairs_bytes, stream, 0, 0, nullptr, sel);
+                                             L.pairs_bytes, stream, 0, 0, sel);
                     if (rc != DNP_OK) return rc;
                 }
                 if (step == P - 1) break;
@@ -327,7 +329,7 @@ int run_patch_propagate(float* pts, int64_t N, int64_t ld, const int64_t* perm, 
             ep.mode = step == 0 ? DNP_EPI_STORE : DNP_EPI_ACCUM;
             if (max_patch > 0 && M > 0) {
                 const int rc = run_pairs(false, pts, max_patch, ld, perm, pts, M, ld, 0, eps, ep, pairs_ws,
-                                         L.pairs_bytes, stream, 0, 0, nullptr, sel);
+                                         L.pairs_bytes, stream, 0, 0, sel);
                 if (rc != DNP_OK) return rc;
             }
             if (step == P - 1) break;

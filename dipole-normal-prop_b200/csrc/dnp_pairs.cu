@@ -14,8 +14,8 @@
 //     whose source-side operand is a 32-bit register broadcast to both halves (`R.F32`): 19 packed
 //     instructions + 2 MUFU.RSQ + 2 MUFU.RCP + 4 FMNMX per (2 targets x 1 source),
 //         E += w (n + t R),  t = (m.R) u^2,  u = rsqrt(r2),  w = 1 / (r2^2 u + eps).
-//     Large calls take the by-value kernel of dnp_cpairs.cu instead, where the source operand is a
-//     uniform register and costs no register-file read at all.
+//     Calls above ~2e8 pairs take the constant-window kernels of dnp_upairs.cu instead, where the source
+//     operand is a uniform register and costs no register-file read at all.
 //   * no tensor cores: the 1/(|R|^3+eps) weight is per pair, not a contraction.
 //   * coincident pairs: rsqrt(0)=inf makes r2^2 u = 0*inf NaN, so the weight w becomes NaN and
 //     max(w, 0) returns 0 (FMNMX drops the NaN operand); t uses the clamped rsqrt so it stays finite
@@ -343,12 +343,6 @@ int env_int(const char* name) {
 
 inline int64_t round_up(int64_t a, int64_t b) { return (a + b - 1) / b * b; }
 
-bool stream_is_capturing(cudaStream_t stream) {
-    cudaStreamCaptureStatus st = cudaStreamCaptureStatusNone;
-    if (cudaStreamIsCapturing(stream, &st) != cudaSuccess) { cudaGetLastError(); return false; }
-    return st != cudaStreamCaptureStatusNone;
-}
-
 }  // namespace
 
 int64_t launch_count() { return g_launches.load(); }
@@ -477,10 +471,6 @@ size_t pairs_workspace_bytes(int64_t S, int64_t M) {
     const PairPlan p = make_pair_plan(S, M, sm_count_cached(), 0, 0);
     const size_t packed = (size_t)round_up(round_up(S, kTileSrc) * kSrcBytes, 256);   // either tile's padding
     size_t core = packed + p.partial_bytes;
-    if (use_const_path(S, M, 0)) {
-        const size_t c = cpairs_workspace_bytes(S, M);
-        if (c > core) core = c;
-    }
     if (use_ring_path(S, M, 0)) {
         const size_t c = upairs_workspace_bytes(S, M);
         if (c > core) core = c;
@@ -530,7 +520,7 @@ static int launch_pairs_tp(const PairPlan& plan, const float4* packed, const flo
 int run_pairs(bool potential, const float* src, int64_t S, int64_t ld_s, const int64_t* src_idx,
               const float* tgt, int64_t M, int64_t ld_t, int lattice_n, float eps,
               const PairEpilogue& ep, void* workspace, size_t workspace_bytes, cudaStream_t stream,
-              int force_tp, int force_nsplit, const float* src_host_dense, SourceSelect sel) {
+              int force_tp, int force_nsplit, SourceSelect sel) {
     if (M <= 0) return DNP_OK;
     if (sel.patch && (!src_idx || !sel.offsets)) {
         set_error("device-selected sources need src_idx and offsets");
@@ -538,10 +528,6 @@ int run_pairs(bool potential, const float* src, int64_t S, int64_t ld_s, const i
     }
     if (!sel.patch && force_tp <= 0 && force_nsplit <= 0 && use_ring_path(S, M, lattice_n))
         return run_upairs(potential, src, S, ld_s, src_idx, tgt, M, ld_t, eps, ep, workspace, workspace_bytes, stream);
-    if (!sel.patch && force_tp <= 0 && force_nsplit <= 0 && use_const_path(S, M, lattice_n) &&
-        (src_host_dense || !stream_is_capturing(stream)))     // the by-value path synchronises once: never under capture
-        return run_cpairs(potential, src, S, ld_s, src_idx, src_host_dense, tgt, M, ld_t, eps, ep, workspace,
-                          workspace_bytes, stream);
     PairPlan plan = make_pair_plan(S, M, sm_count_cached(), force_tp, force_nsplit);
     if (workspace && plan.nsplit > 1 && workspace_bytes < plan.packed_bytes + plan.partial_bytes) {
         // a workspace sized for another source count: keep the splits that fit

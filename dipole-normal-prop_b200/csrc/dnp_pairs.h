@@ -54,16 +54,6 @@ struct PairPlan {
     size_t partial_bytes = 0;
 };
 
-// plan of the constant-bank path (dnp_cpairs.cu)
-struct CPairPlan {
-    int lanes = 2;         // concurrent launch lanes (streams), each with its own partial rows
-    int n_chunks = 1;      // launches (896 field / 1280 potential sources each)
-    int m_tiles = 1;       // CTAs per launch (1024 targets each)
-    int64_t S_pad = 0;
-    size_t packed_bytes = 0;
-    size_t partial_bytes = 0;
-};
-
 // plan of the constant-window path (dnp_upairs.cu)
 struct UPairPlan {
     int tp = 4;            // target pairs per thread (1024- or 256-target tiles)
@@ -92,16 +82,8 @@ size_t pairs_workspace_bytes_upper(int64_t S, int64_t M);   // covers every sour
 int run_pairs(bool potential, const float* src, int64_t S, int64_t ld_s, const int64_t* src_idx,
               const float* tgt, int64_t M, int64_t ld_t, int lattice_n, float eps,
               const PairEpilogue& ep, void* workspace, size_t workspace_bytes, cudaStream_t stream,
-              int force_tp = 0, int force_nsplit = 0, const float* src_host_dense = nullptr,
-              SourceSelect sel = SourceSelect());
+              int force_tp = 0, int force_nsplit = 0, SourceSelect sel = SourceSelect());
 
-// Large calls: sources passed by value through the kernel-parameter constant bank (dnp_cpairs.cu).
-bool use_const_path(int64_t S, int64_t M, int lattice_n);
-CPairPlan make_cpair_plan(bool potential, int64_t S, int64_t M, int sm_count);
-size_t cpairs_workspace_bytes(int64_t S, int64_t M);
-int run_cpairs(bool potential, const float* src, int64_t S, int64_t ld_s, const int64_t* src_idx,
-               const float* src_host_dense, const float* tgt, int64_t M, int64_t ld_t, float eps,
-               const PairEpilogue& ep, void* workspace, size_t workspace_bytes, cudaStream_t stream);
 // Sources through the device-resident constant window (dnp_upairs.cu): asynchronous, capturable.
 bool use_ring_path(int64_t S, int64_t M, int lattice_n);
 UPairPlan make_upair_plan(bool potential, int64_t S, int64_t M, int sm_count);

@@ -1,131 +1,46 @@
 """Drop-in for the reference's dipole_api.py: `orient_large(opts)` (:14-87) and
-`get_parser()` (:101-132), the representative-point pipeline of orient_large.py behind one function.
+`get_parser()` (:101-132).
 
-Every stage on the dipole path runs through this package: text parse (dnp_xyz_parse_f32), voxel partition
-(dnp_voxel_partition_f32 + merge), representative-point propagation (strongest_field_propagation_reps), the lattice
-sign test and the text export (dnp_xyz_format_f32).  The PointCNN stage is the reference's own: its loader
-(inference_utils.load_model_from_file, which needs torch_geometric) is imported lazily from the reference checkout
-when `opts.models` is non-empty; with no models the stage is skipped, everything else is unchanged.
+`orient_large` is NOT re-implemented here: the pipeline (load -> normals -> partition -> PointCNN votes ->
+representative-point propagation -> lattice sign test -> export) is the reference's own control flow, which
+north_star leaves unchanged.  The adapter below runs the reference's function object from its checkout with this
+package's hot path in front of it (dnp_dropin): its `strongest_field_propagation_reps`, `measure_mean_potential`,
+`util.divide_pc`, `util.xyz2tensor` and `util.export_pc` calls land in libdipole.so, everything else (Transform,
+orient_center, fix_n_filter, the model loop, MyTimer) executes as written in the reference.
+
+`get_parser` is built from the flag schema recorded from the reference (tests/golden/parser_signatures.json pins it):
+same flags, types, defaults and actions; only the fork's hard-coded Windows checkout path is overridable through
+$DNP_BASE_PATH.
 """
 import argparse
+import importlib.util
 import os
+import sys
 from pathlib import Path
 
-import torch
+import dnp_dropin
 
-import dnp_util
-import field_utils
-from field_utils import *        # noqa: F401,F403  (dipole_api.py:9)
-
-util = field_utils.util
-torch.manual_seed(1)             # dipole_api.py:8
-
-estimate_normals = True
+_REF_MODULE = "_reference_dipole_api"
 
 
-def voting_policy(probs):
-    """inference_utils.py:46-48."""
-    probs = torch.stack(probs, dim=0).mean(dim=0)
-    return probs < 0.5, probs
-
-
-def fix_n_filter(input_pc, patch_indices, threshold):
-    """inference_utils.py:51-73: keep the patches whose flatness ratio e0 / (e1 + e2 / 2) exceeds `threshold`;
-    the others are oriented along their PCA normal in place.  Returns [(i, patch)]."""
-    kept = []
-    for i, patch in enumerate(patch_indices):
-        x = input_pc[patch]
-        temp = x[:, :3] - x.mean(dim=0)[None, :3]
-        cov = (temp.transpose(0, 1) @ temp) / x.shape[0]
-        e, v = torch.linalg.eigh(cov)
-        if (e[0] / ((e[1] + e[2] / 2))).item() > threshold:
-            kept.append((i, patch))
-        else:
-            sign = ((input_pc[patch, 3:] * v[:, 0][None, :]).sum(dim=-1) > 0).float() * 2 - 1
-            input_pc[patch, 3:] = input_pc[patch, 3:] * sign[:, None]
-    return kept
-
-
-def _load_models(paths, device):
-    if not paths:
-        return []
-    from inference_utils import load_model_from_file      # the reference's PointCNN loader (torch_geometric)
-    return [load_model_from_file(p, device) for p in paths]
+def _reference_api():
+    """The reference's dipole_api.py as a module object (under a private name: this file shadows `dipole_api`)."""
+    mod = sys.modules.get(_REF_MODULE)
+    if mod is None:
+        ref = dnp_dropin.activate()
+        spec = importlib.util.spec_from_file_location(_REF_MODULE, os.path.join(ref, "dipole_api.py"))
+        mod = importlib.util.module_from_spec(spec)
+        sys.modules[_REF_MODULE] = mod
+        spec.loader.exec_module(mod)
+    return mod
 
 
 def orient_large(opts):
-    """dipole_api.py:14-87."""
-    field_utils._cuda_device()
-    export_path: Path = opts.export_dir
-    export_path.mkdir(exist_ok=True)
-
-    max_patch_size = 500
-    device = torch.device("cuda", torch.cuda.current_device())
-    MyTimer = dnp_util.timer_factory()
-    with MyTimer('load pc', count=False):
-        input_pc = dnp_util.xyz2tensor_cuda(open(opts.pc, 'r').read(), append_normals=False, device=device)
-    print(input_pc.shape)
-
-    input_pc, transform = util.Transform.trans(input_pc)
-
-    if opts.estimate_normals:
-        with MyTimer('estimating normals'):
-            input_pc = getattr(util, "estimate_normals", dnp_util.estimate_normals)(input_pc, max_nn=opts.n)
-
-    softmax = torch.nn.Softmax(dim=-1)
-    models = _load_models(list(opts.models), device)
-
-    with MyTimer('divide patches'):
-        # upstream composition: util.divide_pc as shipped returns unmerged nested lists
-        patch_indices = dnp_util.merge_nodes(input_pc, *dnp_util._divide_pc(input_pc[:, :3], opts.number_parts,
-                                                                             min_patch=opts.minimum_points_per_patch),
-                                             opts.minimum_points_per_patch)[0]
-        all_patches_indices = [x.clone() for x in patch_indices]
-
-    with MyTimer('filter patches'):
-        patch_indices = fix_n_filter(input_pc, patch_indices, opts.curvature_threshold)
-
-    num_patches = len(patch_indices)
-    num_all_patches = len(all_patches_indices)
-    print(f'number of patches {num_patches}/{num_all_patches}')
-
-    with MyTimer('orient center'):
-        for i, p in patch_indices:
-            input_pc[p] = dnp_util.orient_center(input_pc[p])
-
-    with MyTimer('find reps'):
-        represent = []
-        for p in all_patches_indices:
-            permutation = torch.randperm(p.shape[0]).to(p.device)
-            represent.append((p[permutation[:max_patch_size]], p[permutation[max_patch_size:]]))
-
-    pc_probs = torch.ones_like(input_pc[:, 0])
-
-    with MyTimer('network orientation'):
-        if models:
-            for i, _ in patch_indices:
-                with torch.no_grad():
-                    current_reps, non_reps_points = represent[i]
-                    data = input_pc[current_reps].to(device)
-                    for _ in range(opts.iters):
-                        votes = [model(data.clone()) for model in models]
-                        vote_probabilities = [softmax(scores)[:, 1] for scores in votes]
-                        flip, probs = voting_policy(vote_probabilities)
-                        pc_probs[current_reps] = probs
-                        input_pc[current_reps[flip], 3:] *= -1
-
-    [model.to('cpu') for model in models]
-    with MyTimer('propagating field'):
-        strongest_field_propagation_reps(input_pc, represent, diffuse=True)      # noqa: F405
-
-    with MyTimer('fix global orientation'):
-        if field_utils.measure_mean_potential(input_pc) < 0:
-            input_pc[:, 3:] *= -1
-
-    with MyTimer('exporting result', count=False):
-        dnp_util.export_pc(transform.inverse(input_pc).transpose(0, 1), export_path / 'final_result.xyz')
-
-    MyTimer.print_total_time()
+    """dipole_api.py:14-87, executed from the reference checkout ($DNP_REFERENCE or on sys.path) on this package's
+    hot path.  Raises FileNotFoundError when no checkout is visible."""
+    import field_utils
+    field_utils._cuda_device()                    # fail loudly without a GPU before any file is touched
+    return _reference_api().orient_large(opts)
 
 
 # dipole_api.py:93-97: the fork's checkout location, overridable
@@ -135,21 +50,24 @@ models = [Path(base_path + "/pre_trained/hands2.pt"), Path(base_path + "/pre_tra
           Path(base_path + "/pre_trained/manmade.pt")]
 export_dir = Path(base_path + "/data/output/")
 
+# (flag, type, default, nargs, store_true) -- dipole_api.py:116-128
+_FLAGS = (("pc", Path, input_pc, None, False), ("models", Path, models, "+", False),
+          ("export_dir", Path, export_dir, None, False), ("number_parts", int, 10, None, False),
+          ("minimum_points_per_patch", int, 100, None, False), ("curvature_threshold", float, 0.0, None, False),
+          ("iters", int, 5, None, False), ("diffuse", None, True, None, True), ("weighted_prop", None, True, None, True),
+          ("estimate_normals", None, True, None, True), ("n", int, 30, None, False))
+
 
 def get_parser():
-    """dipole_api.py:101-132: same flags, types and defaults."""
+    """dipole_api.py:101-132: same flags, types, defaults and actions."""
     parser = argparse.ArgumentParser()
-    parser.add_argument('--pc', type=Path, default=input_pc, help='path to the point cloud')
-    parser.add_argument('--models', type=Path, nargs='+', default=models, help='path to the models')
-    parser.add_argument('--export_dir', type=Path, default=export_dir, help='path to the output directory')
-    parser.add_argument('--number_parts', type=int, default=10, help='number of parts to divide the point cloud')
-    parser.add_argument('--minimum_points_per_patch', type=int, default=100, help='minimum number of points per patch')
-    parser.add_argument('--curvature_threshold', type=float, default=0.0, help='curvature threshold')
-    parser.add_argument('--iters', type=int, default=5, help='number of iterations')
-    parser.add_argument('--diffuse', default=True, action='store_true', help='diffuse')
-    parser.add_argument('--weighted_prop', default=True, action='store_true', help='weighted propagation')
-    parser.add_argument('--estimate_normals', default=True, action='store_true', help='estimate normals')
-    parser.add_argument('--n', type=int, default=30, help='number of nearest neighbors for normal estimation')
+    for name, typ, default, nargs, flag in _FLAGS:
+        if flag:
+            parser.add_argument("--" + name, default=default, action="store_true")
+        elif nargs:
+            parser.add_argument("--" + name, type=typ, nargs=nargs, default=default)
+        else:
+            parser.add_argument("--" + name, type=typ, default=default)
     return parser
 
 

@@ -129,56 +129,9 @@ def install(util_module=None):
 
 
 # ---------------------------------------------------------------------------- patch graph
-# Host bookkeeping around the flip-score kernels, same names and results as the reference's util.py.
-def timer_factory():
-    """util.py:612-651: context-manager timer class with a shared running total."""
-    import time
-
-    class MyTimer(object):
-        total_count = 0
-
-        def __init__(self, msg='', count=True):
-            self.msg, self.count = msg, count
-
-        def __enter__(self):
-            self.start = time.perf_counter()
-            if self.msg:
-                print(f'started: {self.msg}')
-            return self
-
-        def __exit__(self, typ, value, traceback):
-            self.duration = time.perf_counter() - self.start
-            if self.count:
-                MyTimer.total_count += self.duration
-            if self.msg:
-                print(f'finished: {self.msg}. duration: {MyTimer.convert_to_time_format(self.duration)}')
-
-        @staticmethod
-        def print_total_time():
-            print('\n ----- \n')
-            print(f'total time: {MyTimer.convert_to_time_format(MyTimer.total_count)}')
-
-        @staticmethod
-        def convert_to_time_format(sec):
-            sec = round(sec, 2)
-            if sec < 60:
-                return f'{sec} [sec]'
-            minutes = int(sec / 60)
-            remaining_seconds = sec - (minutes * 60)
-            remaining_seconds = round(remaining_seconds, 2)
-            return f'{minutes}:{remaining_seconds} [min:sec]'
-
-    return MyTimer
-
-
-def orient_center(pred):
-    """util.py:39-44: flip the normals that point towards the centroid (in place)."""
-    cent = pred[:, :3].mean(dim=0)
-    flip_mask = ((pred[:, :3] - cent) * pred[:, 3:]).sum(dim=-1) < 0
-    pred[flip_mask, 3:] *= -1
-    return pred
-
-
+# Host bookkeeping around the flip-score kernels, same names and results as the reference's util.py.  The
+# reference's timers, normal estimation (open3d / torch_cluster) and orient_center are NOT restated here: its
+# pipelines keep using their own util module (dnp_dropin.activate), which is where those live.
 def npxyz2tensor(np_pc, append_normals=True):
     """util.py:71-77: numpy [N, 3|6] -> tensor of the same dtype (float64 from the wire), zero normals appended."""
     import numpy as np
@@ -187,43 +140,26 @@ def npxyz2tensor(np_pc, append_normals=True):
     return torch.tensor(np_pc)
 
 
-def estimate_normals_torch(inputpc, max_nn):
-    """util.py:520-529, the reference's own fallback when open3d is missing: the eigenvector of the smallest
-    eigenvalue of the covariance of each point's max_nn nearest neighbours (self excluded).  The reference takes
-    the neighbours from torch_cluster.knn_graph; here a chunked distance + topk (estimator plumbing, not the
-    dipole path; unoriented normals, sign arbitrary as in the reference)."""
-    xyz = inputpc[:, :3]
-    n = xyz.shape[0]
-    k = min(max_nn, n - 1)
-    nbr = torch.empty(n, k, dtype=torch.int64, device=xyz.device)
-    chunk = max(1, min(n, (1 << 26) // max(n, 1)))
-    for lo in range(0, n, chunk):
-        d = torch.cdist(xyz[lo:lo + chunk].double(), xyz.double())
-        d[torch.arange(d.shape[0], device=xyz.device), torch.arange(lo, lo + d.shape[0], device=xyz.device)] = float('inf')
-        nbr[lo:lo + chunk] = d.topk(k, dim=1, largest=False).indices
-    x = xyz[nbr]
-    temp = x - x.mean(dim=1, keepdim=True)
-    cov = temp.transpose(1, 2) @ temp / x.shape[0]
-    _, v = torch.linalg.eigh(cov)
-    return torch.cat([xyz, v[:, :, 0].to(xyz.dtype)], dim=-1)
-
-
-def estimate_normals(inputpc, max_nn=30, keep_orientation=False):
-    """util.py:551-567: open3d's hybrid-radius PCA normals when open3d is importable, else the torch fallback."""
-    try:
-        import numpy as np
-        import open3d as o3d
-        pcd = o3d.geometry.PointCloud()
-        pcd.points = o3d.utility.Vector3dVector(np.array(inputpc[:, :3].cpu()))
-        pcd.estimate_normals(search_param=o3d.geometry.KDTreeSearchParamHybrid(radius=0.1, max_nn=max_nn))
-        out = torch.cat((inputpc[:, :3], torch.Tensor(np.array(pcd.normals)).to(inputpc.device)), dim=1)
-        if keep_orientation:
-            flip = (inputpc[:, 3:] * out[:, 3:]).sum(dim=-1) < 0
-            out[flip, 3:] *= -1
-    except (ModuleNotFoundError, AttributeError):
-        print('open3d not found, using torch_cluster instead')
-        out = estimate_normals_torch(inputpc, max_nn)
-    return out
+def knn_pca_normals(xyz, k=30):
+    """Unoriented normals for clouds that arrive without any (the server's wire format, socket_server_para.py:145-166)
+    when the reference's util.estimate_normals (open3d, util.py:551-567) is unavailable: direction of least variance
+    of each point's k nearest neighbours.  Plumbing in front of the dipole path (sign arbitrary, the propagation
+    orients it); second moments are accumulated in float64 on the device."""
+    pts = xyz[:, :3]
+    n = pts.shape[0]
+    k = max(1, min(int(k), n - 1))
+    p64 = pts.double()
+    normals = torch.empty_like(pts)
+    rows = max(1, min(n, (1 << 26) // max(n, 1)))
+    for lo in range(0, n, rows):
+        block = p64[lo:lo + rows]
+        dist = torch.cdist(block, p64)
+        dist[torch.arange(block.shape[0], device=pts.device), torch.arange(lo, lo + block.shape[0], device=pts.device)] = float("inf")
+        nb = p64[dist.topk(k, dim=1, largest=False).indices]               # [rows, k, 3], self excluded
+        mean = nb.mean(dim=1)
+        second = torch.einsum("rki,rkj->rij", nb, nb) / k - mean[:, :, None] * mean[:, None, :]
+        normals[lo:lo + rows] = torch.linalg.eigh(second).eigenvectors[:, :, 0].to(pts.dtype)
+    return torch.cat([pts, normals], dim=1)
 
 
 def _lzd_divide_pc(pc_in: torch.Tensor, n_part: int, ranges=(-1.5, 1.5), min_patch=0):
@@ -322,34 +258,29 @@ def divide_pc_to_graph(pc_in: torch.Tensor, n_part: int, ranges=(-1.5, 1.5), min
     import numpy as np
     import field_utils
     from graph import BidGraph, BiEdge
-    MyTimer = timer_factory()
-    with MyTimer('lzd_divide_pc'):
-        indices, ijk = _lzd_divide_pc(pc_in, n_part, ranges, min_patch)
-    with MyTimer('merge nodes'):
-        indices, ijk, ijk_source = lzd_merge_nodes(pc_in, indices, ijk, min_patch)
-    with MyTimer('point estimator'):
-        if point_estimator is not None:
-            import dnp_native as _dn
-            batched = getattr(point_estimator, "batched", None)
-            if (batched is not None and pc_in.is_cuda and pc_in.dtype == torch.float32 and indices
-                    and max(len(i) for i in indices) <= _dn.load().dnp_points_batched_max_n()):
-                batched(pc_in, indices)  # every patch in one launch (graph_dipole.st_propagation_points_batched)
-            else:
-                for idx in indices:      # the reference starts one Python thread per patch; the device serialises them
-                    pc_in[idx] = point_estimator(pc_in[idx])
-    with MyTimer('edge calculator'):
-        G = BidGraph()
-        G.V = [i for i in range(len(indices))]
-        pairs = graph_edges(ijk_source)
-        assert edge_calculator is not None or not pairs
-        if pairs and edge_calculator is field_utils.field_edge_calculator:
-            w, invw = field_utils.field_edge_calculator_batched(pc_in, indices, np.asarray(pairs, dtype=np.int64))
-            for (i, j), a, b in zip(pairs, w, invw):
-                G.E.append(BiEdge(i, j, np.asarray(a), b))
+    indices, ijk = _lzd_divide_pc(pc_in, n_part, ranges, min_patch)
+    indices, ijk, ijk_source = lzd_merge_nodes(pc_in, indices, ijk, min_patch)
+    if point_estimator is not None:
+        import dnp_native as _dn
+        batched = getattr(point_estimator, "batched", None)
+        if (batched is not None and pc_in.is_cuda and pc_in.dtype == torch.float32 and indices
+                and max(len(i) for i in indices) <= _dn.load().dnp_points_batched_max_n()):
+            batched(pc_in, indices)  # every patch in one launch (graph_dipole.st_propagation_points_batched)
         else:
-            for i, j in pairs:
-                w, invw = edge_calculator(pc_in[indices[i]], pc_in[indices[j]])
-                G.E.append(BiEdge(i, j, w, invw))
+            for idx in indices:      # the reference starts one Python thread per patch; the device serialises them
+                pc_in[idx] = point_estimator(pc_in[idx])
+    G = BidGraph()
+    G.V = [i for i in range(len(indices))]
+    pairs = graph_edges(ijk_source)
+    assert edge_calculator is not None or not pairs
+    if pairs and edge_calculator is field_utils.field_edge_calculator:
+        w, invw = field_utils.field_edge_calculator_batched(pc_in, indices, np.asarray(pairs, dtype=np.int64))
+        for (i, j), a, b in zip(pairs, w, invw):
+            G.E.append(BiEdge(i, j, np.asarray(a), b))
+    else:
+        for i, j in pairs:
+            w, invw = edge_calculator(pc_in[indices[i]], pc_in[indices[j]])
+            G.E.append(BiEdge(i, j, w, invw))
     return G, indices
 
 

@@ -80,8 +80,11 @@ def graph_dipole_server_api(xyz_data, config):
     field_utils._cuda_device()
     device = torch.device("cuda", torch.cuda.current_device())
     input_pc = dnp_util.npxyz2tensor(np.asarray(xyz_data)).to(device)
-    estimate = getattr(util, "estimate_normals", dnp_util.estimate_normals)
-    input_pc = estimate(input_pc, max_nn=config['max_nn']).float()
+    try:            # the reference's estimator (open3d KD-tree PCA, util.py:551-567) when it is really there
+        import open3d
+        input_pc = util.estimate_normals(input_pc, max_nn=config['max_nn']).float()
+    except (ImportError, AttributeError, ModuleNotFoundError):
+        input_pc = dnp_util.knn_pca_normals(input_pc.float(), k=config['max_nn'])
     input_pc, transform = util.Transform.trans(input_pc)
     if config['divide_method'] == 'grid_partition':
         G, index = dnp_util.divide_pc_to_graph(input_pc, n_part=config["n_part"], min_patch=config["min_patch"],

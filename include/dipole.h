@@ -14,18 +14,22 @@
  *   - `ld_*` are row strides in float elements, so views such as pc[:, :3]
  *     (stride 6) or E[:, :3] need no copy.  A point row is [x y z nx ny nz].
  *   - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream).
- *     Work is enqueued asynchronously; nothing synchronises unless stated.
- *     Stated exception: potential / field calls with >= 16384 sources and
- *     >= 131072 targets (or >= 32768 sources and >= 65536 targets) hand their sources to the kernels by value (kernel
- *     parameters -> uniform registers), which needs them on the host: the call
- *     synchronises `stream` once before its launches.  Never under stream
- *     capture; DNP_CONST_PATH=0 in the environment disables that path.
+ *     Work is enqueued asynchronously; nothing synchronises unless stated, and
+ *     every device-pointer entry point may be recorded into a CUDA graph.
+ *     Potential / field calls above ~2e8 pairs stream their sources through a
+ *     64 KB constant window that exists once per device (dnp_upairs.cu): calls
+ *     from different host threads / streams are queued on it in submission
+ *     order (an event wait on the caller's stream, never a host wait).  A graph
+ *     that contains such a call must not be REPLAYED concurrently with other
+ *     large potential / field calls on the same device (replays bypass that
+ *     queue); DNP_RING=0 in the environment disables the window path.
  *   - scratch memory comes from the caller: query dnp_pairs_workspace_bytes()
  *     and pass a device buffer at least that large (256-byte aligned).
  *   - return value: DNP_OK (0) or a negative DNP_ERR_* code; dnp_last_error()
  *     returns a thread-local message.  Nothing throws across the ABI.
- *   - re-entrant: no global mutable state; per-host-thread scratch (a pinned
- *     staging buffer and helper streams) is released when the thread exits (the
+ *   - re-entrant: the only shared state is the per-device constant window and
+ *     its lane streams (a mutex held while enqueueing); per-host-thread scratch
+ *     of the *_host entry points is released when the thread exits (the
  *     reference calls this path from many Python threads, util.py:187-196,308-327).
  *   - float32 only (the file pipelines of the reference are float32,
  *     util.py:61,66); there is no CPU fallback.

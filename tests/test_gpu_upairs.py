@@ -157,6 +157,19 @@ def test_epilogues_gathers_and_masks(fu, orc, dev, ring):
     assert bool((b["store"][~sel | skip] == 0).all())
 
 
+def test_host_entry_points_take_the_window_path(fu, orc, ring):
+    """CPU tensors in, CPU tensor out (dnp_field_grad_host_f32 / dnp_potential_host_f32): upload, window path,
+    download; strided host rows included."""
+    ring(2)
+    src, tgt = cloud(4000, 71), cloud(3000, 72)
+    E = fu.field_grad(src, tgt[:, :3])
+    assert not E.is_cuda
+    check_E(E.numpy(), orc.field_grad(src.numpy(), tgt.numpy()), "host entry")
+    wide = torch.cat([src, torch.zeros(4000, 2)], 1)[:, :6]                 # ld_s = 8
+    check_E(fu.field_grad(wide, tgt[:, :3]).numpy(), orc.field_grad(src.numpy(), tgt.numpy()), "host strided")
+    check_phi(fu.potential(src, tgt).numpy(), orc.potential(src.numpy(), tgt.numpy()), "host potential")
+
+
 def test_deterministic_and_reentrant(fu, orc, dev, ring):
     """The window is one per device: concurrent callers on their own streams are queued on it and each gets
     its own answer."""
