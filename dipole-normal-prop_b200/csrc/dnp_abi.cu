@@ -6,6 +6,7 @@
 // state besides cached device properties and a launch counter, so it is safe to
 // call from many host threads (the reference does: util.py:187-196,308-327).
 #include <stdarg.h>
+#include <stdlib.h>
 #include <stdio.h>
 #include <string.h>
 
@@ -96,6 +97,11 @@ int dnp_lattice_mean_potential_f32(const float* src, int64_t S, int64_t ld_s,
     DNP_REQUIRE(ld_s >= 6, "row stride too small");
     const int64_t M = (int64_t)n * n * n;
     const size_t need = pairs_workspace_bytes(S, M);
+    // callers that only want the mean (every pipeline) take the sources-in-registers kernel; DNP_LATTICE_FAST=0 keeps
+    // the generic path (A/B measurements)
+    const char* fast = getenv("DNP_LATTICE_FAST");
+    if (!phi_opt && !(fast && fast[0] == '0') && workspace && workspace_bytes >= lattice_mean_workspace_bytes())
+        return run_lattice_mean(src, S, ld_s, n, mean_out, workspace, workspace_bytes, (cudaStream_t)stream);
     if (!workspace || workspace_bytes < need) {
         set_error("workspace too small: need %zu bytes, got %zu", need, workspace_bytes);
         return DNP_ERR_WORKSPACE;

@@ -91,6 +91,10 @@ size_t upairs_workspace_bytes(int64_t S, int64_t M);
 int run_upairs(bool potential, const float* src, int64_t S, int64_t ld_s, const int64_t* src_idx, const float* tgt,
                int64_t M, int64_t ld_t, float eps, const PairEpilogue& ep, void* workspace, size_t workspace_bytes,
                cudaStream_t stream);
+// Mean potential over the n^3 lattice with the sources in registers and the nodes as uniform operands (dnp_lattice.cu).
+size_t lattice_mean_workspace_bytes();
+int run_lattice_mean(const float* src, int64_t S, int64_t ld_s, int n, float* mean_out, void* workspace,
+                     size_t workspace_bytes, cudaStream_t stream);
 // fixed-order sum of `nsplit` partial row sets + the fused epilogue; set_stride = floats between row sets
 // (0: M rows of 1 / 3 floats)
 int run_split_reduce(bool potential, const float* partial, int nsplit, int64_t M, const PairEpilogue& ep,

@@ -84,22 +84,27 @@ def measure_mean_potential_sharded(pc, n=10, group=None, compute=None):
 
 def slice_patches(offsets, rank, world):
     """Per-patch block slices of a CSR: returns (gather_index, new_offsets) such that
-    perm[gather_index] / new_offsets is the CSR of this rank's share of every patch."""
-    off = offsets.cpu().tolist()
-    idx, new_off = [], [0]
-    for p in range(len(off) - 1):
-        a, b = shard_range(off[p + 1] - off[p], rank, world)
-        idx.extend(range(off[p] + a, off[p] + b))
-        new_off.append(len(idx))
-    return torch.tensor(idx, dtype=torch.int64), torch.tensor(new_off, dtype=torch.int64)
+    perm[gather_index] / new_offsets is the CSR of this rank's share of every patch (shard_range per patch).
+    Vectorised on the device of `offsets`: no per-patch Python work."""
+    off = torch.as_tensor(offsets, dtype=torch.int64)
+    sizes = off[1:] - off[:-1]
+    base, rem = sizes // world, sizes % world
+    start = rank * base + torch.clamp(rem, max=rank)                    # shard_range(n, rank, world), all patches at once
+    count = base + (rank < rem).to(torch.int64)
+    new_off = torch.zeros_like(off)
+    new_off[1:] = torch.cumsum(count, 0)
+    total = int(new_off[-1])
+    patch = torch.repeat_interleave(torch.arange(sizes.numel(), device=off.device), count, output_size=total)
+    idx = torch.arange(total, device=off.device) - new_off[:-1][patch] + (off[:-1] + start)[patch]
+    return idx, new_off
 
 
 def edge_interactions_sharded(pts, perm, offsets, edges, eps=1e-5, group=None, compute=None):
     """Per-edge interactions sum_t n_t . E_S(t) with the targets of EVERY patch sliced over the ranks
     and the partial sums combined by a single all_reduce(SUM) over the edge vector."""
     rank, world = _rank_world(group)
-    gidx, t_off = slice_patches(offsets, rank, world)
-    t_perm = perm[gidx.to(perm.device)]
+    gidx, t_off = slice_patches(torch.as_tensor(offsets).to(perm.device), rank, world)
+    t_perm = perm[gidx]
     fn = compute or (lambda tp, to: _dn.edge_interactions_batched(pts, perm, offsets, edges, eps=eps,
                                                                    tgt_perm=tp, tgt_offsets=to))
     partial = fn(t_perm, t_off.to(perm.device))

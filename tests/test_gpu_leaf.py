@@ -304,6 +304,35 @@ def test_lattice_node_potentials(golden, orc, dev):
     assert abs(mean.item() - phi.double().mean().item()) <= 1e-6 * abs(mean.item())
 
 
+@pytest.mark.parametrize("S", [1, 255, 257, 4099, 300001])
+@pytest.mark.parametrize("n", [10, 7, 13])
+def test_lattice_mean_kernel_vs_float64_oracle(orc, dev, S, n):
+    """The mean-only kernel (dnp_lattice.cu: sources in registers, nodes uniform, one running sum per thread)
+    against the float64 oracle over the same n^3 nodes; ragged source counts, other lattice sides, a strided
+    view, and sources placed exactly ON lattice nodes (coincident pairs contribute 0)."""
+    import dnp_native
+    pc = cloud(S, 900 + S)
+    pc[:, :3] *= 1.6                                         # spans several lattice cells
+    k = min(S, 5)
+    idx = torch.arange(k)
+    pc[:k, 0] = ((idx % n).float() / n - 0.5) * 2            # exactly on nodes
+    pc[:k, 1] = (((idx + 1) % n).float() / n - 0.5) * 2
+    pc[:k, 2] = (((idx + 2) % n).float() / n - 0.5) * 2
+    ar = torch.arange(n ** 3)
+    grid = ((torch.stack([ar // (n * n), (ar // n) % n, ar % n], 1).float() / n) - 0.5) * 2     # util.py:26-36
+    phi64 = orc.potential(pc.numpy(), grid.numpy(), drop_coincident=True)      # the product's documented rule
+    want = float(np.mean(phi64))
+    scale = float(np.mean(np.abs(phi64)))
+    got = dnp_native.lattice_mean_potential(pc.to(dev), n=n).item()
+    assert abs(got - want) <= 1e-4 * abs(want) + 1e-5 * scale, (got, want)
+    wide = torch.zeros(S, 9)
+    wide[:, 1:7] = pc
+    got_view = dnp_native.lattice_mean_potential(wide.to(dev)[:, 1:7], n=n).item()
+    assert got_view == got                                    # same kernel, same order: bit-equal
+    mean_generic, phi = dnp_native.lattice_mean_potential(pc.to(dev), n=n, want_phi=True)
+    assert abs(got - mean_generic.item()) <= 1e-4 * abs(want) + 1e-5 * scale
+
+
 # ------------------------------------------------------------------ a4 patch-pair flip scores
 def test_edge_scores_golden(fu, golden, dev):
     g = golden("edge")
