@@ -147,7 +147,6 @@ lattice_sum_kernel(const __grid_constant__ LatticeTable tab, const __grid_consta
     }
 }
 
-inline int64_t round_up_l(int64_t a, int64_t b) { return (a + b - 1) / b * b; }
 
 }  // namespace
 

@@ -34,6 +34,7 @@
 #include <mutex>
 
 #include "dnp_common.cuh"
+#include "dnp_epilogue.cuh"
 #include "dnp_pairs.h"
 
 namespace dnp {
@@ -45,6 +46,7 @@ constexpr int kWindowFloats = 16128;               // 64 512 B of the 64 KB cons
 constexpr int kSlotFloats = 8064;                  // two slots of 32 256 B ...
 constexpr int kQuarterFloats = 4032;               // ... or four of 16 128 B (more launches in flight for fewer targets)
 constexpr int kMaxSlots = 4;
+constexpr int kFixTiles = 1 << 20;                 // target tiles a fused single-launch call may have (4 MB of counters)
 constexpr float kRsqrtClampU = 1.152921504606847e18f;   // 2^60
 constexpr float kRsqrtClampPhiU = 1.099511627776e12f;   // 2^40
 
@@ -93,10 +95,23 @@ __global__ void fill_window_kernel(const float4* __restrict__ from, float4* __re
 // Where each CTA's share of the (tile, source) space starts.  Computed on the host and passed by value so that
 // the kernel reads it with LDCU: everything the source index depends on has to stay in the uniform datapath
 // (an in-kernel division would land in vector registers and turn every LDCU of the window into an LDC).
-constexpr int kMaxGrid = 148 * 8 + 16;
+constexpr int kMaxGrid = 148 * 12 + 16;
 struct ShareTable {
     int tile[kMaxGrid];          // first tile of CTA c
-    unsigned q_way[kMaxGrid];    // first source QUAD inside that tile | (partial row set of that first segment << 16)
+    // first source QUAD inside that tile (9 bits) | partial row set of that first segment << 9 (7 bits) |
+    // CTAs sharing the tile the share BEGINS in << 16 (8 bits) | CTAs sharing the tile it ENDS in << 24 (8 bits).
+    // One word on purpose: a third table read per CTA made ptxas give up the uniform datapath (see the note below).
+    unsigned q_way[kMaxGrid];
+};
+
+// What a single-launch call does with a finished segment (fused != 0): a tile covered by ONE segment goes straight
+// through the epilogue; a cut tile's segments store their partial rows, and whichever CTA arrives last at the
+// tile's counter sums the rows of all ways IN WAY ORDER (so the result does not depend on who is last) and applies
+// the epilogue.  Counters live in a per-device buffer that is all zero between calls (the last arriver resets).
+struct FusedFix {
+    int enabled;
+    int* counters;
+    PairEpilogue ep;
 };
 
 // One launch: the window slot at float offset win_off (4 n_q sources) x all target tiles.  CTA c owns per_q quads of the flattened
@@ -108,7 +123,8 @@ struct ShareTable {
 // became an LDC.64 (tests/test_abi.py::test_window_kernel_reads_sources_through_uniform_registers guards this).
 template <bool kPotential, int TP>
 __global__ void __launch_bounds__(kUBlock, (TP >= 4 ? 3 : (TP == 2 ? 5 : 8)))
-upairs_kernel(const __grid_constant__ ShareTable tab, int win_q, int n_q, int m_tiles, int per_q, UTargets T, float eps, float* __restrict__ part, int64_t way_stride) {
+upairs_kernel(const __grid_constant__ ShareTable tab, int win_q, int n_q, int m_tiles, int per_q, UTargets T,
+              float eps, float* __restrict__ part, int64_t way_stride, const __grid_constant__ FusedFix fix) {
     constexpr int ST = Win<kPotential>::kStride;
     constexpr int kFold = Win<kPotential>::kFold;
     constexpr int NC = kPotential ? 1 : 3;
@@ -120,11 +136,16 @@ upairs_kernel(const __grid_constant__ ShareTable tab, int win_q, int n_q, int m_
     // all source positions in QUADS (4 sources; n_q and the table): lets ptxas prove the alignment of the
     // LDCU.64 window reads, and keeps shifts / divisions out of the kernel
     int tile = tab.tile[blockIdx.x];
-    int q_first = (int)(tab.q_way[blockIdx.x] & 0xffffu);
+    int q_first = (int)(tab.q_way[blockIdx.x] & 0x1ffu);
     // which partial row set: the number of CTA boundaries between the start of the tile and the segment; later
     // segments of this CTA start their tile, i.e. way 0
-    int way = (int)(tab.q_way[blockIdx.x] >> 16);
+    int way = (int)((tab.q_way[blockIdx.x] >> 9) & 0x7fu);
     int left = per_q;                                 // quads this CTA still owns
+    // CTAs sharing the tile this segment lies in (meaningful for cut tiles only): the share's first tile now, the
+    // tile it ends in for every later segment
+    int n_ways = (int)((tab.q_way[blockIdx.x] >> 16) & 0xffu);
+    const int n_ways_end = (int)(tab.q_way[blockIdx.x] >> 24);
+    __shared__ int s_is_last;
 
     while (left > 0 && tile < m_tiles) {
         int q_last = q_first + left;
@@ -228,26 +249,91 @@ upairs_kernel(const __grid_constant__ ShareTable tab, int win_q, int n_q, int m_
             }
         }
 
-        // accumulate into this segment's partial row set (zeroed at the start of the call)
         float* rows = part + (int64_t)way * way_stride;
+        if (!fix.enabled) {
+            // several launches share the row sets: accumulate (zeroed at the start of the call)
 #pragma unroll
-        for (int j = 0; j < TP; ++j) {
-            float ex[2], ey[2], ez[2];
-            unpack2(tx[j], ex[0], ex[1]);
-            unpack2(ty[j], ey[0], ey[1]);
-            unpack2(tz[j], ez[0], ez[1]);
+            for (int j = 0; j < TP; ++j) {
+                float ex[2], ey[2], ez[2];
+                unpack2(tx[j], ex[0], ex[1]);
+                unpack2(ty[j], ey[0], ey[1]);
+                unpack2(tz[j], ez[0], ez[1]);
 #pragma unroll
-            for (int h = 0; h < 2; ++h) {
-                const int64_t m = tile_base + (int64_t)(2 * j + h) * kUBlock + tid;
-                if (m >= T.M) continue;
-                float* o = rows + m * NC;
-                if (kPotential) {
-                    o[0] += ex[h];
-                } else {
-                    o[0] += ex[h]; o[1] += ey[h]; o[2] += ez[h];
+                for (int h = 0; h < 2; ++h) {
+                    const int64_t m = tile_base + (int64_t)(2 * j + h) * kUBlock + tid;
+                    if (m >= T.M) continue;
+                    float* o = rows + m * NC;
+                    if (kPotential) {
+                        o[0] += ex[h];
+                    } else {
+                        o[0] += ex[h]; o[1] += ey[h]; o[2] += ez[h];
+                    }
                 }
             }
+        } else {
+            const bool whole = q_first == 0 && q_last == n_q;
+            if (!whole) {
+#pragma unroll
+                for (int j = 0; j < TP; ++j) {
+                    float ex[2], ey[2], ez[2];
+                    unpack2(tx[j], ex[0], ex[1]);
+                    unpack2(ty[j], ey[0], ey[1]);
+                    unpack2(tz[j], ez[0], ez[1]);
+#pragma unroll
+                    for (int h = 0; h < 2; ++h) {
+                        const int64_t m = tile_base + (int64_t)(2 * j + h) * kUBlock + tid;
+                        if (m >= T.M) continue;
+                        float* o = rows + m * NC;
+                        if (kPotential) {
+                            __stcg(o, ex[h]);
+                        } else {
+                            __stcg(o, ex[h]); __stcg(o + 1, ey[h]); __stcg(o + 2, ez[h]);
+                        }
+                    }
+                }
+                __threadfence();
+                __syncthreads();
+                if (tid == 0) {
+                    const int seen = atomicAdd(fix.counters + tile, 1);
+                    // the last arriver learns the number of row sets through shared memory (0: not last); routing it
+                    // through memory also keeps the table word out of the loop bound below (see the note above)
+                    s_is_last = seen == n_ways - 1 ? n_ways : 0;
+                    if (s_is_last) fix.counters[tile] = 0;             // everyone has arrived: clean for the next call
+                }
+                __syncthreads();
+            }
+            const int n_sum = whole ? 0 : s_is_last;
+            if (whole || n_sum) {
+                if (!whole) __threadfence();
+#pragma unroll
+                for (int j = 0; j < TP; ++j) {
+                    float ex[2], ey[2], ez[2];
+                    unpack2(tx[j], ex[0], ex[1]);
+                    unpack2(ty[j], ey[0], ey[1]);
+                    unpack2(tz[j], ez[0], ez[1]);
+#pragma unroll
+                    for (int h = 0; h < 2; ++h) {
+                        const int64_t m = tile_base + (int64_t)(2 * j + h) * kUBlock + tid;
+                        if (m >= T.M) continue;
+                        const int64_t r = T.tgt_idx ? T.tgt_idx[m] : m;
+                        if (T.tgt_skip && T.tgt_skip[r]) continue;
+                        float vx = ex[h], vy = ey[h], vz = ez[h];
+                        if (!whole) {                                  // fixed order: way 0, 1, ... (L2 reads)
+                            vx = vy = vz = 0.f;
+                            for (int w = 0; w < n_sum; ++w) {
+                                const float* o = part + (int64_t)w * way_stride + m * NC;
+                                vx += __ldcg(o);
+                                if (!kPotential) { vy += __ldcg(o + 1); vz += __ldcg(o + 2); }
+                            }
+                        }
+                        if (kPotential) apply_potential_epilogue(fix.ep, r, vx);
+                        else apply_field_epilogue(fix.ep, r, vx, vy, vz);
+                    }
+                }
+            }
+            __syncthreads();                                           // s_is_last is reused by the next segment
         }
+        n_ways = n_ways_end;
         left -= q_last - q_first;
         ++tile;
         q_first = 0;
@@ -391,6 +477,7 @@ struct DeviceRing {
     bool has_last = false;
     cudaStream_t last_stream = nullptr;
     float* window = nullptr;               // global address of c_window on this device
+    int* counters = nullptr;               // per-tile arrival counters of the fused fix-up, all zero between calls
 
     cudaError_t prepare() {
         if (ready) return cudaSuccess;
@@ -402,6 +489,8 @@ struct DeviceRing {
         if ((e = cudaEventCreateWithFlags(&fork, cudaEventDisableTiming)) != cudaSuccess) return e;
         if ((e = cudaEventCreateWithFlags(&last_done, cudaEventDisableTiming)) != cudaSuccess) return e;
         if ((e = cudaGetSymbolAddress(reinterpret_cast<void**>(&window), c_window)) != cudaSuccess) return e;
+        if ((e = cudaMalloc(reinterpret_cast<void**>(&counters), (size_t)kFixTiles * sizeof(int))) != cudaSuccess) return e;
+        if ((e = cudaMemset(counters, 0, (size_t)kFixTiles * sizeof(int))) != cudaSuccess) return e;
         ready = true;
         return cudaSuccess;
     }
@@ -443,47 +532,52 @@ cudaError_t fill_slot(DeviceRing& ring, int win_off, const float* from, size_t b
 int build_shares(int m_tiles, int n_src, int grid, int per, ShareTable* tab) {
     const int n_q = n_src >> 2, per_q = per >> 2;
     const int64_t total_q = (int64_t)m_tiles * n_q;
+    // CTAs touching tile t: those whose share [c per_q, (c + 1) per_q) meets [t n_q, (t + 1) n_q)
+    auto ctas_of_tile = [&](int64_t t) {
+        const int64_t first = (t * n_q) / per_q, last = ((t + 1) * n_q - 1) / per_q;
+        return (int)(last - first + 1);
+    };
     int max_way = 0;
-    int owner = 0;        // the CTA whose share contains the START of the tile that `begin` lies in
     for (int c = 0; c < grid; ++c) {
         const int64_t begin = (int64_t)c * per_q;
         int64_t end = begin + per_q;
         if (end > total_q) end = total_q;
         const int64_t tile = begin < total_q ? begin / n_q : m_tiles;
-        // a share that starts inside a tile continues it: its way is its distance from the tile's owner
-        const int way = (end > begin && begin != tile * n_q) ? c - owner : 0;
+        // a share that starts inside a tile continues it: its way is its distance from the CTA holding the tile's start
+        const int way = (end > begin && begin != tile * n_q) ? c - (int)((tile * n_q) / per_q) : 0;
         if (way > max_way) max_way = way;
         if (tab) {
             tab->tile[c] = (int)tile;
-            tab->q_way[c] = (unsigned)(begin - tile * n_q) | ((unsigned)way << 16);
+            const int wb = end > begin ? ctas_of_tile(tile) : 1, we = end > begin ? ctas_of_tile((end - 1) / n_q) : 1;
+            tab->q_way[c] = (unsigned)(begin - tile * n_q) | ((unsigned)way << 9) | ((unsigned)wb << 16) | ((unsigned)we << 24);
         }
-        if (end < total_q && end % n_q != 0 && (end / n_q) * n_q >= begin) owner = c;   // c opened the tile `end` is in
     }
     return max_way + 1;
 }
 
 template <bool kPotential, int TP>
-void launch_shares(const UPairPlan& plan, int win_off, const UTargets& T, float eps, float* part, cudaStream_t stream) {
+void launch_shares(const UPairPlan& plan, int win_off, const UTargets& T, float eps, float* part, const FusedFix& fix,
+                   cudaStream_t stream) {
     ShareTable tab;
     build_shares(plan.m_tiles, plan.chunk, plan.grid, plan.per, &tab);
     upairs_kernel<kPotential, TP><<<plan.grid, kUBlock, 0, stream>>>(tab, win_off >> 2, plan.chunk >> 2, plan.m_tiles,
-                                                                      plan.per >> 2, T, eps, part, plan.way_stride);
+                                                                      plan.per >> 2, T, eps, part, plan.way_stride, fix);
 }
 
 // one launch over the slot at win_off: whole tiles (plan.whole_tiles) or equal shares
 void launch_chunk(bool potential, const UPairPlan& plan, int win_off, const UTargets& T, float eps, float* part,
-                  int first, cudaStream_t stream) {
+                  int first, const FusedFix& fix, cudaStream_t stream) {
     if (plan.whole_tiles) {
         if (potential) upairs_tile_kernel<true><<<plan.m_tiles, kUBlock, 0, stream>>>(win_off >> 2, plan.chunk, T, eps, part, first);
         else upairs_tile_kernel<false><<<plan.m_tiles, kUBlock, 0, stream>>>(win_off >> 2, plan.chunk, T, eps, part, first);
         return;
     }
     if (potential) {
-        if (plan.tp == 4) launch_shares<true, 4>(plan, win_off, T, eps, part, stream);
-        else launch_shares<true, 1>(plan, win_off, T, eps, part, stream);
+        if (plan.tp == 4) launch_shares<true, 4>(plan, win_off, T, eps, part, fix, stream);
+        else launch_shares<true, 1>(plan, win_off, T, eps, part, fix, stream);
     } else {
-        if (plan.tp == 4) launch_shares<false, 4>(plan, win_off, T, eps, part, stream);
-        else launch_shares<false, 1>(plan, win_off, T, eps, part, stream);
+        if (plan.tp == 4) launch_shares<false, 4>(plan, win_off, T, eps, part, fix, stream);
+        else launch_shares<false, 1>(plan, win_off, T, eps, part, fix, stream);
     }
 }
 
@@ -549,6 +643,9 @@ UPairPlan make_upair_plan(bool potential, int64_t S, int64_t M, int sm_count) {
         // one full wave of shares; shares shorter than ~48 sources are not worth their prologue
         const int64_t total = (int64_t)p.m_tiles * p.chunk;
         int64_t grid = (int64_t)sm_count * resident;
+        // a call of ONE launch has no neighbour launch to fill its tail: finer shares (5 per SM instead of the 3
+        // resident ones) let the hardware scheduler even out the SMs (tools/ring_probe.py, profiles/README.md r02)
+        if (p.n_chunks == 1 && p.tp == 4) grid = (int64_t)sm_count * 5;
         { const int forced = env_int_u("DNP_RING_GRID", 0); if (forced > 0) grid = forced; }
         if (grid > kMaxGrid) grid = kMaxGrid;
         const int64_t min_share = 48;
@@ -591,19 +688,9 @@ int run_upairs(bool potential, const float* src, int64_t S, int64_t ld_s, const 
     float* packed = reinterpret_cast<float*>(workspace);
     float* partial = reinterpret_cast<float*>(reinterpret_cast<unsigned char*>(workspace) + plan.packed_bytes);
     const int stride = potential ? 6 : 9;
-
-    {
-        const int threads = 256;
-        const unsigned blocks = (unsigned)((plan.S_pad + threads - 1) / threads);
-        if (potential)
-            pack_window_kernel<true><<<blocks, threads, 0, stream>>>(src, S < 0 ? 0 : S, ld_s, src_idx, plan.S_pad, packed);
-        else
-            pack_window_kernel<false><<<blocks, threads, 0, stream>>>(src, S < 0 ? 0 : S, ld_s, src_idx, plan.S_pad, packed);
-        count_launch(1);
-        DNP_CHECK_CUDA(cudaGetLastError());
-        // cut tiles accumulate into zeroed row sets; whole-tile launches store on a lane's first launch instead
-        if (!plan.whole_tiles) DNP_CHECK_CUDA(cudaMemsetAsync(partial, 0, plan.partial_bytes, stream));
-    }
+    // a call of ONE launch is fused: sources are packed straight into the window and cut tiles are summed by their
+    // last-arriving CTA inside the launch -- no staging copy, no zeroing, no reduction pass (DNP_RING_FUSED=0: off)
+    const bool fused = plan.lanes == 1 && !plan.whole_tiles && plan.m_tiles <= kFixTiles && env_int_u("DNP_RING_FUSED", 1) != 0;
 
     const UTargets T{tgt, M, ld_t, ep.tgt_idx, ep.tgt_skip};
     const size_t chunk_bytes = (size_t)plan.chunk * stride * sizeof(float);
@@ -616,11 +703,29 @@ int run_upairs(bool potential, const float* src, int64_t S, int64_t ld_s, const 
         const bool cap = capturing(stream);
         // queue behind the previous user of the window (same stream: already ordered)
         if (!cap && ring.has_last && ring.last_stream != stream) DNP_CHECK_CUDA(cudaStreamWaitEvent(stream, ring.last_done, 0));
+        {
+            const int threads = 256;
+            const unsigned blocks = (unsigned)((plan.S_pad + threads - 1) / threads);
+            float* dst = fused ? ring.window : packed;
+            if (potential)
+                pack_window_kernel<true><<<blocks, threads, 0, stream>>>(src, S < 0 ? 0 : S, ld_s, src_idx, plan.S_pad, dst);
+            else
+                pack_window_kernel<false><<<blocks, threads, 0, stream>>>(src, S < 0 ? 0 : S, ld_s, src_idx, plan.S_pad, dst);
+            count_launch(1);
+            DNP_CHECK_CUDA(cudaGetLastError());
+            // cut tiles of multi-launch calls accumulate into zeroed row sets; whole-tile launches store on a lane's
+            // first launch, fused calls store every segment
+            if (!plan.whole_tiles && !fused) DNP_CHECK_CUDA(cudaMemsetAsync(partial, 0, plan.partial_bytes, stream));
+        }
+        FusedFix fix;
+        fix.enabled = fused ? 1 : 0;
+        fix.counters = ring.counters;
+        fix.ep = ep;
         timer_mark(stream);
         if (plan.lanes == 1) {
-            cudaError_t e = fill_slot(ring, 0, packed, chunk_bytes, stream);
+            cudaError_t e = fused ? cudaSuccess : fill_slot(ring, 0, packed, chunk_bytes, stream);
             if (e != cudaSuccess) rc = cuda_fail(e, "window fill");
-            else launch_chunk(potential, plan, 0, T, eps, partial, 1, stream);
+            else launch_chunk(potential, plan, 0, T, eps, partial, 1, fix, stream);
             count_launch(1);
         } else {
             DNP_CHECK_CUDA(cudaEventRecord(ring.fork, stream));
@@ -630,7 +735,7 @@ int run_upairs(bool potential, const float* src, int64_t S, int64_t ld_s, const 
                 const int win_off = l * plan.slot_floats;
                 cudaError_t e = fill_slot(ring, win_off, packed + (size_t)k * plan.chunk * stride, chunk_bytes, ring.lane[l]);
                 if (e != cudaSuccess) { rc = cuda_fail(e, "window fill"); break; }
-                launch_chunk(potential, plan, win_off, T, eps, partial + (int64_t)l * lane_stride, k < plan.lanes,
+                launch_chunk(potential, plan, win_off, T, eps, partial + (int64_t)l * lane_stride, k < plan.lanes, fix,
                              ring.lane[l]);
             }
             count_launch(plan.n_chunks);
@@ -650,7 +755,7 @@ int run_upairs(bool potential, const float* src, int64_t S, int64_t ld_s, const 
             ring.last_stream = stream;
         }
     }
-    if (rc != DNP_OK) return rc;
+    if (rc != DNP_OK || fused) return rc;
     return run_split_reduce(potential, partial, plan.lanes * plan.ways, M, ep, stream, plan.way_stride);
 }
 

@@ -218,11 +218,12 @@ def field_apply(sources, targets, eps, mode, out=None, ld_out=None, normals=None
     return out
 
 
-def field_grad(sources, targets, eps=1e-5, out=None, accumulate=False):
+def field_grad(sources, targets, eps=1e-5, out=None, accumulate=False, nonfinite=None):
+    """nonfinite: optional int32 device counter, incremented by the number of Inf / NaN components zeroed."""
     tgt, _ = _rows(targets, 3, "targets")
     if out is None:
         out = torch.empty(tgt.shape[0], 3, dtype=torch.float32, device=tgt.device)
-    return field_apply(sources, tgt, eps, EPI_ACCUM if accumulate else EPI_STORE, out=out)
+    return field_apply(sources, tgt, eps, EPI_ACCUM if accumulate else EPI_STORE, out=out, nonfinite=nonfinite)
 
 
 def edge_interaction(S_pts, T_pts, eps=1e-5):

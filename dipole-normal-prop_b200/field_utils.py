@@ -21,8 +21,9 @@ Known, documented divergences (DESIGN.md "Parity"):
     zeroes the whole leaf total of that target instead (field_utils.py:53-54), a
     result that depends on its chunking.  Degenerate input only.
   * `recursive` / `max_pts` are accepted and ignored: memory is O(S + M).
-  * the NaN/Inf warnings of field_grad (field_utils.py:110-113) are not printed;
-    non-finite components are zeroed in the kernel epilogue without a host sync.
+  * the NaN/Inf warnings of field_grad (field_utils.py:110-113) are printed only when
+    REPORT_NONFINITE is set (one host sync per call); non-finite components are always
+    zeroed in the kernel epilogue.
 """
 import torch
 import numpy as np
@@ -35,6 +36,10 @@ except Exception:  # reference checkout (or its open3d dependency) not importabl
 import dnp_native as _dn
 
 ALLOW_FLOAT64_CAST = False
+# field_utils.py:110-113 prints how many Inf / NaN components field_grad zeroed, at the price of two host
+# synchronisations per leaf.  Here the count comes from a device counter of the kernel epilogue; reading it is one
+# synchronisation per call, so the warning is opt-in.
+REPORT_NONFINITE = False
 NATIVE_PATCH_LOOP = True      # greedy patch loops behind one native call (dnp_patch_propagate_f32)
 
 _EPS_DEFAULT = 1e-5
@@ -153,7 +158,14 @@ def field_grad(sources, means, eps=1e-5, recursive=True, max_pts=15000):
     s, cast = _check_dtype(sources, "sources")
     m, cast_m = _check_dtype(means, "means")
     if _both_cuda(s, m):
-        out = _dn.field_grad(s, m, eps=eps)
+        if REPORT_NONFINITE:
+            counter = torch.zeros(1, dtype=torch.int32, device=m.device)
+            out = _dn.field_grad(s, m, eps=eps, nonfinite=counter)
+            bad = int(counter.item())
+            if bad:
+                print("warning: %d inf / nan in field_grad" % bad)            # field_utils.py:110-113
+        else:
+            out = _dn.field_grad(s, m, eps=eps)
     else:
         out = _dn.field_grad_host(s, m, eps=eps)
     return out.to(cast) if cast else out

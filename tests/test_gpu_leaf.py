@@ -276,6 +276,23 @@ def test_concurrent_host_threads(fu, orc, dev):
         check_E(got[i].cpu().numpy(), want[i], f"thread {i}")
 
 
+def test_nonfinite_components_are_zeroed_and_reported_on_request(fu, dev, capsys, monkeypatch):
+    """field_utils.py:110-115: Inf / NaN totals are zeroed; the reference prints their count, here on request."""
+    src = cloud(3000, 71)
+    src[5, 3] = float("nan")                       # a NaN moment poisons every target it touches
+    tgt = cloud(500, 72, cols=3)
+    for ring_mode in ("0", "2"):                   # shared-memory kernel and the window kernel (fused epilogue)
+        monkeypatch.setenv("DNP_RING", ring_mode)
+        monkeypatch.setattr(fu, "REPORT_NONFINITE", False)
+        E = fu.field_grad(src.to(dev), tgt.to(dev))
+        assert bool((E == 0).all()) and capsys.readouterr().out == ""
+        monkeypatch.setattr(fu, "REPORT_NONFINITE", True)
+        fu.field_grad(src.to(dev), tgt.to(dev))
+        assert "warning: 1500 inf / nan in field_grad" in capsys.readouterr().out
+        fu.field_grad(cloud(100, 73).to(dev), tgt.to(dev))
+        assert capsys.readouterr().out == ""
+
+
 # ------------------------------------------------------------------ a3 lattice sign test
 def test_lattice_golden(fu, golden, orc, dev):
     g = golden("lattice")

@@ -115,12 +115,15 @@ def test_size_rule_selects_the_window_path(fu, dev, ring):
     assert dn.launch_count() - n0 <= 3
 
 
-def test_epilogues_gathers_and_masks(fu, orc, dev, ring):
-    """Every fused epilogue + src_idx / tgt_idx / tgt_skip through the window path equals the shared-memory path."""
+@pytest.mark.parametrize("n_src", [700, 1700])
+def test_epilogues_gathers_and_masks(fu, orc, dev, ring, n_src):
+    """Every fused epilogue + src_idx / tgt_idx / tgt_skip through the window path equals the shared-memory path.
+    700 sources = one launch (epilogue applied inside the kernel, cut tiles summed by their last CTA);
+    1700 = two launches + the reduction pass."""
     import dnp_native as dn
     g = torch.Generator().manual_seed(61)
     pts = cloud(5000, 62).to(dev)
-    src_idx = torch.randperm(5000, generator=g)[:1700].to(dev)
+    src_idx = torch.randperm(5000, generator=g)[:n_src].to(dev)
     tgt_idx = torch.randperm(5000, generator=g)[:2900].to(dev)
     skip = (torch.rand(5000, generator=g) < 0.3).to(dev)
     results = {}
@@ -215,6 +218,40 @@ def test_call_is_asynchronous_and_captures_into_a_cuda_graph(fu, orc, dev, ring)
         torch.cuda.synchronize()
         assert torch.equal(E, want)
     check_E(E.cpu().numpy(), orc.field_grad(src.cpu().numpy(), tgt.cpu().numpy()), "graph replay")
+
+
+@pytest.mark.parametrize("S,M", [(500, 9001), (896, 300000), (640, 40000)])
+def test_single_launch_calls_fused_fixup(fu, orc, dev, ring, monkeypatch, S, M):
+    """One-launch calls: cut tiles are summed in way order by whichever CTA arrives last, so the result is
+    bit-identical to the unfused path (zeroed rows + reduction pass), run after run, also through a CUDA graph
+    (the arrival counters clean themselves up)."""
+    import dnp_native as dn
+    src, tgt = cloud(S, 21).to(dev), cloud(M, 22, cols=3).to(dev)
+    ring(2)
+    n0 = dn.launch_count()
+    E = fu.field_grad(src, tgt)
+    assert dn.launch_count() - n0 == 2                      # pack into the window + ONE kernel
+    for _ in range(3):
+        assert torch.equal(fu.field_grad(src, tgt), E)
+    phi = fu.potential(src, tgt)
+    monkeypatch.setenv("DNP_RING_FUSED", "0")
+    n0 = dn.launch_count()
+    assert torch.equal(fu.field_grad(src, tgt), E)
+    assert dn.launch_count() - n0 == 3                      # pack, kernel, reduction pass
+    assert torch.equal(fu.potential(src, tgt), phi)
+    monkeypatch.delenv("DNP_RING_FUSED")
+    if M <= 40000:
+        check_E(E.cpu().numpy(), orc.field_grad(src.cpu().numpy(), tgt.cpu().numpy()), "fused")
+    out = torch.empty(M, 3, device=dev)
+    torch.cuda.synchronize()
+    graph = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(graph):
+        dn.field_grad(src, tgt, out=out)
+    for _ in range(3):
+        out.zero_()
+        graph.replay()
+        torch.cuda.synchronize()
+        assert torch.equal(out, E)
 
 
 # ------------------------------------------------------------------ the benchmarked sizes, unforced
