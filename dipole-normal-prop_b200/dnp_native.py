@@ -533,24 +533,45 @@ def flip_solve(A, B, exact_max_n=FLIP_EXACT_MAX, replicas=None, sweeps=None, see
 
 
 # ------------------------------------------------------------------ text IO + wire format
+class _PinnedStage:
+    """Per-thread pinned host buffer for the text in / text out copies (reused between calls: pinning 125 MB costs
+    more than copying it)."""
+    _local = __import__("threading").local()
+
+    @classmethod
+    def get(cls, nbytes):
+        buf = getattr(cls._local, "buf", None)
+        if buf is None or buf.numel() < nbytes:
+            buf = torch.empty(max(int(nbytes), 1 << 20), dtype=torch.uint8).pin_memory()
+            cls._local.buf = buf
+        return buf
+
+
 def xyz_parse(text_bytes, device=None):
-    """util.xyz2tensor's parse on the device.  text_bytes: bytes / bytearray / uint8 tensor with the file's content.
-    Returns (rows [n, 6] float32 CUDA tensor, column mask, first unparsable line or -1, number of lines)."""
+    """util.xyz2tensor's parse on the device.  text_bytes: bytes / bytearray / memoryview / uint8 tensor with the
+    file's content.  Returns (rows [n, 6] float32 CUDA tensor, column mask, first unparsable line or -1, number of
+    lines).  Host side: ONE copy of the text into a reused pinned buffer, one asynchronous upload; the lines are
+    counted on the device (no Python pass over the text)."""
+    import warnings
     lib = load()
     require_cuda()
-    if isinstance(text_bytes, torch.Tensor):
-        host = text_bytes
-        n_lines = int((host == 10).sum().item()) + 1
-    else:
-        n_lines = text_bytes.count(b"\n") + 1
-        host = torch.frombuffer(bytearray(text_bytes), dtype=torch.uint8) if len(text_bytes) else \
-            torch.empty(0, dtype=torch.uint8)
     dev = torch.device(device) if device is not None else torch.device("cuda", torch.cuda.current_device())
-    txt = host.to(dev, non_blocking=False)
+    if isinstance(text_bytes, torch.Tensor):
+        txt = text_bytes.to(dev, non_blocking=True)
+    elif len(text_bytes) == 0:
+        txt = torch.empty(0, dtype=torch.uint8, device=dev)
+    else:
+        with warnings.catch_warnings():
+            warnings.simplefilter("ignore")                 # read-only buffer: it is only read
+            view = torch.frombuffer(memoryview(text_bytes), dtype=torch.uint8)
+        stage = _PinnedStage.get(view.numel())[:view.numel()]
+        stage.copy_(view)
+        txt = stage.to(dev, non_blocking=True)
     n_bytes = txt.numel()
-    out = torch.empty(n_lines, 6, dtype=torch.float32, device=dev)
-    counts = torch.empty(4, dtype=torch.int64, device=dev)
     with torch.cuda.device(dev):
+        n_lines = int((txt == 10).sum().item()) + 1        # also orders the pinned buffer's reuse after the upload
+        out = torch.empty(n_lines, 6, dtype=torch.float32, device=dev)
+        counts = torch.empty(4, dtype=torch.int64, device=dev)
         nbytes = lib.dnp_xyz_parse_workspace_bytes(n_bytes, n_lines)
         if nbytes == 0:
             raise DipoleError("xyz parse: at most 2 GiB of text per call")
@@ -561,8 +582,10 @@ def xyz_parse(text_bytes, device=None):
     return out[:rows], mask, bad, lines
 
 
-def xyz_format(pc_rows):
-    """util.export_pc's text for a [N, C] float32 CUDA tensor (any strides): returns the bytes."""
+def xyz_format(pc_rows, as_view=False):
+    """util.export_pc's text for a [N, C] float32 CUDA tensor (any strides): returns the bytes, or with as_view a
+    memoryview of this thread's pinned staging buffer (valid until the next text call of the thread; what
+    dnp_util.export_pc writes to the file without another copy)."""
     lib = load()
     if pc_rows.dtype != torch.float32 or not pc_rows.is_cuda or pc_rows.dim() != 2:
         raise TypeError("xyz_format needs a 2-D float32 CUDA tensor")
@@ -580,7 +603,12 @@ def xyz_format(pc_rows):
         ws = torch.empty(nbytes, dtype=torch.uint8, device=dev)
         _check(lib.dnp_xyz_format_f32(_ptr(pc_rows), n, c, pc_rows.stride(0), pc_rows.stride(1), _ptr(out), cap,
                                       _ptr(n_out), _ptr(ws), nbytes, _stream(pc_rows)))
-    return out[:int(n_out.item())].cpu().numpy().tobytes()
+        size = int(n_out.item())
+        stage = _PinnedStage.get(size)[:size]
+        stage.copy_(out[:size], non_blocking=True)
+        torch.cuda.current_stream(dev).synchronize()
+    view = memoryview(stage.numpy())
+    return view if as_view else view.tobytes()
 
 
 def wire_decode(xyz_f64, device=None):

@@ -289,10 +289,10 @@ def xyz2tensor_cuda(txt, append_normals=True, device=None):
     """util.py:53-69 with the result left on the GPU.  `txt`: str or bytes.  Line splitting, the "nan" filter, the
     single-space tokenisation, float() rounding and the float32 cast all happen in dnp_xyz_parse_f32."""
     import dnp_native as _dn
-    raw = txt.encode("utf-8", errors="surrogateescape") if isinstance(txt, str) else bytes(txt)
+    raw = txt.encode("utf-8", errors="surrogateescape") if isinstance(txt, str) else txt
     rows, mask, bad, _ = _dn.xyz_parse(raw, device=device)
     if bad >= 0:
-        line = raw.split(b"\n")[bad].strip()
+        line = bytes(raw).split(b"\n")[bad].strip()
         raise ValueError(f"could not convert string to float in line {bad}: {line[:80]!r}")
     if rows.shape[0] == 0:
         raise RuntimeError("stack expects a non-empty TensorList")             # torch.stack([]) in the reference
@@ -309,20 +309,21 @@ def xyz2tensor(txt, append_normals=True):
     return xyz2tensor_cuda(txt, append_normals).cpu()
 
 
-def export_text(pc):
-    """The text util.export_pc writes for pc [C, N] (it iterates pc.transpose(0, 1)): bytes, no trailing newline."""
+def export_text(pc, as_view=False):
+    """The text util.export_pc writes for pc [C, N] (it iterates pc.transpose(0, 1)): bytes, no trailing newline
+    (as_view: a memoryview of the calling thread's pinned staging buffer instead, see dnp_native.xyz_format)."""
     import dnp_native as _dn
     _dn.require_cuda()
     if pc.dtype != torch.float32:
         raise TypeError(f"export_pc formats float32 clouds (got {pc.dtype})")
     dev = pc.device if pc.is_cuda else torch.device("cuda", torch.cuda.current_device())
-    return _dn.xyz_format(pc.detach().to(dev).transpose(0, 1))
+    return _dn.xyz_format(pc.detach().to(dev).transpose(0, 1), as_view=as_view)
 
 
 def export_pc(pc, dest):
-    """util.py:46-51."""
+    """util.py:46-51.  The text goes from the device to a pinned buffer and from there straight into the file."""
     with open(dest, 'wb+') as file:
-        file.write(export_text(pc))
+        file.write(export_text(pc, as_view=True))
 
 
 def wire_decode(payload, device=None):
