@@ -410,7 +410,7 @@ def ncu_traffic(points):
     """DRAM bytes per launch of the dominant kernel from the committed `ncu --set full` capture (profiles/),
     or None when no capture exists for this size."""
     try:
-        t = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))[f"cpairs_kernel_field_896x{points}"]
+        t = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))[f"upairs_tile_kernel_field_896x{points}"]
         return t["dram_bytes_read"] + t["dram_bytes_write"]
     except (OSError, KeyError, ValueError):
         return None
@@ -537,10 +537,10 @@ def main():
 
     if rank == 0:
         value = world * pairs_per_step * args.steps / (ms_total * 1e-3)
-        # one timed region per step: the fork->join span of the step's chunk launches (dnp_cpairs.cu runs them on
+        # one timed region per step: the fork->join span of the step's chunk launches (dnp_upairs.cu runs them on
         # overlapping lanes, so single-launch durations are not separable; the region is what the events see)
         k_ms = sum(kernel_ms) / max(len(kernel_ms), 1)
-        chunk_launches = ((P + 223) // 224 * 224 + 895) // 896        # blocks of 896 sources (dnp_cpairs.cu)
+        chunk_launches = (P + 895) // 896                             # window slots of 896 sources (dnp_upairs.cu)
         achieved = pairs_per_step * FLOP_PER_PAIR_FIELD / (k_ms * 1e-3) / 1e12
         peak = 2.0 * fma_per_s / 1e12
         nominal = info["sm_count"] * 128 * 2 * info["sm_clock_khz"] * 1e3 / 1e12
@@ -557,8 +557,9 @@ def main():
             "gpu_launches": int(launches),
             "clocks": clocks.summary(),
             "roofline": {
-                "bound": "fp32", "kernel": "dnp::cpairs_kernel<false> (all-pairs field, sources by value in uniform "
-                                           "registers; one launch = 896 sources x all targets)",
+                "bound": "fp32", "kernel": "dnp::upairs_tile_kernel<false> (all-pairs field, sources in uniform registers "
+                                           "fed from the device-filled constant window; one launch = 896 sources x all "
+                                           "targets)",
                 "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak,
                 "peak_source": "measured on this GPU in this process: packed FFMA2 issue microbenchmark "
                                "(dnp_microbench kind 1) x 2 flop; MEASURED_PEAKS.json holds only HBM and bf16 peaks",
@@ -572,7 +573,10 @@ def main():
                 "sfu_peak_gops": sfu_ops / (sfu_ms * 1e-3) / 1e9,
                 "sfu_frac": 2.0 * pairs_per_step / (k_ms * 1e-3) / (sfu_ops / (sfu_ms * 1e-3)),
                 "hbm_algorithmic_gbs": chunk_launches * (P * 12 + 2 * P * 12) / (k_ms * 1e-3) / 1e9,
-                "traffic": ncu_traffic(P)},
+                "traffic": ncu_traffic(P),
+                "traffic_note": "DRAM bytes of ONE launch under ncu, which flushes the caches before it; all 1171 launches "
+                                "of a step move 82 MB in total with warm caches (profiles/r02_dram_warm_summary.txt) "
+                                "against 50 MB algorithmic"},
         }
         if parity is not None:
             line["dist_parity"] = parity
@@ -683,11 +687,13 @@ def extras(dn, field_utils, dev, src, tgt):
     ms = best_ms(lambda: dn.voxel_partition(pc3, 41), 3)
     out["partition_1M_pts_41_parts_ms"] = ms
     out["partition_algorithmic_gbs"] = (1 << 20) * 20 / ms / 1e6        # 12 B/point read + 8 B/point of perm written
+    dnp_util.divide_pc(pc3, 41, min_patch=100)
+    torch.cuda.synchronize()
     t0 = time.perf_counter()
-    idx, cells = dnp_util._divide_pc(pc3[:, :3], 41)
-    merged, _ = dnp_util.merge_nodes(pc3, idx, cells, 100)
+    merged = dnp_util.divide_pc(pc3, 41, min_patch=100)
     torch.cuda.synchronize()
     out["partition_plus_merge_python_api_ms"] = (time.perf_counter() - t0) * 1e3
+    out["partition_patches"] = len(merged)
     out["partition_reference_cpu_s_build_container"] = "5.8 s for 10 000 points at n_part 41 (tests/golden/partition.npz, ok_divide_seconds)"
     # patch-graph flip solve (graph.MIQP): exhaustive walk at 36 patches, annealing at 300
     gq = torch.Generator().manual_seed(99)

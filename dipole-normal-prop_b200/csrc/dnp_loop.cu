@@ -373,6 +373,18 @@ __global__ void loop_cover_kernel(const int64_t* __restrict__ perm, int64_t T, i
     if (atomicExch(flags + r, 1) == 0) atomicAdd(counts, 1);
 }
 
+// rest rows that are ALSO patch (representative) rows: the loop caches every CTA's normals in shared memory once, and
+// a "rest" flip only reaches the cloud in global memory -- with such an overlap a later patch would be scored from
+// stale normals (the reference flips pts[rest_patch] at once, field_utils.py:250-252), so the call is refused
+__global__ void loop_rest_overlap_kernel(const int64_t* __restrict__ rest_perm, int64_t R, int64_t N,
+                                         const int* __restrict__ flags, int* __restrict__ counts) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= R) return;
+    const int64_t r = rest_perm[i];
+    if (r < 0 || r >= N) { atomicAdd(counts + 1, 1); return; }
+    if (flags[r]) atomicAdd(counts + 2, 1);
+}
+
 inline size_t up256(size_t v) { return (v + 255) & ~(size_t)255; }
 
 size_t loop_smem_bytes(int cap_rows, int cap_src, int P) {
@@ -433,7 +445,13 @@ int run_patch_loop_persistent(float* pts, int64_t N, int64_t ld, const int64_t* 
     DNP_CHECK_CUDA(cudaMemsetAsync(counts, 0, 256, stream));
     loop_cover_kernel<<<(unsigned)((T + 255) / 256), 256, 0, stream>>>(perm, T, N, flags, counts);
     count_launch(1);
-    int host_counts[2] = {0, 0};
+    const int64_t R = rest_perm ? rest_offsets_host[P] - rest_offsets_host[0] : 0;
+    if (R > 0) {
+        loop_rest_overlap_kernel<<<(unsigned)((R + 255) / 256), 256, 0, stream>>>(rest_perm + rest_offsets_host[0], R, N,
+                                                                                  flags, counts);
+        count_launch(1);
+    }
+    int host_counts[3] = {0, 0, 0};
     DNP_CHECK_CUDA(cudaMemcpyAsync(host_counts, counts, sizeof(host_counts), cudaMemcpyDeviceToHost, stream));
     DNP_CHECK_CUDA(cudaStreamSynchronize(stream));
     if (host_counts[1] != 0) {
@@ -441,6 +459,7 @@ int run_patch_loop_persistent(float* pts, int64_t N, int64_t ld, const int64_t* 
         return DNP_ERR_INVALID;
     }
     if (host_counts[0] != T) return DNP_OK;                                           // overlapping patches
+    if (host_counts[2] != 0) return DNP_OK;                                           // rest rows among the patch rows
 
     // rest offsets on the device (they arrive on the host): reuse the flags area, no longer needed
     int64_t* rest_off_dev = nullptr;

@@ -109,11 +109,85 @@ def merge_nodes(pts, indices, ijk, min_patch):
     return new_indices, new_ijk
 
 
+def merge_cells(size0, cells, n_part, min_patch):
+    """The sequential merge rule of util.merge_nodes (util.py:448-492) over integer cell ids: size0[c] points in
+    cell c, cells[c] = (i, j, k).  Returns (kept patch ids, members[patch] = its cells in merge order, sizes)."""
+    P0 = len(size0)
+    side = int(n_part) + 4                                           # cell coordinates shifted by 1: neighbours stay >= 0
+    key_of = [((int(c[0]) + 1) * side + (int(c[1]) + 1)) * side + (int(c[2]) + 1) for c in cells]
+    owner = dict(zip(key_of, range(P0)))                             # cell key -> patch currently owning it
+    deltas = [(a * side + b) * side + c for a in (-1, 0, 1) for b in (-1, 0, 1) for c in (-1, 0, 1)]
+    members = [[i] for i in range(P0)]                               # cells of patch i, in merge order
+    size = list(size0)
+    remaining, sweeps = True, 0
+    while remaining and sweeps < 10:                                 # util.py:463-466: at most 10 sweeps
+        remaining = False
+        sweeps += 1
+        for i in range(P0):
+            if members[i] and size[i] < min_patch:
+                best = -1
+                for c in members[i]:
+                    k = key_of[c]
+                    for d in deltas:
+                        j = owner.get(k + d, -1)
+                        if j != i and j > best:                      # find_dij keeps the LAST neighbouring patch
+                            best = j
+                if best != -1:
+                    members[best].extend(members[i])
+                    size[best] += size[i]
+                    for c in members[i]:
+                        owner[key_of[c]] = best
+                    members[i], size[i] = [], 0
+                    if size[best] < min_patch:
+                        remaining = True
+    if sweeps == 10:
+        print('recursive merge failed to merge some patches')
+    kept = [i for i in range(P0) if members[i] and size[i] >= min_patch]
+    return kept, members, size
+
+
+def partition_patches(pc_in: torch.Tensor, n_part: int, ranges=(-1.5, 1.5), min_patch=0, want_ijk=False):
+    """merge_nodes(pc, *_divide_pc(pc[:, :3], n_part), min_patch) -- the patches the pipelines work on -- without
+    materialising one tensor per CELL: the voxel partition stays a CSR on the device, the merge (same sequential
+    rule, util.py:448-492) runs on the host over integer cell ids, and the merged patches are gathered with one
+    device pass.  At --number_parts 41 a 1M-point cloud has several thousand occupied cells but ~1000 patches.
+    Returns the list of per-patch row tensors (and with want_ijk the per-patch lists of cells [i, j, k])."""
+    import numpy as np
+    import dnp_native as _dn
+    _dn.require_cuda()
+    if pc_in.dtype != torch.float32:
+        raise TypeError(f"pc_in must be float32 (got {pc_in.dtype})")
+    dev = pc_in.device if pc_in.is_cuda else torch.device("cuda", torch.cuda.current_device())
+    perm, offsets, ijk = _dn.voxel_partition(pc_in[:, :3].to(dev), n_part, ranges)
+    off = offsets.cpu().numpy()
+    cells = ijk.cpu().numpy().astype(np.int64)
+    P0 = cells.shape[0]
+    if P0 == 0:
+        return ([], []) if want_ijk else []
+    size0 = (off[1:] - off[:-1]).tolist()
+    kept, members, size = merge_cells(size0, cells, n_part, min_patch)
+    if not kept:
+        return ([], []) if want_ijk else []
+    order = np.fromiter((c for i in kept for c in members[i]), dtype=np.int64)
+    counts = torch.from_numpy(np.asarray(size0, dtype=np.int64)[order]).to(dev)
+    starts = offsets[:-1][torch.from_numpy(order).to(dev)]
+    pos = torch.cumsum(counts, 0) - counts
+    total = int(sum(size[i] for i in kept))
+    rep = torch.repeat_interleave(torch.arange(order.shape[0], device=dev), counts, output_size=total)
+    rows = perm[torch.arange(total, device=dev) - pos[rep] + starts[rep]].to(pc_in.device)
+    patches = list(torch.split(rows, [size[i] for i in kept]))
+    if not want_ijk:
+        return patches
+    cells_t = torch.from_numpy(cells)
+    return patches, [[cells_t[c] for c in members[i]] for i in kept]
+
+
 def divide_pc(pc_in: torch.Tensor, n_part: int, ranges=(-1.5, 1.5), min_patch=0):
-    """util.py:338-341 as shipped: the cells of _divide_pc, unmerged (the upstream composition that the pipelines
-    expect is merge_nodes(pc, *_divide_pc(...), min_patch)[0])."""
-    indices, ijk = _divide_pc(pc_in, n_part, ranges, min_patch)
-    return indices
+    """util.divide_pc as the pipelines USE it (orient_pointcloud.py:25-27, orient_large.py:33-35, dipole_api.py:38-40:
+    a list of per-patch row tensors, cloned and indexed): the upstream composition merge_nodes(pc, *_divide_pc(...),
+    min_patch)[0].  The fork's util.py:338-341 returns the unmerged nested cell lists instead, on which those very
+    call sites raise -- there is no working behaviour of the shipped function to keep."""
+    return partition_patches(pc_in, n_part, ranges, min_patch)
 
 
 def install(util_module=None):

@@ -36,6 +36,13 @@ except Exception:  # reference checkout (or its open3d dependency) not importabl
 import dnp_native as _dn
 
 ALLOW_FLOAT64_CAST = False
+# field_utils.py:53-54: a target that coincides with a source makes the reference's LEAF total for that target NaN,
+# which it replaces by 0 -- the target loses the contribution of every source that shares a max_pts-leaf with its twin,
+# a result that depends on the recursive chunking.  The kernels drop only the coincident PAIR (the documented
+# default).  With this switch `potential` reproduces the reference's value on such degenerate inputs: it re-creates
+# the leaf decomposition of `recursive` / `max_pts` and subtracts, for every affected target, the partial sums of the
+# leaves that hold a twin (extra launches only for affected targets).
+REFERENCE_NAN_SEMANTICS = False
 # field_utils.py:110-113 prints how many Inf / NaN components field_grad zeroed, at the price of two host
 # synchronisations per leaf.  Here the count comes from a device counter of the kernel epilogue; reading it is one
 # synchronisation per call, so the warning is opt-in.
@@ -122,9 +129,14 @@ def _csr(idx_list, dev):
 
 
 def _flattest_patch(pts, perm, offsets):
-    """argmin_p |smallest eigenvalue of cov(xyz of patch p)|, first on ties (field_utils.py:230-233,303-306)."""
-    cov = _dn.patch_covariance(pts, perm, offsets).cpu().numpy()
-    lam0 = np.linalg.eigvalsh(cov)[:, 0]
+    """argmin_p |smallest eigenvalue of cov(xyz of patch p)|, first on ties (field_utils.py:230-233,303-306).
+    The covariances come from the device in float64 (fixed order) and are rounded to float32 before a float32
+    `eigh`, the precision util.pca_eigen_values works in (util.py:495-500): on clouds with several exactly planar
+    patches lambda_0 is rounding noise, and its magnitude -- hence the arg-min -- depends on that precision.
+    Known divergence (DESIGN.md "Parity"): the float32 covariance itself is accumulated in another order than
+    `temp.T @ temp`, so between exactly planar patches the start patch can still differ from the reference's."""
+    cov = _dn.patch_covariance(pts, perm, offsets).to(torch.float32).cpu()
+    lam0 = torch.linalg.eigvalsh(cov)[:, 0].numpy()
     return int(np.argmin(np.abs(lam0)))
 
 
@@ -145,11 +157,74 @@ def potential(sources, means, eps=1e-5, recursive=True, max_pts=15000):
     `eps` is unused by the reference as well; `recursive` / `max_pts` are ignored (no chunking needed)."""
     s, cast = _check_dtype(sources, "sources")
     m, cast_m = _check_dtype(means, "means")
-    if _both_cuda(s, m):
+    if REFERENCE_NAN_SEMANTICS:
+        dev = s.device if s.is_cuda else _cuda_device()
+        out = _potential_with_leaf_laundering(s.to(dev), m.to(dev), recursive, max_pts).to(m.device)
+    elif _both_cuda(s, m):
         out = _dn.potential(s, m)
     else:
         out = _dn.potential_host(s, m)
     return out.to(cast) if cast else out
+
+
+def _leaves(S, M, recursive, max_pts):
+    """(source range, target range) of every leaf of the reference's recursion (field_utils.py:23-44)."""
+    todo, out = [(0, S, 0, M)], []
+    while todo:
+        sa, sb, ta, tb = todo.pop()
+        ns, nt = sb - sa, tb - ta
+        split_src = recursive and ns > max_pts and (nt <= max_pts or ns > nt)
+        split_tgt = recursive and not split_src and nt > max_pts
+        if split_src:
+            mid = sa + int(ns / 2)
+            todo += [(sa, mid, ta, tb), (mid, sb, ta, tb)]
+        elif split_tgt:
+            mid = ta + int(nt / 2)
+            todo += [(sa, sb, ta, mid), (sa, sb, mid, tb)]
+        else:
+            out.append((sa, sb, ta, tb))
+    return out
+
+
+def _potential_with_leaf_laundering(s, m, recursive, max_pts):
+    """REFERENCE_NAN_SEMANTICS: the pair-dropping potential minus, per target, the partial sums of the leaves in
+    which one of its coincident sources lies (those leaf totals are NaN -> 0 in the reference)."""
+    phi = _dn.potential(s, m)
+    S, M = s.shape[0], m.shape[0]
+    if S == 0 or M == 0:
+        return phi
+    # exact coordinate coincidences (+0.0 == -0.0, NaN never equal): rows grouped by value
+    xyz = torch.cat([s[:, :3], m[:, :3]], 0) + 0.0
+    finite = ~torch.isnan(xyz).any(dim=1)
+    _, inv = torch.unique(xyz, dim=0, return_inverse=True)
+    src_id, tgt_id = inv[:S], inv[S:]
+    present = torch.zeros(int(inv.max()) + 1, dtype=torch.bool, device=s.device)
+    present[src_id[finite[:S]]] = True
+    hit_t = torch.nonzero(present[tgt_id] & finite[S:]).flatten()
+    if hit_t.numel() == 0:
+        return phi
+    # (target, source) twin pairs: sort the sources by group id once, then look every hit target's group up
+    order = torch.argsort(src_id, stable=True)
+    sorted_ids = src_id[order]
+    lo = torch.searchsorted(sorted_ids, tgt_id[hit_t])
+    hi = torch.searchsorted(sorted_ids, tgt_id[hit_t], right=True)
+    counts = hi - lo
+    t_rep = torch.repeat_interleave(hit_t, counts)
+    pos = torch.arange(int(counts.sum()), device=s.device) - torch.repeat_interleave(torch.cumsum(counts, 0) - counts, counts)
+    s_rep = order[torch.repeat_interleave(lo, counts) + pos]
+    # affected targets are rebuilt leaf by leaf, as the reference sums them: a leaf holding a twin contributes 0
+    phi[hit_t] = 0
+    for sa, sb, ta, tb in _leaves(S, M, bool(recursive), int(max_pts)):
+        rows = hit_t[(hit_t >= ta) & (hit_t < tb)]
+        if rows.numel() == 0:
+            continue
+        twin_here = (t_rep >= ta) & (t_rep < tb) & (s_rep >= sa) & (s_rep < sb)
+        dirty = torch.zeros(M, dtype=torch.bool, device=s.device)
+        dirty[t_rep[twin_here]] = True
+        rows = rows[~dirty[rows]]
+        if rows.numel():
+            phi[rows] += _dn.potential(s[sa:sb], m[rows].contiguous())
+    return phi
 
 
 def field_grad(sources, means, eps=1e-5, recursive=True, max_pts=15000):
@@ -355,7 +430,8 @@ def xie_propagation_points_onbfstree(pts: torch.Tensor, eps, diffuse=False, star
                                      treshold=0.1, times=1, use_pw=False, knn_mask=-1, C=3):
     """field_utils.py:654-709.  `times` BFS orders over the thresholded kNN graph, one propagation chain per order
     (one launch, a cluster per chain), the chains aligned by the flip vote (MIQP on the pairwise disagreement
-    counts), then a per-point majority vote flips pts[:, 3:] in place.  Returns None like the reference."""
+    counts), then a per-point majority vote flips pts[:, 3:] in place.  Returns the per-point flip mask
+    `cnts > times / 2` (bool [N], on pts' device) like the reference (:709)."""
     import graph
     assert times % 2 == 1 and times > 0
     with torch.no_grad():
@@ -383,7 +459,9 @@ def xie_propagation_points_onbfstree(pts: torch.Tensor, eps, diffuse=False, star
         status = torch.as_tensor(status != 0, device=status_all.device)
         aligned = status_all ^ status[None, :]
         cnts = aligned.int().sum(dim=1)
-        pts[(cnts > times / 2).to(pts.device), 3:] *= -1
+        flipped = (cnts > times / 2).to(pts.device)
+        pts[flipped, 3:] *= -1
+    return flipped
 
 
 def _reps_loop_per_call(pts, rep_idx, rest_idx, perm, offsets, start, E, diffuse):

@@ -91,7 +91,8 @@ LAST_STATUS = {}     # informational: objective / bound / status of the calling 
 
 def MIQP(A, B, **solver_options):
     """graph.py:444-470: the x in {0,1}^n maximising cal_loss(x, A, B), as a float64 array; prints the objective
-    like the reference.  n <= 36: exhaustive (optimal).  Larger n: annealing + descent on the GPU; the returned
+    like the reference.  n <= 36: exhaustive, i.e. optimal up to float32 rounding of the energies (the 2^(n-1) walk runs on float32
+    couplings; the best 32 candidates are re-evaluated in double).  Larger n: annealing + descent on the GPU; the returned
     point is optimal whenever it reaches the bound sum_pairs max(A, B) (always the case for an unfrustrated
     patch graph), otherwise the best found (`graph.LAST_STATUS`).  Of the two globally flipped twins, which
     have the same objective, the one flipping fewer patches is returned."""

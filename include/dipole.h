@@ -288,7 +288,8 @@ DNP_API int dnp_voxel_partition_f32(const float* pts, int64_t N, int64_t ld,
  * graph.py:431-442), which the reference hands to Gurobi (gurobipy, unpinned, absent here):
  *     maximise  sum_ij A_ij (1 - (x_i - x_j)^2) + B_ij (x_i - x_j)^2   over x in {0,1}^n.
  * A, B: device float64 [n, n] row-major with row stride ld (the matrices of BidGraph.to_matrix,
- * graph.py:136-152; need not be symmetric).  n <= min(exact_max_n, 40): exhaustive enumeration (optimal);
+ * graph.py:136-152; need not be symmetric).  n <= min(exact_max_n, 40): exhaustive enumeration (optimal up to
+ * float32 rounding of the energies: the walk is float32, its 32 best candidates are re-evaluated in double);
  * larger n (<= 4096): `replicas` annealing chains of `sweeps` sweeps + descent, deterministic in `seed`.
  * x_out[n] (uint8, 1 = flip the patch), obj_out[0] = objective of x_out (double, as cal_loss),
  * obj_out[1] = the bound sum of the larger of A, B per pair; status_out[0] = 1 exhaustive, 2 bound reached

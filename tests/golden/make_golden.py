@@ -408,6 +408,29 @@ def gen_large(fu, util):
     save("large", **out)
 
 
+def gen_potsem(fu, util):
+    """field_utils.potential on targets that coincide with sources (field_utils.py:53-54: the whole LEAF total of
+    such a target becomes NaN -> 0, so the result depends on the max_pts recursion): small cases with several leaves,
+    for the opt-in exact mode of the drop-in (field_utils.REFERENCE_NAN_SEMANTICS)."""
+    g = torch.Generator().manual_seed(2718)
+    out = {}
+    cl = rand_cloud(g, 300)
+    out["self_pc"] = cl
+    for mp in (100, 64, 15000):
+        out[f"self_phi_max{mp}"] = fu.potential(cl, cl, max_pts=mp)
+    src, tgt = rand_cloud(g, 257), rand_cloud(g, 301)
+    hit = torch.randperm(301, generator=g)[:40]
+    tgt[hit, :3] = src[torch.randperm(257, generator=g)[:40], :3]
+    tgt[hit[0], 0] = -0.0
+    src[0, 0] = 0.0                                                    # +0 / -0 coordinates still coincide
+    tgt[hit[0], 1:3] = src[0, 1:3]
+    out["mix_src"], out["mix_tgt"], out["mix_hit"] = src, tgt, hit
+    for mp in (100, 64, 15000):
+        out[f"mix_phi_max{mp}"] = fu.potential(src, tgt, max_pts=mp)
+    out["mix_phi_nonrecursive"] = fu.potential(src, tgt, recursive=False)
+    save("potential_semantics", **out)
+
+
 def gen_signatures(fu, util):
     """Names, parameter names and defaults of every hot-path function, so the
     drop-in's signatures can be compared with the reference's on a box without the reference."""
@@ -728,7 +751,7 @@ def gen_parser(fu, util):
 GENERATORS = {"signatures": gen_signatures, "leaf": gen_leaf, "edge": gen_edge, "transfer": gen_transfer, "lattice": gen_lattice,
               "points": gen_points, "patches": gen_patches, "reps": gen_reps, "xie": gen_xie, "partition": gen_partition,
               "graph": gen_graph, "patchgraph": gen_patchgraph, "textio": gen_textio, "parser": gen_parser,
-              "large": gen_large}
+              "large": gen_large, "potsem": gen_potsem}
 
 if __name__ == "__main__":
     torch.manual_seed(0)

@@ -293,6 +293,32 @@ def test_reps_propagation_golden(fu, golden, dev, tag, diffuse, loop, monkeypatc
     assert np.array_equal(pts[:, :3].cpu().numpy(), g["pc_in"][:, :3])
 
 
+def test_rest_rows_overlapping_other_patches_agree_across_schedules(fu, golden, dev, monkeypatch):
+    """A patch's "rest" rows may include representative rows of ANOTHER, still unvisited patch (the public
+    signature allows it): the reference flips them at once (field_utils.py:250-252) and scores that patch from the
+    flipped normals later.  The persistent kernel caches normals per CTA, so it must refuse such input and the
+    three schedules must still agree."""
+    g = golden("reps_prop")
+    reps = list(zip(_patches(g["rep_perm"], g["rep_off"]), _patches(g["rest_perm"], g["rest_off"])))
+    # every patch's rest additionally contains 5 representative rows of the next patch
+    reps = [(r, torch.cat([q, reps[(i + 1) % len(reps)][0][:5]])) for i, (r, q) in enumerate(reps)]
+    results = {}
+    for loop in ("persistent", "device", "host"):
+        monkeypatch.setattr(fu, "NATIVE_PATCH_LOOP", True)
+        if loop == "persistent":
+            monkeypatch.delenv("DNP_PATCH_LOOP", raising=False)     # default choice: must fall through by itself
+        else:
+            monkeypatch.setenv("DNP_PATCH_LOOP", loop)
+        pts = torch.from_numpy(g["pc_in"].copy()).to(dev)
+        fu.strongest_field_propagation_reps(pts, [(r.to(dev), q.to(dev)) for r, q in reps], diffuse=False)
+        results[loop] = pts[:, 3:].cpu()
+    assert torch.equal(results["persistent"], results["device"]) and torch.equal(results["device"], results["host"])
+    monkeypatch.setenv("DNP_PATCH_LOOP", "persistent")              # forcing it is refused, not silently wrong
+    with pytest.raises(Exception):
+        pts = torch.from_numpy(g["pc_in"].copy()).to(dev)
+        fu.strongest_field_propagation_reps(pts, [(r.to(dev), q.to(dev)) for r, q in reps], diffuse=False)
+
+
 def test_reps_propagation_weights_vs_oracle(fu, golden, orc, dev):
     g = golden("reps_prop")
     reps_np = list(zip([p.numpy() for p in _patches(g["rep_perm"], g["rep_off"])],

@@ -150,8 +150,10 @@ def test_bfstree_vote_matches_reference(golden, dev, times):
     g = golden("graph")
     pts = torch.from_numpy(g["tree_pc"]).to(dev)
     work = pts.clone()
-    assert field_utils.xie_propagation_points_onbfstree(work, 1e-2, diffuse=True, starting_point=0, times=times, k=10,
-                                                        treshold=0.1) is None
+    mask = field_utils.xie_propagation_points_onbfstree(work, 1e-2, diffuse=True, starting_point=0, times=times, k=10,
+                                                        treshold=0.1)
+    assert mask.dtype == torch.bool and mask.shape == (pts.shape[0],) and mask.device == work.device     # :709
+    assert torch.equal(work[mask, 3:], -pts[mask, 3:]) and torch.equal(work[~mask, 3:], pts[~mask, 3:])
     got = work.cpu().numpy()
     want = g[f"tree_result_t{times}"]
     assert np.array_equal(got[:, :3], want[:, :3])

@@ -276,6 +276,39 @@ def test_concurrent_host_threads(fu, orc, dev):
         check_E(got[i].cpu().numpy(), want[i], f"thread {i}")
 
 
+def test_reference_nan_semantics_switch(fu, golden, dev, monkeypatch):
+    """field_utils.py:53-54 on targets that coincide with sources: the reference zeroes the LEAF total, so the value
+    depends on max_pts.  Default: only the pair is dropped (documented divergence); with REFERENCE_NAN_SEMANTICS the
+    reference's values come back for every chunking, exact zeros included."""
+    g = golden("potential_semantics")
+    cl = torch.from_numpy(g["self_pc"]).to(dev)
+    src, tgt = torch.from_numpy(g["mix_src"]).to(dev), torch.from_numpy(g["mix_tgt"]).to(dev)
+    hit = g["mix_hit"]
+    clean = np.setdiff1d(np.arange(301), hit)
+    default = fu.potential(src, tgt).cpu().numpy()
+    check_phi(default[clean], g["mix_phi_max15000"][clean], "default, untouched targets")
+    assert np.abs(default[hit]).min() > 0 and np.all(g["mix_phi_max15000"][hit] == 0)        # the divergence
+    monkeypatch.setattr(fu, "REFERENCE_NAN_SEMANTICS", True)
+    for mp in (100, 64, 15000):
+        got = fu.potential(src, tgt, max_pts=mp).cpu().numpy()
+        want = g[f"mix_phi_max{mp}"]
+        assert np.array_equal(got == 0, want == 0), mp
+        check_phi(got, want, f"mixed max_pts={mp}")
+        got = fu.potential(cl, cl, max_pts=mp).cpu().numpy()
+        want = g[f"self_phi_max{mp}"]
+        assert np.array_equal(got == 0, want == 0), mp
+        check_phi(got, want, f"self max_pts={mp}")
+    got = fu.potential(src, tgt, recursive=False).cpu().numpy()
+    check_phi(got, g["mix_phi_nonrecursive"], "non-recursive")
+    assert np.array_equal(fu.potential(src.cpu(), tgt.cpu(), max_pts=64).numpy() == 0, g["mix_phi_max64"] == 0)
+    # inputs without coincidences are untouched by the switch
+    a, b = cloud(500, 1).to(dev), cloud(400, 2).to(dev)
+    monkeypatch.setattr(fu, "REFERENCE_NAN_SEMANTICS", False)
+    base = fu.potential(a, b)
+    monkeypatch.setattr(fu, "REFERENCE_NAN_SEMANTICS", True)
+    assert torch.equal(fu.potential(a, b), base)
+
+
 def test_nonfinite_components_are_zeroed_and_reported_on_request(fu, dev, capsys, monkeypatch):
     """field_utils.py:110-115: Inf / NaN totals are zeroed; the reference prints their count, here on request."""
     src = cloud(3000, 71)

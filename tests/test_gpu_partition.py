@@ -43,7 +43,14 @@ def test_divide_and_merge_golden(golden, dev, tag, on_gpu):
     merged, mijk = dnp_util.merge_nodes(pc, idx, ijk, min_patch)
     perm, off = csr(merged)
     assert np.array_equal(perm, g[f"{tag}_merged_perm"]) and np.array_equal(off, g[f"{tag}_merged_offsets"])
-    assert len(dnp_util.divide_pc(pc, n_part, min_patch=min_patch)) == len(idx)
+    # the fused path the pipelines call (util.divide_pc): the same merged patches and cells, the reference's order
+    fast, fast_ijk = dnp_util.partition_patches(pc, n_part, min_patch=min_patch, want_ijk=True)
+    perm, off = csr(fast)
+    assert np.array_equal(perm, g[f"{tag}_merged_perm"]) and np.array_equal(off, g[f"{tag}_merged_offsets"])
+    assert np.array_equal(torch.stack([c for sub in fast_ijk for c in sub]).numpy(), g[f"{tag}_merged_ijk"])
+    assert all(p.device == pc.device and p.dtype == torch.int64 for p in fast)
+    again = dnp_util.divide_pc(pc, n_part, min_patch=min_patch)
+    assert len(again) == len(fast) and all(torch.equal(a, b) for a, b in zip(again, fast))
 
 
 @pytest.mark.parametrize("n,n_part", [(1, 1), (7, 2), (1000, 3), (50000, 41), (300000, 255)])

@@ -257,3 +257,19 @@ def test_fast_merge_equals_the_reference_scan(golden, tag):
     assert np.array_equal(p2, g[f"{tag}_merged_perm"]) and np.array_equal(o2, g[f"{tag}_merged_offsets"])
     assert np.array_equal(torch.stack([c for sub in mijk for c in sub]).numpy(), g[f"{tag}_merged_ijk"])
     assert np.array_equal(np.concatenate([[0], np.cumsum([len(s) for s in mijk])]), g[f"{tag}_merged_ijk_offsets"])
+
+
+@pytest.mark.parametrize("tag", ["fandisk", "ok", "hand"])
+def test_integer_cell_merge_equals_the_reference_scan(golden, tag):
+    """dnp_util.merge_cells (the host half of the fused partition_patches path) against the reference's own merge
+    output: same patches, same cell order inside every patch; no GPU."""
+    import dnp_util
+    g = golden("partition")
+    off, ijk = g[f"{tag}_cell_offsets"], g[f"{tag}_cell_ijk"]
+    kept, members, size = dnp_util.merge_cells((off[1:] - off[:-1]).tolist(), ijk, int(g[f"{tag}_n_part"]),
+                                               int(g[f"{tag}_min_patch"]))
+    perm = g[f"{tag}_cell_perm"]
+    rows = np.concatenate([perm[off[c]:off[c + 1]] for i in kept for c in members[i]])
+    assert np.array_equal(rows, g[f"{tag}_merged_perm"])
+    assert np.array_equal(np.concatenate([[0], np.cumsum([size[i] for i in kept])]), g[f"{tag}_merged_offsets"])
+    assert np.array_equal(np.stack([ijk[c] for i in kept for c in members[i]]), g[f"{tag}_merged_ijk"])
