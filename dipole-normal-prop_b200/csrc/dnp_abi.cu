@@ -465,6 +465,15 @@ int dnp_xie_field_f32(const float* src, int64_t S, int64_t ld_s, const float* tg
 
 int64_t dnp_xie_max_n(int knn) { return xie_max_n(knn != 0); }
 
+int dnp_knn_radius2_f64(const float* src, int64_t S, int64_t ld_s, const float* tgt, int64_t M, int64_t ld_t, int k,
+                        double* radius2, void* stream) {
+    DNP_REQUIRE(S >= 0 && M >= 0, "negative size");
+    if (S == 0) return DNP_OK;
+    DNP_REQUIRE(src && tgt && radius2, "null pointer");
+    DNP_REQUIRE(ld_s >= 3 && ld_t >= 3, "row stride too small");
+    return run_knn_radius2(src, S, ld_s, tgt, M, ld_t, k, radius2, (cudaStream_t)stream);
+}
+
 size_t dnp_xie_workspace_bytes(int64_t N, int64_t T) { return xie_workspace_bytes(N, T); }
 
 int dnp_xie_propagate_in_order_f32(const float* pts, int64_t N, int64_t ld, const int64_t* order, int64_t T,

@@ -8,6 +8,7 @@
 // and one host sync per remaining patch per step) and the abs().argmax() at
 // :247,319 by two launches and no host synchronisation.
 #include "dnp_common.cuh"
+#include "dnp_pairmath.cuh"
 #include "dnp_pairs.h"
 #include "dnp_scores.h"
 
@@ -15,25 +16,9 @@ namespace dnp {
 
 namespace {
 
-constexpr int kEdgeThreads = 256;
-constexpr int kEdgeChunk = 512;                   // sources staged per pass (12 KB)
-constexpr float kRsqrtClamp = 1.152921504606847e18f;
-
-// scalar twin of pair_field_x2 (dnp_pairs.cu): same formula, same SFU approximations
-__device__ __forceinline__ void pair_field_scalar(float px, float py, float pz, float nx, float ny, float nz,
-                                                  float qx, float qy, float qz, float eps,
-                                                  float& ax, float& ay, float& az, float& bx, float& by, float& bz) {
-    const float rx = px - qx, ry = py - qy, rz = pz - qz;
-    const float r2 = fmaf(rz, rz, fmaf(ry, ry, rx * rx));
-    const float u = rsqrt_sfu(r2);
-    const float uc = fminf(u, kRsqrtClamp);
-    const float den = fmaf(r2, r2 * u, eps);
-    const float w = fmaxf(rcp_sfu(den), 0.f);
-    const float d = fmaf(nz, rz, fmaf(ny, ry, nx * rx));
-    const float c = (d * w) * (uc * uc);
-    ax = fmaf(w, nx, ax); ay = fmaf(w, ny, ay); az = fmaf(w, nz, az);
-    bx = fmaf(c, rx, bx); by = fmaf(c, ry, by); bz = fmaf(c, rz, bz);
-}
+constexpr int kEdgeThreads = 256;                 // the per-patch reduction kernels below
+constexpr int kEdgeBlock = 128;                   // edge kernel: 128 threads x 2 targets = one 256-target slice per pass
+constexpr int kEdgeChunk = 256;                   // sources staged per pass (48 B each: 12 KB)
 
 __device__ __forceinline__ float block_sum_256(float v, float* warp_part) {
     v = warp_sum(v);
@@ -47,49 +32,76 @@ __device__ __forceinline__ float block_sum_256(float v, float* warp_part) {
     return r;   // valid in warp 0
 }
 
-__global__ void __launch_bounds__(kEdgeThreads)
+// One CTA per edge.  The source patch is staged through shared memory in the all-pairs kernel's packed row layout
+// ([x y z nx | ny nz mx my | mz . . .], m = -3 n) and read back with broadcast LDS.128; a thread owns a target PAIR
+// (rows t and t + 128 of the current 256-target slice) and runs the packed 19-instruction pair arithmetic of
+// dnp_pairmath.cuh.  Warps whose targets are all past the end of the patch skip the arithmetic (they still help
+// staging), so a 1048-row patch costs 4.1 slices of work, not 5.  Fixed-order block reduction, no atomics.
+__global__ void __launch_bounds__(kEdgeBlock)
 edge_interactions_kernel(const float* __restrict__ pts, int64_t ld, const int64_t* __restrict__ perm,
                          const int64_t* __restrict__ offsets, const int64_t* __restrict__ tperm,
                          const int64_t* __restrict__ toffsets, const int64_t* __restrict__ edges, float eps,
                          float* __restrict__ out) {
-    __shared__ float4 s_src[kEdgeChunk * 2];      // [x y z nx] [ny nz 0 0]
+    __shared__ float4 s_src[kEdgeChunk * 3];
     __shared__ float warp_part[32];
     const int64_t e = blockIdx.x;
     const int64_t ps = edges[2 * e], pt = edges[2 * e + 1];
     const int64_t s0 = offsets[ps], ns = offsets[ps + 1] - s0;
     const int64_t t0 = toffsets[pt], nt = toffsets[pt + 1] - t0;
+    const f32x2 eps2 = pack2(eps, eps), zero2 = pack2(0.f, 0.f);
     float total = 0.f;
-    for (int64_t tb = 0; tb < nt; tb += kEdgeThreads) {
-        const int64_t t = tb + threadIdx.x;
-        float qx = 0.f, qy = 0.f, qz = 0.f, tnx = 0.f, tny = 0.f, tnz = 0.f;
-        if (t < nt) {
-            const float* q = pts + tperm[t0 + t] * ld;
-            qx = q[0]; qy = q[1]; qz = q[2]; tnx = q[3]; tny = q[4]; tnz = q[5];
+    for (int64_t tb = 0; tb < nt; tb += 2 * kEdgeBlock) {
+        const int64_t ta = tb + threadIdx.x, tc = ta + kEdgeBlock;
+        float q[2][6] = {{0.f, 0.f, 0.f, 0.f, 0.f, 0.f}, {0.f, 0.f, 0.f, 0.f, 0.f, 0.f}};
+        if (ta < nt) {
+            const float* p = pts + tperm[t0 + ta] * ld;
+#pragma unroll
+            for (int c = 0; c < 6; ++c) q[0][c] = p[c];
         }
-        float ex = 0.f, ey = 0.f, ez = 0.f;
+        if (tc < nt) {
+            const float* p = pts + tperm[t0 + tc] * ld;
+#pragma unroll
+            for (int c = 0; c < 6; ++c) q[1][c] = p[c];
+        }
+        // does this warp own any target of the slice?  (lane 0 holds the warp's smallest row)
+        const bool warp_live = tb + (threadIdx.x & ~31) < nt;
+        const f32x2 qx = pack2(q[0][0], q[1][0]), qy = pack2(q[0][1], q[1][1]), qz = pack2(q[0][2], q[1][2]);
+        f32x2 ex = zero2, ey = zero2, ez = zero2;
         for (int64_t sb = 0; sb < ns; sb += kEdgeChunk) {
             const int n_here = (int)min((int64_t)kEdgeChunk, ns - sb);
             __syncthreads();
-            for (int i = threadIdx.x; i < n_here; i += kEdgeThreads) {
+            for (int i = threadIdx.x; i < n_here; i += kEdgeBlock) {
                 const float* p = pts + perm[s0 + sb + i] * ld;
-                s_src[2 * i] = make_float4(p[0], p[1], p[2], p[3]);
-                s_src[2 * i + 1] = make_float4(p[4], p[5], 0.f, 0.f);
+                float v[6];
+#pragma unroll
+                for (int c = 0; c < 6; ++c) v[c] = p[c];
+                pack_source_row(v, s_src + 3 * i);
             }
             __syncthreads();
-            float ax = 0.f, ay = 0.f, az = 0.f, bx = 0.f, by = 0.f, bz = 0.f;
+            if (warp_live) {
+                f32x2 ax = zero2, ay = zero2, az = zero2;
 #pragma unroll 4
-            for (int i = 0; i < n_here; ++i) {
-                const float4 A = s_src[2 * i], B = s_src[2 * i + 1];
-                pair_field_scalar(A.x, A.y, A.z, A.w, B.x, B.y, qx, qy, qz, eps, ax, ay, az, bx, by, bz);
+                for (int i = 0; i < n_here; ++i) {
+                    const SrcX2 src(s_src[3 * i], s_src[3 * i + 1], s_src[3 * i + 2]);
+                    pair_field_x2(src, qx, qy, qz, eps2, ax, ay, az);
+                }
+                ex = add2(ex, ax); ey = add2(ey, ay); ez = add2(ez, az);
             }
-            ex += fmaf(-3.f, bx, ax); ey += fmaf(-3.f, by, ay); ez += fmaf(-3.f, bz, az);
         }
-        // non-finite field components are zeroed like the leaf does (field_utils.py:110-115): a NaN point makes
-        // the field of every target it touches vanish instead of poisoning the score
-        if (!(fabsf(ex) <= 3.402823466e38f)) ex = 0.f;
-        if (!(fabsf(ey) <= 3.402823466e38f)) ey = 0.f;
-        if (!(fabsf(ez) <= 3.402823466e38f)) ez = 0.f;
-        if (t < nt) total += __fadd_rn(__fadd_rn(__fmul_rn(ex, tnx), __fmul_rn(ey, tny)), __fmul_rn(ez, tnz));
+        float fx[2], fy[2], fz[2];
+        unpack2(ex, fx[0], fx[1]);
+        unpack2(ey, fy[0], fy[1]);
+        unpack2(ez, fz[0], fz[1]);
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            // non-finite field components are zeroed like the leaf does (field_utils.py:110-115): a NaN point makes
+            // the field of every target it touches vanish instead of poisoning the score
+            if (!(fabsf(fx[h]) <= 3.402823466e38f)) fx[h] = 0.f;
+            if (!(fabsf(fy[h]) <= 3.402823466e38f)) fy[h] = 0.f;
+            if (!(fabsf(fz[h]) <= 3.402823466e38f)) fz[h] = 0.f;
+            if ((h == 0 ? ta : tc) < nt)
+                total += __fadd_rn(__fadd_rn(__fmul_rn(fx[h], q[h][3]), __fmul_rn(fy[h], q[h][4])), __fmul_rn(fz[h], q[h][5]));
+        }
     }
     __syncthreads();
     const float r = block_sum_256(total, warp_part);
@@ -214,7 +226,7 @@ int run_edge_interactions_batched(const float* pts, int64_t ld, const int64_t* p
                                   cudaStream_t stream) {
     (void)P;
     if (n_edges <= 0) return DNP_OK;
-    edge_interactions_kernel<<<(unsigned)n_edges, kEdgeThreads, 0, stream>>>(pts, ld, perm, offsets, tgt_perm,
+    edge_interactions_kernel<<<(unsigned)n_edges, kEdgeBlock, 0, stream>>>(pts, ld, perm, offsets, tgt_perm,
                                                                              tgt_offsets, edges, eps, out);
     count_launch(1);
     DNP_CHECK_CUDA(cudaGetLastError());

@@ -100,6 +100,8 @@ int run_patch_lattice_sign(float* pts, int64_t ld, const int64_t* offsets, int64
 int run_xie_matrix(bool field, const float* src, int64_t S, int64_t ld_s, const float* tgt, int64_t M, int64_t ld_t,
                    float C, const double* rad2, float* out, int64_t ld_o, cudaStream_t stream);
 int64_t xie_max_n(bool knn);
+int run_knn_radius2(const float* src, int64_t S, int64_t ld_s, const float* tgt, int64_t M, int64_t ld_t, int k,
+                    double* out, cudaStream_t stream);
 size_t xie_workspace_bytes(int64_t N, int64_t T);
 int run_xie_propagate(const float* pts, int64_t N, int64_t ld, const int64_t* order, int64_t T, float C,
                       const double* rad2, int diffuse, uint8_t* flips, float* inter, void* workspace,

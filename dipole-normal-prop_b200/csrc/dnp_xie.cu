@@ -350,4 +350,59 @@ int run_xie_propagate(const float* pts, int64_t N, int64_t ld, const int64_t* or
     return DNP_OK;
 }
 
+// ---------------------------------------------------------------- k-th neighbour radius (the kNN mask, :447-455)
+// out[s] = squared distance (double, exact differences of the float coordinates: the expression xie_pair tests) from
+// source s to its k-th nearest target.  The reference builds a scipy KD-tree per call; round 1 used torch cdist +
+// topk (S x M doubles materialised in chunks).  Here: one thread per source, targets staged through shared
+// memory, the k smallest distances kept in a per-thread sorted array (insertion only when a candidate beats the
+// current k-th, which becomes rare after the first few hundred targets).  k <= 64.
+namespace {
+constexpr int kKnnThreads = 128;
+constexpr int kKnnTile = 1024;
+constexpr int kKnnMax = 64;
+
+__global__ void __launch_bounds__(kKnnThreads)
+knn_radius2_kernel(const float* __restrict__ src, int64_t S, int64_t ld_s, const float* __restrict__ tgt, int64_t M,
+                   int64_t ld_t, int k, double* __restrict__ out) {
+    __shared__ float st[kKnnTile * 3];
+    const int64_t s = (int64_t)blockIdx.x * kKnnThreads + threadIdx.x;
+    double px = 0.0, py = 0.0, pz = 0.0;
+    if (s < S) { px = src[s * ld_s]; py = src[s * ld_s + 1]; pz = src[s * ld_s + 2]; }
+    double best[kKnnMax];                                 // ascending; best[k - 1] is the current k-th
+#pragma unroll 1
+    for (int i = 0; i < k; ++i) best[i] = 1.0e300;
+    for (int64_t t0 = 0; t0 < M; t0 += kKnnTile) {
+        const int n_here = (int)min((int64_t)kKnnTile, M - t0);
+        __syncthreads();
+        for (int i = threadIdx.x; i < n_here * 3; i += kKnnThreads) st[i] = tgt[(t0 + i / 3) * ld_t + i % 3];
+        __syncthreads();
+        if (s >= S) continue;
+        for (int j = 0; j < n_here; ++j) {
+            const double dx = px - (double)st[3 * j], dy = py - (double)st[3 * j + 1], dz = pz - (double)st[3 * j + 2];
+            const double d2 = __dadd_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)), __dmul_rn(dz, dz));
+            if (d2 < best[k - 1]) {
+                int i = k - 1;
+                while (i > 0 && best[i - 1] > d2) { best[i] = best[i - 1]; --i; }
+                best[i] = d2;
+            }
+        }
+    }
+    if (s < S) out[s] = best[k - 1];
+}
+}  // namespace
+
+int run_knn_radius2(const float* src, int64_t S, int64_t ld_s, const float* tgt, int64_t M, int64_t ld_t, int k,
+                    double* out, cudaStream_t stream) {
+    if (S <= 0) return DNP_OK;
+    if (k < 1 || k > kKnnMax || k > M) {
+        set_error("k must be in [1, min(%d, targets)] (got %d)", kKnnMax, k);
+        return DNP_ERR_INVALID;
+    }
+    knn_radius2_kernel<<<(unsigned)((S + kKnnThreads - 1) / kKnnThreads), kKnnThreads, 0, stream>>>(src, S, ld_s, tgt, M,
+                                                                                               ld_t, k, out);
+    count_launch(1);
+    DNP_CHECK_CUDA(cudaGetLastError());
+    return DNP_OK;
+}
+
 }  // namespace dnp

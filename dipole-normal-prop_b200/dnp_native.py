@@ -47,6 +47,7 @@ SYMBOLS = [
     ("dnp_xie_interaction_f32", _i32, [_vp, _i64, _i64, _vp, _i64, _i64, _f32, _vp, _vp, _i64, _vp]),
     ("dnp_xie_field_f32", _i32, [_vp, _i64, _i64, _vp, _i64, _i64, _f32, _vp, _vp, _i64, _vp]),
     ("dnp_xie_max_n", _i64, [_i32]),
+    ("dnp_knn_radius2_f64", _i32, [_vp, _i64, _i64, _vp, _i64, _i64, _i32, _vp, _vp]),
     ("dnp_xie_workspace_bytes", _sz, [_i64, _i64]),
     ("dnp_xie_propagate_in_order_f32", _i32, [_vp, _i64, _i64, _vp, _i64, _f32, _vp, _i32, _vp, _vp, _vp, _sz, _vp]),
     ("dnp_voxel_partition_workspace_bytes", _sz, [_i64]),
@@ -411,18 +412,20 @@ def patch_lattice_sign(pts, offsets, n=10, flip=True):
     return mean
 
 
-def knn_radius2(sources, targets, k, chunk=2048):
+def knn_radius2(sources, targets, k):
     """Squared distance (float64) from every source to its k-th nearest target: the kNN mask of
-    field_utils.py:447-455 as one radius per source.  Plumbing in torch; exact differences of the float
-    coordinates in double, the same expression the kernels evaluate."""
-    s = sources[:, :3].double()
-    t = targets[:, :3].double()
-    k = min(int(k), t.shape[0])
-    out = torch.empty(s.shape[0], dtype=torch.float64, device=s.device)
-    for a in range(0, s.shape[0], chunk):
-        d = s[a:a + chunk, None, :] - t[None, :, :]
-        d2 = (d[..., 0] * d[..., 0] + d[..., 1] * d[..., 1]) + d[..., 2] * d[..., 2]
-        out[a:a + chunk] = torch.topk(d2, k, dim=1, largest=False).values[:, -1]
+    field_utils.py:447-455 as one radius per source (dnp_knn_radius2_f64; exact differences of the float coordinates in
+    double, the same expression the xie kernels test)."""
+    lib = load()
+    src, ld_s = _rows(sources, 3, "sources")
+    tgt, ld_t = _rows(targets, 3, "targets")
+    k = min(int(k), tgt.shape[0])
+    out = torch.empty(src.shape[0], dtype=torch.float64, device=src.device)
+    if src.shape[0] == 0:
+        return out
+    with torch.cuda.device(src.device):
+        _check(lib.dnp_knn_radius2_f64(_ptr(src), src.shape[0], ld_s, _ptr(tgt), tgt.shape[0], ld_t, k, _ptr(out),
+                                       _stream(src)))
     return out
 
 
@@ -533,20 +536,6 @@ def flip_solve(A, B, exact_max_n=FLIP_EXACT_MAX, replicas=None, sweeps=None, see
 
 
 # ------------------------------------------------------------------ text IO + wire format
-class _PinnedStage:
-    """Per-thread pinned host buffer for the text in / text out copies (reused between calls: pinning 125 MB costs
-    more than copying it)."""
-    _local = __import__("threading").local()
-
-    @classmethod
-    def get(cls, nbytes):
-        buf = getattr(cls._local, "buf", None)
-        if buf is None or buf.numel() < nbytes:
-            buf = torch.empty(max(int(nbytes), 1 << 20), dtype=torch.uint8).pin_memory()
-            cls._local.buf = buf
-        return buf
-
-
 def xyz_parse(text_bytes, device=None):
     """util.xyz2tensor's parse on the device.  text_bytes: bytes / bytearray / memoryview / uint8 tensor with the
     file's content.  Returns (rows [n, 6] float32 CUDA tensor, column mask, first unparsable line or -1, number of
@@ -564,12 +553,10 @@ def xyz_parse(text_bytes, device=None):
         with warnings.catch_warnings():
             warnings.simplefilter("ignore")                 # read-only buffer: it is only read
             view = torch.frombuffer(memoryview(text_bytes), dtype=torch.uint8)
-        stage = _PinnedStage.get(view.numel())[:view.numel()]
-        stage.copy_(view)
-        txt = stage.to(dev, non_blocking=True)
+        txt = view.to(dev)
     n_bytes = txt.numel()
     with torch.cuda.device(dev):
-        n_lines = int((txt == 10).sum().item()) + 1        # also orders the pinned buffer's reuse after the upload
+        n_lines = int((txt == 10).sum().item()) + 1
         out = torch.empty(n_lines, 6, dtype=torch.float32, device=dev)
         counts = torch.empty(4, dtype=torch.int64, device=dev)
         nbytes = lib.dnp_xyz_parse_workspace_bytes(n_bytes, n_lines)
@@ -584,8 +571,7 @@ def xyz_parse(text_bytes, device=None):
 
 def xyz_format(pc_rows, as_view=False):
     """util.export_pc's text for a [N, C] float32 CUDA tensor (any strides): returns the bytes, or with as_view a
-    memoryview of this thread's pinned staging buffer (valid until the next text call of the thread; what
-    dnp_util.export_pc writes to the file without another copy)."""
+    memoryview of the downloaded buffer (what dnp_util.export_pc writes to the file without another copy)."""
     lib = load()
     if pc_rows.dtype != torch.float32 or not pc_rows.is_cuda or pc_rows.dim() != 2:
         raise TypeError("xyz_format needs a 2-D float32 CUDA tensor")
@@ -603,11 +589,8 @@ def xyz_format(pc_rows, as_view=False):
         ws = torch.empty(nbytes, dtype=torch.uint8, device=dev)
         _check(lib.dnp_xyz_format_f32(_ptr(pc_rows), n, c, pc_rows.stride(0), pc_rows.stride(1), _ptr(out), cap,
                                       _ptr(n_out), _ptr(ws), nbytes, _stream(pc_rows)))
-        size = int(n_out.item())
-        stage = _PinnedStage.get(size)[:size]
-        stage.copy_(out[:size], non_blocking=True)
-        torch.cuda.current_stream(dev).synchronize()
-    view = memoryview(stage.numpy())
+        host = out[:int(n_out.item())].cpu().numpy()
+    view = memoryview(host)
     return view if as_view else view.tobytes()
 
 

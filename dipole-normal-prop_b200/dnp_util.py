@@ -385,7 +385,7 @@ def xyz2tensor(txt, append_normals=True):
 
 def export_text(pc, as_view=False):
     """The text util.export_pc writes for pc [C, N] (it iterates pc.transpose(0, 1)): bytes, no trailing newline
-    (as_view: a memoryview of the calling thread's pinned staging buffer instead, see dnp_native.xyz_format)."""
+    (as_view: a memoryview of the downloaded buffer instead, see dnp_native.xyz_format)."""
     import dnp_native as _dn
     _dn.require_cuda()
     if pc.dtype != torch.float32:
@@ -395,7 +395,7 @@ def export_text(pc, as_view=False):
 
 
 def export_pc(pc, dest):
-    """util.py:46-51.  The text goes from the device to a pinned buffer and from there straight into the file."""
+    """util.py:46-51.  The text goes from the device to a host buffer and from there straight into the file."""
     with open(dest, 'wb+') as file:
         file.write(export_text(pc, as_view=True))
 

@@ -259,6 +259,13 @@ DNP_API int dnp_xie_field_f32(const float* src, int64_t S, int64_t ld_s,
  * cluster per chain with the points in shared memory (N <= dnp_xie_max_n()).
  * workspace: dnp_xie_workspace_bytes(N, T) device bytes, only needed with diffuse.            */
 DNP_API int64_t dnp_xie_max_n(int knn);
+
+/* the kNN mask of field_utils.xie_field / xie_intersaction (field_utils.py:447-455: a scipy KD-tree query of the
+ * knn_mask nearest targets per source) as ONE squared radius per source: radius2[s] = squared distance (double, exact
+ * differences of the float coordinates) from source s to its k-th nearest target, 1 <= k <= min(64, M).  The xie
+ * kernels keep a pair iff |R|^2 <= radius2[s].  One thread per source, targets staged through shared memory.       */
+DNP_API int dnp_knn_radius2_f64(const float* src, int64_t S, int64_t ld_s, const float* tgt, int64_t M, int64_t ld_t,
+                        int k, double* radius2, void* stream);
 DNP_API size_t dnp_xie_workspace_bytes(int64_t N, int64_t T);
 DNP_API int dnp_xie_propagate_in_order_f32(const float* pts, int64_t N, int64_t ld,
                                    const int64_t* order, int64_t T,

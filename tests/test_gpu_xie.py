@@ -138,3 +138,22 @@ def test_errors(fu, dev):
     big = int(dn.load().dnp_xie_max_n(0)) + 1
     with pytest.raises(dn.DipoleError):
         dn.xie_propagate_in_order(torch.zeros(big, 6, device=dev), torch.arange(big)[None])
+
+
+@pytest.mark.parametrize("S,M,k", [(1, 1, 1), (300, 257, 16), (5000, 7001, 30), (2049, 1024, 64)])
+def test_knn_radius_kernel(dev, S, M, k):
+    """dnp_knn_radius2_f64 (the kNN mask of field_utils.py:447-455 as one radius per source) against a float64
+    all-distances + sort: exact equality (both take exact differences of the float coordinates in double)."""
+    import dnp_native as dn
+    g = torch.Generator().manual_seed(S + M + k)
+    src, tgt = torch.rand(S, 6, generator=g).float().to(dev), torch.rand(M, 3, generator=g).float().to(dev)
+    if M > 10:
+        tgt[5] = tgt[4]                                             # duplicated targets: ties at the k-th distance
+    got = dn.knn_radius2(src, tgt, k)
+    d = src[:, None, :3].double() - tgt[None, :, :3].double()
+    d2 = (d[..., 0] * d[..., 0] + d[..., 1] * d[..., 1]) + d[..., 2] * d[..., 2]
+    want = torch.sort(d2, dim=1).values[:, min(k, M) - 1]
+    assert torch.equal(got, want)
+    wide = torch.zeros(S, 9, device=dev)
+    wide[:, 2:8] = src
+    assert torch.equal(dn.knn_radius2(wide[:, 2:8], tgt, k), want)   # strided view
