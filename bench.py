@@ -204,6 +204,20 @@ def dist_parity(dn, dist, dnp_dist, dev, rank, world):
     inter = dnp_dist.edge_interactions_sharded(src, perm, offsets, edges)
     one = dn.edge_interactions_batched(src, perm, offsets.to(dev), edges.to(dev))
     checks["edge_interactions_allreduced_within_tolerance"] = bool(((inter - one).abs() <= 2e-4 * one.abs() + 1e-3).all())
+    # the C ABI's own multi-GPU entry points (dnp_comm.cu: NCCL enqueued by the library on the kernels' stream; the
+    # 128-byte id is the only thing that travels through torch.distributed)
+    ident = (dn.comm_unique_id() if rank == 0 else torch.zeros(128, dtype=torch.uint8)).to(dev)
+    dist.broadcast(ident, 0)
+    dn.comm_init(ident.cpu(), rank, world)
+    try:
+        checks["c_abi_field_grad_sharded_equals_dnp_dist"] = bool(torch.equal(dn.field_grad_sharded(src, tgt, gather=True), E_full))
+        abi_inter = dn.edge_interactions_sharded(src, perm, offsets, edges)
+        checks["c_abi_edge_interactions_allreduced"] = bool(((abi_inter - one).abs() <= 2e-4 * one.abs() + 1e-3).all())
+        abi_mean = dn.lattice_mean_potential_sharded(src)
+        checks["c_abi_lattice_mean_sharded"] = bool((abi_mean - want).abs() <= 1e-4 * want.abs())
+        torch.cuda.synchronize()
+    finally:
+        dn.comm_destroy()
     # identical on every rank (all_gather / all_reduce results): compare bit patterns through a MAX and a MIN reduce
     sig = torch.stack([E_full.view(torch.int32).sum(dtype=torch.int64), inter.view(torch.int32).sum(dtype=torch.int64)])
     hi, lo = sig.clone(), sig.clone()

@@ -48,6 +48,14 @@ SYMBOLS = [
     ("dnp_xie_field_f32", _i32, [_vp, _i64, _i64, _vp, _i64, _i64, _f32, _vp, _vp, _i64, _vp]),
     ("dnp_xie_max_n", _i64, [_i32]),
     ("dnp_knn_radius2_f64", _i32, [_vp, _i64, _i64, _vp, _i64, _i64, _i32, _vp, _vp]),
+    ("dnp_comm_unique_id", _i32, [_vp]),
+    ("dnp_comm_init", _i32, [_vp, _i32, _i32]),
+    ("dnp_comm_destroy", _i32, []),
+    ("dnp_comm_rank", _i32, [_vp, _vp]),
+    ("dnp_sharded_workspace_bytes", _sz, [_i64, _i64, _i64, _i64]),
+    ("dnp_field_grad_sharded_f32", _i32, [_vp, _i64, _i64, _vp, _i64, _i64, _f32, _vp, _i64, _i32, _vp, _sz, _vp]),
+    ("dnp_edge_interactions_sharded_f32", _i32, [_vp, _i64, _vp, _vp, _i64, _i64, _vp, _i64, _f32, _vp, _vp, _sz, _vp]),
+    ("dnp_lattice_mean_potential_sharded_f32", _i32, [_vp, _i64, _i64, _i32, _vp, _vp, _sz, _vp]),
     ("dnp_xie_workspace_bytes", _sz, [_i64, _i64]),
     ("dnp_xie_propagate_in_order_f32", _i32, [_vp, _i64, _i64, _vp, _i64, _f32, _vp, _i32, _vp, _vp, _vp, _sz, _vp]),
     ("dnp_voxel_partition_workspace_bytes", _sz, [_i64]),
@@ -653,6 +661,67 @@ def potential_host(sources, targets, device=None, out=None):
     dev = torch.cuda.current_device() if device is None else int(device)
     _check(lib.dnp_potential_host_f32(_ptr(s), s.shape[0], ld_s, _ptr(t), t.shape[0], ld_t, _ptr(out), dev))
     return out
+
+
+# ------------------------------------------------------------------ multi-GPU entry points of the C ABI (dnp_comm.cu)
+def comm_unique_id():
+    """128-byte NCCL id (uint8 CPU tensor) created by the calling rank; hand it to the other ranks by any means."""
+    ident = torch.zeros(128, dtype=torch.uint8)
+    _check(load().dnp_comm_unique_id(_ptr(ident)))
+    return ident
+
+
+def comm_init(ident, rank, world):
+    ident = ident.cpu().contiguous()
+    _check(load().dnp_comm_init(_ptr(ident), int(rank), int(world)))
+
+
+def comm_destroy():
+    _check(load().dnp_comm_destroy())
+
+
+def field_grad_sharded(sources, targets, eps=1e-5, gather=True):
+    """dnp_field_grad_sharded_f32: this rank's block of E (all blocks when gather) -- shard kernels + NCCL exchange on
+    the caller's stream, no torch.distributed involved."""
+    lib = load()
+    src, ld_s = _rows(sources, 6, "sources")
+    tgt, ld_t = _rows(targets, 3, "targets")
+    S, M = src.shape[0], tgt.shape[0]
+    E = torch.zeros(M, 3, dtype=torch.float32, device=tgt.device)
+    with torch.cuda.device(tgt.device):
+        nbytes = lib.dnp_sharded_workspace_bytes(S, M, 0, 0)
+        ws = torch.empty(nbytes, dtype=torch.uint8, device=tgt.device)
+        _check(lib.dnp_field_grad_sharded_f32(_ptr(src), S, ld_s, _ptr(tgt), M, ld_t, float(eps), _ptr(E), 3,
+                                              int(bool(gather)), _ptr(ws), nbytes, _stream(tgt)))
+    return E
+
+
+def edge_interactions_sharded(pts, perm, offsets, edges, eps=1e-5):
+    """dnp_edge_interactions_sharded_f32: per-edge sums with the target patches sliced over the ranks + ONE all-reduce."""
+    lib = load()
+    p, ld = _rows(pts, 6, "pts")
+    dev = p.device
+    perm, offsets, edges = _idx(perm, dev, "perm"), _idx(offsets, dev, "offsets"), _idx(edges, dev, "edges")
+    P, rows = offsets.numel() - 1, perm.numel()
+    out = torch.empty(edges.shape[0], dtype=torch.float32, device=dev)
+    with torch.cuda.device(dev):
+        nbytes = lib.dnp_sharded_workspace_bytes(1, 1, P, rows)
+        ws = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+        _check(lib.dnp_edge_interactions_sharded_f32(_ptr(p), ld, _ptr(perm), _ptr(offsets), P, rows, _ptr(edges),
+                                                     edges.shape[0], float(eps), _ptr(out), _ptr(ws), nbytes, _stream(p)))
+    return out
+
+
+def lattice_mean_potential_sharded(sources, n=10):
+    lib = load()
+    src, ld_s = _rows(sources, 6, "pc")
+    mean = torch.empty((), dtype=torch.float32, device=src.device)
+    with torch.cuda.device(src.device):
+        nbytes = lib.dnp_sharded_workspace_bytes(src.shape[0], n ** 3, 0, 0)
+        ws = torch.empty(nbytes, dtype=torch.uint8, device=src.device)
+        _check(lib.dnp_lattice_mean_potential_sharded_f32(_ptr(src), src.shape[0], ld_s, int(n), _ptr(mean), _ptr(ws),
+                                                          nbytes, _stream(src)))
+    return mean
 
 
 # ------------------------------------------------------------------ measurement helpers

@@ -365,6 +365,37 @@ DNP_API int dnp_profile_end(float* kernel_ms_host, int capacity, int* n_kernels)
  * Returns elapsed ms and the operation count.                                     */
 DNP_API int dnp_microbench(int kind, int iters, float* ms_out, double* ops_out, void* stream);
 
+/* ------------------------------------------------------------------ multi-GPU (dnp_comm.cu)
+ * The reference is single-process, single-device: this block is net-new.  One process per GPU;
+ * the collective is enqueued on the SAME stream as the shard's kernels, so a non-PyTorch host gets the whole sharded
+ * call from one function.  NCCL is loaded at run time (dlopen "libnccl.so.2" or $DNP_NCCL_LIB): single-GPU users never
+ * touch it.  dnp_comm_unique_id: rank 0 creates the 128-byte id and hands it to the other ranks by any means;
+ * dnp_comm_init: every rank, on the device it will compute on; one communicator per process.
+ *   dnp_field_grad_sharded_f32   field_grad (field_utils.py:61-116) with the TARGETS block-sharded (the first M % world
+ *       ranks own one row more), sources replicated: this rank fills its block of E[M, 3]; gather != 0: the blocks are
+ *       exchanged in one NCCL group so that every rank ends with the full array (needs ld_e == 3).
+ *   dnp_edge_interactions_sharded_f32   the per-edge sums of field_edge_calculator (field_utils.py:145-160) with every
+ *       target patch sliced over the ranks and ONE ncclAllReduce(sum) over out[n_edges]; patch_rows = offsets[P].
+ *   dnp_lattice_mean_potential_sharded_f32   measure_mean_potential (field_utils.py:7-9) with the SOURCES sharded
+ *       (1000 nodes are too few to shard) and ONE ncclAllReduce of the scalar.
+ * workspace: dnp_sharded_workspace_bytes(S, M, P, patch_rows) device bytes.                                          */
+DNP_API int dnp_comm_unique_id(void* id128);
+DNP_API int dnp_comm_init(const void* id128, int rank, int world);
+DNP_API int dnp_comm_destroy(void);
+DNP_API int dnp_comm_rank(int* rank, int* world);
+DNP_API size_t dnp_sharded_workspace_bytes(int64_t S, int64_t M, int64_t P, int64_t patch_rows);
+DNP_API int dnp_field_grad_sharded_f32(const float* src, int64_t S, int64_t ld_s,
+                               const float* tgt, int64_t M, int64_t ld_t,
+                               float eps, float* E, int64_t ld_e, int gather,
+                               void* workspace, size_t workspace_bytes, void* stream);
+DNP_API int dnp_edge_interactions_sharded_f32(const float* pts, int64_t ld,
+                                      const int64_t* perm, const int64_t* offsets, int64_t P, int64_t patch_rows,
+                                      const int64_t* edges, int64_t n_edges,
+                                      float eps, float* out,
+                                      void* workspace, size_t workspace_bytes, void* stream);
+DNP_API int dnp_lattice_mean_potential_sharded_f32(const float* src, int64_t S, int64_t ld_s, int n, float* mean_out,
+                                           void* workspace, size_t workspace_bytes, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -49,8 +49,21 @@ def _worker(rank, world, port, out_dir):
     offsets = torch.tensor([0, 400, 401, 1200, 2500, 3010, 20001])
     edges = torch.tensor([[0, 1], [1, 0], [2, 3], [3, 2], [4, 0], [1, 1], [5, 4]])
     w, invw = dnp_dist.edge_scores_sharded(src, perm, offsets, edges)
+    # the same three calls through the C ABI's own multi-GPU entry points (dnp_comm.cu: NCCL on the kernels' stream,
+    # no torch.distributed on the data path); the id travels through the process group only
+    import dnp_native as dn
+    ident = dn.comm_unique_id() if rank == 0 else torch.zeros(128, dtype=torch.uint8)
+    ident_dev = ident.to(dev)
+    dist.broadcast(ident_dev, 0)
+    dn.comm_init(ident_dev.cpu(), rank, world)
+    abi_E = dn.field_grad_sharded(src, tgt, gather=True)
+    abi_inter = dn.edge_interactions_sharded(src, perm, offsets, edges)
+    abi_mean = dn.lattice_mean_potential_sharded(src)
+    torch.cuda.synchronize()
+    dn.comm_destroy()
     torch.save({"E_full": E_full.cpu(), "phi_full": phi_full.cpu(), "E_local": E_local.cpu(), "mean": mean.cpu(),
-                "w": w.cpu(), "range": dnp_dist.shard_range(150003, rank, world)}, os.path.join(out_dir, f"rank{rank}.pt"))
+                "w": w.cpu(), "range": dnp_dist.shard_range(150003, rank, world), "abi_E": abi_E.cpu(),
+                "abi_inter": abi_inter.cpu(), "abi_mean": abi_mean.cpu()}, os.path.join(out_dir, f"rank{rank}.pt"))
     dist.barrier()
     dist.destroy_process_group()
 
@@ -88,6 +101,15 @@ def test_world_size_2_nccl(tmp_path, dev):
         want, _ = field_utils.field_edge_calculator(S, T)
         got = res[0]["w"][e].item()
         assert abs(got - float(want)) <= 2e-4 * abs(float(want)) + 1e-3, (e, got, float(want))
+    # C-ABI multi-GPU entry points: the same shards and kernels, so the gathered field is bit-identical to dnp_dist's
+    assert torch.equal(res[0]["abi_E"], res[0]["E_full"]) and torch.equal(res[1]["abi_E"], res[0]["E_full"])
+    sizes = torch.tensor(offsets[1:]) - torch.tensor(offsets[:-1])
+    e = torch.tensor(edges)
+    w_abi = (res[0]["abi_inter"] * 2) / sizes[e[:, 0]].float() * sizes[e[:, 1]].float()
+    assert torch.equal(res[0]["abi_inter"], res[1]["abi_inter"])
+    assert bool(((w_abi - res[0]["w"]).abs() <= 1e-6 * res[0]["w"].abs() + 1e-6).all())
+    for r in range(world):
+        assert abs(res[r]["abi_mean"].item() - want_mean) <= 1e-4 * abs(want_mean)
     np.save(os.path.join(tmp_path, "ok.npy"), np.zeros(1))
 
 
