@@ -41,6 +41,8 @@ static int invalid(const char* msg) {
 
 using namespace dnp;
 
+#define DNP_STR2(x) #x
+#define DNP_STR(x) DNP_STR2(x)
 #define DNP_REQUIRE(cond, msg) \
     do {                       \
         if (!(cond)) return invalid(msg); \
@@ -51,6 +53,14 @@ extern "C" {
 const char* dnp_last_error(void) { return t_error; }
 
 int dnp_version(void) { return 100; }
+
+#ifndef DNP_SOURCE_HASH
+#define DNP_SOURCE_HASH "unknown"
+#endif
+const char* dnp_build_info(void) {
+    return "libdipole sm_100a sources=" DNP_SOURCE_HASH " nvcc=" DNP_STR(__CUDACC_VER_MAJOR__) "." DNP_STR(__CUDACC_VER_MINOR__)
+           " built=" __DATE__;
+}
 
 int dnp_device_info(int* sm_count, int* sm_clock_khz, int* cc_major, int* cc_minor) {
     int dev = 0;

@@ -23,6 +23,7 @@ _sz = ctypes.c_size_t
 SYMBOLS = [
     ("dnp_last_error", ctypes.c_char_p, []),
     ("dnp_version", _i32, []),
+    ("dnp_build_info", ctypes.c_char_p, []),
     ("dnp_device_info", _i32, [ctypes.POINTER(_i32)] * 4),
     ("dnp_pairs_workspace_bytes", _sz, [_i64, _i64]),
     ("dnp_potential_f32", _i32, [_vp, _i64, _i64, _vp, _vp, _i64, _i64, _vp, _i32, _vp, _sz, _vp]),
@@ -86,8 +87,25 @@ class DipoleError(RuntimeError):
     pass
 
 
+def source_hash():
+    """The hash csrc/Makefile compiles into the library: sha256 over every .cu / .cuh / .h of csrc/ (sorted) and
+    include/dipole.h; None when the sources are not next to the library (an installed copy)."""
+    import glob
+    import hashlib
+    csrc = os.path.join(os.path.dirname(os.path.abspath(__file__)), "csrc")
+    header = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "include", "dipole.h")
+    files = sorted(glob.glob(os.path.join(csrc, "*.cu")) + glob.glob(os.path.join(csrc, "*.cuh")) +
+                   glob.glob(os.path.join(csrc, "*.h")), key=os.path.basename)
+    if not files or not os.path.exists(header):
+        return None
+    h = hashlib.sha256()
+    for f in files + [header]:
+        h.update(open(f, "rb").read())
+    return h.hexdigest()[:16]
+
+
 def load():
-    """Load libdipole.so (once).  Fails loudly if the CUDA extension is missing."""
+    """Load libdipole.so (once).  Fails loudly if the CUDA extension is missing or was built from other sources."""
     global _lib
     if _lib is None:
         with _lock:
@@ -101,6 +119,11 @@ def load():
                     fn = getattr(lib, name)
                     fn.restype = restype
                     fn.argtypes = argtypes
+                want = source_hash()
+                info = lib.dnp_build_info().decode()
+                if want is not None and f"sources={want}" not in info:
+                    raise ImportError(f"{LIB_PATH} was built from other sources ({info}; this tree hashes to {want}): "
+                                      "rebuild it with `make -C dipole-normal-prop_b200/csrc`")
                 _lib = lib
     return _lib
 

@@ -66,6 +66,10 @@ extern "C" {
 
 DNP_API const char* dnp_last_error(void);
 DNP_API int dnp_version(void);
+/* "libdipole sm_100a sources=<16 hex digits> nvcc=<version> built=<date>": the hash covers every .cu / .cuh / .h of
+ * csrc/ plus this header, in sorted order (csrc/Makefile); dnp_native.load() refuses a library whose hash differs from
+ * the source tree it sits in. */
+DNP_API const char* dnp_build_info(void);
 
 /* SM count and clocks of the current device (for roofline arithmetic). */
 DNP_API int dnp_device_info(int* sm_count, int* sm_clock_khz, int* cc_major, int* cc_minor);

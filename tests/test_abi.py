@@ -32,6 +32,19 @@ def test_library_is_built():
     assert os.path.exists(LIB), "build libdipole.so first: python -c 'import __graft_entry__ as g; g.build()'"
 
 
+def test_library_was_built_from_this_source_tree(monkeypatch):
+    """Build provenance: csrc/Makefile compiles a hash of every source into the library; dnp_native.load() refuses a
+    prebuilt libdipole.so whose hash differs from the tree it sits in (the .so is git-ignored but travels to the GPU
+    box with the snapshot)."""
+    import dnp_native
+    info = dnp_native.load().dnp_build_info().decode()
+    assert "sm_100a" in info and f"sources={dnp_native.source_hash()}" in info, info
+    monkeypatch.setattr(dnp_native, "_lib", None)
+    monkeypatch.setattr(dnp_native, "source_hash", lambda: "0123456789abcdef")
+    with pytest.raises(ImportError, match="built from other sources"):
+        dnp_native.load()
+
+
 def test_header_and_exports_agree():
     decl, exp = declared_symbols(), exported_symbols()
     assert len(decl) >= 15
