@@ -6,8 +6,19 @@
 
 namespace dnp {
 
-constexpr float kRsqrtClamp = 1.152921504606847e18f;   // 2^60: clamp^2 is finite (field: c = d w u^2)
-constexpr float kRsqrtClampPhi = 1.099511627776e12f;   // 2^40: clamp^3 is finite (potential: d u^3)
+constexpr float kRsqrtClamp = 1.152921504606847e18f;   // 2^60: clamp^2 is finite (field: t = d u^2)
+// Issue-slot economy (profiles/README.md r02): on B200 a packed FFMA2 / FMUL2 / FADD2 costs TWO issue cycles and every
+// other instruction one, and the all-pairs loops are issue-bound (field: 2 x 19 + 4 MUFU + 4 FMNMX + LDCU = 47 cycles
+// per pair of pairs, measured).  Two of the four FMNMX were only there to turn NaN into 0 on a coincident pair; the
+// two constants below get the same exact zero out of the FMA pipe for free.
+// field: |R|^4 is formed as r2 * r2 + kTinyR4, so that at R = 0 (u = rsqrt(0) = +inf) den = kTinyR4 * inf + eps = +inf
+// and w = rcp(+inf) = +0 exactly, with no 0 * inf NaN to launder.  1e-37 is a normal float; it changes r^4 by less
+// than 1 ulp whenever |R| > 2e-8.
+constexpr float kTinyR4 = 1.0e-37f;
+// potential: r2 is formed as ... + rx * rx + kTinyR2, so that u = rsqrt(r2) stays finite (<= 1e12, u^3 <= 1e36) and a
+// coincident pair adds (n.R) u^3 = 0 * finite = 0 exactly.  1e-24 changes r2 by less than 1 ulp whenever |R| > 4e-9
+// (two distinct float32 coordinates of a unit-box cloud are at least 6e-8 apart away from the origin).
+constexpr float kTinyR2 = 1.0e-24f;
 
 // ------------------------------------------------------------------ per-pair arithmetic, packed
 // one source, broadcast to both halves of every packed operation (ptxas emits the `R.F32` operand form)
@@ -35,10 +46,11 @@ __device__ __forceinline__ void pair_field_x2(const SrcX2& s, f32x2 qx, f32x2 qy
     const float ua = rsqrt_sfu(r2a), ub = rsqrt_sfu(r2b);                 // +inf on a coincident pair
     const f32x2 u = pack2(ua, ub);
     const f32x2 uc = pack2(fminf(ua, kRsqrtClamp), fminf(ub, kRsqrtClamp));
-    const f32x2 den = fma2(mul2(r2, r2), u, eps2);                        // |R|^3 + eps; 0*inf = NaN if R = 0
+    const f32x2 tiny4 = pack2(kTinyR4, kTinyR4);
+    const f32x2 den = fma2(fma2(r2, r2, tiny4), u, eps2);                 // |R|^3 + eps; tiny * inf = +inf if R = 0
     float da, db;
     unpack2(den, da, db);
-    const f32x2 w = pack2(fmaxf(rcp_sfu(da), 0.f), fmaxf(rcp_sfu(db), 0.f));   // NaN -> 0
+    const f32x2 w = pack2(rcp_sfu(da), rcp_sfu(db));                      // rcp(+inf) = +0: a coincident pair adds 0
     const f32x2 d = fma2(s.mz, rz, fma2(s.my, ry, mul2(s.mx, rx)));       // -3 n.R (exactly 0 when R = 0)
     const f32x2 t = mul2(d, mul2(uc, uc));
     const f32x2 vx = fma2(t, rx, s.nx), vy = fma2(t, ry, s.ny), vz = fma2(t, rz, s.nz);
@@ -48,13 +60,14 @@ __device__ __forceinline__ void pair_field_x2(const SrcX2& s, f32x2 qx, f32x2 qy
 // potential: phi += (n.R) / r^3                                         (12 packed FP32 ops)
 __device__ __forceinline__ void pair_potential_x2(const SrcX2& s, f32x2 qx, f32x2 qy, f32x2 qz, f32x2& phi) {
     const f32x2 rx = sub2(s.px, qx), ry = sub2(s.py, qy), rz = sub2(s.pz, qz);
-    const f32x2 r2 = fma2(rz, rz, fma2(ry, ry, mul2(rx, rx)));
+    const f32x2 tiny2 = pack2(kTinyR2, kTinyR2);
+    const f32x2 r2 = fma2(rz, rz, fma2(ry, ry, fma2(rx, rx, tiny2)));
     float r2a, r2b;
     unpack2(r2, r2a, r2b);
-    // coincident pair: n.R is exactly 0 and the clamped rsqrt^3 stays finite, so the pair adds 0
-    const f32x2 uc = pack2(fminf(rsqrt_sfu(r2a), kRsqrtClampPhi), fminf(rsqrt_sfu(r2b), kRsqrtClampPhi));
+    // coincident pair: n.R is exactly 0 and rsqrt(kTinyR2)^3 is finite, so the pair adds 0
+    const f32x2 u = pack2(rsqrt_sfu(r2a), rsqrt_sfu(r2b));
     const f32x2 d = fma2(s.nz, rz, fma2(s.ny, ry, mul2(s.nx, rx)));
-    phi = fma2(d, mul2(mul2(uc, uc), uc), phi);
+    phi = fma2(d, mul2(mul2(u, u), u), phi);
 }
 
 }  // namespace dnp

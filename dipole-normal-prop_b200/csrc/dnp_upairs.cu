@@ -35,6 +35,7 @@
 
 #include "dnp_common.cuh"
 #include "dnp_epilogue.cuh"
+#include "dnp_pairmath.cuh"
 #include "dnp_pairs.h"
 
 namespace dnp {
@@ -47,10 +48,12 @@ constexpr int kSlotFloats = 8064;                  // two slots of 32 256 B ...
 constexpr int kQuarterFloats = 4032;               // ... or four of 16 128 B (more launches in flight for fewer targets)
 constexpr int kMaxSlots = 4;
 constexpr int kFixTiles = 1 << 20;                 // target tiles a fused single-launch call may have (4 MB of counters)
-constexpr float kRsqrtClampU = 1.152921504606847e18f;   // 2^60
-constexpr float kRsqrtClampPhiU = 1.099511627776e12f;   // 2^40
+constexpr float kRsqrtClampU = kRsqrtClamp;         // 2^60 (dnp_pairmath.cuh, with kTinyR4 / kTinyR2)
 
 __constant__ float c_window[kWindowFloats];
+// kTinyR4 / kTinyR2 from the constant bank: as uniform-register operands they cost no vector register (an immediate
+// would be re-materialised with MOVs inside the loop)
+__constant__ float c_tiny[2] = {kTinyR4, kTinyR2};
 
 template <bool kPotential>
 struct Win {
@@ -132,6 +135,8 @@ upairs_kernel(const __grid_constant__ ShareTable tab, int win_q, int n_q, int m_
     const float* __restrict__ win = c_window + 4 * win_q;     // slot offsets in units of 4 floats: 16-byte aligned reads
     const f32x2 zero2 = pack2(0.f, 0.f);
     const f32x2 eps2 = pack2(eps, eps);
+    const float t4 = c_tiny[0], t2 = c_tiny[1];
+    const f32x2 tiny4 = pack2(t4, t4), tiny2 = pack2(t2, t2);
 
     // all source positions in QUADS (4 sources; n_q and the table): lets ptxas prove the alignment of the
     // LDCU.64 window reads, and keeps shifts / divisions out of the kernel
@@ -192,13 +197,12 @@ upairs_kernel(const __grid_constant__ ShareTable tab, int win_q, int n_q, int m_
 #pragma unroll
                         for (int j = 0; j < TP; ++j) {
                             const f32x2 rx = sub2(px2, qx[j]), ry = sub2(py2, qy[j]), rz = sub2(pz2, qz[j]);
-                            const f32x2 r2 = fma2(rz, rz, fma2(ry, ry, mul2(rx, rx)));
+                            const f32x2 r2 = fma2(rz, rz, fma2(ry, ry, fma2(rx, rx, tiny2)));
                             float r2a, r2b;
                             unpack2(r2, r2a, r2b);
-                            const f32x2 uc = pack2(fminf(rsqrt_sfu(r2a), kRsqrtClampPhiU),
-                                                   fminf(rsqrt_sfu(r2b), kRsqrtClampPhiU));
+                            const f32x2 u = pack2(rsqrt_sfu(r2a), rsqrt_sfu(r2b));      // finite: r2 >= kTinyR2
                             const f32x2 d = fma2(nz2, rz, fma2(ny2, ry, mul2(nx2, rx)));
-                            phi[j] = fma2(d, mul2(mul2(uc, uc), uc), phi[j]);
+                            phi[j] = fma2(d, mul2(mul2(u, u), u), phi[j]);
                         }
                     }
                 }
@@ -229,10 +233,10 @@ upairs_kernel(const __grid_constant__ ShareTable tab, int win_q, int n_q, int m_
                             const float ua = rsqrt_sfu(r2a), ub = rsqrt_sfu(r2b);      // +inf on a coincident pair
                             const f32x2 u = pack2(ua, ub);
                             const f32x2 uc = pack2(fminf(ua, kRsqrtClampU), fminf(ub, kRsqrtClampU));
-                            const f32x2 den = fma2(mul2(r2, r2), u, eps2);             // |R|^3 + eps; NaN if R = 0
+                            const f32x2 den = fma2(fma2(r2, r2, tiny4), u, eps2);      // |R|^3 + eps; +inf if R = 0
                             float da, db;
                             unpack2(den, da, db);
-                            const f32x2 w = pack2(fmaxf(rcp_sfu(da), 0.f), fmaxf(rcp_sfu(db), 0.f));   // NaN -> 0
+                            const f32x2 w = pack2(rcp_sfu(da), rcp_sfu(db));           // rcp(+inf) = +0
                             const f32x2 d = fma2(mz2, rz, fma2(my2, ry, mul2(mx2, rx)));   // -3 n.R
                             const f32x2 t = mul2(d, mul2(uc, uc));
                             const f32x2 vx = fma2(t, rx, nx2), vy = fma2(t, ry, ny2), vz = fma2(t, rz, nz2);
@@ -376,6 +380,8 @@ upairs_tile_kernel(int win_q, int n_src, UTargets T, float eps, float* __restric
 
     const f32x2 zero2 = pack2(0.f, 0.f);
     const f32x2 eps2 = pack2(eps, eps);
+    const float t4 = c_tiny[0], t2 = c_tiny[1];
+    const f32x2 tiny4 = pack2(t4, t4), tiny2 = pack2(t2, t2);
     f32x2 tx[TP], ty[TP], tz[TP];
 #pragma unroll
     for (int j = 0; j < TP; ++j) { tx[j] = zero2; ty[j] = zero2; tz[j] = zero2; }
@@ -394,12 +400,12 @@ upairs_tile_kernel(int win_q, int n_src, UTargets T, float eps, float* __restric
 #pragma unroll
                 for (int j = 0; j < TP; ++j) {
                     const f32x2 rx = sub2(px2, qx[j]), ry = sub2(py2, qy[j]), rz = sub2(pz2, qz[j]);
-                    const f32x2 r2 = fma2(rz, rz, fma2(ry, ry, mul2(rx, rx)));
+                    const f32x2 r2 = fma2(rz, rz, fma2(ry, ry, fma2(rx, rx, tiny2)));
                     float r2a, r2b;
                     unpack2(r2, r2a, r2b);
-                    const f32x2 uc = pack2(fminf(rsqrt_sfu(r2a), kRsqrtClampPhiU), fminf(rsqrt_sfu(r2b), kRsqrtClampPhiU));
+                    const f32x2 u = pack2(rsqrt_sfu(r2a), rsqrt_sfu(r2b));              // finite: r2 >= kTinyR2
                     const f32x2 d = fma2(nz2, rz, fma2(ny2, ry, mul2(nx2, rx)));
-                    phi[j] = fma2(d, mul2(mul2(uc, uc), uc), phi[j]);
+                    phi[j] = fma2(d, mul2(mul2(u, u), u), phi[j]);
                 }
             }
 #pragma unroll
@@ -408,11 +414,16 @@ upairs_tile_kernel(int win_q, int n_src, UTargets T, float eps, float* __restric
             f32x2 ax[TP], ay[TP], az[TP];
 #pragma unroll
             for (int j = 0; j < TP; ++j) { ax[j] = ay[j] = az[j] = zero2; }
-#pragma unroll 4
-            for (int s = s0; s < s0 + kFold; ++s) {
-                const float px = win[9 * s], py = win[9 * s + 1], pz = win[9 * s + 2];
-                const float nx = win[9 * s + 3], ny = win[9 * s + 4], nz = win[9 * s + 5];
-                const float mx = win[9 * s + 6], my = win[9 * s + 7], mz = win[9 * s + 8];
+            for (int s = s0; s < s0 + kFold; s += 4) {
+                const float4* wq = reinterpret_cast<const float4*>(win + 9 * s);
+                float v[36];
+#pragma unroll
+                for (int i = 0; i < 9; ++i) { const float4 f = wq[i]; v[4*i] = f.x; v[4*i+1] = f.y; v[4*i+2] = f.z; v[4*i+3] = f.w; }
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                const float px = v[9*k], py = v[9*k + 1], pz = v[9*k + 2];
+                const float nx = v[9*k + 3], ny = v[9*k + 4], nz = v[9*k + 5];
+                const float mx = v[9*k + 6], my = v[9*k + 7], mz = v[9*k + 8];
                 const f32x2 px2 = pack2(px, px), py2 = pack2(py, py), pz2 = pack2(pz, pz);
                 const f32x2 nx2 = pack2(nx, nx), ny2 = pack2(ny, ny), nz2 = pack2(nz, nz);
                 const f32x2 mx2 = pack2(mx, mx), my2 = pack2(my, my), mz2 = pack2(mz, mz);
@@ -425,14 +436,15 @@ upairs_tile_kernel(int win_q, int n_src, UTargets T, float eps, float* __restric
                     const float ua = rsqrt_sfu(r2a), ub = rsqrt_sfu(r2b);
                     const f32x2 u = pack2(ua, ub);
                     const f32x2 uc = pack2(fminf(ua, kRsqrtClampU), fminf(ub, kRsqrtClampU));
-                    const f32x2 den = fma2(mul2(r2, r2), u, eps2);
+                    const f32x2 den = fma2(fma2(r2, r2, tiny4), u, eps2);
                     float da, db;
                     unpack2(den, da, db);
-                    const f32x2 w = pack2(fmaxf(rcp_sfu(da), 0.f), fmaxf(rcp_sfu(db), 0.f));
+                    const f32x2 w = pack2(rcp_sfu(da), rcp_sfu(db));
                     const f32x2 d = fma2(mz2, rz, fma2(my2, ry, mul2(mx2, rx)));
                     const f32x2 t = mul2(d, mul2(uc, uc));
                     const f32x2 vx = fma2(t, rx, nx2), vy = fma2(t, ry, ny2), vz = fma2(t, rz, nz2);
                     ax[j] = fma2(w, vx, ax[j]); ay[j] = fma2(w, vy, ay[j]); az[j] = fma2(w, vz, az[j]);
+                }
                 }
             }
 #pragma unroll
