@@ -110,7 +110,7 @@ int dnp_lattice_mean_potential_f32(const float* src, int64_t S, int64_t ld_s,
     // callers that only want the mean (every pipeline) take the sources-in-registers kernel; DNP_LATTICE_FAST=0 keeps
     // the generic path (A/B measurements)
     const char* fast = getenv("DNP_LATTICE_FAST");
-    if (!phi_opt && !(fast && fast[0] == '0') && workspace && workspace_bytes >= lattice_mean_workspace_bytes())
+    if (!phi_opt && n <= 255 && !(fast && fast[0] == '0') && workspace && workspace_bytes >= lattice_mean_workspace_bytes())
         return run_lattice_mean(src, S, ld_s, n, mean_out, workspace, workspace_bytes, (cudaStream_t)stream);
     if (!workspace || workspace_bytes < need) {
         set_error("workspace too small: need %zu bytes, got %zu", need, workspace_bytes);

@@ -27,7 +27,10 @@ namespace {
 
 constexpr int kLBlock = 128;
 constexpr int kLMaxGrid = 148 * 8 + 16;
-constexpr float kLClamp = 1.099511627776e12f;      // 2^40: clamp^3 is finite
+// r2 is formed as rx * rx + kLTiny + ..., so that rsqrt stays finite (<= 1e12, cubed <= 1e36) and a source exactly on
+// a node adds (n.R) u^3 = 0 * finite = 0 with no clamp instruction (dnp_pairmath.cuh: every non-FMA instruction is an
+// issue cycle; without the two FMNMX the step is purely MUFU-bound)
+constexpr float kLTiny = 1.0e-24f;
 
 struct LatticeTable {
     float c[256];                                  // node coordinate per index, util.py:26-36
@@ -46,6 +49,7 @@ lattice_sum_kernel(const __grid_constant__ LatticeTable tab, const __grid_consta
     const int n = N > 0 ? N : n_rt;
     const int tid = threadIdx.x;
     const f32x2 zero2 = pack2(0.f, 0.f);
+    const f32x2 tiny2 = pack2(tab.c[255], tab.c[255]);          // kLTiny, delivered through the constant bank
     int tile = shares.tile[blockIdx.x];
     int x = shares.x0[blockIdx.x];
     int left = per;                                // (tile, x) items this CTA still owns
@@ -84,9 +88,10 @@ lattice_sum_kernel(const __grid_constant__ LatticeTable tab, const __grid_consta
 #pragma unroll
             for (int j = 0; j < TP; ++j) {
                 const f32x2 rx = sub2(px[j], qx2);                           // R = source - node (field_utils.py:47)
-                rx2[j] = mul2(rx, rx);
+                rx2[j] = fma2(rx, rx, tiny2);
                 dx[j] = mul2(mx[j], rx);
             }
+#pragma unroll 1
             for (int yi = 0; yi < n; ++yi) {
                 const float qy = tab.c[yi];
                 const f32x2 qy2 = pack2(qy, qy);
@@ -111,8 +116,8 @@ lattice_sum_kernel(const __grid_constant__ LatticeTable tab, const __grid_consta
                         const f32x2 d = fma2(mz[j], rz, dxy[j]);
                         float r2a, r2b;
                         unpack2(r2, r2a, r2b);
-                        const f32x2 uc = pack2(fminf(rsqrt_sfu(r2a), kLClamp), fminf(rsqrt_sfu(r2b), kLClamp));
-                        phi[j] = fma2(d, mul2(mul2(uc, uc), uc), phi[j]);
+                        const f32x2 u = pack2(rsqrt_sfu(r2a), rsqrt_sfu(r2b));      // finite: r2 >= kLTiny
+                        phi[j] = fma2(d, mul2(mul2(u, u), u), phi[j]);
                     }
                 }
 #pragma unroll
@@ -155,7 +160,7 @@ size_t lattice_mean_workspace_bytes() { return (size_t)kLMaxGrid * sizeof(float)
 // mean_out[0] = (1 / n^3) sum_nodes sum_sources potential.  workspace: lattice_mean_workspace_bytes().
 int run_lattice_mean(const float* src, int64_t S, int64_t ld_s, int n, float* mean_out, void* workspace,
                      size_t workspace_bytes, cudaStream_t stream) {
-    if (n < 1 || n > 256) {
+    if (n < 1 || n > 255) {
         set_error("lattice side out of range");
         return DNP_ERR_INVALID;
     }
@@ -171,6 +176,7 @@ int run_lattice_mean(const float* src, int64_t S, int64_t ld_s, int n, float* me
         volatile float h = q - 0.5f;
         tab.c[i] = i < n ? h * 2.f : 0.f;
     }
+    tab.c[255] = kLTiny;                               // n <= 255 nodes per axis use the table; the last slot carries the constant
     // few sources: 2 per thread (256-source tiles) so that the tiles x n items cover the machine
     const int sms = sm_count_cached();
     const int tp = S >= (int64_t)sms * 3 * kLBlock * 8 ? 4 : 1;

@@ -86,14 +86,26 @@ def test_window_fill_modes_agree_bitwise(fu, dev, ring, fill):
             assert torch.equal(fu.field_grad(src, tgt), want)
 
 
-def test_coincident_pairs_and_eps(fu, orc, dev, ring):
-    ring(2)
+@pytest.mark.parametrize("shape", [1, 2])
+def test_coincident_pairs_and_eps(fu, orc, dev, ring, shape):
+    """Exact duplicates of targets among the sources (field_utils.py:98-106: such a pair contributes 0).  The
+    whole-tile kernel runs a clamp-free fast fold and repairs a fold that met a duplicate (NaN in its partial sums)
+    by re-running it with the clamped arithmetic: every target of this test takes that repair path once, and a
+    second cloud has duplicates in only a few folds."""
+    ring(2, shape=shape)
     src = cloud(3000, 41)
     tgt = src.clone()[:2000]                      # every target coincides with one source
     for eps in (1e-5, 1e-6, 0.0):
         E = fu.field_grad(src.to(dev), tgt.to(dev), eps=eps).cpu().numpy()
         assert np.isfinite(E).all()
         check_E(E, orc.field_grad(src.numpy(), tgt.numpy(), eps=eps), f"coincident eps={eps}")
+        check_phi(fu.potential(src.to(dev), tgt.to(dev)).cpu().numpy(),
+                  orc.potential(src.numpy(), tgt.numpy(), drop_coincident=True), "coincident potential")
+    few = cloud(5000, 43)
+    tgt2 = cloud(3000, 44)
+    tgt2[[7, 1500, 2999], :3] = few[[4999, 0, 2600], :3]
+    E = fu.field_grad(few.to(dev), tgt2.to(dev)).cpu().numpy()
+    check_E(E, orc.field_grad(few.numpy(), tgt2.numpy()), "a few duplicates")
     one = cloud(1, 5).to(dev)
     assert bool((fu.field_grad(one, one) == 0).all())            # exactly zero, field_utils.py:98-106
     assert bool((fu.potential(one, one) == 0).all())
