@@ -37,6 +37,10 @@ struct SrcX2 {
 };
 
 // field: E += w (n + t R) with w = 1/(r^3+eps), t = (m.R) / r^2, m = -3 n            (19 packed FP32 ops)
+// kSafe = false leaves out the clamp of u: a coincident pair then makes t = 0 * inf = NaN, which poisons the caller's
+// partial sums -- the caller checks them (sums_nonfinite) and re-runs the same sources with kSafe = true, where the
+// pair adds exactly 0.  Duplicates of a target among the sources are rare; the two FMNMX are paid on every pair.
+template <bool kSafe = true>
 __device__ __forceinline__ void pair_field_x2(const SrcX2& s, f32x2 qx, f32x2 qy, f32x2 qz, f32x2 eps2,
                                               f32x2& ax, f32x2& ay, f32x2& az) {
     const f32x2 rx = sub2(s.px, qx), ry = sub2(s.py, qy), rz = sub2(s.pz, qz);
@@ -45,7 +49,7 @@ __device__ __forceinline__ void pair_field_x2(const SrcX2& s, f32x2 qx, f32x2 qy
     unpack2(r2, r2a, r2b);
     const float ua = rsqrt_sfu(r2a), ub = rsqrt_sfu(r2b);                 // +inf on a coincident pair
     const f32x2 u = pack2(ua, ub);
-    const f32x2 uc = pack2(fminf(ua, kRsqrtClamp), fminf(ub, kRsqrtClamp));
+    const f32x2 uc = kSafe ? pack2(fminf(ua, kRsqrtClamp), fminf(ub, kRsqrtClamp)) : u;
     const f32x2 tiny4 = pack2(kTinyR4, kTinyR4);
     const f32x2 den = fma2(fma2(r2, r2, tiny4), u, eps2);                 // |R|^3 + eps; tiny * inf = +inf if R = 0
     float da, db;
@@ -55,6 +59,15 @@ __device__ __forceinline__ void pair_field_x2(const SrcX2& s, f32x2 qx, f32x2 qy
     const f32x2 t = mul2(d, mul2(uc, uc));
     const f32x2 vx = fma2(t, rx, s.nx), vy = fma2(t, ry, s.ny), vz = fma2(t, rz, s.nz);
     ax = fma2(w, vx, ax); ay = fma2(w, vy, ay); az = fma2(w, vz, az);
+}
+
+// true if any of the three partial sums is NaN or Inf (x * 0 is NaN for both)
+__device__ __forceinline__ bool sums_nonfinite(f32x2 ax, f32x2 ay, f32x2 az) {
+    float a, b, chk = 0.f;
+    unpack2(ax, a, b); chk = fmaf(a, 0.f, chk); chk = fmaf(b, 0.f, chk);
+    unpack2(ay, a, b); chk = fmaf(a, 0.f, chk); chk = fmaf(b, 0.f, chk);
+    unpack2(az, a, b); chk = fmaf(a, 0.f, chk); chk = fmaf(b, 0.f, chk);
+    return chk != 0.f;
 }
 
 // potential: phi += (n.R) / r^3                                         (12 packed FP32 ops)

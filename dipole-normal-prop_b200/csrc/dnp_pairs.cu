@@ -179,7 +179,22 @@ pairs_kernel(const float4* __restrict__ packed, int tiles_total, int nsplit,
                 const SrcX2 src(sp[3 * s], sp[3 * s + 1], sp[3 * s + 2]);
 #pragma unroll
                 for (int j = 0; j < TP; ++j)
-                    pair_field_x2(src, qx[j], qy[j], qz[j], eps2, ax[j], ay[j], az[j]);
+                    pair_field_x2<false>(src, qx[j], qy[j], qz[j], eps2, ax[j], ay[j], az[j]);
+            }
+            // clamp-free fast pass; a duplicate of a target in this tile shows up as NaN and the tile is redone
+            bool bad = false;
+#pragma unroll
+            for (int j = 0; j < TP; ++j) bad |= sums_nonfinite(ax[j], ay[j], az[j]);
+            if (__any_sync(0xffffffffu, bad)) {
+#pragma unroll
+                for (int j = 0; j < TP; ++j) { ax[j] = ay[j] = az[j] = zero2; }
+#pragma unroll 2
+                for (int s = 0; s < TS; ++s) {
+                    const SrcX2 src(sp[3 * s], sp[3 * s + 1], sp[3 * s + 2]);
+#pragma unroll
+                    for (int j = 0; j < TP; ++j)
+                        pair_field_x2<true>(src, qx[j], qy[j], qz[j], eps2, ax[j], ay[j], az[j]);
+                }
             }
 #pragma unroll
             for (int j = 0; j < TP; ++j) {               // tile sums folded into the totals

@@ -95,6 +95,65 @@ __global__ void fill_window_kernel(const float4* __restrict__ from, float4* __re
     if (i < n4) to[i] = from[i];
 }
 
+// Field contributions of window sources [s0, s0 + n) (n a multiple of 4) to TP target pairs.
+// kSafe = false: no clamp at all -- a coincident pair (r2 = 0, u = +inf) makes t = (m.R) u^2 = 0 * inf = NaN and
+// poisons that lane's sums, which the caller detects and repairs by re-running the fold with kSafe = true (clamped
+// u: the pair then adds exactly 0).  Coincidences are exact duplicates of a target among the sources: rare, and every
+// FMNMX saved is an issue cycle of the ~45 a pair of pairs costs (dnp_pairmath.cuh).
+template <int TP, bool kSafe>
+__device__ __forceinline__ void field_fold(const float* __restrict__ win, int s0, int n, const f32x2 (&qx)[TP],
+                                           const f32x2 (&qy)[TP], const f32x2 (&qz)[TP], f32x2 eps2, f32x2 tiny4,
+                                           f32x2 (&ax)[TP], f32x2 (&ay)[TP], f32x2 (&az)[TP]) {
+    for (int s = s0; s < s0 + n; s += 4) {
+        const float4* wq = reinterpret_cast<const float4*>(win + 9 * s);
+        float v[36];
+#pragma unroll
+        for (int i = 0; i < 9; ++i) { const float4 f = wq[i]; v[4 * i] = f.x; v[4 * i + 1] = f.y; v[4 * i + 2] = f.z; v[4 * i + 3] = f.w; }
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const float px = v[9 * k], py = v[9 * k + 1], pz = v[9 * k + 2];
+            const float nx = v[9 * k + 3], ny = v[9 * k + 4], nz = v[9 * k + 5];
+            const float mx = v[9 * k + 6], my = v[9 * k + 7], mz = v[9 * k + 8];
+            const f32x2 px2 = pack2(px, px), py2 = pack2(py, py), pz2 = pack2(pz, pz);
+            const f32x2 nx2 = pack2(nx, nx), ny2 = pack2(ny, ny), nz2 = pack2(nz, nz);
+            const f32x2 mx2 = pack2(mx, mx), my2 = pack2(my, my), mz2 = pack2(mz, mz);
+#pragma unroll
+            for (int j = 0; j < TP; ++j) {
+                const f32x2 rx = sub2(px2, qx[j]), ry = sub2(py2, qy[j]), rz = sub2(pz2, qz[j]);
+                const f32x2 r2 = fma2(rz, rz, fma2(ry, ry, mul2(rx, rx)));
+                float r2a, r2b;
+                unpack2(r2, r2a, r2b);
+                const float ua = rsqrt_sfu(r2a), ub = rsqrt_sfu(r2b);              // +inf on a coincident pair
+                const f32x2 u = pack2(ua, ub);
+                const f32x2 uc = kSafe ? pack2(fminf(ua, kRsqrtClampU), fminf(ub, kRsqrtClampU)) : u;
+                const f32x2 den = fma2(fma2(r2, r2, tiny4), u, eps2);              // |R|^3 + eps; +inf if R = 0
+                float da, db;
+                unpack2(den, da, db);
+                const f32x2 w = pack2(rcp_sfu(da), rcp_sfu(db));                   // rcp(+inf) = +0
+                const f32x2 d = fma2(mz2, rz, fma2(my2, ry, mul2(mx2, rx)));       // -3 n.R (exactly 0 when R = 0)
+                const f32x2 t = mul2(d, mul2(uc, uc));
+                const f32x2 vx = fma2(t, rx, nx2), vy = fma2(t, ry, ny2), vz = fma2(t, rz, nz2);
+                ax[j] = fma2(w, vx, ax[j]); ay[j] = fma2(w, vy, ay[j]); az[j] = fma2(w, vz, az[j]);
+            }
+        }
+    }
+}
+
+// true if any of the partial sums is NaN or Inf (x * 0 is NaN for both)
+template <int TP>
+__device__ __forceinline__ bool any_nonfinite(const f32x2 (&ax)[TP], const f32x2 (&ay)[TP], const f32x2 (&az)[TP]) {
+    float chk = 0.f;
+#pragma unroll
+    for (int j = 0; j < TP; ++j) {
+        float a, b;
+        unpack2(ax[j], a, b); chk = fmaf(a, 0.f, chk); chk = fmaf(b, 0.f, chk);
+        unpack2(ay[j], a, b); chk = fmaf(a, 0.f, chk); chk = fmaf(b, 0.f, chk);
+        unpack2(az[j], a, b); chk = fmaf(a, 0.f, chk); chk = fmaf(b, 0.f, chk);
+    }
+    return chk != 0.f;                                                             // NaN != 0
+}
+
+
 // Where each CTA's share of the (tile, source) space starts.  Computed on the host and passed by value so that
 // the kernel reads it with LDCU: everything the source index depends on has to stay in the uniform datapath
 // (an in-kernel division would land in vector registers and turn every LDCU of the window into an LDC).
@@ -213,36 +272,11 @@ upairs_kernel(const __grid_constant__ ShareTable tab, int win_q, int n_q, int m_
                 f32x2 ax[TP], ay[TP], az[TP];
 #pragma unroll
                 for (int j = 0; j < TP; ++j) { ax[j] = ay[j] = az[j] = zero2; }
-                for (int s4 = 4 * f0; s4 < 4 * f1; s4 += 4) {
-                    __builtin_assume((s4 & 3) == 0);
+                field_fold<TP, false>(win, 4 * f0, 4 * (f1 - f0), qx, qy, qz, eps2, tiny4, ax, ay, az);
+                if (__any_sync(0xffffffffu, any_nonfinite<TP>(ax, ay, az))) {    // a duplicate of a target among the sources
 #pragma unroll
-                    for (int k = 0; k < 4; ++k) {
-                        const int s = s4 + k;
-                        const float px = win[ST * s], py = win[ST * s + 1], pz = win[ST * s + 2];
-                        const float nx = win[ST * s + 3], ny = win[ST * s + 4], nz = win[ST * s + 5];
-                        const float mx = win[ST * s + 6], my = win[ST * s + 7], mz = win[ST * s + 8];
-                        const f32x2 px2 = pack2(px, px), py2 = pack2(py, py), pz2 = pack2(pz, pz);
-                        const f32x2 nx2 = pack2(nx, nx), ny2 = pack2(ny, ny), nz2 = pack2(nz, nz);
-                        const f32x2 mx2 = pack2(mx, mx), my2 = pack2(my, my), mz2 = pack2(mz, mz);
-#pragma unroll
-                        for (int j = 0; j < TP; ++j) {
-                            const f32x2 rx = sub2(px2, qx[j]), ry = sub2(py2, qy[j]), rz = sub2(pz2, qz[j]);
-                            const f32x2 r2 = fma2(rz, rz, fma2(ry, ry, mul2(rx, rx)));
-                            float r2a, r2b;
-                            unpack2(r2, r2a, r2b);
-                            const float ua = rsqrt_sfu(r2a), ub = rsqrt_sfu(r2b);      // +inf on a coincident pair
-                            const f32x2 u = pack2(ua, ub);
-                            const f32x2 uc = pack2(fminf(ua, kRsqrtClampU), fminf(ub, kRsqrtClampU));
-                            const f32x2 den = fma2(fma2(r2, r2, tiny4), u, eps2);      // |R|^3 + eps; +inf if R = 0
-                            float da, db;
-                            unpack2(den, da, db);
-                            const f32x2 w = pack2(rcp_sfu(da), rcp_sfu(db));           // rcp(+inf) = +0
-                            const f32x2 d = fma2(mz2, rz, fma2(my2, ry, mul2(mx2, rx)));   // -3 n.R
-                            const f32x2 t = mul2(d, mul2(uc, uc));
-                            const f32x2 vx = fma2(t, rx, nx2), vy = fma2(t, ry, ny2), vz = fma2(t, rz, nz2);
-                            ax[j] = fma2(w, vx, ax[j]); ay[j] = fma2(w, vy, ay[j]); az[j] = fma2(w, vz, az[j]);
-                        }
-                    }
+                    for (int j = 0; j < TP; ++j) { ax[j] = ay[j] = az[j] = zero2; }
+                    field_fold<TP, true>(win, 4 * f0, 4 * (f1 - f0), qx, qy, qz, eps2, tiny4, ax, ay, az);
                 }
 #pragma unroll
                 for (int j = 0; j < TP; ++j) {
@@ -345,64 +379,6 @@ upairs_kernel(const __grid_constant__ ShareTable tab, int win_q, int n_q, int m_
     }
 }
 
-
-// Field contributions of window sources [s0, s0 + n) (n a multiple of 4) to TP target pairs.
-// kSafe = false: no clamp at all -- a coincident pair (r2 = 0, u = +inf) makes t = (m.R) u^2 = 0 * inf = NaN and
-// poisons that lane's sums, which the caller detects and repairs by re-running the fold with kSafe = true (clamped
-// u: the pair then adds exactly 0).  Coincidences are exact duplicates of a target among the sources: rare, and every
-// FMNMX saved is an issue cycle of the ~45 a pair of pairs costs (dnp_pairmath.cuh).
-template <int TP, bool kSafe>
-__device__ __forceinline__ void field_fold(const float* __restrict__ win, int s0, int n, const f32x2 (&qx)[TP],
-                                           const f32x2 (&qy)[TP], const f32x2 (&qz)[TP], f32x2 eps2, f32x2 tiny4,
-                                           f32x2 (&ax)[TP], f32x2 (&ay)[TP], f32x2 (&az)[TP]) {
-    for (int s = s0; s < s0 + n; s += 4) {
-        const float4* wq = reinterpret_cast<const float4*>(win + 9 * s);
-        float v[36];
-#pragma unroll
-        for (int i = 0; i < 9; ++i) { const float4 f = wq[i]; v[4 * i] = f.x; v[4 * i + 1] = f.y; v[4 * i + 2] = f.z; v[4 * i + 3] = f.w; }
-#pragma unroll
-        for (int k = 0; k < 4; ++k) {
-            const float px = v[9 * k], py = v[9 * k + 1], pz = v[9 * k + 2];
-            const float nx = v[9 * k + 3], ny = v[9 * k + 4], nz = v[9 * k + 5];
-            const float mx = v[9 * k + 6], my = v[9 * k + 7], mz = v[9 * k + 8];
-            const f32x2 px2 = pack2(px, px), py2 = pack2(py, py), pz2 = pack2(pz, pz);
-            const f32x2 nx2 = pack2(nx, nx), ny2 = pack2(ny, ny), nz2 = pack2(nz, nz);
-            const f32x2 mx2 = pack2(mx, mx), my2 = pack2(my, my), mz2 = pack2(mz, mz);
-#pragma unroll
-            for (int j = 0; j < TP; ++j) {
-                const f32x2 rx = sub2(px2, qx[j]), ry = sub2(py2, qy[j]), rz = sub2(pz2, qz[j]);
-                const f32x2 r2 = fma2(rz, rz, fma2(ry, ry, mul2(rx, rx)));
-                float r2a, r2b;
-                unpack2(r2, r2a, r2b);
-                const float ua = rsqrt_sfu(r2a), ub = rsqrt_sfu(r2b);              // +inf on a coincident pair
-                const f32x2 u = pack2(ua, ub);
-                const f32x2 uc = kSafe ? pack2(fminf(ua, kRsqrtClampU), fminf(ub, kRsqrtClampU)) : u;
-                const f32x2 den = fma2(fma2(r2, r2, tiny4), u, eps2);              // |R|^3 + eps; +inf if R = 0
-                float da, db;
-                unpack2(den, da, db);
-                const f32x2 w = pack2(rcp_sfu(da), rcp_sfu(db));                   // rcp(+inf) = +0
-                const f32x2 d = fma2(mz2, rz, fma2(my2, ry, mul2(mx2, rx)));       // -3 n.R (exactly 0 when R = 0)
-                const f32x2 t = mul2(d, mul2(uc, uc));
-                const f32x2 vx = fma2(t, rx, nx2), vy = fma2(t, ry, ny2), vz = fma2(t, rz, nz2);
-                ax[j] = fma2(w, vx, ax[j]); ay[j] = fma2(w, vy, ay[j]); az[j] = fma2(w, vz, az[j]);
-            }
-        }
-    }
-}
-
-// true if any of the partial sums is NaN or Inf (x * 0 is NaN for both)
-template <int TP>
-__device__ __forceinline__ bool any_nonfinite(const f32x2 (&ax)[TP], const f32x2 (&ay)[TP], const f32x2 (&az)[TP]) {
-    float chk = 0.f;
-#pragma unroll
-    for (int j = 0; j < TP; ++j) {
-        float a, b;
-        unpack2(ax[j], a, b); chk = fmaf(a, 0.f, chk); chk = fmaf(b, 0.f, chk);
-        unpack2(ay[j], a, b); chk = fmaf(a, 0.f, chk); chk = fmaf(b, 0.f, chk);
-        unpack2(az[j], a, b); chk = fmaf(a, 0.f, chk); chk = fmaf(b, 0.f, chk);
-    }
-    return chk != 0.f;                                                             // NaN != 0
-}
 
 // The same arithmetic with ONE target tile per CTA and the whole slot per CTA (no share table, no cut tiles): the
 // launch shape of calls with many chunks and >= 256 target tiles, where 2 or 4 launches in flight (one per lane)
