@@ -635,6 +635,7 @@ def extras(dn, field_utils, dev, src, tgt):
     out["potential_frac_fp32_nominal"] = P * P / ms * 1e3 * FLOP_PER_PAIR_POTENTIAL / (148 * 128 * 2 * 1.965e9)
     ms = best_ms(lambda: dn.lattice_mean_potential(src))
     out["lattice_test_ms"] = ms
+    out["cfg5_sweep"] = cfg5_sweep(dn, dev)
     out["lattice_pairs_per_s"] = P * 1000 / ms * 1e3
     # streamed sign phase (HBM-bound): 24 B read + 12 B written per point
     big = torch.randn(1 << 24, 6, device=dev)
@@ -791,6 +792,72 @@ def _parse_only(dn, txt_dev, n_lines):
     ws = torch.empty(nbytes, dtype=torch.uint8, device=dev)
     dn._check(lib.dnp_xyz_parse_f32(dn._ptr(txt_dev), txt_dev.numel(), n_lines, dn._ptr(out), n_lines, dn._ptr(counts),
                                     dn._ptr(ws), nbytes, dn._stream(txt_dev)))
+
+
+def cfg5_sweep(dn, dev):
+    """BASELINE config 5 / SURVEY.md section 8(d): the synthetic all-pairs sweep at its other sizes (1M x 1M is the
+    headline), each with the rate, the fraction of the nominal FP32 peak and the error of sampled targets against the
+    same sum evaluated in float64 (torch on the device: a referee for the arithmetic, not the oracle)."""
+    eps = 1e-5
+    rows = []
+    for k, (S, M) in enumerate([(65536, 65536), (262144, 262144), (65536, 4194304), (4194304, 4194304)]):
+        g = torch.Generator().manual_seed(1234 + k)
+        src = torch.rand(S, 6, generator=g) - 0.5
+        src[:, 3:] = torch.nn.functional.normalize(src[:, 3:], dim=1)
+        tgt = torch.rand(M, 3, generator=g) - 0.5
+        src, tgt = src.to(dev), tgt.to(dev)
+        row = {"sources": S, "targets": M}
+        for name, flop in (("field", FLOP_PER_PAIR_FIELD), ("potential", FLOP_PER_PAIR_POTENTIAL)):
+            out = torch.empty((M, 3) if name == "field" else (M,), device=dev)
+            call = (lambda: dn.field_grad(src, tgt, eps=eps, out=out)) if name == "field" else \
+                (lambda: dn.potential(src, tgt, out=out))
+            big = S * M > 4e12
+            if not big:
+                call()
+            best = float("inf")
+            for _ in range(1 if big else 3):
+                torch.cuda.synchronize()
+                a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                a.record()
+                call()
+                b.record()
+                torch.cuda.synchronize()
+                best = min(best, a.elapsed_time(b))
+            rate = S * M / best * 1e3
+            row[name] = {"ms": best, "pairs_per_s": rate, "frac_fp32_nominal": rate * flop / (148 * 128 * 2 * 1.965e9),
+                         "timed_runs": 1 if big else 3}
+            # float64 referee on 64 evenly spaced targets
+            pick = torch.linspace(0, M - 1, 64, device=dev).long()
+            q = tgt[pick].double()
+            ref = torch.zeros((64, 3) if name == "field" else (64,), device=dev, dtype=torch.float64)
+            mag = torch.zeros(64, device=dev, dtype=torch.float64)
+            for c0 in range(0, S, 1 << 19):
+                sc = src[c0:c0 + (1 << 19)].double()
+                R = sc[:, None, :3] - q[None]
+                r = R.norm(dim=-1)
+                n = sc[:, None, 3:]
+                if name == "field":
+                    Ru = torch.where(r[..., None] > 0, R / r[..., None].clamp_min(1e-300), torch.zeros_like(R))
+                    e = (3.0 * (n * Ru).sum(-1, keepdim=True) * Ru - n) / (r ** 3 + eps)[..., None]
+                    e = torch.where(r[..., None] > 0, e, torch.zeros_like(e))
+                    ref -= e.sum(0)
+                else:
+                    ph = torch.where(r > 0, (n * R).sum(-1) / r.clamp_min(1e-300) ** 3, torch.zeros_like(r))
+                    ref += ph.sum(0)
+                    mag += ph.abs().sum(0)
+            got = out[pick].double()
+            if name == "field":
+                err = (got - ref).norm(dim=1) / ref.norm(dim=1).clamp_min(1e-300)
+            else:
+                # the potential of a random cloud passes through 0: scale by the sum of the magnitudes
+                err = (got - ref).abs() / mag.clamp_min(1e-300)
+            row[name]["rel_err_vs_f64_median"] = float(err.median())
+            row[name]["rel_err_vs_f64_max"] = float(err.max())
+            row[name]["rel_err_scale"] = "|E64| per target" if name == "field" else "sum of |phi_s| per target"
+            del out
+        rows.append(row)
+        del src, tgt
+    return rows
 
 
 def surface_cloud(n, seed):

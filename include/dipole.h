@@ -206,8 +206,8 @@ DNP_API int dnp_points_propagate_f32(float* pts, int64_t N, int64_t ld, int64_t 
  * that are exactly the target rows -- checked with one 8-byte read per call) run all P steps inside ONE persistent
  * cooperative kernel (loop state in shared memory, one grid barrier per step).  Otherwise every launch reads its row
  * range from the device-resident winner, all P steps are enqueued without a host read and the call returns after the
- * last launch has been enqueued.  Only when a patch is large enough for the by-value all-pairs kernel (>= 16 384
- * rows, sources are kernel parameters) does the loop read the winner back once per step (8 bytes).  With a trace
+ * last launch has been enqueued.  Only when a patch is large enough for the constant-window all-pairs kernel (>= 16 384
+ * rows; its launches are planned on the host) does the loop read the winner back once per step (8 bytes).  With a trace
  * requested the call synchronises `stream` once at the end.  DNP_PATCH_LOOP=persistent|device|host forces a
  * schedule.                                                                                                  */
 DNP_API size_t dnp_patch_propagate_workspace_bytes(int64_t N, int64_t P, int64_t max_patch, int64_t n_tgt);

@@ -40,7 +40,7 @@ def _worker(rank, world, port, out_dir):
     dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
     import dnp_dist
 
-    src, tgt = _cloud(20001, 1).to(dev), _cloud(150003, 2).to(dev)      # uneven shards; large enough for the by-value kernel
+    src, tgt = _cloud(20001, 1).to(dev), _cloud(150003, 2).to(dev)      # uneven shards; large enough for the constant-window kernel
     E_full = dnp_dist.field_grad_sharded(src, tgt, gather=True)
     phi_full = dnp_dist.potential_sharded(src, tgt, gather=True)
     E_local = dnp_dist.field_grad_sharded(src, tgt)

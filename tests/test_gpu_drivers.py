@@ -436,7 +436,7 @@ def test_schedules_agree_on_random_clouds():
 def test_patch_loop_captures_into_a_cuda_graph(dev, golden, monkeypatch):
     """The device-driven schedule has no host read inside the loop, so the whole greedy loop (P steps, ~4 launches
     each) records into ONE CUDA graph and replays on new data; under capture the library never takes a path that
-    synchronises (the persistent kernel's precondition check, the by-value field kernel)."""
+    synchronises (the persistent kernel's precondition check, the host-driven schedule)."""
     import dnp_native
     monkeypatch.delenv("DNP_PATCH_LOOP", raising=False)
     g = golden("patch_prop")

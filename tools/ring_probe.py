@@ -1,6 +1,5 @@
-"""A/B timing of the three all-pairs paths on one GPU (development tool): the constant-window kernel
-(dnp_upairs.cu, DNP_RING), the by-value kernel of round 1 (dnp_cpairs.cu, DNP_CONST_PATH) and the shared-memory
-kernel (dnp_pairs.cu).  CUDA events around the native call, best of 5 groups.  Prints one JSON line per case."""
+"""A/B timing of the all-pairs paths on one GPU (development tool): the constant-window kernels (dnp_upairs.cu,
+DNP_RING and its DNP_RING_* knobs) and the shared-memory kernel (dnp_pairs.cu, DNP_RING=0).  CUDA events around the native call, best of 5 groups.  Prints one JSON line per case."""
 import json
 import os
 import sys
@@ -55,7 +54,7 @@ def case(S, M, potential=False):
     reps = max(1, min(20, int(2e11 / pairs)))
     res = {}
     configs = [("window", dict(DNP_RING=2)), ("window_tp1", dict(DNP_RING=2, DNP_RING_TP=1)),
-               ("by_value", dict(DNP_RING=0, DNP_CONST_PATH=2)), ("smem", dict(DNP_RING=0, DNP_CONST_PATH=0))]
+               ("smem", dict(DNP_RING=0))]
     for spec in EXTRA:                      # name=ENV:VAL,ENV:VAL from the command line
         name, envs = spec.split("=", 1)
         configs.append((name, dict(e.split(":") for e in envs.split(","))))
