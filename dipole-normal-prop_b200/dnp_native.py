@@ -104,12 +104,54 @@ def source_hash():
     return h.hexdigest()[:16]
 
 
+_BUILD_MARK = b"libdipole sm_100a sources="
+
+
+def embedded_hash(path=LIB_PATH):
+    """The source hash inside a built library (the literal dnp_build_info returns), read WITHOUT loading it."""
+    import mmap
+    with open(path, "rb") as f, mmap.mmap(f.fileno(), 0, access=mmap.ACCESS_READ) as m:
+        i = m.find(_BUILD_MARK)
+        if i < 0:
+            return None
+        return m[i + len(_BUILD_MARK):i + len(_BUILD_MARK) + 16].decode("ascii", "replace")
+
+
+def _rebuild_if_stale():
+    """A missing library, or one built from other sources than the tree next to it, is rebuilt in place before it is
+    loaded when nvcc is on the machine (the GPU boxes carry the build container's toolchain); the processes of one
+    job serialise on a lock file and re-check after acquiring it.  DNP_NO_AUTOBUILD=1 turns this off; without nvcc,
+    or if the build fails, load() raises as before.  There is still no CPU fallback: this only ever runs `make`."""
+    import fcntl
+    import shutil
+    import subprocess
+    import sys
+    want = source_hash()
+    if want is None or os.environ.get("DNP_NO_AUTOBUILD") == "1":
+        return
+    csrc = os.path.join(os.path.dirname(os.path.abspath(__file__)), "csrc")
+
+    def stale():
+        return not os.path.exists(LIB_PATH) or embedded_hash() != want
+    if not stale() or not (shutil.which("nvcc") or os.path.exists("/usr/local/cuda/bin/nvcc")):
+        return
+    with open(os.path.join(csrc, ".build.lock"), "w") as lock:
+        fcntl.flock(lock, fcntl.LOCK_EX)
+        if stale():
+            print(f"dnp_native: {LIB_PATH} does not match the sources next to it (tree {want}); running make",
+                  file=sys.stderr, flush=True)
+            env = dict(os.environ, PATH=os.environ.get("PATH", "") + ":/usr/local/cuda/bin")
+            subprocess.run(["make", "-C", csrc, "-j8"], stdout=subprocess.DEVNULL, stderr=subprocess.PIPE, env=env,
+                           check=False)
+
+
 def load():
     """Load libdipole.so (once).  Fails loudly if the CUDA extension is missing or was built from other sources."""
     global _lib
     if _lib is None:
         with _lock:
             if _lib is None:
+                _rebuild_if_stale()
                 if not os.path.exists(LIB_PATH):
                     raise ImportError(
                         f"{LIB_PATH} is missing: build it with `python __graft_entry__.py` "

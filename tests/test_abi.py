@@ -39,10 +39,20 @@ def test_library_was_built_from_this_source_tree(monkeypatch):
     import dnp_native
     info = dnp_native.load().dnp_build_info().decode()
     assert "sm_100a" in info and f"sources={dnp_native.source_hash()}" in info, info
+    assert dnp_native.embedded_hash() == dnp_native.source_hash()      # readable without loading the library
+    # a stale library: load() first tries `make` in csrc/ (nvcc is on the build container and on the GPU boxes) ...
+    made = []
+    monkeypatch.setattr(subprocess, "run", lambda cmd, **kw: made.append(cmd))
     monkeypatch.setattr(dnp_native, "_lib", None)
     monkeypatch.setattr(dnp_native, "source_hash", lambda: "0123456789abcdef")
+    with pytest.raises(ImportError, match="built from other sources"):      # ... and refuses what is still stale
+        dnp_native.load()
+    assert made and made[0][0] == "make"
+    made.clear()
+    monkeypatch.setenv("DNP_NO_AUTOBUILD", "1")
     with pytest.raises(ImportError, match="built from other sources"):
         dnp_native.load()
+    assert not made
 
 
 def test_header_and_exports_agree():
