@@ -385,6 +385,8 @@ upairs_kernel(const __grid_constant__ ShareTable tab, int win_q, int n_q, int m_
 // keep every SM supplied with CTAs that start and end at different times.  `first`: this lane's first launch
 // stores its partial rows, later launches accumulate (launches of a lane are serialised by its stream).
 // n_src is a multiple of the fold (224 field / 336 potential sources).
+// (16 targets per thread for the potential -- 3 LDCU.64 per 8 packed groups instead of 4 -- measured 2.6 % SLOWER at
+// 1M x 1M, profiles/README.md r02b: the issue model's 0.25 cycle per group is less than what 160 registers cost.)
 template <bool kPotential, int TP = 4>
 __global__ void __launch_bounds__(kUBlock, 3)
 upairs_tile_kernel(int win_q, int n_src, UTargets T, float eps, float* __restrict__ part, int first) {
@@ -586,8 +588,7 @@ void launch_shares(const UPairPlan& plan, int win_off, const UTargets& T, float 
 void launch_chunk(bool potential, const UPairPlan& plan, int win_off, const UTargets& T, float eps, float* part,
                   int first, const FusedFix& fix, cudaStream_t stream) {
     if (plan.whole_tiles) {
-        if (potential && plan.tp == 8) upairs_tile_kernel<true, 8><<<plan.m_tiles, kUBlock, 0, stream>>>(win_off >> 2, plan.chunk, T, eps, part, first);
-        else if (potential) upairs_tile_kernel<true><<<plan.m_tiles, kUBlock, 0, stream>>>(win_off >> 2, plan.chunk, T, eps, part, first);
+        if (potential) upairs_tile_kernel<true><<<plan.m_tiles, kUBlock, 0, stream>>>(win_off >> 2, plan.chunk, T, eps, part, first);
         else upairs_tile_kernel<false><<<plan.m_tiles, kUBlock, 0, stream>>>(win_off >> 2, plan.chunk, T, eps, part, first);
         return;
     }
@@ -635,13 +636,6 @@ UPairPlan make_upair_plan(bool potential, int64_t S, int64_t M, int sm_count) {
         p.tp = 4;
         p.m_tiles = (int)tiles4;
         p.lanes = tiles4 * 2 >= (int64_t)slots3 * 23 / 10 ? 2 : 4;
-        // potential, many targets: 16 per thread (2048-target tiles), 3 LDCU.64 of a source serve 8 packed groups
-        const int64_t tiles8 = (tiles4 + 1) / 2;
-        const int tile_tp = env_int_u("DNP_RING_TILE_TP", 0);
-        if (potential && p.lanes == 2 && (tile_tp == 8 || (tile_tp == 0 && false))) {
-            p.tp = 8;
-            p.m_tiles = (int)tiles8;
-        }
         { const int forced = env_int_u("DNP_RING_LANES", 0); if (forced == 2 || forced == 4) p.lanes = forced; }
         const int cap = p.lanes == 2 ? cap2 : cap4;
         p.slot_floats = p.lanes == 2 ? kSlotFloats : kQuarterFloats;

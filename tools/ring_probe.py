@@ -85,10 +85,15 @@ if __name__ == "__main__":
         shapes = [(1 << 20, 1 << 20)]
     if len(sys.argv) > 1 and sys.argv[1] == "multi":
         shapes = [(2000, 65536), (5000, 524288), (20000, 200000), (65536, 65536), (262144, 262144)]
-    if len(sys.argv) > 1 and "x" in sys.argv[1]:
-        shapes = [tuple(int(v) for v in t.split("x")) for t in sys.argv[1].split(",")]
+    pot_shapes = []
+    if len(sys.argv) > 1 and "x" in sys.argv[1]:                 # 500x524288,p65536x4194304 (p: potential)
+        toks = sys.argv[1].split(",")
+        shapes = [tuple(int(v) for v in t.split("x")) for t in toks if not t.startswith("p")]
+        pot_shapes = [tuple(int(v) for v in t[1:].split("x")) for t in toks if t.startswith("p")]
     for S, M in shapes:
         case(S, M)
+    for S, M in pot_shapes:
+        case(S, M, potential=True)
     if len(sys.argv) <= 1 or sys.argv[1] in ("big",):
         for S, M in ([(1 << 20, 1 << 20)] if len(sys.argv) > 1 else [(65536, 65536), (1 << 20, 1000)]):
             case(S, M, potential=True)
