@@ -752,9 +752,13 @@ def extras(dn, field_utils, dev, src, tgt):
     out["xyz_export_1M_pts_e2e_ms"] = (time.perf_counter() - t0) * 1e3
     del view
     with tempfile.TemporaryDirectory() as tmp:
-        t0 = time.perf_counter()
-        dnp_util.export_pc(rows.transpose(0, 1), os.path.join(tmp, "cloud.xyz"))     # util.export_pc: ... and into a file
-        out["xyz_export_1M_pts_to_file_ms"] = (time.perf_counter() - t0) * 1e3
+        times = []
+        for k in range(3):                                       # a new file every time; the first call also pins 8 MB
+            t0 = time.perf_counter()
+            dnp_util.export_pc(rows.transpose(0, 1), os.path.join(tmp, f"cloud{k}.xyz"))   # util.export_pc: ... into a file
+            times.append((time.perf_counter() - t0) * 1e3)
+        out["xyz_export_1M_pts_to_file_ms"] = min(times)
+        out["xyz_export_1M_pts_to_file_first_call_ms"] = times[0]
     text = dnp_util.export_text(rows.transpose(0, 1))
     out["xyz_text_bytes"] = len(text)
     out["xyz_format_1M_pts_ms"] = best_ms(lambda: _format_only(dn, rows), 2)

@@ -9,6 +9,8 @@
 #include <stdlib.h>
 #include <stdio.h>
 #include <string.h>
+#include <errno.h>
+#include <unistd.h>
 
 #include <chrono>
 
@@ -548,6 +550,98 @@ int dnp_xyz_format_f32(const float* pts, int64_t n_rows, int cols, int64_t ld_ro
     DNP_REQUIRE(n_bytes_out && (n_rows == 0 || (pts && out)), "null pointer");
     return run_xyz_format(pts, n_rows, cols, ld_row, ld_col, out, capacity, n_bytes_out, workspace, workspace_bytes,
                           (cudaStream_t)stream);
+}
+
+// util.export_pc to an open file: format on the device, then the text goes through two pinned 4 MB buffers straight
+// into write(2) -- the copy of chunk k + 1 runs while chunk k is written, and no host buffer of the size of the file
+// is ever allocated (its page faults cost more than the whole device side).
+namespace {
+constexpr size_t kExportChunk = 4u << 20;
+inline size_t up256z(size_t v) { return (v + 255) & ~(size_t)255; }
+}  // namespace
+
+size_t dnp_xyz_export_workspace_bytes(int64_t n_values) {
+    const size_t fmt = xyz_format_workspace_bytes(n_values);
+    if (fmt == 0) return 0;
+    return up256z(fmt) + up256z((size_t)25 * (size_t)n_values) + 256;
+}
+
+int dnp_xyz_export_fd_f32(const float* pts, int64_t n_rows, int cols, int64_t ld_row, int64_t ld_col, int fd,
+                          int64_t* n_bytes_host, void* workspace, size_t workspace_bytes, void* stream_) {
+    DNP_REQUIRE(n_rows >= 0 && cols >= 1, "bad size");
+    DNP_REQUIRE(fd >= 0, "bad file descriptor");
+    if (n_bytes_host) *n_bytes_host = 0;
+    if (n_rows == 0) return DNP_OK;
+    DNP_REQUIRE(pts, "null pointer");
+    const int64_t n_values = n_rows * cols;
+    const size_t need = dnp_xyz_export_workspace_bytes(n_values);
+    DNP_REQUIRE(need != 0, "xyz export: too many values for one call");
+    if (!workspace || workspace_bytes < need) {
+        set_error("workspace too small: need %zu bytes (dnp_xyz_export_workspace_bytes), got %zu", need, workspace_bytes);
+        return DNP_ERR_WORKSPACE;
+    }
+    cudaStream_t stream = (cudaStream_t)stream_;
+    const size_t fmt = up256z(xyz_format_workspace_bytes(n_values));
+    const size_t cap = (size_t)25 * (size_t)n_values;
+    unsigned char* ws = reinterpret_cast<unsigned char*>(workspace);
+    char* text = reinterpret_cast<char*>(ws + fmt);
+    int64_t* count_dev = reinterpret_cast<int64_t*>(ws + fmt + up256z(cap));
+    int rc = run_xyz_format(pts, n_rows, cols, ld_row, ld_col, text, (int64_t)cap, count_dev, ws, fmt, stream);
+    if (rc != DNP_OK) return rc;
+    int device = 0;
+    DNP_CHECK_CUDA(cudaGetDevice(&device));
+    cudaError_t e = t_host.prepare(device, 0, 2 * kExportChunk);
+    if (e != cudaSuccess) return cuda_fail(e, "pinned staging");
+    unsigned char* pin = t_host.pin;
+    DNP_CHECK_CUDA(cudaMemcpyAsync(pin, count_dev, sizeof(int64_t), cudaMemcpyDeviceToHost, stream));
+    DNP_CHECK_CUDA(cudaStreamSynchronize(stream));
+    int64_t total = 0;
+    memcpy(&total, pin, sizeof(total));
+    if (total < 0 || (size_t)total > cap) {
+        set_error("xyz export: formatted size %lld outside the buffer", (long long)total);
+        return DNP_ERR_INVALID;
+    }
+    cudaEvent_t ev[2] = {nullptr, nullptr};
+    for (int k = 0; k < 2; ++k)
+        if ((e = cudaEventCreateWithFlags(&ev[k], cudaEventDisableTiming)) != cudaSuccess) {
+            if (ev[0]) cudaEventDestroy(ev[0]);
+            return cuda_fail(e, "cudaEventCreate");
+        }
+    const int64_t n_chunks = (total + (int64_t)kExportChunk - 1) / (int64_t)kExportChunk;
+    auto chunk_len = [&](int64_t k) {
+        const int64_t left = total - k * (int64_t)kExportChunk;
+        return (size_t)(left < (int64_t)kExportChunk ? left : (int64_t)kExportChunk);
+    };
+    auto issue = [&](int64_t k) {
+        cudaError_t err = cudaMemcpyAsync(pin + (k & 1) * kExportChunk, text + k * (int64_t)kExportChunk, chunk_len(k),
+                                          cudaMemcpyDeviceToHost, stream);
+        if (err == cudaSuccess) err = cudaEventRecord(ev[k & 1], stream);
+        return err;
+    };
+    rc = DNP_OK;
+    if (n_chunks > 0 && (e = issue(0)) != cudaSuccess) rc = cuda_fail(e, "download");
+    for (int64_t k = 0; k < n_chunks && rc == DNP_OK; ++k) {
+        if (k + 1 < n_chunks && (e = issue(k + 1)) != cudaSuccess) { rc = cuda_fail(e, "download"); break; }
+        if ((e = cudaEventSynchronize(ev[k & 1])) != cudaSuccess) { rc = cuda_fail(e, "cudaEventSynchronize"); break; }
+        const unsigned char* p = pin + (k & 1) * kExportChunk;
+        size_t left = chunk_len(k);
+        while (left > 0) {
+            const ssize_t w = write(fd, p, left);
+            if (w < 0) {
+                if (errno == EINTR) continue;
+                set_error("xyz export: write failed: %s", strerror(errno));
+                rc = DNP_ERR_IO;
+                break;
+            }
+            p += w;
+            left -= (size_t)w;
+        }
+    }
+    if (rc != DNP_OK) cudaStreamSynchronize(stream);          // no copy may still target the staging buffers
+    cudaEventDestroy(ev[0]);
+    cudaEventDestroy(ev[1]);
+    if (rc == DNP_OK && n_bytes_host) *n_bytes_host = total;
+    return rc;
 }
 
 int dnp_wire_decode_f64(const double* xyz, int64_t n, float* out, int64_t ld, void* stream) {

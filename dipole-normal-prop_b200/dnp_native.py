@@ -69,6 +69,8 @@ SYMBOLS = [
     ("dnp_xyz_parse_f32", _i32, [_vp, _i64, _i64, _vp, _i64, _vp, _vp, _sz, _vp]),
     ("dnp_xyz_format_workspace_bytes", _sz, [_i64]),
     ("dnp_xyz_format_f32", _i32, [_vp, _i64, _i32, _i64, _i64, _vp, _i64, _vp, _vp, _sz, _vp]),
+    ("dnp_xyz_export_workspace_bytes", _sz, [_i64]),
+    ("dnp_xyz_export_fd_f32", _i32, [_vp, _i64, _i32, _i64, _i64, _i32, _vp, _vp, _sz, _vp]),
     ("dnp_wire_decode_f64", _i32, [_vp, _i64, _vp, _i64, _vp]),
     ("dnp_wire_encode_f64", _i32, [_vp, _i64, _i64, _vp, _vp]),
     ("dnp_field_grad_host_f32", _i32, [_vp, _i64, _i64, _vp, _i64, _i64, _f32, _vp, _i32]),
@@ -665,6 +667,28 @@ def xyz_format(pc_rows, as_view=False):
         host = out[:int(n_out.item())].cpu().numpy()
     view = memoryview(host)
     return view if as_view else view.tobytes()
+
+
+def xyz_export_fd(pc_rows, fd):
+    """util.export_pc's text for a [N, C] float32 CUDA tensor (any strides), written to the open file descriptor `fd`
+    by the library (device -> two pinned staging buffers -> write(2), no host copy of the whole text).  Returns the
+    number of bytes written."""
+    lib = load()
+    if pc_rows.dtype != torch.float32 or not pc_rows.is_cuda or pc_rows.dim() != 2:
+        raise TypeError("xyz_export_fd needs a 2-D float32 CUDA tensor")
+    n, c = pc_rows.shape
+    if n == 0 or c == 0:
+        return 0
+    dev = pc_rows.device
+    written = ctypes.c_int64(0)
+    with torch.cuda.device(dev):
+        nbytes = lib.dnp_xyz_export_workspace_bytes(n * c)
+        if nbytes == 0:
+            raise DipoleError("xyz export: too many values for one call")
+        ws = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+        _check(lib.dnp_xyz_export_fd_f32(_ptr(pc_rows), n, c, pc_rows.stride(0), pc_rows.stride(1), int(fd),
+                                         ctypes.byref(written), _ptr(ws), nbytes, _stream(pc_rows)))
+    return int(written.value)
 
 
 def wire_decode(xyz_f64, device=None):

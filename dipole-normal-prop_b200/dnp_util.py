@@ -395,9 +395,15 @@ def export_text(pc, as_view=False):
 
 
 def export_pc(pc, dest):
-    """util.py:46-51.  The text goes from the device to a host buffer and from there straight into the file."""
+    """util.py:46-51.  The text is formatted on the device and streamed into the file by the library
+    (dnp_xyz_export_fd_f32: pinned staging, the download of a chunk overlaps the write of the previous one)."""
+    import dnp_native as _dn
+    _dn.require_cuda()
+    if pc.dtype != torch.float32:
+        raise TypeError(f"export_pc formats float32 clouds (got {pc.dtype})")
+    dev = pc.device if pc.is_cuda else torch.device("cuda", torch.cuda.current_device())
     with open(dest, 'wb+') as file:
-        file.write(export_text(pc, as_view=True))
+        _dn.xyz_export_fd(pc.detach().to(dev).transpose(0, 1), file.fileno())
 
 
 def wire_decode(payload, device=None):

@@ -55,6 +55,7 @@ extern "C" {
 #define DNP_ERR_CUDA (-2)      /* a CUDA runtime call failed */
 #define DNP_ERR_WORKSPACE (-3) /* workspace missing or too small */
 #define DNP_ERR_NO_DEVICE (-4) /* no sm_100 device visible */
+#define DNP_ERR_IO (-5)        /* a write to the caller's file descriptor failed */
 
 /* fused epilogues of the all-pairs field kernel (K7 in SURVEY.md section 2.2) */
 #define DNP_EPI_STORE 0     /* out[r,0:3]  = E_r                      field_utils.py:96-116        */
@@ -327,7 +328,11 @@ DNP_API int dnp_flip_solve_f64(const double* A, const double* B, int64_t n, int6
  * n_bytes_out: device int64.
  * dnp_wire_decode_f64 / dnp_wire_encode_f64: the server payloads (socket_server_para.py:145-166,191):
  * N x 3 float64 -> [N, 6] float32 rows with zero normals, and [N, 6] float32 rows -> N x 6 float64.
- * All fully asynchronous.                                                                                       */
+ * All fully asynchronous, except dnp_xyz_export_fd_f32: the same text as dnp_xyz_format_f32, written to the open file
+ * descriptor `fd` (util.export_pc's `open(dest, 'w+')` + write, util.py:46-51).  The text is formatted in `workspace`
+ * (device, dnp_xyz_export_workspace_bytes) and streamed through two pinned 4 MB buffers kept per host thread, the
+ * download of one chunk overlapping the write(2) of the previous one; returns after the last write,
+ * *n_bytes_host (optional) = bytes written.                                                                      */
 DNP_API size_t dnp_xyz_parse_workspace_bytes(int64_t n_bytes, int64_t max_lines);
 DNP_API int dnp_xyz_parse_f32(const char* txt, int64_t n_bytes, int64_t max_lines,
                       float* out, int64_t max_rows, int64_t* counts,
@@ -336,6 +341,9 @@ DNP_API size_t dnp_xyz_format_workspace_bytes(int64_t n_values);
 DNP_API int dnp_xyz_format_f32(const float* pts, int64_t n_rows, int cols, int64_t ld_row, int64_t ld_col,
                        char* out, int64_t capacity, int64_t* n_bytes_out,
                        void* workspace, size_t workspace_bytes, void* stream);
+DNP_API size_t dnp_xyz_export_workspace_bytes(int64_t n_values);
+DNP_API int dnp_xyz_export_fd_f32(const float* pts, int64_t n_rows, int cols, int64_t ld_row, int64_t ld_col,
+                          int fd, int64_t* n_bytes_host, void* workspace, size_t workspace_bytes, void* stream);
 DNP_API int dnp_wire_decode_f64(const double* xyz, int64_t n, float* out, int64_t ld, void* stream);
 DNP_API int dnp_wire_encode_f64(const float* pts, int64_t n, int64_t ld, double* out, void* stream);
 

@@ -114,6 +114,38 @@ def test_round_trip_at_full_size(dev):
     assert torch.equal(back.view(torch.int32), pc.view(torch.int32))
 
 
+def test_export_to_file_streams_the_same_text(dev, tmp_path):
+    """dnp_xyz_export_fd_f32 (what export_pc calls): the file holds exactly the bytes of export_text, for texts
+    shorter than one 4 MB staging chunk, of a few chunks with a ragged tail, and of ~30 chunks; appending to an
+    open descriptor works (the library only calls write(2)); a failed write is reported, not ignored."""
+    import os
+    import dnp_native
+    import dnp_util
+    g = torch.Generator().manual_seed(12)
+    for n in (1, 7, 3000, 90001, 1 << 18):
+        pc = (torch.randn(n, 6, generator=g) * 10.0 ** torch.randint(-8, 8, (n, 1), generator=g).float()).to(dev)
+        want = dnp_util.export_text(pc.transpose(0, 1))
+        dest = tmp_path / f"cloud_{n}.xyz"
+        dnp_util.export_pc(pc.transpose(0, 1), dest)
+        assert open(dest, "rb").read() == want, n
+    with open(tmp_path / "two.xyz", "wb") as f:
+        f.write(b"# header\n")
+        f.flush()
+        wrote = dnp_native.xyz_export_fd(pc[:5], f.fileno())
+    body = open(tmp_path / "two.xyz", "rb").read()
+    assert body == b"# header\n" + dnp_util.export_text(pc[:5].transpose(0, 1)) and wrote == len(body) - 9
+    assert dnp_native.xyz_export_fd(pc[:0], 1) == 0
+    fd = os.open(tmp_path / "readonly.xyz", os.O_CREAT | os.O_RDONLY)
+    try:
+        with pytest.raises(dnp_native.DipoleError, match="write failed"):
+            dnp_native.xyz_export_fd(pc[:100], fd)
+    finally:
+        os.close(fd)
+    # the library stays usable after the failure
+    dnp_util.export_pc(pc[:100].transpose(0, 1), tmp_path / "after.xyz")
+    assert open(tmp_path / "after.xyz", "rb").read() == dnp_util.export_text(pc[:100].transpose(0, 1))
+
+
 def test_ok_xyz_rows(golden, dev):
     """The shipped demo cloud through the parser (first 2000 rows recorded from the reference)."""
     import dnp_util
