@@ -132,6 +132,12 @@ __global__ void slice_gather_kernel(const int64_t* __restrict__ perm, const int6
 
 inline size_t up256(size_t v) { return (v + 255) & ~(size_t)255; }
 
+// ShardHook::combine of the sharded greedy loop: sum the per-patch vectors of all ranks in place, on the loop's stream
+int combine_interactions(void*, float* vals, int64_t n, cudaStream_t stream) {
+    if (g_world > 1) DNP_CHECK_NCCL(g_nccl.AllReduce(vals, vals, (size_t)n, kNcclFloat32, kNcclSum, g_comm, stream));
+    return DNP_OK;
+}
+
 }  // namespace
 
 }  // namespace dnp
@@ -251,6 +257,31 @@ int dnp_edge_interactions_sharded_f32(const float* pts, int64_t ld, const int64_
     if (rc != DNP_OK) return rc;
     if (g_world > 1) DNP_CHECK_NCCL(g_nccl.AllReduce(out, out, (size_t)n_edges, kNcclFloat32, kNcclSum, g_comm, st));
     return DNP_OK;
+}
+
+int dnp_patch_propagate_sharded_f32(float* pts, int64_t N, int64_t ld, const int64_t* perm, const int64_t* offsets_dev,
+                                    const int64_t* offsets_host, int64_t P, const int64_t* rest_perm,
+                                    const int64_t* rest_offsets_host, const int64_t* tgt_idx, int64_t n_tgt,
+                                    const uint8_t* owned, int64_t start_patch, float eps, int diffuse, float* E,
+                                    int64_t ld_e, int32_t* order_host, float* value_host, void* workspace,
+                                    size_t workspace_bytes, void* stream) {
+    int rc = require_comm();
+    if (rc != DNP_OK) return rc;
+    if (N < 0 || P < 0 || n_tgt < 0) { set_error("negative size"); return DNP_ERR_INVALID; }
+    if (P == 0) return DNP_OK;
+    if (!pts || !perm || !offsets_dev || !offsets_host || !E || !owned || ld < 6 || ld_e < 3 || eps < 0.f ||
+        (rest_perm == nullptr) != (rest_offsets_host == nullptr) || (n_tgt > 0 && !tgt_idx)) {
+        set_error("bad argument (the sharded loop needs the owned-patch mask and this rank's target rows)");
+        return DNP_ERR_INVALID;
+    }
+    ShardHook hook;
+    hook.owned = owned;
+    hook.combine = combine_interactions;
+    // a rank that owns no patch still takes part in every all-reduce: its target list is empty, not absent
+    static const int64_t no_rows[1] = {0};
+    return run_patch_propagate(pts, N, ld, perm, offsets_dev, offsets_host, P, rest_perm, rest_offsets_host,
+                               n_tgt > 0 ? tgt_idx : no_rows, n_tgt, start_patch, eps, diffuse, E, ld_e, order_host,
+                               value_host, workspace, workspace_bytes, (cudaStream_t)stream, &hook);
 }
 
 int dnp_lattice_mean_potential_sharded_f32(const float* src, int64_t S, int64_t ld_s, int n, float* mean_out,

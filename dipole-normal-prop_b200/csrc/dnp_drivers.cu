@@ -205,7 +205,7 @@ int run_patch_propagate(float* pts, int64_t N, int64_t ld, const int64_t* perm, 
                         const int64_t* offsets_host, int64_t P, const int64_t* rest_perm,
                         const int64_t* rest_offsets_host, const int64_t* tgt_idx, int64_t n_tgt, int64_t start_patch,
                         float eps, int diffuse, float* E, int64_t ld_e, int32_t* order_host, float* value_host,
-                        void* workspace, size_t workspace_bytes, cudaStream_t stream) {
+                        void* workspace, size_t workspace_bytes, cudaStream_t stream, const ShardHook* shard) {
     if (P <= 0) return DNP_OK;
     if (start_patch < 0 || start_patch >= P) {
         set_error("start patch %lld out of range [0, %lld)", (long long)start_patch, (long long)P);
@@ -249,7 +249,8 @@ int run_patch_propagate(float* pts, int64_t N, int64_t ld, const int64_t* perm, 
 
     // DNP_PATCH_LOOP=persistent|device|host overrides the schedule (tests run all of them and compare)
     const char* forced = getenv("DNP_PATCH_LOOP");
-    if (!forced || forced[0] == 'p') {
+    // (sharded over ranks: the targets are this rank's patches only, so the one-kernel loop does not apply)
+    if (!shard && (!forced || forced[0] == 'p')) {
         // small cloud, disjoint patches covering the targets: the whole loop in one cooperative launch (dnp_loop.cu)
         int taken = 0;
         const int rc = run_patch_loop_persistent(pts, N, ld, perm, offsets_dev, offsets_host, P, rest_perm,
@@ -307,7 +308,7 @@ int run_patch_propagate(float* pts, int64_t N, int64_t ld, const int64_t* perm, 
                 }
                 if (step == P - 1) break;
                 const int rc = run_patch_interactions(E, ld_e, normals, ld, perm, offsets_dev, P, active, inter,
-                                                      nullptr, nullptr, stream);
+                                                      nullptr, nullptr, stream, PatchAdvance(), shard);
                 if (rc != DNP_OK) return rc;
             }
         } else {
@@ -339,7 +340,7 @@ int run_patch_propagate(float* pts, int64_t N, int64_t ld, const int64_t* perm, 
             adv.value = value_dev;
             adv.step = (int)(step + 1);
             const int rc = run_patch_interactions(E, ld_e, normals, ld, perm, offsets_dev, P, active, inter, best_idx,
-                                                  best_val, stream, adv);
+                                                  best_val, stream, adv, shard);
             if (rc != DNP_OK) return rc;
         }
         }
@@ -384,7 +385,7 @@ int run_patch_propagate(float* pts, int64_t N, int64_t ld, const int64_t* perm, 
         }
         if (step == P - 1) break;
         const int rc = run_patch_interactions(E, ld_e, normals, ld, perm, offsets_dev, P, active, inter, best_idx,
-                                              best_val, stream);                 // :244-247,316-319
+                                              best_val, stream, PatchAdvance(), shard);   // :244-247,316-319
         if (rc != DNP_OK) return rc;
         struct { int32_t idx; float val; } best;
         DNP_CHECK_CUDA(cudaMemcpyAsync(&best, best_idx, sizeof(best), cudaMemcpyDeviceToHost, stream));

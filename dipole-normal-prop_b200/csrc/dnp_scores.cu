@@ -112,10 +112,11 @@ edge_interactions_kernel(const float* __restrict__ pts, int64_t ld, const int64_
 __global__ void __launch_bounds__(kEdgeThreads)
 patch_interactions_kernel(const float* __restrict__ E, int64_t ld_e, const float* __restrict__ normals,
                           int64_t ld_n, const int64_t* __restrict__ perm, const int64_t* __restrict__ offsets,
-                          const uint8_t* __restrict__ active, float* __restrict__ out) {
+                          const uint8_t* __restrict__ active, const uint8_t* __restrict__ owned,
+                          float* __restrict__ out) {
     __shared__ float warp_part[32];
     const int64_t p = blockIdx.x;
-    if (active && !active[p]) {
+    if ((active && !active[p]) || (owned && !owned[p])) {
         if (threadIdx.x == 0) out[p] = 0.f;
         return;
     }
@@ -235,11 +236,17 @@ int run_edge_interactions_batched(const float* pts, int64_t ld, const int64_t* p
 
 int run_patch_interactions(const float* E, int64_t ld_e, const float* normals, int64_t ld_n, const int64_t* perm,
                            const int64_t* offsets, int64_t P, const uint8_t* active, float* out,
-                           int32_t* best_idx, float* best_val, cudaStream_t stream, PatchAdvance adv) {
+                           int32_t* best_idx, float* best_val, cudaStream_t stream, PatchAdvance adv,
+                           const ShardHook* shard) {
     if (P <= 0) return DNP_OK;
     patch_interactions_kernel<<<(unsigned)P, kEdgeThreads, 0, stream>>>(E, ld_e, normals, ld_n, perm, offsets, active,
-                                                                       out);
+                                                                       shard ? shard->owned : nullptr, out);
     count_launch(1);
+    if (shard && shard->combine) {
+        DNP_CHECK_CUDA(cudaGetLastError());
+        const int rc = shard->combine(shard->ctx, out, P, stream);
+        if (rc != DNP_OK) return rc;
+    }
     if (best_idx && best_val) {
         patch_argmax_kernel<<<1, 1024, 0, stream>>>(out, active, P, best_idx, best_val, adv);
         count_launch(1);

@@ -55,9 +55,19 @@ __device__ __forceinline__ unsigned long long block_first_absmax(const float* __
 }
 #endif
 
+// Multi-GPU greedy loop (dnp_comm.cu): every patch is OWNED by one rank, which holds its rows as targets and computes
+// its interaction; `owned` (device, P bytes) zeroes the others and `combine` sums the vectors of all ranks on the stream
+// (x + 0 is exact, so every rank sees the owner's value bit for bit) before anything reads them.
+struct ShardHook {
+    const uint8_t* owned = nullptr;
+    int (*combine)(void* ctx, float* vals, int64_t n, cudaStream_t stream) = nullptr;
+    void* ctx = nullptr;
+};
+
 int run_patch_interactions(const float* E, int64_t ld_e, const float* normals, int64_t ld_n, const int64_t* perm,
                            const int64_t* offsets, int64_t P, const uint8_t* active, float* out,
-                           int32_t* best_idx, float* best_val, cudaStream_t stream, PatchAdvance adv = PatchAdvance());
+                           int32_t* best_idx, float* best_val, cudaStream_t stream, PatchAdvance adv = PatchAdvance(),
+                           const ShardHook* shard = nullptr);
 
 // The whole greedy patch loop as one persistent cooperative kernel (dnp_loop.cu), for small clouds with disjoint
 // patches covering the targets; *taken = 0 when the preconditions do not hold (the caller runs its own schedule).
@@ -88,7 +98,7 @@ int run_patch_propagate(float* pts, int64_t N, int64_t ld, const int64_t* perm, 
                         const int64_t* offsets_host, int64_t P, const int64_t* rest_perm,
                         const int64_t* rest_offsets_host, const int64_t* tgt_idx, int64_t n_tgt, int64_t start_patch,
                         float eps, int diffuse, float* E, int64_t ld_e, int32_t* order_host, float* value_host,
-                        void* workspace, size_t workspace_bytes, cudaStream_t stream);
+                        void* workspace, size_t workspace_bytes, cudaStream_t stream, const ShardHook* shard = nullptr);
 
 int64_t points_batched_max_n();
 int run_points_propagate_batched(float* pts, int64_t ld, const int64_t* offsets, int64_t P, int64_t max_patch,

@@ -57,6 +57,8 @@ SYMBOLS = [
     ("dnp_field_grad_sharded_f32", _i32, [_vp, _i64, _i64, _vp, _i64, _i64, _f32, _vp, _i64, _i32, _vp, _sz, _vp]),
     ("dnp_edge_interactions_sharded_f32", _i32, [_vp, _i64, _vp, _vp, _i64, _i64, _vp, _i64, _f32, _vp, _vp, _sz, _vp]),
     ("dnp_lattice_mean_potential_sharded_f32", _i32, [_vp, _i64, _i64, _i32, _vp, _vp, _sz, _vp]),
+    ("dnp_patch_propagate_sharded_f32", _i32, [_vp, _i64, _i64, _vp, _vp, _vp, _i64, _vp, _vp, _vp, _i64, _vp, _i64, _f32,
+                                               _i32, _vp, _i64, _vp, _vp, _vp, _sz, _vp]),
     ("dnp_xie_workspace_bytes", _sz, [_i64, _i64]),
     ("dnp_xie_propagate_in_order_f32", _i32, [_vp, _i64, _i64, _vp, _i64, _f32, _vp, _i32, _vp, _vp, _vp, _sz, _vp]),
     ("dnp_voxel_partition_workspace_bytes", _sz, [_i64]),
@@ -416,12 +418,14 @@ def points_propagate(pts, diffuse=False, starting_point=0, eps=1e-6, want_trace=
 
 # ------------------------------------------------------------------ "xie" interaction
 def patch_propagate(pts, perm, offsets, start_patch, E, diffuse=False, eps=1e-5, rest_perm=None, rest_offsets=None,
-                    tgt_idx=None, want_trace=False, offsets_host=None):
+                    tgt_idx=None, want_trace=False, offsets_host=None, owned=None):
     """The whole greedy patch loop of strongest_field_propagation{,_reps} in one native call
     (dnp_patch_propagate_f32), in place on pts [N, 6]; E [N, 3] must be zero and receives the final field.
     offsets / rest_offsets may be tensors on any device (a host copy is made: the launch shapes need the sizes);
     pass the device tensor as `offsets` AND its host copy as `offsets_host` to avoid any copy inside the call (needed
-    to record the call into a CUDA graph).  Returns (order, values) as numpy arrays when want_trace."""
+    to record the call into a CUDA graph).  Returns (order, values) as numpy arrays when want_trace.
+    owned (uint8 [P], this rank's patches) selects the multi-GPU loop, dnp_patch_propagate_sharded_f32: tgt_idx must
+    then be the rows of the owned patches (may be empty) and comm_init must have been called on every rank."""
     import numpy as np
     lib = load()
     p, ld = _rows(pts, 6, "pts")
@@ -449,12 +453,20 @@ def patch_propagate(pts, perm, offsets, start_patch, E, diffuse=False, eps=1e-5,
     with torch.cuda.device(dev):
         nbytes = lib.dnp_patch_propagate_workspace_bytes(N, P, max_patch, n_tgt)
         ws = torch.empty(max(nbytes, 1), dtype=torch.uint8, device=dev)
-        _check(lib.dnp_patch_propagate_f32(
-            _ptr(p), N, ld, _ptr(perm), _ptr(off_dev), ctypes.c_void_p(off_host.ctypes.data), P, _ptr(rest_perm),
-            ctypes.c_void_p(rest_host.ctypes.data if rest_host is not None else 0), _ptr(tgt_idx), n_tgt,
-            int(start_patch), float(eps), int(bool(diffuse)), _ptr(e), ld_e,
-            ctypes.c_void_p(order.ctypes.data if want_trace else 0),
-            ctypes.c_void_p(values.ctypes.data if want_trace else 0), _ptr(ws), nbytes, _stream(p)))
+        head = (_ptr(p), N, ld, _ptr(perm), _ptr(off_dev), ctypes.c_void_p(off_host.ctypes.data), P, _ptr(rest_perm),
+                ctypes.c_void_p(rest_host.ctypes.data if rest_host is not None else 0), _ptr(tgt_idx), n_tgt)
+        tail = (int(start_patch), float(eps), int(bool(diffuse)), _ptr(e), ld_e,
+                ctypes.c_void_p(order.ctypes.data if want_trace else 0),
+                ctypes.c_void_p(values.ctypes.data if want_trace else 0), _ptr(ws), nbytes, _stream(p))
+        if owned is None:
+            _check(lib.dnp_patch_propagate_f32(*head, *tail))
+        else:
+            if tgt_idx is None:
+                raise ValueError("the sharded loop needs tgt_idx (the rows of this rank's patches)")
+            owned = owned.to(device=dev, dtype=torch.uint8).contiguous()
+            if owned.numel() != P:
+                raise ValueError("owned must have one entry per patch")
+            _check(lib.dnp_patch_propagate_sharded_f32(*head, _ptr(owned), *tail))
     return (order[:P], values[:P]) if want_trace else None
 
 

@@ -390,7 +390,16 @@ DNP_API int dnp_microbench(int kind, int iters, float* ms_out, double* ops_out, 
  *       target patch sliced over the ranks and ONE ncclAllReduce(sum) over out[n_edges]; patch_rows = offsets[P].
  *   dnp_lattice_mean_potential_sharded_f32   measure_mean_potential (field_utils.py:7-9) with the SOURCES sharded
  *       (1000 nodes are too few to shard) and ONE ncclAllReduce of the scalar.
- * workspace: dnp_sharded_workspace_bytes(S, M, P, patch_rows) device bytes.                                          */
+ *   dnp_patch_propagate_sharded_f32   the greedy patch loop of dnp_patch_propagate_f32 (field_utils.py:239-265,
+ *       311-335) with the TARGETS sharded by patch ownership ("inner field updates can be
+ *       target-sharded, the arg-max then needs one all-reduce per step"): the cloud is replicated, every patch is owned
+ *       by exactly one rank (`owned`: device uint8[P], this rank's patches), tgt_idx / n_tgt = the rows of this rank's
+ *       patches.  Per step every rank adds the chosen patch's field to ITS rows, sums E.n over ITS patches, and ONE
+ *       ncclAllReduce(sum) of the P-vector (zeros for patches owned elsewhere: the sum is exact, all ranks see identical
+ *       values) precedes the arg-max, which every rank takes itself -- so all ranks visit and flip the same patches and
+ *       end with identical pts.  E holds the final field on this rank's rows only.  All ranks pass the same
+ *       start_patch.  workspace: dnp_patch_propagate_workspace_bytes(N, P, max_patch, n_tgt).
+ * workspace of the first three: dnp_sharded_workspace_bytes(S, M, P, patch_rows) device bytes.                         */
 DNP_API int dnp_comm_unique_id(void* id128);
 DNP_API int dnp_comm_init(const void* id128, int rank, int world);
 DNP_API int dnp_comm_destroy(void);
@@ -407,6 +416,13 @@ DNP_API int dnp_edge_interactions_sharded_f32(const float* pts, int64_t ld,
                                       void* workspace, size_t workspace_bytes, void* stream);
 DNP_API int dnp_lattice_mean_potential_sharded_f32(const float* src, int64_t S, int64_t ld_s, int n, float* mean_out,
                                            void* workspace, size_t workspace_bytes, void* stream);
+DNP_API int dnp_patch_propagate_sharded_f32(float* pts, int64_t N, int64_t ld,
+                                    const int64_t* perm, const int64_t* offsets_dev, const int64_t* offsets_host,
+                                    int64_t P, const int64_t* rest_perm, const int64_t* rest_offsets_host,
+                                    const int64_t* tgt_idx, int64_t n_tgt, const uint8_t* owned,
+                                    int64_t start_patch, float eps, int diffuse,
+                                    float* E, int64_t ld_e, int32_t* order_host, float* value_host,
+                                    void* workspace, size_t workspace_bytes, void* stream);
 
 #ifdef __cplusplus
 }

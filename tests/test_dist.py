@@ -133,3 +133,129 @@ def test_single_process_is_identity(orc):
     src, tgt = _cloud(50, 1), _cloud(20, 2)
     f = lambda s, t: torch.from_numpy(orc.field_grad(s.numpy(), t.numpy()))
     assert torch.equal(dnp_dist.field_grad_sharded(src, tgt, gather=True, compute=f), f(src, tgt))
+
+
+# ---------------------------------------------------------------------------- sharded greedy patch propagation
+class _OracleBackend:
+    """CPU stand-in for the library calls of dnp_dist's sharded drivers: the reference's op chain
+    (oracle/torch_port.py) with the sharded protocol of dnp_patch_propagate_sharded_f32 spelled out step by step --
+    this rank adds the chosen patch's field to ITS rows, sums E.n over ITS patches, one all_reduce, every rank takes
+    the arg-max."""
+
+    def flattest_patch(self, pts, perm, offsets):
+        from oracle import torch_drivers
+        groups = [perm[offsets[p]:offsets[p + 1]] for p in range(len(offsets) - 1)]
+        return torch_drivers._flattest(pts, groups)
+
+    def greedy_loop(self, pts, perm, offsets, start, E, diffuse, rest_perm, rest_offsets, tgt_rows, owned):
+        from oracle.torch_port import field_grad
+        P = len(offsets) - 1
+        rows = [perm[offsets[p]:offsets[p + 1]] for p in range(P)]
+        rest = [rest_perm[rest_offsets[p]:rest_offsets[p + 1]] for p in range(P)] if rest_perm is not None else None
+        is_tgt = torch.zeros(pts.shape[0], dtype=torch.bool)
+        is_tgt[tgt_rows] = True
+        settled = torch.zeros(pts.shape[0], dtype=torch.bool)
+        active = torch.ones(P, dtype=torch.bool)
+        cur = start
+        self.order = [cur]
+        for step in range(P):
+            active[cur] = False
+            settled[rows[cur]] = True
+            skip = torch.zeros_like(settled)
+            if diffuse:
+                skip[rows[cur]] = True                       # :256-261 only the source patch itself
+            else:
+                skip = settled                               # :264-265
+            mine = torch.nonzero(is_tgt & ~skip).flatten()
+            if mine.numel():
+                E[mine] += field_grad(pts[rows[cur]], pts[mine, :3], eps=1e-5)
+            if step == P - 1:
+                break
+            inter = torch.zeros(P)
+            for p in range(P):
+                if active[p] and owned[p]:
+                    inter[p] = (E[rows[p]] * pts[rows[p], 3:]).sum(dim=-1).sum()
+            dist.all_reduce(inter)
+            cand = inter.abs() * active
+            cur = int(torch.argmax(torch.where(active, cand, torch.full_like(cand, -1.0))))
+            self.order.append(cur)
+            if inter[cur] < 0:                               # :250-252
+                pts[rows[cur], 3:] *= -1
+                if rest is not None:
+                    pts[rest[cur], 3:] *= -1
+
+    def sign_strict(self, E, pts, rows):
+        dots = (E[rows] * pts[rows, 3:]).sum(-1)
+        pts[rows, 3:] = pts[rows, 3:] * ((dots > 0).float() * 2 - 1)[:, None]
+
+    def transfer_sign(self, pts, src_rows, tgt_rows):
+        from oracle.torch_port import field_grad
+        E = field_grad(pts[src_rows], pts[tgt_rows, :3], eps=1e-5)
+        dots = (E * pts[tgt_rows, 3:]).sum(-1)
+        pts[tgt_rows, 3:] = pts[tgt_rows, 3:] * ((dots > 0).float() * 2 - 1)[:, None]
+
+
+def _surface(n, seed):
+    g = torch.Generator().manual_seed(seed)
+    d = torch.nn.functional.normalize(torch.randn(n, 3, generator=g), dim=1)
+    pc = torch.cat([d * torch.tensor([0.45, 0.35, 0.25]), torch.nn.functional.normalize(d / torch.tensor([0.45, 0.35, 0.25]), dim=1)], 1)
+    pc[torch.rand(n, generator=g) < 0.5, 3:] *= -1
+    return pc.float()
+
+
+def _patches(pc, P):
+    order = torch.argsort(pc[:, 0] * 5 + pc[:, 1], stable=True)
+    return list(torch.chunk(order, P))
+
+
+def _prop_worker(rank, world, port, out_dir):
+    for p in (ROOT, PKG):
+        if p not in sys.path:
+            sys.path.insert(0, p)
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    import dnp_dist
+    out = {}
+    for diffuse in (False, True):
+        pc = _surface(900, 4)
+        chunks = _patches(pc, 7)                                   # 7 patches on 2 ranks: uneven ownership
+        reps = [(c[:40], c[40:]) for c in chunks]
+        be = _OracleBackend()
+        dnp_dist.strongest_field_propagation_reps_sharded(pc, reps, diffuse=diffuse, backend=be)
+        out[f"reps_{diffuse}"] = (pc.clone(), list(be.order))
+        pc = _surface(700, 5)
+        chunks = _patches(pc, 5)
+        be = _OracleBackend()
+        dnp_dist.strongest_field_propagation_sharded(pc, [(i, c) for i, c in enumerate(chunks)][:3], chunks,
+                                                     diffuse=diffuse, backend=be)
+        out[f"all_{diffuse}"] = (pc.clone(), list(be.order))
+    assert dnp_dist.patch_owner_mask(7, rank, world).tolist() == [int(p % world == rank) for p in range(7)]
+    torch.save(out, os.path.join(out_dir, f"prop_rank{rank}.pt"))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.timeout(600)
+def test_sharded_greedy_propagation_world_size_2_gloo(tmp_path):
+    """Patch ownership + one all_reduce per step + the exchanges after the loop: both ranks end with the same cloud,
+    and it is the cloud the single-process driver (the reference's op sequence, oracle/torch_drivers.py) produces."""
+    from oracle import torch_drivers
+    world = 2
+    mp.spawn(_prop_worker, args=(world, _free_port(), str(tmp_path)), nprocs=world, join=True)
+    res = [torch.load(os.path.join(tmp_path, f"prop_rank{r}.pt")) for r in range(world)]
+    for diffuse in (False, True):
+        for key in (f"reps_{diffuse}", f"all_{diffuse}"):
+            assert torch.equal(res[0][key][0], res[1][key][0]), key          # identical on every rank, bit for bit
+            assert res[0][key][1] == res[1][key][1], key
+        pc = _surface(900, 4)
+        chunks = _patches(pc, 7)
+        trace = []
+        torch_drivers.propagate_representatives(pc, [(c[:40], c[40:]) for c in chunks], diffuse=diffuse, trace=trace)
+        assert trace == res[0][f"reps_{diffuse}"][1]
+        assert torch.equal(pc, res[0][f"reps_{diffuse}"][0])
+        pc = _surface(700, 5)
+        chunks = _patches(pc, 5)
+        trace = []
+        torch_drivers.propagate_patches(pc, [(i, c) for i, c in enumerate(chunks)][:3], chunks, diffuse=diffuse, trace=trace)
+        assert trace == res[0][f"all_{diffuse}"][1]
+        assert torch.equal(pc, res[0][f"all_{diffuse}"][0])
