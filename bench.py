@@ -314,6 +314,32 @@ def multi_gpu_blocks(args, dn, dist, dev, rank, world):
                           "pairs_per_s": pairs / (ms_e * 1e-3), "all_reduce_ms": ar_ms,
                           "all_reduce_bytes": int(edges.shape[0]) * 4, "checksum": float(w.double().abs().sum().item()),
                           "api": "dnp_dist.edge_scores_sharded: per-patch target slices + one all_reduce(SUM)"}
+
+    # ---- BASELINE config 3 stand-in on the ranks: greedy propagation over the representatives of 1000 patches of the
+    # same 1M-point cloud, targets sharded by patch ownership with one all-reduce of the interaction vector per step
+    # (dnp_patch_propagate_sharded_f32), then the reps -> rest field sharded over the remaining rows
+    reps = [(c[:500].to(dev), c[500:].to(dev)) for c in chunks]
+    work = pcd.clone()
+    dnp_dist.strongest_field_propagation_reps_sharded(work, reps, diffuse=True)
+
+    def run_reps():
+        w2 = pcd.clone()
+        dnp_dist.strongest_field_propagation_reps_sharded(w2, reps, diffuse=True)
+        return w2
+    ms_r, w2 = ev_ms(run_reps)
+    sig = w2[:, 3:].contiguous().view(torch.int32).sum(dtype=torch.int64).reshape(1)
+    hi, lo = sig.clone(), sig.clone()
+    if world > 1:
+        dist.all_reduce(hi, op=dist.ReduceOp.MAX)
+        dist.all_reduce(lo, op=dist.ReduceOp.MIN)
+    flipped = int((w2[:, 3:] != pcd[:, 3:]).any(dim=1).sum().item())
+    out["cfg3_reps_propagation"] = {
+        "points": 1 << 20, "patches": 1000, "representatives_per_patch": 500, "diffuse": True, "ms": ms_r,
+        "identical_on_all_ranks": bool(torch.equal(hi, lo)), "points_flipped": flipped,
+        "all_reduce_per_step_bytes": 4000, "steps": 999,
+        "api": "dnp_dist.strongest_field_propagation_reps_sharded: patches owned round robin, one all_reduce(SUM) "
+               "of the [P] interaction vector per greedy step, final field sharded over the remaining rows"}
+    dnp_dist.release_comm()
     return out
 
 

@@ -188,6 +188,10 @@ class _CudaBackend:
         return field_utils._flattest_patch(pts, perm, offsets)
 
     def greedy_loop(self, pts, perm, offsets, start, E, diffuse, rest_perm, rest_offsets, tgt_rows, owned):
+        if _rank_world(self.group)[1] == 1:          # one rank owns everything: the single-GPU loop, no communicator
+            _dn.patch_propagate(pts, perm, offsets, start, E, diffuse=diffuse, eps=1e-5, rest_perm=rest_perm,
+                                rest_offsets=rest_offsets, tgt_idx=tgt_rows)
+            return
         ensure_comm(self.group)
         _dn.patch_propagate(pts, perm, offsets, start, E, diffuse=diffuse, eps=1e-5, rest_perm=rest_perm,
                             rest_offsets=rest_offsets, tgt_idx=tgt_rows, owned=owned)
