@@ -98,14 +98,18 @@ class ClockSampler:
 
 
 # ---------------------------------------------------------------------------------------------- CPU arm
-def time_cpu_port(n_src, n_tgt, repeats=1):
-    """Seconds per field_grad(n_src x n_tgt) of the torch port on all host cores (best of `repeats`)."""
+def time_cpu_port(n_src, n_tgt, repeats=1, potential=False):
+    """Seconds per field_grad (or potential) of n_src x n_tgt points in the torch port on all host cores (best of
+    `repeats`)."""
     from oracle import torch_port
     src, tgt = cloud(n_src, 1), cloud(n_tgt, 2, cols=3)
     best = float("inf")
     for _ in range(repeats):
         t0 = time.perf_counter()
-        torch_port.field_grad(src, tgt, eps=EPS)
+        if potential:
+            torch_port.potential(src, tgt)
+        else:
+            torch_port.field_grad(src, tgt, eps=EPS)
         best = min(best, time.perf_counter() - t0)
     return best
 
@@ -115,7 +119,9 @@ def cpu_baseline_block(n):
     time_cpu_port(2048, 2048)                          # warm the thread pool and the allocator
     m = 2 * n                                          # > max_pts = 15000 at the default n: the chunking runs too
     sec = time_cpu_port(n, m)
+    sec_phi = time_cpu_port(n, m, potential=True)
     return {"value": n * m / sec, "unit": UNIT, "cores": torch.get_num_threads(), "kind": "port",
+            "potential_pairs_per_s": n * m / sec_phi,
             "host_cpus": os.cpu_count(), "drivers": cpu_driver_seconds(full=False),
             "sample": f"oracle/torch_port.field_grad (the reference's op chain and chunking, field_utils.py:61-116), "
                       f"float32, {n} sources x {m} targets = {n * m:.3e} pairs, one run of {sec:.1f} s"}
@@ -435,6 +441,8 @@ def run_reference_arm(args, rank, world):
               f"the {args.points} x {args.points} per-GPU workload; the reference is pure Python/torch and does not "
               f"travel to this box, so its op chain is ported (bit-exact vs tests/golden/leaf.npz)")
     extras = {} if args.no_extras else cpu_driver_seconds(full=True)
+    if not args.no_extras:       # field_utils.potential (field_utils.py:12-55) on the same sample shape, once
+        extras["potential_pairs_per_s"] = n * 2 * n / time_cpu_port(n, 2 * n, potential=True)
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": sec / args.steps * 1e3,
