@@ -18,6 +18,8 @@
 // A source that sits exactly on a node contributes 0 (n.R = 0 exactly, clamped rsqrt), as in dnp_pairs.cu.
 #include <stdlib.h>
 
+#include <atomic>
+
 #include "dnp_common.cuh"
 #include "dnp_pairs.h"
 
@@ -153,6 +155,13 @@ lattice_sum_kernel(const __grid_constant__ LatticeTable tab, const __grid_consta
 }
 
 
+// Scratch of dnp_lattice_mean_potential_noalloc_f32 (below): the per-CTA partial sums, one float per CTA of the largest
+// grid the kernel is ever launched with.  File scope: every device that loads the library holds these 4.9 KB until
+// the process exits.  In HOST code this name is a stand-in, not a device address -- the launcher gets the address of
+// the current device's copy from cudaGetSymbolAddress.
+constexpr size_t kStaticPartialFloats = kLMaxGrid;
+static __device__ __align__(256) float g_static_partials[kStaticPartialFloats];
+
 }  // namespace
 
 size_t lattice_mean_workspace_bytes() { return (size_t)kLMaxGrid * sizeof(float); }
@@ -210,3 +219,46 @@ int run_lattice_mean(const float* src, int64_t S, int64_t ld_s, int n, float* me
 }
 
 }  // namespace dnp
+
+// ------------------------------------------------------------------ allocation-free entry point
+// No counterpart in the reference: added for callers that cannot allocate
+// (CUDA graph capture, serving loops, harnesses that forbid cudaMalloc).  Same kernels as the workspace variant.
+extern "C" int dnp_lattice_mean_potential_noalloc_f32(const float* src, int64_t S, int64_t ld_s, int n, float* mean_out,
+                                                      void* stream) {
+    using namespace dnp;
+    if (S < 0 || S > DNP_NOALLOC_MAX_SOURCES) {
+        set_error("dnp_lattice_mean_potential_noalloc_f32: %lld sources, the allocation-free variant takes at most %lld "
+                  "(DNP_NOALLOC_MAX_SOURCES); use dnp_lattice_mean_potential_f32 with a workspace",
+                  (long long)S, (long long)DNP_NOALLOC_MAX_SOURCES);
+        return DNP_ERR_INVALID;
+    }
+    if (n < 1 || n > DNP_NOALLOC_MAX_LATTICE) {
+        set_error("dnp_lattice_mean_potential_noalloc_f32: lattice side %d outside [1, %d] (DNP_NOALLOC_MAX_LATTICE)", n,
+                  DNP_NOALLOC_MAX_LATTICE);
+        return DNP_ERR_INVALID;
+    }
+    if (!mean_out || (S > 0 && !src) || ld_s < 6) {
+        set_error("dnp_lattice_mean_potential_noalloc_f32: null pointer or row stride below 6");
+        return DNP_ERR_INVALID;
+    }
+    // the device address of THIS device's copy of the array, looked up once per device with that device current
+    static std::atomic<int> have[kMaxDevices];
+    static float* address[kMaxDevices];
+    int dev = 0;
+    DNP_CHECK_CUDA(cudaGetDevice(&dev));
+    float* partials = nullptr;
+    if (dev >= 0 && dev < kMaxDevices && have[dev].load(std::memory_order_acquire)) {
+        partials = address[dev];
+    } else {
+        DNP_CHECK_CUDA(cudaGetSymbolAddress(reinterpret_cast<void**>(&partials), g_static_partials));
+        if (dev >= 0 && dev < kMaxDevices) {
+            address[dev] = partials;
+            have[dev].store(1, std::memory_order_release);
+        }
+    }
+    // nothing has to start at zero: every CTA of the launch stores its own slot and the final sum reads exactly the
+    // slots of this launch, so the previous call's contents are never seen
+    return run_lattice_mean(src, S, ld_s, n, mean_out, partials, kStaticPartialFloats * sizeof(float),
+                            (cudaStream_t)stream);
+}
+

@@ -57,6 +57,7 @@ SYMBOLS = [
     ("dnp_field_grad_sharded_f32", _i32, [_vp, _i64, _i64, _vp, _i64, _i64, _f32, _vp, _i64, _i32, _vp, _sz, _vp]),
     ("dnp_edge_interactions_sharded_f32", _i32, [_vp, _i64, _vp, _vp, _i64, _i64, _vp, _i64, _f32, _vp, _vp, _sz, _vp]),
     ("dnp_lattice_mean_potential_sharded_f32", _i32, [_vp, _i64, _i64, _i32, _vp, _vp, _sz, _vp]),
+    ("dnp_lattice_mean_potential_noalloc_f32", _i32, [_vp, _i64, _i64, _i32, _vp, _vp]),
     ("dnp_patch_propagate_sharded_f32", _i32, [_vp, _i64, _i64, _vp, _vp, _vp, _i64, _vp, _vp, _vp, _i64, _vp, _i64, _f32,
                                                _i32, _vp, _i64, _vp, _vp, _vp, _sz, _vp]),
     ("dnp_xie_workspace_bytes", _sz, [_i64, _i64]),
@@ -822,6 +823,21 @@ def lattice_mean_potential_sharded(sources, n=10):
         ws = torch.empty(nbytes, dtype=torch.uint8, device=src.device)
         _check(lib.dnp_lattice_mean_potential_sharded_f32(_ptr(src), src.shape[0], ld_s, int(n), _ptr(mean), _ptr(ws),
                                                           nbytes, _stream(src)))
+    return mean
+
+
+def lattice_mean_potential_noalloc(sources, n=10, out=None):
+    """dnp_lattice_mean_potential_noalloc_f32: the lattice test's mean potential with the library's static device
+    scratch instead of a workspace -- the CALL allocates nothing (pass `out`, a float32 CUDA scalar, to keep this
+    wrapper allocation-free too).  Calls on one device share the scratch: do not overlap them on the GPU."""
+    lib = load()
+    src, ld_s = _rows(sources, 6, "pc")
+    mean = out if out is not None else torch.empty((), dtype=torch.float32, device=src.device)
+    if mean.dtype != torch.float32 or mean.device != src.device or mean.numel() != 1:
+        raise TypeError("out must be a float32 scalar on the sources' device")
+    with torch.cuda.device(src.device):
+        _check(lib.dnp_lattice_mean_potential_noalloc_f32(_ptr(src), src.shape[0], ld_s, int(n), _ptr(mean),
+                                                          _stream(src)))
     return mean
 
 

@@ -424,6 +424,23 @@ DNP_API int dnp_patch_propagate_sharded_f32(float* pts, int64_t N, int64_t ld,
                                     float* E, int64_t ld_e, int32_t* order_host, float* value_host,
                                     void* workspace, size_t workspace_bytes, void* stream);
 
+/* ------------------------------------------------------------------ allocation-free variant
+ * No counterpart in the reference: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid allocation).
+ * dnp_lattice_mean_potential_noalloc_f32 = dnp_lattice_mean_potential_f32(phi_opt = NULL) -- the global-orientation
+ * test's mean dipole potential over the n^3 lattice -- WITHOUT a workspace argument: the per-CTA partial sums live in a
+ * file-scope `static __device__` array of the library (1200 floats = 4800 bytes, held by every GPU that loads the
+ * library until the process exits).  The call makes no cudaMalloc / cudaFree / allocating library call; the caller
+ * still owns src and mean_out (device).  Limits, rejected with DNP_ERR_INVALID and a message: S <=
+ * DNP_NOALLOC_MAX_SOURCES, 1 <= n <= DNP_NOALLOC_MAX_LATTICE.  All calls on a device SHARE the array (it keeps the last
+ * call's contents; nothing needs clearing, a call overwrites every slot it reads): calls that may overlap on the GPU
+ * -- different streams, or host threads on different streams -- RACE on it and must be serialised by the caller.
+ * Asynchronous on `stream`, like the workspace variant.                                                            */
+#define DNP_NOALLOC_MAX_SOURCES ((int64_t)1 << 24)   /* 16 777 216 sources */
+#define DNP_NOALLOC_MAX_LATTICE 255
+DNP_API int dnp_lattice_mean_potential_noalloc_f32(const float* src, int64_t S, int64_t ld_s, int n, float* mean_out,
+                                           void* stream);
+
 #ifdef __cplusplus
 }
 #endif
