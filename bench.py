@@ -342,9 +342,11 @@ def multi_gpu_blocks(args, dn, dist, dev, rank, world):
     out["cfg3_reps_propagation"] = {
         "points": 1 << 20, "patches": 1000, "representatives_per_patch": 500, "diffuse": True, "ms": ms_r,
         "identical_on_all_ranks": bool(torch.equal(hi, lo)), "points_flipped": flipped,
-        "all_reduce_per_step_bytes": 4000, "steps": 999,
+        "schedule": "slab (dnp_slab.cu): every rank computes the field slabs of the patches it owns against all "
+                    "representatives, then the greedy decisions run on the all-reduced P x P matrix",
+        "all_reduce_bytes": [1000 * 1000 * 4, 500 * 1000 * 12], "steps": 999,
         "api": "dnp_dist.strongest_field_propagation_reps_sharded: patches owned round robin, one all_reduce(SUM) "
-               "of the [P] interaction vector per greedy step, final field sharded over the remaining rows"}
+               "of the [P, P] interaction matrix and one of the [T, 3] field, final field sharded over the remaining rows"}
     dnp_dist.release_comm()
     return out
 

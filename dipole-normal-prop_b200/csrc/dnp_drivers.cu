@@ -170,6 +170,13 @@ __global__ void cur_init_kernel(int32_t* cur, int32_t start, int32_t* order, flo
 
 inline size_t up256(size_t v) { return (v + 255) & ~(size_t)255; }
 
+// DNP_PATCH_LOOP=slab forces the slab schedule wherever it fits; unforced it is taken where it pays
+bool slab_wanted(int64_t P, int64_t T, int64_t max_patch) {
+    const char* forced = getenv("DNP_PATCH_LOOP");
+    if (forced) return forced[0] == 's' && slab_schedule_fits(P, T, max_patch);
+    return slab_schedule_pays(P, T, max_patch);
+}
+
 struct DriverLayout {
     size_t settled, scratch, active, inter, best, cur, rest_off, order, value, loop, loop_bytes, pairs, pairs_bytes, total;
 };
@@ -191,6 +198,11 @@ DriverLayout driver_layout(int64_t N, int64_t P, int64_t max_patch, int64_t M) {
     L.pairs_bytes = pairs_workspace_bytes_upper(max_patch, M);
     L.pairs = off; off += up256(L.pairs_bytes);
     L.total = off;
+    // the slab schedule (dnp_slab.cu) runs INSTEAD of the other two and lays its buffers over theirs
+    if (slab_wanted(P, M, max_patch)) {
+        const size_t with_slabs = L.loop + patch_slab_workspace_bytes(N, P, M);
+        if (with_slabs > L.total) L.total = with_slabs;
+    }
     return L;
 }
 
@@ -260,6 +272,23 @@ int run_patch_propagate(float* pts, int64_t N, int64_t ld, const int64_t* perm, 
         if (taken) return DNP_OK;
         if (forced) {
             set_error("DNP_PATCH_LOOP=persistent: the preconditions of the persistent loop do not hold");
+            return DNP_ERR_INVALID;
+        }
+    }
+    // large loops: all per-patch fields as independent launches, then the loop on the interaction matrix (dnp_slab.cu)
+    {
+        const int64_t T_all = offsets_host[P] - offsets_host[0];
+        if (slab_wanted(P, T_all, max_patch) && workspace_bytes > L.loop) {
+            int taken = 0;
+            const int rc = run_patch_loop_slab(pts, N, ld, perm, offsets_dev, offsets_host, P, rest_perm,
+                                               rest_offsets_host, tgt_idx, n_tgt, start_patch, eps, diffuse, E, ld_e,
+                                               order_host, value_host, ws + L.loop, workspace_bytes - L.loop, stream,
+                                               shard, &taken);
+            if (rc != DNP_OK) return rc;
+            if (taken) return DNP_OK;
+        }
+        if (forced && forced[0] == 's') {
+            set_error("DNP_PATCH_LOOP=slab: the preconditions of the slab schedule do not hold");
             return DNP_ERR_INVALID;
         }
     }

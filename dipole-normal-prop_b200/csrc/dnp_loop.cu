@@ -397,6 +397,28 @@ size_t patch_loop_workspace_bytes(int64_t N, int64_t P) {
     return up256((size_t)N * 4) + 256 + up256((size_t)2 * P * sm_count_cached() * 4 + 64) + up256((size_t)P * 4) * 2;
 }
 
+int check_patch_cover(const int64_t* perm, int64_t T, int64_t N, const int64_t* rest_rows, int64_t R, int* flags,
+                      int* counts, cudaStream_t stream, int* ok) {
+    *ok = 0;
+    DNP_CHECK_CUDA(cudaMemsetAsync(flags, 0, (size_t)N * 4, stream));
+    DNP_CHECK_CUDA(cudaMemsetAsync(counts, 0, 256, stream));
+    loop_cover_kernel<<<(unsigned)((T + 255) / 256), 256, 0, stream>>>(perm, T, N, flags, counts);
+    count_launch(1);
+    if (R > 0) {
+        loop_rest_overlap_kernel<<<(unsigned)((R + 255) / 256), 256, 0, stream>>>(rest_rows, R, N, flags, counts);
+        count_launch(1);
+    }
+    int host_counts[3] = {0, 0, 0};
+    DNP_CHECK_CUDA(cudaMemcpyAsync(host_counts, counts, sizeof(host_counts), cudaMemcpyDeviceToHost, stream));
+    DNP_CHECK_CUDA(cudaStreamSynchronize(stream));
+    if (host_counts[1] != 0) {
+        set_error("patch rows out of range [0, %lld)", (long long)N);
+        return DNP_ERR_INVALID;
+    }
+    *ok = host_counts[0] == T && host_counts[2] == 0;
+    return DNP_OK;
+}
+
 // Returns DNP_OK and sets *taken = 1 when the loop ran here; *taken = 0 (nothing launched that matters) when the
 // preconditions do not hold and the caller has to run the multi-launch schedule.
 int run_patch_loop_persistent(float* pts, int64_t N, int64_t ld, const int64_t* perm, const int64_t* offsets_dev,

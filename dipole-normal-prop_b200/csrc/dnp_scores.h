@@ -79,6 +79,23 @@ int run_patch_loop_persistent(float* pts, int64_t N, int64_t ld, const int64_t* 
                               float* value_host, void* workspace, size_t workspace_bytes, cudaStream_t stream,
                               int* taken);
 
+// disjoint patches (perm[0..T) distinct rows of [0, N)) and no rest row among them?  flags: N ints, counts: 64 ints of
+// scratch; one 12-byte read on the stream.  *ok = 0: overlapping input (not an error); rows out of range: DNP_ERR_INVALID.
+int check_patch_cover(const int64_t* perm, int64_t T, int64_t N, const int64_t* rest_rows, int64_t R, int* flags,
+                      int* counts, cudaStream_t stream, int* ok);
+
+// The greedy patch loop as P independent per-patch field launches + a loop on the P x P interaction matrix
+// (dnp_slab.cu); *taken = 0 when the preconditions do not hold.
+bool slab_schedule_fits(int64_t P, int64_t T, int64_t max_patch);
+bool slab_schedule_pays(int64_t P, int64_t T, int64_t max_patch);
+size_t patch_slab_workspace_bytes(int64_t N, int64_t P, int64_t T);
+int run_patch_loop_slab(float* pts, int64_t N, int64_t ld, const int64_t* perm, const int64_t* offsets_dev,
+                        const int64_t* offsets_host, int64_t P, const int64_t* rest_perm,
+                        const int64_t* rest_offsets_host, const int64_t* tgt_idx, int64_t n_tgt, int64_t start_patch,
+                        float eps, int diffuse, float* E, int64_t ld_e, int32_t* order_host, float* value_host,
+                        void* workspace, size_t workspace_bytes, cudaStream_t stream, const ShardHook* shard,
+                        int* taken);
+
 int run_patch_covariance(const float* pts, int64_t ld, const int64_t* perm, const int64_t* offsets, int64_t P,
                          double* cov, cudaStream_t stream);
 

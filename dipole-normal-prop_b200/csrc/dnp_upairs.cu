@@ -387,9 +387,12 @@ upairs_kernel(const __grid_constant__ ShareTable tab, int win_q, int n_q, int m_
 // n_src is a multiple of the fold (224 field / 336 potential sources).
 // (16 targets per thread for the potential -- 3 LDCU.64 per 8 packed groups instead of 4 -- measured 2.6 % SLOWER at
 // 1M x 1M, profiles/README.md r02b: the issue model's 0.25 cycle per group is less than what 160 registers cost.)
-template <bool kPotential, int TP = 4>
+// kRagged (field only): n_src is any multiple of 4 and the last fold is shorter -- one launch per PATCH of the
+// greedy drivers' slab schedule (run_upairs_patch_slabs below), whose patches are a few hundred rows.
+template <bool kPotential, int TP = 4, bool kRagged = false>
 __global__ void __launch_bounds__(kUBlock, 3)
 upairs_tile_kernel(int win_q, int n_src, UTargets T, float eps, float* __restrict__ part, int first) {
+    static_assert(!(kPotential && kRagged), "ragged folds exist for the field only");
     constexpr int kFold = Win<kPotential>::kFold;
     const float* __restrict__ win = c_window + 4 * win_q;     // slot offsets in units of 4 floats: 16-byte aligned reads
     const int tid = threadIdx.x;
@@ -449,11 +452,12 @@ upairs_tile_kernel(int win_q, int n_src, UTargets T, float eps, float* __restric
             f32x2 ax[TP], ay[TP], az[TP];
 #pragma unroll
             for (int j = 0; j < TP; ++j) { ax[j] = ay[j] = az[j] = zero2; }
-            field_fold<TP, false>(win, s0, kFold, qx, qy, qz, eps2, tiny4, ax, ay, az);
+            const int n_fold = kRagged ? min(kFold, n_src - s0) : kFold;
+            field_fold<TP, false>(win, s0, n_fold, qx, qy, qz, eps2, tiny4, ax, ay, az);
             if (__any_sync(0xffffffffu, any_nonfinite<TP>(ax, ay, az))) {        // a duplicate of a target among the sources
 #pragma unroll
                 for (int j = 0; j < TP; ++j) { ax[j] = ay[j] = az[j] = zero2; }
-                field_fold<TP, true>(win, s0, kFold, qx, qy, qz, eps2, tiny4, ax, ay, az);
+                field_fold<TP, true>(win, s0, n_fold, qx, qy, qz, eps2, tiny4, ax, ay, az);
             }
 #pragma unroll
             for (int j = 0; j < TP; ++j) {
@@ -777,6 +781,133 @@ int run_upairs(bool potential, const float* src, int64_t S, int64_t ld_s, const 
     }
     if (rc != DNP_OK || fused) return rc;
     return run_split_reduce(potential, partial, plan.lanes * plan.ways, M, ep, stream, plan.way_stride);
+}
+
+
+// ---------------------------------------------------------------- one field slab per patch (dnp_slab.cu)
+namespace {
+
+// Window rows [x y z | n | -3n] of every patch of a CSR, patch p at row pad_off[p] (a multiple of 4; rows between the
+// end of a patch and the next multiple of 4 are null dipoles).
+__global__ void pack_patches_kernel(const float* __restrict__ src, int64_t ld, const int64_t* __restrict__ perm,
+                                    const int64_t* __restrict__ offsets, const int64_t* __restrict__ pad_off, int P,
+                                    int64_t total_pad, float* __restrict__ packed) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= total_pad) return;
+    int lo = 0, hi = P;                                   // last p with pad_off[p] <= i (empty patches repeat a value)
+    while (hi - lo > 1) {
+        const int mid = (lo + hi) >> 1;
+        if (pad_off[mid] <= i) lo = mid; else hi = mid;
+    }
+    const int64_t local = i - pad_off[lo], o = offsets[lo], n = offsets[lo + 1] - o;
+    float v[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    if (local < n) {
+        const float* q = src + perm[o + local] * ld;
+#pragma unroll
+        for (int c = 0; c < 6; ++c) v[c] = __ldg(q + c);
+    }
+    float* w = packed + 9 * i;
+#pragma unroll
+    for (int c = 0; c < 6; ++c) w[c] = v[c];
+    w[6] = v[3] * -3.f; w[7] = v[4] * -3.f; w[8] = v[5] * -3.f;
+}
+
+}  // namespace
+
+size_t upairs_slab_packed_bytes(int64_t total_pad) {
+    return (size_t)round_up_u((total_pad > 0 ? total_pad : 4) * 9 * (int64_t)sizeof(float), 256);
+}
+
+// slabs[p][m][0..3) = field of patch p's rows (current normals) at target m = row tgt_idx[m] of pts, for every patch
+// with skip_host[p] == 0: one whole-tile launch per (patch, chunk of <= one window slot), launches of different
+// patches rotating over the lanes -- independent launches, so the tail wave of one overlaps the head of the next and
+// the whole batch runs at the rate of one large call.  Empty patches get a zeroed slab.  Asynchronous.
+int run_upairs_patch_slabs(const float* pts, int64_t ld, const int64_t* perm, const int64_t* offsets_dev,
+                           const int64_t* offsets_host, const int64_t* pad_off_dev, const int64_t* pad_off_host,
+                           int64_t P, const uint8_t* skip_host, const int64_t* tgt_idx, int64_t M, float eps,
+                           float* packed, float* slabs, int64_t slab_stride, cudaStream_t stream) {
+    if (P <= 0 || M <= 0) return DNP_OK;
+    int dev = 0;
+    DNP_CHECK_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= kMaxDevices) {
+        set_error("device index %d out of range", dev);
+        return DNP_ERR_INVALID;
+    }
+    const int64_t total_pad = pad_off_host[P];
+    const int64_t tiles = (M + (int64_t)kUBlock * 8 - 1) / ((int64_t)kUBlock * 8);
+    const int slots3 = sm_count_cached() * 3;
+    // as many launches in flight as the window has room for whole patches: 4 slots of 448 sources, 3 of 596, else 2
+    // of 896 (4 quarter slots when a launch is too few CTAs) -- a lane's next launch waits for its previous one, so
+    // more lanes leave fewer CTA slots idle at the tail of every launch
+    int64_t max_n4 = 4;
+    for (int64_t p = 0; p < P; ++p) {
+        if (skip_host && skip_host[p]) continue;
+        const int64_t n4 = round_up_u(offsets_host[p + 1] - offsets_host[p], 4);
+        if (n4 > max_n4) max_n4 = n4;
+    }
+    int lanes = tiles * 2 >= (int64_t)slots3 * 23 / 10 ? 2 : 4;
+    if (max_n4 <= kWindowFloats / 4 / 9 / 4 * 4) lanes = 4;
+    else if (max_n4 <= kWindowFloats / 3 / 9 / 4 * 4) lanes = 3;
+    { const int forced = env_int_u("DNP_RING_LANES", 0); if (forced >= 2 && forced <= 4) lanes = forced; }
+    const int slot_floats = kWindowFloats / lanes;                            // 8064 / 5376 / 4032: multiples of 4
+    const int cap = slot_floats / 9 / 4 * 4;                                  // 896 / 596 / 448 sources per launch
+    const UTargets T{pts, M, ld, tgt_idx, nullptr};
+    DeviceRing& ring = g_ring[dev];
+    int rc = DNP_OK;
+    std::lock_guard<std::mutex> lock(ring.mu);
+    DNP_CHECK_CUDA(ring.prepare());
+    const bool capt = capturing(stream);
+    if (!capt && ring.has_last && ring.last_stream != stream) DNP_CHECK_CUDA(cudaStreamWaitEvent(stream, ring.last_done, 0));
+    if (total_pad > 0) {
+        pack_patches_kernel<<<(unsigned)((total_pad + 255) / 256), 256, 0, stream>>>(
+            pts, ld, perm, offsets_dev, pad_off_dev, (int)P, total_pad, packed);
+        count_launch(1);
+        DNP_CHECK_CUDA(cudaGetLastError());
+    }
+    timer_mark(stream);
+    DNP_CHECK_CUDA(cudaEventRecord(ring.fork, stream));
+    for (int l = 0; l < lanes; ++l) DNP_CHECK_CUDA(cudaStreamWaitEvent(ring.lane[l], ring.fork, 0));
+    int64_t launches = 0, turn = 0;
+    for (int64_t p = 0; p < P && rc == DNP_OK; ++p) {
+        if (skip_host && skip_host[p]) continue;
+        const int64_t n = offsets_host[p + 1] - offsets_host[p];
+        const int l = (int)(turn++ % lanes);
+        float* slab = slabs + p * slab_stride;
+        if (n <= 0) {
+            cudaError_t e = cudaMemsetAsync(slab, 0, (size_t)M * 3 * sizeof(float), ring.lane[l]);
+            if (e != cudaSuccess) rc = cuda_fail(e, "slab clear");
+            continue;
+        }
+        const int64_t n4 = round_up_u(n, 4);
+        const int64_t n_chunks = (n4 + cap - 1) / cap;
+        const int64_t even = round_up_u((n4 + n_chunks - 1) / n_chunks, 4);      // equal chunks, not cap + a sliver
+        for (int64_t c0 = 0; c0 < n4; c0 += even) {
+            const int cn = (int)(n4 - c0 < even ? n4 - c0 : even);
+            const int win_off = l * slot_floats;
+            cudaError_t e = fill_slot(ring, win_off, packed + (size_t)(pad_off_host[p] + c0) * 9,
+                                      (size_t)cn * 9 * sizeof(float), ring.lane[l]);
+            if (e != cudaSuccess) { rc = cuda_fail(e, "window fill"); break; }
+            upairs_tile_kernel<false, 4, true><<<(unsigned)tiles, kUBlock, 0, ring.lane[l]>>>(win_off >> 2, cn, T, eps, slab,
+                                                                                              c0 == 0 ? 1 : 0);
+            ++launches;
+        }
+    }
+    count_launch((int)launches);
+    for (int l = 0; l < lanes; ++l) {            // always re-join
+        cudaEventRecord(ring.lane_done[l], ring.lane[l]);
+        cudaStreamWaitEvent(stream, ring.lane_done[l], 0);
+    }
+    timer_mark(stream);
+    if (rc == DNP_OK) {
+        cudaError_t e = cudaGetLastError();
+        if (e != cudaSuccess) rc = cuda_fail(e, "patch slab launch");
+    }
+    if (!capt) {
+        cudaEventRecord(ring.last_done, stream);
+        ring.has_last = true;
+        ring.last_stream = stream;
+    }
+    return rc;
 }
 
 }  // namespace dnp

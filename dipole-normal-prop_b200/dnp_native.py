@@ -453,6 +453,8 @@ def patch_propagate(pts, perm, offsets, start_patch, E, diffuse=False, eps=1e-5,
     N = p.shape[0]
     with torch.cuda.device(dev):
         nbytes = lib.dnp_patch_propagate_workspace_bytes(N, P, max_patch, n_tgt)
+        if owned is not None:     # the slab schedule takes ALL patch rows as targets on every rank (dnp_slab.cu)
+            nbytes = max(nbytes, lib.dnp_patch_propagate_workspace_bytes(N, P, max_patch, int(perm.numel())))
         ws = torch.empty(max(nbytes, 1), dtype=torch.uint8, device=dev)
         head = (_ptr(p), N, ld, _ptr(perm), _ptr(off_dev), ctypes.c_void_p(off_host.ctypes.data), P, _ptr(rest_perm),
                 ctypes.c_void_p(rest_host.ctypes.data if rest_host is not None else 0), _ptr(tgt_idx), n_tgt)

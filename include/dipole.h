@@ -209,8 +209,13 @@ DNP_API int dnp_points_propagate_f32(float* pts, int64_t N, int64_t ld, int64_t 
  * range from the device-resident winner, all P steps are enqueued without a host read and the call returns after the
  * last launch has been enqueued.  Only when a patch is large enough for the constant-window all-pairs kernel (>= 16 384
  * rows; its launches are planned on the host) does the loop read the winner back once per step (8 bytes).  With a trace
- * requested the call synchronises `stream` once at the end.  DNP_PATCH_LOOP=persistent|device|host forces a
- * schedule.                                                                                                  */
+ * requested the call synchronises `stream` once at the end.  Large loops (>= 32 768 target rows, patches of >= 128
+ * rows on average, same disjointness check) take the SLAB schedule when P x T x 12 bytes fit DNP_SLAB_MAX_MB (default
+ * 24576): the field of every patch at every target is computed first -- P independent whole-tile launches at the rate
+ * of one large call, one [T, 3] slab per patch inside the workspace -- then the greedy decisions run on the P x P
+ * matrix of per-patch sums in one CTA and E is assembled from the slabs in visit order; same decisions, no chain of
+ * dependent one-wave field launches (dnp_slab.cu).  DNP_PATCH_LOOP=persistent|slab|device|host forces a schedule
+ * (the workspace query reads the same variable), DNP_SLAB=0 turns the slab schedule off.                       */
 DNP_API size_t dnp_patch_propagate_workspace_bytes(int64_t N, int64_t P, int64_t max_patch, int64_t n_tgt);
 DNP_API int dnp_patch_propagate_f32(float* pts, int64_t N, int64_t ld,
                             const int64_t* perm, const int64_t* offsets_dev, const int64_t* offsets_host, int64_t P,
@@ -398,7 +403,11 @@ DNP_API int dnp_microbench(int kind, int iters, float* ms_out, double* ops_out, 
  *       ncclAllReduce(sum) of the P-vector (zeros for patches owned elsewhere: the sum is exact, all ranks see identical
  *       values) precedes the arg-max, which every rank takes itself -- so all ranks visit and flip the same patches and
  *       end with identical pts.  E holds the final field on this rank's rows only.  All ranks pass the same
- *       start_patch.  workspace: dnp_patch_propagate_workspace_bytes(N, P, max_patch, n_tgt).
+ *       start_patch.  workspace: dnp_patch_propagate_workspace_bytes(N, P, max_patch, n_tgt).  With a workspace of
+ *       dnp_patch_propagate_workspace_bytes(N, P, max_patch, offsets[P]) bytes (if larger) large loops take the slab
+ *       schedule instead, split by SOURCE patch: every rank computes the slabs of the patches it owns against all
+ *       patch rows, ONE ncclAllReduce of the P x P matrix (rows of other ranks are zeros) replaces the per-step
+ *       all-reduces, every rank takes the same decisions on it, and one all-reduce of the [T, 3] partial fields gives E.
  * workspace of the first three: dnp_sharded_workspace_bytes(S, M, P, patch_rows) device bytes.                         */
 DNP_API int dnp_comm_unique_id(void* id128);
 DNP_API int dnp_comm_init(const void* id128, int rank, int world);

@@ -188,4 +188,4 @@ def test_window_kernel_reads_sources_through_uniform_registers():
         assert ops["FFMA2.FTZ"] + ops["FMUL2.FTZ"] + ops["FADD2.FTZ"] >= 12 * 4 and ops["FFMA"] == 0, (name, dict(ops))
         assert ops["MUFU.RSQ"] > 0
         seen += 1
-    assert seen == 6                    # field / potential x (8, 2 targets per thread shares, whole tiles)
+    assert seen == 7                    # field / potential x (8, 2 targets per thread shares, whole tiles) + ragged field tiles

@@ -159,11 +159,13 @@ PROP_CASES = [("reps", 60000, 48, 500, False), ("reps", 60000, 48, 500, True), (
               ("all", 20000, 37, 0, False), ("all", 20000, 37, 0, True), ("all", 400, 1, 0, True)]
 
 
-def _prop_worker(rank, world, port, out_dir):
+def _prop_worker(rank, world, port, out_dir, loop):
     for p in (ROOT, PKG):
         if p not in sys.path:
             sys.path.insert(0, p)
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    if loop:
+        os.environ["DNP_PATCH_LOOP"] = loop
     torch.cuda.set_device(rank)
     dev = torch.device("cuda", rank)
     dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
@@ -186,8 +188,10 @@ def _prop_worker(rank, world, port, out_dir):
 
 
 @pytest.mark.timeout(900)
-def test_sharded_greedy_propagation_world_size_2_nccl(tmp_path, dev):
-    """dnp_patch_propagate_sharded_f32 (targets sharded by patch ownership, one ncclAllReduce per greedy step) behind
+@pytest.mark.parametrize("loop", [None, "slab"])
+def test_sharded_greedy_propagation_world_size_2_nccl(tmp_path, dev, loop, monkeypatch):
+    """dnp_patch_propagate_sharded_f32 (targets sharded by patch ownership, one ncclAllReduce per greedy step; or, loop =
+    "slab", the slab schedule split by source patch with one all-reduce of the P x P matrix and one of the field) behind
     dnp_dist.strongest_field_propagation{,_reps}_sharded: both ranks end with the same cloud, and it carries the
     decisions of the single-GPU driver on the same input (60 000 points / 48 patches / 24 000 representatives is the
     size BASELINE.md section 2 timed; patch counts that do not divide by the world size, a rank without patches)."""
@@ -195,7 +199,8 @@ def test_sharded_greedy_propagation_world_size_2_nccl(tmp_path, dev):
         pytest.skip("needs 2 GPUs (gpurun --gpus 2)")
     import field_utils
     world = 2
-    mp.spawn(_prop_worker, args=(world, _free_port(), str(tmp_path)), nprocs=world, join=True)
+    monkeypatch.delenv("DNP_PATCH_LOOP", raising=False)
+    mp.spawn(_prop_worker, args=(world, _free_port(), str(tmp_path), loop), nprocs=world, join=True)
     res = [torch.load(os.path.join(tmp_path, f"prop_rank{r}.pt")) for r in range(world)]
     for k, (kind, n, P, n_rep, diffuse) in enumerate(PROP_CASES):
         assert torch.equal(res[0][k], res[1][k]), PROP_CASES[k]

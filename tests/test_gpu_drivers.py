@@ -21,7 +21,7 @@ def _patches(perm, off):
     return [torch.from_numpy(perm[off[i]:off[i + 1]].copy()) for i in range(len(off) - 1)]
 
 
-LOOPS = ["persistent", "device", "device_unfused", "host", "per_call"]
+LOOPS = ["persistent", "slab", "device", "device_unfused", "host", "per_call"]
 
 
 def _spy_order(fu, monkeypatch, loop):
@@ -33,7 +33,7 @@ def _spy_order(fu, monkeypatch, loop):
     native = loop != "per_call"
     monkeypatch.setattr(fu, "NATIVE_PATCH_LOOP", native)
     if native:
-        monkeypatch.setenv("DNP_PATCH_LOOP", loop if loop in ("host", "persistent") else "device")
+        monkeypatch.setenv("DNP_PATCH_LOOP", loop if loop in ("host", "persistent", "slab") else "device")
         if loop == "device_unfused":                      # separate arg-max / commit / pack launches per step
             monkeypatch.setenv("DNP_PATCH_LOOP_UNFUSED", "1")
         else:
@@ -305,6 +305,7 @@ def test_rest_rows_overlapping_other_patches_agree_across_schedules(fu, golden, 
     results = {}
     for loop in ("persistent", "device", "host"):
         monkeypatch.setattr(fu, "NATIVE_PATCH_LOOP", True)
+        monkeypatch.setenv("DNP_SLAB_MIN_ROWS", "1")                # ... and so must the slab schedule (dnp_slab.cu)
         if loop == "persistent":
             monkeypatch.delenv("DNP_PATCH_LOOP", raising=False)     # default choice: must fall through by itself
         else:
@@ -313,10 +314,11 @@ def test_rest_rows_overlapping_other_patches_agree_across_schedules(fu, golden, 
         fu.strongest_field_propagation_reps(pts, [(r.to(dev), q.to(dev)) for r, q in reps], diffuse=False)
         results[loop] = pts[:, 3:].cpu()
     assert torch.equal(results["persistent"], results["device"]) and torch.equal(results["device"], results["host"])
-    monkeypatch.setenv("DNP_PATCH_LOOP", "persistent")              # forcing it is refused, not silently wrong
-    with pytest.raises(Exception):
-        pts = torch.from_numpy(g["pc_in"].copy()).to(dev)
-        fu.strongest_field_propagation_reps(pts, [(r.to(dev), q.to(dev)) for r, q in reps], diffuse=False)
+    for forced in ("persistent", "slab"):                           # forcing it is refused, not silently wrong
+        monkeypatch.setenv("DNP_PATCH_LOOP", forced)
+        with pytest.raises(Exception):
+            pts = torch.from_numpy(g["pc_in"].copy()).to(dev)
+            fu.strongest_field_propagation_reps(pts, [(r.to(dev), q.to(dev)) for r, q in reps], diffuse=False)
 
 
 def test_reps_propagation_weights_vs_oracle(fu, golden, orc, dev):
@@ -365,8 +367,8 @@ def test_native_patch_loop_equals_per_call_loop(fu, dev, diffuse, monkeypatch):
     assert torch.equal(out["host"][0], out["per_call"][0])
     assert torch.equal(out["host"][1], out["per_call"][1])
     assert orders["device"] == orders["device_unfused"] == orders["host"] == orders["per_call"]
-    assert orders["persistent"] == orders["host"]
-    for loop in ("persistent", "device", "device_unfused"):
+    assert orders["persistent"] == orders["host"] and orders["slab"] == orders["host"]
+    for loop in ("persistent", "slab", "device", "device_unfused"):
         assert torch.equal(out[loop][0], out["host"][0])                  # pure sign flips either way
         assert torch.equal(out[loop][1], out["host"][1])
     radial = (out["device"][0][:, 3:] * d).sum(-1)
@@ -419,6 +421,93 @@ def test_persistent_loop_edge_cases(fu, dev, monkeypatch):
         fu.strongest_field_propagation(b, [], patches)
         monkeypatch.delenv("DNP_PATCH_LOOP")
         assert torch.equal(a, b)
+
+
+def test_slab_schedule_edge_cases_and_field(fu, dev, monkeypatch):
+    """The slab schedule (dnp_slab.cu: per-patch field slabs, the greedy loop on the P x P matrix) on the shapes its
+    bookkeeping can get wrong -- empty and one-row patches, patches that are not a multiple of 4 rows, a patch larger
+    than one window slot (several chunk launches into one slab), rest rows -- against the host-driven launches:
+    same visit order, same normals, and the same running field E up to float32 summation order, diffuse or not."""
+    import dnp_native
+    pc, d = _surface(9000, 15)
+    order = torch.randperm(9000, generator=torch.Generator().manual_seed(16))
+    cuts = [0, 1, 2, 2, 301, 302, 1103, 3400, 3400, 5001, 9000]         # 2297- and 3999-row patches: 3 and 5+ chunks
+    ragged = [order[a:b] for a, b in zip(cuts[:-1], cuts[1:])]
+    flipped = pc.clone()
+    for pt in ragged[::2]:
+        flipped[pt, 3:] *= -1
+    perm = torch.cat(ragged).to(dev)
+    offsets = torch.tensor(cuts, dtype=torch.int64)
+    for diffuse in (False, True):
+        res = {}
+        for loop in ("slab", "host"):
+            monkeypatch.setenv("DNP_PATCH_LOOP", loop)
+            work, E = flipped.clone().to(dev), torch.zeros(9000, 3, device=dev)
+            o, v = dnp_native.patch_propagate(work, perm, offsets, 6, E, diffuse=diffuse, want_trace=True)
+            res[loop] = (list(o), v, work.cpu(), E.cpu())
+        a, b = res["slab"], res["host"]
+        assert a[0] == b[0]
+        assert torch.equal(a[2], b[2])
+        assert np.allclose(a[1], b[1], rtol=2e-4, atol=1e-4 * np.abs(b[1]).max())
+        scale = b[3].norm(dim=-1).max()
+        assert ((a[3] - b[3]).norm(dim=-1).max() / scale).item() < 1e-5
+    # representatives + rest rows through the reference-facing call
+    reps = [(pt[:(len(pt) + 1) // 2], pt[(len(pt) + 1) // 2:]) for pt in ragged if len(pt) > 0]
+    out = {}
+    for loop in ("slab", "host"):
+        monkeypatch.setenv("DNP_PATCH_LOOP", loop)
+        work = flipped.clone().to(dev)
+        fu.strongest_field_propagation_reps(work, reps, diffuse=True)
+        out[loop] = work.cpu()
+    assert torch.equal(out["slab"], out["host"])
+    # overlapping patches / patches that do not cover the cloud: forced -> a clear error; unforced -> fall through
+    for patches in ([order[:5000], order[4000:]], [order[:3000], order[3000:6000]]):
+        monkeypatch.setenv("DNP_PATCH_LOOP", "slab")
+        with pytest.raises(dnp_native.DipoleError, match="slab"):
+            fu.strongest_field_propagation(pc.clone().to(dev), [], patches)
+        monkeypatch.delenv("DNP_PATCH_LOOP")
+        monkeypatch.setenv("DNP_SLAB_MIN_ROWS", "1")
+        a = pc.clone().to(dev)
+        fu.strongest_field_propagation(a, [], patches)
+        monkeypatch.delenv("DNP_SLAB_MIN_ROWS")
+        monkeypatch.setenv("DNP_PATCH_LOOP", "host")
+        b = pc.clone().to(dev)
+        fu.strongest_field_propagation(b, [], patches)
+        assert torch.equal(a, b)
+
+
+def test_slab_schedule_is_the_default_for_large_loops(fu, dev, monkeypatch):
+    """250 000 representatives in 250 patches: nothing forced, the call must take the slab schedule (told by
+    its launch count) and decide like the device-driven launches."""
+    import dnp_native
+    monkeypatch.delenv("DNP_PATCH_LOOP", raising=False)
+    pc, d = _surface(260000, 21)
+    key = torch.argsort(pc[:, 0] * 7 + pc[:, 1] * 3 + pc[:, 2], stable=True)
+    chunks = torch.chunk(key, 250)
+    for c in chunks[::2]:
+        pc[c, 3:] *= -1
+    reps = [(c[:1000].to(dev), c[1000:].to(dev)) for c in chunks]
+    perm = torch.cat([r for r, _ in reps])
+    offsets = torch.arange(251, dtype=torch.int64) * 1000
+    rest = torch.cat([q for _, q in reps])
+    rest_off = torch.tensor([0] + [q.numel() for _, q in reps], dtype=torch.int64).cumsum(0)
+    res = {}
+    for loop in (None, "device"):
+        if loop:
+            monkeypatch.setenv("DNP_PATCH_LOOP", loop)
+        work, E = pc.clone().to(dev), torch.zeros(260000, 3, device=dev)
+        n0 = dnp_native.launch_count()
+        o, v = dnp_native.patch_propagate(work, perm, offsets, 3, E, diffuse=True, rest_perm=rest, rest_offsets=rest_off,
+                                          tgt_idx=perm, want_trace=True)
+        res[loop] = (list(o), work.cpu(), E.cpu(), dnp_native.launch_count() - n0)
+    # slab: cover check 2 + targets + pack + 3 chunk launches per 1000-row patch (quarter window slots) + 4
+    assert res[None][3] == 8 + 3 * 250 and res["device"][3] == 3 * 250 - 1, (res[None][3], res["device"][3])
+    assert res[None][0] == res["device"][0]
+    assert torch.equal(res[None][1], res["device"][1])
+    scale = res["device"][2].norm(dim=-1).max()
+    assert ((res[None][2] - res["device"][2]).norm(dim=-1).max() / scale).item() < 1e-5
+    radial = (res[None][1][perm.cpu(), 3:] * d[perm.cpu()]).sum(-1)
+    assert abs(torch.sign(radial).mean()) > 0.99
 
 
 def test_schedules_agree_on_random_clouds():

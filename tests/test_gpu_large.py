@@ -27,7 +27,7 @@ def _bits(normals, pc_in):
     return np.packbits(((normals * pc_in[:, 3:]).sum(-1) < 0).numpy())
 
 
-@pytest.mark.parametrize("loop", ["persistent", "device", "host"])
+@pytest.mark.parametrize("loop", ["persistent", "slab", "device", "host"])
 @pytest.mark.parametrize("tag,diffuse", [("plain", False), ("diffuse", True)])
 def test_cfg3_standin_60000_points_48_patches(fu, golden, dev, tag, diffuse, loop, monkeypatch):
     import bench
