@@ -228,13 +228,15 @@ bool slab_schedule_fits(int64_t P, int64_t T, int64_t max_patch) {
     return (double)P * (double)T * 12.0 <= cap;
 }
 
-// ... and whether it is WORTH it when nothing is forced: the window kernel wants >= 32 768 targets and patches of a
-// few hundred rows (one launch per patch); smaller loops belong to the persistent kernel or the device-driven launches.
+// ... and whether it is WORTH it when nothing is forced: one launch per patch is 1024 targets per CTA and 3 or 4
+// launches are in flight (the lanes), so the machine (444 resident CTAs) is only kept full from ~224 target tiles on;
+// patches of >= 128 rows on average keep the per-launch overheads small.  Smaller loops belong to the persistent kernel
+// or the device-driven launches, whose all-pairs kernel shapes its grid to a small target set.
 bool slab_schedule_pays(int64_t P, int64_t T, int64_t max_patch) {
     if (!slab_schedule_fits(P, T, max_patch)) return false;
     const char* min_rows = getenv("DNP_SLAB_MIN_ROWS");                 // tests: any loop of at least that many rows
     if (min_rows) return T >= atoll(min_rows);
-    return T >= 32768 && T >= 128 * P;
+    return T >= 224 * 1024 && T >= 128 * P;
 }
 
 size_t patch_slab_workspace_bytes(int64_t N, int64_t P, int64_t T) { return slab_layout(N, P, T).total; }

@@ -72,11 +72,25 @@ def make(name):
     if name == "partition":
         pc = surface_cloud(n, 10).to(dev)
         return (lambda: dn.voxel_partition(pc, 41)), "voxel partition 1M pts, 41 parts (cell_key_kernel + CUB)", n * 20.0, "bytes"
+    if name == "slab":
+        pc = surface_cloud(n, 10)
+        _, _, chunks = patches_1000(pc)
+        reps = [c[:500].to(dev) for c in chunks]
+        perm = torch.cat(reps)
+        offsets = torch.arange(1001, dtype=torch.int64) * 500
+        rest = torch.cat([c[500:] for c in chunks]).to(dev)
+        rest_off = torch.tensor([0] + [c.numel() - 500 for c in chunks], dtype=torch.int64).cumsum(0)
+        pcd = pc.to(dev)
+
+        def run():
+            work, E = pcd.clone(), torch.zeros(n, 3, device=dev)
+            dn.patch_propagate(work, perm, offsets, 0, E, diffuse=True, rest_perm=rest, rest_offsets=rest_off, tgt_idx=perm)
+        return run, "greedy loop, 1000 patches x 500 representatives, diffuse (slab schedule: upairs_tile_kernel<false,4,true> + slab_*)", 500.0 * 500000 * 1000, "pairs"
     raise SystemExit(f"unknown workload {name}")
 
 
 NAMES = ["field", "potential", "shares", "fused", "smem", "lattice", "points", "points_grid", "edges", "patch_inter", "sign",
-         "xie", "partition"]
+         "xie", "partition", "slab"]
 
 if __name__ == "__main__":
     which = sys.argv[1] if len(sys.argv) > 1 else "all"
