@@ -92,6 +92,7 @@ int run_upairs(bool potential, const float* src, int64_t S, int64_t ld_s, const 
                int64_t M, int64_t ld_t, float eps, const PairEpilogue& ep, void* workspace, size_t workspace_bytes,
                cudaStream_t stream);
 // One field slab per patch of a CSR (the slab schedule of the greedy drivers, dnp_slab.cu): see dnp_upairs.cu.
+int upairs_slab_quantum();                 // patches are padded to a multiple of this many window rows
 size_t upairs_slab_packed_bytes(int64_t total_pad);
 int run_upairs_patch_slabs(const float* pts, int64_t ld, const int64_t* perm, const int64_t* offsets_dev,
                            const int64_t* offsets_host, const int64_t* pad_off_dev, const int64_t* pad_off_host,

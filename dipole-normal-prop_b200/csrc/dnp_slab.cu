@@ -208,7 +208,7 @@ SlabLayout slab_layout(int64_t N, int64_t P, int64_t T) {
     L.value = off; off += up256((size_t)P * 4);
     L.skip = off; off += up256((size_t)P);
     L.dense = off; off += up256((size_t)T * 12);
-    L.packed = off; off += upairs_slab_packed_bytes(T + 3 * P);
+    L.packed = off; off += upairs_slab_packed_bytes(T + (upairs_slab_quantum() - 1) * P);
     L.slab_stride = (3 * T + 63) / 64 * 64;
     L.slabs = off; off += up256((size_t)P * L.slab_stride * 4);
     L.total = off;
@@ -294,10 +294,12 @@ int run_patch_loop_slab(float* pts, int64_t N, int64_t ld, const int64_t* perm, 
     if (rc_cover != DNP_OK) return rc_cover;
     if (!ok) return DNP_OK;
 
-    // patch p's window rows start at a multiple of 4 (16-byte aligned quads in the constant window)
+    // patch p's window rows start at a multiple of the kernel's quantum (12 rows: 16-byte aligned, whole iterations)
+    const int64_t quantum = upairs_slab_quantum();
     std::vector<int64_t> pad_off((size_t)P + 1);
     pad_off[0] = 0;
-    for (int64_t p = 0; p < P; ++p) pad_off[p + 1] = pad_off[p] + ((offsets_host[p + 1] - offsets_host[p] + 3) & ~(int64_t)3);
+    for (int64_t p = 0; p < P; ++p)
+        pad_off[p + 1] = pad_off[p] + (offsets_host[p + 1] - offsets_host[p] + quantum - 1) / quantum * quantum;
     DNP_CHECK_CUDA(cudaMemcpyAsync(pad_off_dev, pad_off.data(), (size_t)(P + 1) * 8, cudaMemcpyHostToDevice, stream));
     if (R > 0)
         DNP_CHECK_CUDA(cudaMemcpyAsync(rest_off_dev, rest_offsets_host, (size_t)(P + 1) * 8, cudaMemcpyHostToDevice,

@@ -47,6 +47,7 @@ constexpr int kWindowFloats = 16128;               // 64 512 B of the 64 KB cons
 constexpr int kSlotFloats = 8064;                  // two slots of 32 256 B ...
 constexpr int kQuarterFloats = 4032;               // ... or four of 16 128 B (more launches in flight for fewer targets)
 constexpr int kMaxSlots = 4;
+constexpr int kSlabQuantum = 12;                   // per-patch launches of the slab schedule: sources per loop iteration
 constexpr int kFixTiles = 1 << 20;                 // target tiles a fused single-launch call may have (4 MB of counters)
 constexpr float kRsqrtClampU = kRsqrtClamp;         // 2^60 (dnp_pairmath.cuh, with kTinyR4 / kTinyR2)
 
@@ -100,11 +101,16 @@ __global__ void fill_window_kernel(const float4* __restrict__ from, float4* __re
 // poisons that lane's sums, which the caller detects and repairs by re-running the fold with kSafe = true (clamped
 // u: the pair then adds exactly 0).  Coincidences are exact duplicates of a target among the sources: rare, and every
 // FMNMX saved is an issue cycle of the ~45 a pair of pairs costs (dnp_pairmath.cuh).
-template <int TP, bool kSafe>
+template <int TP, bool kSafe, int kQuads = 1>
 __device__ __forceinline__ void field_fold(const float* __restrict__ win, int s0, int n, const f32x2 (&qx)[TP],
                                            const f32x2 (&qy)[TP], const f32x2 (&qz)[TP], f32x2 eps2, f32x2 tiny4,
                                            f32x2 (&ax)[TP], f32x2 (&ay)[TP], f32x2 (&az)[TP]) {
-    for (int s = s0; s < s0 + n; s += 4) {
+    // kQuads > 1 (n a multiple of 4 kQuads): that many source quads per iteration, for callers whose n is a run-time
+    // value -- ptxas unrolls a loop of constant length three quads deep by itself, a loop of unknown length not at all
+    for (int sq = s0; sq < s0 + n; sq += 4 * kQuads)
+#pragma unroll
+    for (int quad = 0; quad < kQuads; ++quad) {
+        const int s = sq + 4 * quad;
         const float4* wq = reinterpret_cast<const float4*>(win + 9 * s);
         float v[36];
 #pragma unroll
@@ -387,13 +393,13 @@ upairs_kernel(const __grid_constant__ ShareTable tab, int win_q, int n_q, int m_
 // n_src is a multiple of the fold (224 field / 336 potential sources).
 // (16 targets per thread for the potential -- 3 LDCU.64 per 8 packed groups instead of 4 -- measured 2.6 % SLOWER at
 // 1M x 1M, profiles/README.md r02b: the issue model's 0.25 cycle per group is less than what 160 registers cost.)
-// kRagged (field only): n_src is any multiple of 4 and the last fold is shorter -- one launch per PATCH of the
+// kRagged (field only): n_src is any multiple of 12 and the last fold is shorter -- one launch per PATCH of the
 // greedy drivers' slab schedule (run_upairs_patch_slabs below), whose patches are a few hundred rows.
 template <bool kPotential, int TP = 4, bool kRagged = false>
 __global__ void __launch_bounds__(kUBlock, 3)
 upairs_tile_kernel(int win_q, int n_src, UTargets T, float eps, float* __restrict__ part, int first) {
     static_assert(!(kPotential && kRagged), "ragged folds exist for the field only");
-    constexpr int kFold = Win<kPotential>::kFold;
+    constexpr int kFold = kRagged ? 228 : Win<kPotential>::kFold;   // ragged: n_src and the fold are multiples of 12
     const float* __restrict__ win = c_window + 4 * win_q;     // slot offsets in units of 4 floats: 16-byte aligned reads
     const int tid = threadIdx.x;
     const int64_t tile_base = (int64_t)blockIdx.x * (kUBlock * 2 * TP);
@@ -453,7 +459,7 @@ upairs_tile_kernel(int win_q, int n_src, UTargets T, float eps, float* __restric
 #pragma unroll
             for (int j = 0; j < TP; ++j) { ax[j] = ay[j] = az[j] = zero2; }
             const int n_fold = kRagged ? min(kFold, n_src - s0) : kFold;
-            field_fold<TP, false>(win, s0, n_fold, qx, qy, qz, eps2, tiny4, ax, ay, az);
+            field_fold<TP, false, kRagged ? 3 : 1>(win, s0, n_fold, qx, qy, qz, eps2, tiny4, ax, ay, az);
             if (__any_sync(0xffffffffu, any_nonfinite<TP>(ax, ay, az))) {        // a duplicate of a target among the sources
 #pragma unroll
                 for (int j = 0; j < TP; ++j) { ax[j] = ay[j] = az[j] = zero2; }
@@ -787,8 +793,8 @@ int run_upairs(bool potential, const float* src, int64_t S, int64_t ld_s, const 
 // ---------------------------------------------------------------- one field slab per patch (dnp_slab.cu)
 namespace {
 
-// Window rows [x y z | n | -3n] of every patch of a CSR, patch p at row pad_off[p] (a multiple of 4; rows between the
-// end of a patch and the next multiple of 4 are null dipoles).
+// Window rows [x y z | n | -3n] of every patch of a CSR, patch p at row pad_off[p] (a multiple of kSlabQuantum; rows
+// between the end of a patch and the next multiple are null dipoles).
 __global__ void pack_patches_kernel(const float* __restrict__ src, int64_t ld, const int64_t* __restrict__ perm,
                                     const int64_t* __restrict__ offsets, const int64_t* __restrict__ pad_off, int P,
                                     int64_t total_pad, float* __restrict__ packed) {
@@ -814,6 +820,8 @@ __global__ void pack_patches_kernel(const float* __restrict__ src, int64_t ld, c
 
 }  // namespace
 
+int upairs_slab_quantum() { return kSlabQuantum; }
+
 size_t upairs_slab_packed_bytes(int64_t total_pad) {
     return (size_t)round_up_u((total_pad > 0 ? total_pad : 4) * 9 * (int64_t)sizeof(float), 256);
 }
@@ -836,21 +844,21 @@ int run_upairs_patch_slabs(const float* pts, int64_t ld, const int64_t* perm, co
     const int64_t total_pad = pad_off_host[P];
     const int64_t tiles = (M + (int64_t)kUBlock * 8 - 1) / ((int64_t)kUBlock * 8);
     const int slots3 = sm_count_cached() * 3;
-    // as many launches in flight as the window has room for whole patches: 4 slots of 448 sources, 3 of 596, else 2
-    // of 896 (4 quarter slots when a launch is too few CTAs) -- a lane's next launch waits for its previous one, so
+    // as many launches in flight as the window has room for whole patches: 4 slots of 444 sources, 3 of 588, else 2
+    // of 888 (4 quarter slots when a launch is too few CTAs) -- a lane's next launch waits for its previous one, so
     // more lanes leave fewer CTA slots idle at the tail of every launch
-    int64_t max_n4 = 4;
+    int64_t max_n4 = kSlabQuantum;
     for (int64_t p = 0; p < P; ++p) {
         if (skip_host && skip_host[p]) continue;
-        const int64_t n4 = round_up_u(offsets_host[p + 1] - offsets_host[p], 4);
+        const int64_t n4 = round_up_u(offsets_host[p + 1] - offsets_host[p], kSlabQuantum);
         if (n4 > max_n4) max_n4 = n4;
     }
     int lanes = tiles * 2 >= (int64_t)slots3 * 23 / 10 ? 2 : 4;
-    if (max_n4 <= kWindowFloats / 4 / 9 / 4 * 4) lanes = 4;
-    else if (max_n4 <= kWindowFloats / 3 / 9 / 4 * 4) lanes = 3;
+    if (max_n4 <= kWindowFloats / 4 / 9 / kSlabQuantum * kSlabQuantum) lanes = 4;
+    else if (max_n4 <= kWindowFloats / 3 / 9 / kSlabQuantum * kSlabQuantum) lanes = 3;
     { const int forced = env_int_u("DNP_RING_LANES", 0); if (forced >= 2 && forced <= 4) lanes = forced; }
     const int slot_floats = kWindowFloats / lanes;                            // 8064 / 5376 / 4032: multiples of 4
-    const int cap = slot_floats / 9 / 4 * 4;                                  // 896 / 596 / 448 sources per launch
+    const int cap = slot_floats / 9 / kSlabQuantum * kSlabQuantum;            // 888 / 588 / 444 sources per launch
     const UTargets T{pts, M, ld, tgt_idx, nullptr};
     DeviceRing& ring = g_ring[dev];
     int rc = DNP_OK;
@@ -878,9 +886,9 @@ int run_upairs_patch_slabs(const float* pts, int64_t ld, const int64_t* perm, co
             if (e != cudaSuccess) rc = cuda_fail(e, "slab clear");
             continue;
         }
-        const int64_t n4 = round_up_u(n, 4);
+        const int64_t n4 = round_up_u(n, kSlabQuantum);
         const int64_t n_chunks = (n4 + cap - 1) / cap;
-        const int64_t even = round_up_u((n4 + n_chunks - 1) / n_chunks, 4);      // equal chunks, not cap + a sliver
+        const int64_t even = round_up_u((n4 + n_chunks - 1) / n_chunks, kSlabQuantum);      // equal chunks, not cap + a sliver
         for (int64_t c0 = 0; c0 < n4; c0 += even) {
             const int cn = (int)(n4 - c0 < even ? n4 - c0 : even);
             const int win_off = l * slot_floats;

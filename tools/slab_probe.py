@@ -42,7 +42,7 @@ def main():
     pcd = pc.to(dev)
     res = {}
     for diffuse in (True, False):
-        for mode in ("slab", "slab2", "slab4", "device"):
+        for mode in (("slab",) if os.environ.get("SLAB_ONLY") else ("slab", "slab2", "slab4", "device")):
             os.environ["DNP_PATCH_LOOP"] = mode[:4] if mode.startswith("slab") else mode
             os.environ.pop("DNP_RING_LANES", None)
             if mode in ("slab2", "slab4"):
@@ -73,6 +73,8 @@ def main():
                               "whole_call_ms": round(ms_whole, 2), "launches": int(launches),
                               "lanes": os.environ.get("DNP_RING_LANES", "auto"),
                               "field_launches_ms": [round(float(x), 2) for x in prof][:4]}), flush=True)
+        if os.environ.get("SLAB_ONLY"):
+            break
         a, b = res[(diffuse, "slab")], res[(diffuse, "device")]
         same_order = a[0] == b[0]
         first = next((i for i, (x, y) in enumerate(zip(a[0], b[0])) if x != y), -1)
