@@ -262,7 +262,12 @@ int run_patch_propagate(float* pts, int64_t N, int64_t ld, const int64_t* perm, 
     // DNP_PATCH_LOOP=persistent|device|host overrides the schedule (tests run all of them and compare)
     const char* forced = getenv("DNP_PATCH_LOOP");
     // (sharded over ranks: the targets are this rank's patches only, so the one-kernel loop does not apply)
-    if (!shard && (!forced || forced[0] == 'p')) {
+    // diffuse loops of >= 98 304 rows: the persistent kernel walks every row at every step (nothing to compact away)
+    // and loses to the slab schedule from there on (tools/loop_size_probe2.py: 150 000 rows 22.0 vs 15.8 ms, 300 000
+    // rows 80.6 vs 53.3 ms); not diffuse it wins wherever it fits (300 000 rows: 47.0 vs 53.3 ms)
+    const int64_t T_rows = offsets_host[P] - offsets_host[0];
+    const bool slab_first = !forced && diffuse && T_rows >= 98304 && slab_wanted(P, T_rows, max_patch);
+    if (!shard && !slab_first && (!forced || forced[0] == 'p')) {
         // small cloud, disjoint patches covering the targets: the whole loop in one cooperative launch (dnp_loop.cu)
         int taken = 0;
         const int rc = run_patch_loop_persistent(pts, N, ld, perm, offsets_dev, offsets_host, P, rest_perm,

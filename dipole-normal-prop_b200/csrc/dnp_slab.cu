@@ -228,15 +228,18 @@ bool slab_schedule_fits(int64_t P, int64_t T, int64_t max_patch) {
     return (double)P * (double)T * 12.0 <= cap;
 }
 
-// ... and whether it is WORTH it when nothing is forced: one launch per patch is 1024 targets per CTA and 3 or 4
-// launches are in flight (the lanes), so the machine (444 resident CTAs) is only kept full from ~224 target tiles on;
-// patches of >= 128 rows on average keep the per-launch overheads small.  Smaller loops belong to the persistent kernel
-// or the device-driven launches, whose all-pairs kernel shapes its grid to a small target set.
+// ... and whether it is WORTH it when nothing is forced (tools/loop_size_probe2.py, profiles/README.md r02d): against
+// the device-driven launches it wins from 60 000 rows on with patches of a few hundred rows (5.3 vs 9.3 ms; 400 000
+// rows: 95 vs 153-188 ms) -- three or four per-patch launches in flight against a chain of dependent ones.  Below
+// ~224 target tiles the machine (444 resident CTAs) is not full, so few LARGE patches on a small target set stay with
+// the device-driven launches, whose all-pairs kernel shapes its grid to the target set; patches of >= 128 rows on
+// average keep the per-launch overheads small.  (The persistent kernel is tried first by the driver where IT wins.)
 bool slab_schedule_pays(int64_t P, int64_t T, int64_t max_patch) {
     if (!slab_schedule_fits(P, T, max_patch)) return false;
     const char* min_rows = getenv("DNP_SLAB_MIN_ROWS");                 // tests: any loop of at least that many rows
     if (min_rows) return T >= atoll(min_rows);
-    return T >= 224 * 1024 && T >= 128 * P;
+    if (T < 128 * P) return false;
+    return T >= 224 * 1024 || (T >= 65536 && max_patch <= 2048);
 }
 
 size_t patch_slab_workspace_bytes(int64_t N, int64_t P, int64_t T) { return slab_layout(N, P, T).total; }

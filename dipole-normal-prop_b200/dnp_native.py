@@ -452,24 +452,44 @@ def patch_propagate(pts, perm, offsets, start_patch, E, diffuse=False, eps=1e-5,
     max_patch = int((off_host[1:] - off_host[:-1]).max()) if P > 0 else 0
     N = p.shape[0]
     with torch.cuda.device(dev):
-        nbytes = lib.dnp_patch_propagate_workspace_bytes(N, P, max_patch, n_tgt)
-        if owned is not None:     # the slab schedule takes ALL patch rows as targets on every rank (dnp_slab.cu)
-            nbytes = max(nbytes, lib.dnp_patch_propagate_workspace_bytes(N, P, max_patch, int(perm.numel())))
-        ws = torch.empty(max(nbytes, 1), dtype=torch.uint8, device=dev)
+        def query():
+            n = lib.dnp_patch_propagate_workspace_bytes(N, P, max_patch, n_tgt)
+            if owned is not None:     # the slab schedule takes ALL patch rows as targets on every rank (dnp_slab.cu)
+                n = max(n, lib.dnp_patch_propagate_workspace_bytes(N, P, max_patch, int(perm.numel())))
+            return n
+        nbytes = query()
+        slab_was = os.environ.get("DNP_SLAB")
+        try:
+            ws = torch.empty(max(nbytes, 1), dtype=torch.uint8, device=dev)
+        except torch.OutOfMemoryError:
+            # the slab schedule's per-patch field slabs (P x T x 12 bytes) do not fit next to what the caller holds:
+            # same decisions through the per-step schedules and their small workspace
+            if slab_was == "0":
+                raise
+            os.environ["DNP_SLAB"] = "0"
+            nbytes = query()
+            ws = torch.empty(max(nbytes, 1), dtype=torch.uint8, device=dev)
         head = (_ptr(p), N, ld, _ptr(perm), _ptr(off_dev), ctypes.c_void_p(off_host.ctypes.data), P, _ptr(rest_perm),
                 ctypes.c_void_p(rest_host.ctypes.data if rest_host is not None else 0), _ptr(tgt_idx), n_tgt)
         tail = (int(start_patch), float(eps), int(bool(diffuse)), _ptr(e), ld_e,
                 ctypes.c_void_p(order.ctypes.data if want_trace else 0),
                 ctypes.c_void_p(values.ctypes.data if want_trace else 0), _ptr(ws), nbytes, _stream(p))
-        if owned is None:
-            _check(lib.dnp_patch_propagate_f32(*head, *tail))
-        else:
-            if tgt_idx is None:
-                raise ValueError("the sharded loop needs tgt_idx (the rows of this rank's patches)")
-            owned = owned.to(device=dev, dtype=torch.uint8).contiguous()
-            if owned.numel() != P:
-                raise ValueError("owned must have one entry per patch")
-            _check(lib.dnp_patch_propagate_sharded_f32(*head, _ptr(owned), *tail))
+        try:
+            if owned is None:
+                _check(lib.dnp_patch_propagate_f32(*head, *tail))
+            else:
+                if tgt_idx is None:
+                    raise ValueError("the sharded loop needs tgt_idx (the rows of this rank's patches)")
+                owned = owned.to(device=dev, dtype=torch.uint8).contiguous()
+                if owned.numel() != P:
+                    raise ValueError("owned must have one entry per patch")
+                _check(lib.dnp_patch_propagate_sharded_f32(*head, _ptr(owned), *tail))
+        finally:
+            if os.environ.get("DNP_SLAB") != slab_was:
+                if slab_was is None:
+                    del os.environ["DNP_SLAB"]
+                else:
+                    os.environ["DNP_SLAB"] = slab_was
     return (order[:P], values[:P]) if want_trace else None
 
 

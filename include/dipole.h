@@ -209,8 +209,9 @@ DNP_API int dnp_points_propagate_f32(float* pts, int64_t N, int64_t ld, int64_t 
  * range from the device-resident winner, all P steps are enqueued without a host read and the call returns after the
  * last launch has been enqueued.  Only when a patch is large enough for the constant-window all-pairs kernel (>= 16 384
  * rows; its launches are planned on the host) does the loop read the winner back once per step (8 bytes).  With a trace
- * requested the call synchronises `stream` once at the end.  Large loops (>= 229 376 target rows, patches of >= 128
- * rows on average, same disjointness check) take the SLAB schedule when P x T x 12 bytes fit DNP_SLAB_MAX_MB (default
+ * requested the call synchronises `stream` once at the end.  Large loops (>= 229 376 target rows, or >= 65 536 with patches of <= 2048
+ * rows; patches of >= 128 rows on average; same disjointness check; when diffuse already from 98 304 rows on, ahead of
+ * the persistent kernel) take the SLAB schedule when P x T x 12 bytes fit DNP_SLAB_MAX_MB (default
  * 24576): the field of every patch at every target is computed first -- P independent whole-tile launches at the rate
  * of one large call, one [T, 3] slab per patch inside the workspace -- then the greedy decisions run on the P x P
  * matrix of per-patch sums in one CTA and E is assembled from the slabs in visit order; same decisions, no chain of

@@ -510,6 +510,42 @@ def test_slab_schedule_is_the_default_for_large_loops(fu, dev, monkeypatch):
     assert abs(torch.sign(radial).mean()) > 0.99
 
 
+def test_slab_workspace_falls_back_when_device_memory_is_short(fu, dev, monkeypatch):
+    """The slab schedule wants P x T x 12 bytes of workspace.  When the allocator cannot give them (here: a per-process
+    memory cap just above what is in use) dnp_native.patch_propagate asks again with DNP_SLAB=0 and runs the per-step
+    schedules in their small workspace: same decisions, and the switch does not leak into the environment."""
+    import dnp_native
+    monkeypatch.delenv("DNP_PATCH_LOOP", raising=False)
+    monkeypatch.delenv("DNP_SLAB", raising=False)
+    pc, d = _surface(130000, 23)
+    key = torch.argsort(pc[:, 0] * 7 + pc[:, 1] * 3 + pc[:, 2], stable=True)
+    chunks = torch.chunk(key, 125)                                        # 125 patches x 1040 rows: 203 MB of slabs
+    for c in chunks[::2]:
+        pc[c, 3:] *= -1
+    perm = torch.cat(chunks).to(dev)
+    offsets = torch.tensor([0] + [c.numel() for c in chunks], dtype=torch.int64).cumsum(0)
+    pcd = pc.to(dev)
+
+    def run():
+        work, E = pcd.clone(), torch.zeros(130000, 3, device=dev)
+        n0 = dnp_native.launch_count()
+        o, _ = dnp_native.patch_propagate(work, perm, offsets, 2, E, diffuse=True, want_trace=True)
+        return list(o), work.cpu(), dnp_native.launch_count() - n0
+    want = run()
+    assert want[2] == 6 + 3 * 125, want[2]                               # slab: cover, targets, pack, 3 chunks per patch, 3
+    torch.cuda.synchronize()
+    torch.cuda.empty_cache()
+    total = torch.cuda.mem_get_info(dev)[1]
+    try:
+        torch.cuda.set_per_process_memory_fraction((torch.cuda.memory_reserved(dev) + (120 << 20)) / total, dev)
+        got = run()
+    finally:
+        torch.cuda.set_per_process_memory_fraction(1.0, dev)
+    assert got[2] != want[2]                                              # another schedule ran ...
+    assert got[0] == want[0] and torch.equal(got[1], want[1])             # ... to the same decisions
+    assert "DNP_SLAB" not in os.environ
+
+
 def test_schedules_agree_on_random_clouds():
     """tools/loop_stress.py: 16 random clouds (40 .. 60 000 points; coherent, ragged, tiny and 1000-row patches; P up to
     several thousand; empty patches; diffuse on / off; with and without rest rows) through the persistent kernel and
