@@ -125,7 +125,8 @@ slab_greedy_kernel(const float* __restrict__ W, int P, int start, float* inter, 
 
 // E of target m = the slabs of the visited patches added in visit order with their signs (own patch skipped; when
 // not diffuse only the visits before the target's own patch), then the target's flip is committed to the cloud.
-// partial != 0 (multi-GPU): only the slabs this rank holds (skip[s] == 0) are added; E is summed over ranks later.
+// Multi-GPU (skip != null, dense != 0): only the slabs this rank holds (skip[s] == 0) are added, into a dense [T, 3]
+// buffer that is summed over the ranks afterwards.
 __global__ void __launch_bounds__(256)
 slab_accumulate_kernel(const float* __restrict__ slabs, int64_t slab_stride, int P, int64_t T,
                        const int32_t* __restrict__ patch_of, const int32_t* __restrict__ order,

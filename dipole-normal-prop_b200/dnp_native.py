@@ -464,7 +464,8 @@ def patch_propagate(pts, perm, offsets, start_patch, E, diffuse=False, eps=1e-5,
         except torch.OutOfMemoryError:
             # the slab schedule's per-patch field slabs (P x T x 12 bytes) do not fit next to what the caller holds:
             # same decisions through the per-step schedules and their small workspace
-            if slab_was == "0":
+            # (not for the sharded loop: every rank must take the same schedule, or their collectives do not match)
+            if slab_was == "0" or owned is not None:
                 raise
             os.environ["DNP_SLAB"] = "0"
             nbytes = query()
