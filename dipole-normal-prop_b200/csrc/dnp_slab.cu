@@ -19,7 +19,7 @@
 //
 // HBM: the slabs are written once (A) and read twice (B, D): 3 x P x T x 12 bytes, i.e. 19 GB for the 1M-point /
 // 1000-patch / 524 288-representative case = 3 ms of HBM time against ~150 ms of FP32 work in A.  Sized for the
-// 180 GB of a B200: the schedule is taken when the slabs fit DNP_SLAB_MAX_MB (default 24 GB).
+// 180 GB of a B200: the schedule is taken when the slabs fit DNP_SLAB_MAX_MB (default 64 GB: a third of the device).
 // Preconditions as for the persistent kernel: disjoint patches that are exactly the target rows, no "rest" row among
 // the patch rows (one 12-byte read per call; not on a capturing stream).
 #include <stdlib.h>
@@ -219,13 +219,13 @@ SlabLayout slab_layout(int64_t N, int64_t P, int64_t T) {
 }  // namespace
 
 // Whether a call of this shape is planned for the slab schedule (the workspace query and the driver must agree).
-// DNP_SLAB_MAX_MB: budget for the slabs (default 24576); DNP_SLAB=0 turns the schedule off.
+// DNP_SLAB_MAX_MB: budget for the slabs (default 65536); DNP_SLAB=0 turns the schedule off.
 bool slab_schedule_fits(int64_t P, int64_t T, int64_t max_patch) {
     const char* off = getenv("DNP_SLAB");
     if (off && off[0] == '0') return false;
     if (P < 1 || P > 8192 || T < 1 || max_patch < 1) return false;
     const char* cap_env = getenv("DNP_SLAB_MAX_MB");
-    const double cap = (cap_env ? atof(cap_env) : 24576.0) * 1048576.0;
+    const double cap = (cap_env ? atof(cap_env) : 65536.0) * 1048576.0;
     return (double)P * (double)T * 12.0 <= cap;
 }
 

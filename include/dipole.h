@@ -212,7 +212,7 @@ DNP_API int dnp_points_propagate_f32(float* pts, int64_t N, int64_t ld, int64_t 
  * requested the call synchronises `stream` once at the end.  Large loops (>= 229 376 target rows, or >= 65 536 with patches of <= 2048
  * rows; patches of >= 128 rows on average; same disjointness check; when diffuse already from 98 304 rows on, ahead of
  * the persistent kernel) take the SLAB schedule when P x T x 12 bytes fit DNP_SLAB_MAX_MB (default
- * 24576): the field of every patch at every target is computed first -- P independent whole-tile launches at the rate
+ * 65536): the field of every patch at every target is computed first -- P independent whole-tile launches at the rate
  * of one large call, one [T, 3] slab per patch inside the workspace -- then the greedy decisions run on the P x P
  * matrix of per-patch sums in one CTA and E is assembled from the slabs in visit order; same decisions, no chain of
  * dependent one-wave field launches (dnp_slab.cu).  DNP_PATCH_LOOP=persistent|slab|device|host forces a schedule
