@@ -393,10 +393,12 @@ upairs_kernel(const __grid_constant__ ShareTable tab, int win_q, int n_q, int m_
 // n_src is a multiple of the fold (224 field / 336 potential sources).
 // (16 targets per thread for the potential -- 3 LDCU.64 per 8 packed groups instead of 4 -- measured 2.6 % SLOWER at
 // 1M x 1M, profiles/README.md r02b: the issue model's 0.25 cycle per group is less than what 160 registers cost.)
+// kPotUnroll / kMinB: sources per iteration of the potential loop and the CTAs per SM the registers are capped for
+// (the field loop is unrolled by ptxas, its 166 registers allow three CTAs).
 // kRagged (field only): n_src is any multiple of 12 and the last fold is shorter -- one launch per PATCH of the
 // greedy drivers' slab schedule (run_upairs_patch_slabs below), whose patches are a few hundred rows.
-template <bool kPotential, int TP = 4, bool kRagged = false>
-__global__ void __launch_bounds__(kUBlock, 3)
+template <bool kPotential, int TP = 4, bool kRagged = false, int kPotUnroll = 2, int kMinB = 3>
+__global__ void __launch_bounds__(kUBlock, kMinB)
 upairs_tile_kernel(int win_q, int n_src, UTargets T, float eps, float* __restrict__ part, int first) {
     static_assert(!(kPotential && kRagged), "ragged folds exist for the field only");
     constexpr int kFold = kRagged ? 228 : Win<kPotential>::kFold;   // ragged: n_src and the fold are multiples of 12
@@ -435,7 +437,7 @@ upairs_tile_kernel(int win_q, int n_src, UTargets T, float eps, float* __restric
             f32x2 phi[TP];
 #pragma unroll
             for (int j = 0; j < TP; ++j) phi[j] = zero2;
-#pragma unroll 2
+#pragma unroll kPotUnroll
             for (int s = s0; s < s0 + kFold; ++s) {
                 const float px = win[6 * s], py = win[6 * s + 1], pz = win[6 * s + 2];
                 const float nx = win[6 * s + 3], ny = win[6 * s + 4], nz = win[6 * s + 5];
@@ -598,7 +600,10 @@ void launch_shares(const UPairPlan& plan, int win_off, const UTargets& T, float 
 void launch_chunk(bool potential, const UPairPlan& plan, int win_off, const UTargets& T, float eps, float* part,
                   int first, const FusedFix& fix, cudaStream_t stream) {
     if (plan.whole_tiles) {
-        if (potential) upairs_tile_kernel<true><<<plan.m_tiles, kUBlock, 0, stream>>>(win_off >> 2, plan.chunk, T, eps, part, first);
+        // potential: four sources per loop iteration at four CTAs per SM (124 registers) -- 2.898e12 pairs/s at 1M x 1M
+        // against 2.832e12 for two sources per iteration; 3 / 4 / 6 / 8 sources at 3 CTAs per SM (134 - 158 registers)
+        // and 4 sources at 5 CTAs (94 registers) are all slower (profiles/README.md r02e)
+        if (potential) upairs_tile_kernel<true, 4, false, 4, 4><<<plan.m_tiles, kUBlock, 0, stream>>>(win_off >> 2, plan.chunk, T, eps, part, first);
         else upairs_tile_kernel<false><<<plan.m_tiles, kUBlock, 0, stream>>>(win_off >> 2, plan.chunk, T, eps, part, first);
         return;
     }
