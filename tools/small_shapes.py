@@ -1,6 +1,6 @@
 """Small instance of every launch shape of the hot path in one process, each checked against the oracle where that is
 cheap: the window kernels are forced at small sizes through DNP_RING=2 (one launch with the fused fix-up, shares on
-two lanes, whole tiles on 2 and 4 lanes), the three patch-loop schedules, the point propagation, partition and text
+two lanes, whole tiles on 2 and 4 lanes), the four patch-loop schedules, the point propagation, partition and text
 IO.  (Written as the workload of a compute-sanitizer pass; that tool is closed on this GPU pool, so this is run plain:
 `python tools/small_shapes.py all`.)  Development tool."""
 import os
@@ -80,7 +80,7 @@ if which in ("all", "drivers"):
     order = torch.argsort(pc[:, 0] * 5 + pc[:, 1], stable=True)
     patches = [c.to(dev) for c in torch.chunk(order, 12)]
     results = []
-    for mode in ("persistent", "device", "host"):
+    for mode in ("persistent", "slab", "device", "host"):
         os.environ["DNP_PATCH_LOOP"] = mode
         work = pc.clone().to(dev)
         field_utils.strongest_field_propagation(work, [], patches, diffuse=True)
