@@ -259,6 +259,11 @@ int dnp_edge_interactions_sharded_f32(const float* pts, int64_t ld, const int64_
     return DNP_OK;
 }
 
+size_t dnp_patch_propagate_sharded_workspace_bytes(int64_t N, int64_t P, int64_t max_patch, int64_t n_tgt,
+                                                   int64_t patch_rows, int64_t n_owned) {
+    return patch_propagate_sharded_workspace_bytes(N, P, max_patch, n_tgt, patch_rows, n_owned);
+}
+
 int dnp_patch_propagate_sharded_f32(float* pts, int64_t N, int64_t ld, const int64_t* perm, const int64_t* offsets_dev,
                                     const int64_t* offsets_host, int64_t P, const int64_t* rest_perm,
                                     const int64_t* rest_offsets_host, const int64_t* tgt_idx, int64_t n_tgt,

@@ -181,7 +181,7 @@ struct DriverLayout {
     size_t settled, scratch, active, inter, best, cur, rest_off, order, value, loop, loop_bytes, pairs, pairs_bytes, total;
 };
 
-DriverLayout driver_layout(int64_t N, int64_t P, int64_t max_patch, int64_t M) {
+DriverLayout driver_layout(int64_t N, int64_t P, int64_t max_patch, int64_t M, bool with_slabs = true) {
     DriverLayout L{};
     size_t off = 0;
     L.settled = off; off += up256((size_t)N);
@@ -199,9 +199,9 @@ DriverLayout driver_layout(int64_t N, int64_t P, int64_t max_patch, int64_t M) {
     L.pairs = off; off += up256(L.pairs_bytes);
     L.total = off;
     // the slab schedule (dnp_slab.cu) runs INSTEAD of the other two and lays its buffers over theirs
-    if (slab_wanted(P, M, max_patch)) {
-        const size_t with_slabs = L.loop + patch_slab_workspace_bytes(N, P, M);
-        if (with_slabs > L.total) L.total = with_slabs;
+    if (with_slabs && slab_wanted(P, M, max_patch)) {
+        const size_t slab_total = L.loop + patch_slab_workspace_bytes(N, P, M);
+        if (slab_total > L.total) L.total = slab_total;
     }
     return L;
 }
@@ -211,6 +211,20 @@ DriverLayout driver_layout(int64_t N, int64_t P, int64_t max_patch, int64_t M) {
 size_t patch_propagate_workspace_bytes(int64_t N, int64_t P, int64_t max_patch, int64_t n_tgt) {
     if (N < 0 || P < 0 || max_patch < 0) return 0;
     return driver_layout(N, P, max_patch, n_tgt > 0 ? n_tgt : N).total;
+}
+
+size_t patch_propagate_sharded_workspace_bytes(int64_t N, int64_t P, int64_t max_patch, int64_t n_tgt,
+                                               int64_t patch_rows, int64_t n_owned) {
+    if (N < 0 || P < 0 || max_patch < 0 || n_tgt < 0 || patch_rows < 0 || n_owned < 0) return 0;
+    // the per-step protocol's buffers for this rank's rows, and -- where the slab schedule applies to the loop over
+    // ALL patch rows -- its buffers with one slab per OWNED patch, laid over the same area
+    const DriverLayout L = driver_layout(N, P, max_patch, n_tgt > 0 ? n_tgt : 1, false);
+    size_t total = L.total;
+    if (slab_wanted(P, patch_rows, max_patch)) {
+        const size_t with_slabs = L.loop + patch_slab_workspace_bytes(N, P, patch_rows, n_owned);
+        if (with_slabs > total) total = with_slabs;
+    }
+    return total;
 }
 
 int run_patch_propagate(float* pts, int64_t N, int64_t ld, const int64_t* perm, const int64_t* offsets_dev,
@@ -233,7 +247,8 @@ int run_patch_propagate(float* pts, int64_t N, int64_t ld, const int64_t* perm, 
         if (n > max_patch) max_patch = n;
     }
     const int64_t M = tgt_idx ? n_tgt : N;
-    const DriverLayout L = driver_layout(N, P, max_patch, M);
+    // (sharded: M counts this rank's rows only; the slab schedule sizes its own buffers from all patch rows below)
+    const DriverLayout L = driver_layout(N, P, max_patch, M, shard == nullptr);
     if (!workspace || workspace_bytes < L.total) {
         set_error("workspace too small: need %zu bytes (dnp_patch_propagate_workspace_bytes), got %zu", L.total,
                   workspace_bytes);

@@ -88,7 +88,7 @@ int check_patch_cover(const int64_t* perm, int64_t T, int64_t N, const int64_t* 
 // (dnp_slab.cu); *taken = 0 when the preconditions do not hold.
 bool slab_schedule_fits(int64_t P, int64_t T, int64_t max_patch);
 bool slab_schedule_pays(int64_t P, int64_t T, int64_t max_patch);
-size_t patch_slab_workspace_bytes(int64_t N, int64_t P, int64_t T);
+size_t patch_slab_workspace_bytes(int64_t N, int64_t P, int64_t T, int64_t n_slabs = -1);
 int run_patch_loop_slab(float* pts, int64_t N, int64_t ld, const int64_t* perm, const int64_t* offsets_dev,
                         const int64_t* offsets_host, int64_t P, const int64_t* rest_perm,
                         const int64_t* rest_offsets_host, const int64_t* tgt_idx, int64_t n_tgt, int64_t start_patch,
@@ -111,6 +111,9 @@ int run_points_propagate(float* pts, int64_t N, int64_t ld, int64_t start, float
 
 // greedy patch propagation loop (dnp_drivers.cu)
 size_t patch_propagate_workspace_bytes(int64_t N, int64_t P, int64_t max_patch, int64_t n_tgt);
+// the sharded loop: n_tgt = rows of this rank's patches, patch_rows = offsets[P], n_owned = patches this rank owns
+size_t patch_propagate_sharded_workspace_bytes(int64_t N, int64_t P, int64_t max_patch, int64_t n_tgt,
+                                               int64_t patch_rows, int64_t n_owned);
 int run_patch_propagate(float* pts, int64_t N, int64_t ld, const int64_t* perm, const int64_t* offsets_dev,
                         const int64_t* offsets_host, int64_t P, const int64_t* rest_perm,
                         const int64_t* rest_offsets_host, const int64_t* tgt_idx, int64_t n_tgt, int64_t start_patch,

@@ -61,7 +61,7 @@ __global__ void slab_targets_kernel(const float* __restrict__ pts, int64_t ld, c
 // independent partial sums per lane, fixed shuffle tree: deterministic.
 __global__ void __launch_bounds__(kInterBlock)
 slab_interactions_kernel(const float* __restrict__ slabs, int64_t slab_stride, const float* __restrict__ nrm,
-                         const int64_t* __restrict__ offsets, int P, const uint8_t* __restrict__ skip,
+                         const int64_t* __restrict__ offsets, int P, const int32_t* __restrict__ slot,
                          float* __restrict__ W) {
     const int p = blockIdx.x;
     const int64_t o = offsets[p] * 3, n3 = (offsets[p + 1] - offsets[p]) * 3;
@@ -69,8 +69,9 @@ slab_interactions_kernel(const float* __restrict__ slabs, int64_t slab_stride, c
     const float* __restrict__ nn = nrm + o;
     const int s_end = min(P, (int)(blockIdx.y + 1) * kInterPerBlock);
     for (int s = blockIdx.y * kInterPerBlock + warp; s < s_end; s += kInterBlock / 32) {
-        if (skip && skip[s]) continue;                                  // slab of another rank
-        const float* __restrict__ e = slabs + (int64_t)s * slab_stride + o;
+        const int sl = slot ? slot[s] : s;
+        if (sl < 0) continue;                                           // slab of another rank
+        const float* __restrict__ e = slabs + (int64_t)sl * slab_stride + o;
         float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
         int64_t i = lane;
         for (; i + 96 < n3; i += 128) {
@@ -125,13 +126,13 @@ slab_greedy_kernel(const float* __restrict__ W, int P, int start, float* inter, 
 
 // E of target m = the slabs of the visited patches added in visit order with their signs (own patch skipped; when
 // not diffuse only the visits before the target's own patch), then the target's flip is committed to the cloud.
-// Multi-GPU (skip != null, dense != 0): only the slabs this rank holds (skip[s] == 0) are added, into a dense [T, 3]
+// Multi-GPU (slot != null, dense != 0): only the slabs this rank holds (slot[s] >= 0) are added, into a dense [T, 3]
 // buffer that is summed over the ranks afterwards.
 __global__ void __launch_bounds__(256)
 slab_accumulate_kernel(const float* __restrict__ slabs, int64_t slab_stride, int P, int64_t T,
                        const int32_t* __restrict__ patch_of, const int32_t* __restrict__ order,
                        const float* __restrict__ sigma, const int32_t* __restrict__ rank,
-                       const uint8_t* __restrict__ skip, int diffuse, const int64_t* __restrict__ perm,
+                       const int32_t* __restrict__ slot, int diffuse, const int64_t* __restrict__ perm,
                        float* __restrict__ E, int64_t ld_e, int dense, float* __restrict__ pts, int64_t ld) {
     const int64_t m = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (m >= T) return;
@@ -143,9 +144,10 @@ slab_accumulate_kernel(const float* __restrict__ slabs, int64_t slab_stride, int
     for (int k = 0; k < k_end; ++k) {
         const int s = order[k];
         if (s < 0) break;
-        if (s == own || (skip && skip[s])) continue;
+        const int sl = slot ? slot[s] : s;
+        if (s == own || sl < 0) continue;
         const float sg = sigma[s];
-        const float* __restrict__ v = col + (int64_t)s * slab_stride;
+        const float* __restrict__ v = col + (int64_t)sl * slab_stride;
         ex += sg * v[0]; ey += sg * v[1]; ez += sg * v[2];
     }
     const int64_t r = perm[m];
@@ -159,10 +161,10 @@ slab_accumulate_kernel(const float* __restrict__ slabs, int64_t slab_stride, int
 
 // multi-GPU: the summed field of this rank's own patches goes to the caller's E (rows of other ranks stay untouched)
 __global__ void slab_scatter_owned_kernel(const float* __restrict__ dense, int64_t T, const int32_t* __restrict__ patch_of,
-                                          const uint8_t* __restrict__ skip, const int64_t* __restrict__ perm,
+                                          const int32_t* __restrict__ slot, const int64_t* __restrict__ perm,
                                           float* __restrict__ E, int64_t ld_e) {
     const int64_t m = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (m >= T || skip[patch_of[m]]) return;
+    if (m >= T || slot[patch_of[m]] < 0) return;
     float* o = E + perm[m] * ld_e;
     o[0] = dense[3 * m]; o[1] = dense[3 * m + 1]; o[2] = dense[3 * m + 2];
 }
@@ -186,12 +188,12 @@ __global__ void slab_rest_flip_kernel(const int64_t* __restrict__ rest_perm, con
 }
 
 struct SlabLayout {
-    size_t flags, counts, pad_off, rest_off, patch_of, nrm, W, inter, active, sigma, rank, order, value, skip, dense,
+    size_t flags, counts, pad_off, rest_off, patch_of, nrm, W, inter, active, sigma, rank, order, value, slot, dense,
         packed, slabs, total;
     int64_t slab_stride;
 };
 
-SlabLayout slab_layout(int64_t N, int64_t P, int64_t T) {
+SlabLayout slab_layout(int64_t N, int64_t P, int64_t T, int64_t n_slabs) {
     SlabLayout L{};
     size_t off = 0;
     L.flags = off; off += up256((size_t)N * 4);
@@ -207,11 +209,11 @@ SlabLayout slab_layout(int64_t N, int64_t P, int64_t T) {
     L.rank = off; off += up256((size_t)P * 4);
     L.order = off; off += up256((size_t)P * 4);
     L.value = off; off += up256((size_t)P * 4);
-    L.skip = off; off += up256((size_t)P);
+    L.slot = off; off += up256((size_t)P * 4);
     L.dense = off; off += up256((size_t)T * 12);
     L.packed = off; off += upairs_slab_packed_bytes(T + (upairs_slab_quantum() - 1) * P);
     L.slab_stride = (3 * T + 63) / 64 * 64;
-    L.slabs = off; off += up256((size_t)P * L.slab_stride * 4);
+    L.slabs = off; off += up256((size_t)(n_slabs > 0 ? n_slabs : 1) * L.slab_stride * 4);
     L.total = off;
     return L;
 }
@@ -243,7 +245,10 @@ bool slab_schedule_pays(int64_t P, int64_t T, int64_t max_patch) {
     return T >= 224 * 1024 || (T >= 65536 && max_patch <= 2048);
 }
 
-size_t patch_slab_workspace_bytes(int64_t N, int64_t P, int64_t T) { return slab_layout(N, P, T).total; }
+// n_slabs: the slabs this call holds -- P on one GPU, the patches the rank owns in the sharded loop
+size_t patch_slab_workspace_bytes(int64_t N, int64_t P, int64_t T, int64_t n_slabs) {
+    return slab_layout(N, P, T, n_slabs < 0 ? P : n_slabs).total;
+}
 
 // Returns DNP_OK and *taken = 1 when the loop ran here; *taken = 0 when the preconditions do not hold.
 int run_patch_loop_slab(float* pts, int64_t N, int64_t ld, const int64_t* perm, const int64_t* offsets_dev,
@@ -269,7 +274,18 @@ int run_patch_loop_slab(float* pts, int64_t N, int64_t ld, const int64_t* perm, 
         if (n > max_patch) max_patch = n;
     }
     if (!slab_schedule_fits(P, T, max_patch)) return DNP_OK;
-    const SlabLayout L = slab_layout(N, P, T);
+    // multi-GPU: this rank computes and holds the slabs of the patches it owns, slot[p] = its slab or -1
+    std::vector<int32_t> slot_host;
+    int64_t n_slabs = P;
+    if (shard) {
+        std::vector<uint8_t> owned((size_t)P);
+        DNP_CHECK_CUDA(cudaMemcpyAsync(owned.data(), shard->owned, (size_t)P, cudaMemcpyDeviceToHost, stream));
+        DNP_CHECK_CUDA(cudaStreamSynchronize(stream));
+        slot_host.resize((size_t)P);
+        n_slabs = 0;
+        for (int64_t p = 0; p < P; ++p) slot_host[p] = owned[p] ? (int32_t)n_slabs++ : -1;
+    }
+    const SlabLayout L = slab_layout(N, P, T, n_slabs);
     if (workspace_bytes < L.total) return DNP_OK;
 
     unsigned char* ws = reinterpret_cast<unsigned char*>(workspace);
@@ -286,7 +302,7 @@ int run_patch_loop_slab(float* pts, int64_t N, int64_t ld, const int64_t* perm, 
     int32_t* rank = reinterpret_cast<int32_t*>(ws + L.rank);
     int32_t* order_dev = reinterpret_cast<int32_t*>(ws + L.order);
     float* value_dev = reinterpret_cast<float*>(ws + L.value);
-    uint8_t* skip_dev = ws + L.skip;
+    int32_t* slot_dev = reinterpret_cast<int32_t*>(ws + L.slot);
     float* dense = reinterpret_cast<float*>(ws + L.dense);
     float* packed = reinterpret_cast<float*>(ws + L.packed);
     float* slabs = reinterpret_cast<float*>(ws + L.slabs);
@@ -308,22 +324,15 @@ int run_patch_loop_slab(float* pts, int64_t N, int64_t ld, const int64_t* perm, 
     if (R > 0)
         DNP_CHECK_CUDA(cudaMemcpyAsync(rest_off_dev, rest_offsets_host, (size_t)(P + 1) * 8, cudaMemcpyHostToDevice,
                                        stream));
-    // multi-GPU: this rank computes the slabs of the patches it owns
-    std::vector<uint8_t> skip_host;
-    if (shard) {
-        skip_host.resize((size_t)P);
-        DNP_CHECK_CUDA(cudaMemcpyAsync(skip_host.data(), shard->owned, (size_t)P, cudaMemcpyDeviceToHost, stream));
-        DNP_CHECK_CUDA(cudaStreamSynchronize(stream));
-        for (int64_t p = 0; p < P; ++p) skip_host[p] = skip_host[p] ? 0 : 1;
-        DNP_CHECK_CUDA(cudaMemcpyAsync(skip_dev, skip_host.data(), (size_t)P, cudaMemcpyHostToDevice, stream));
-    }
-    const uint8_t* skip = shard ? skip_dev : nullptr;
+    if (shard)
+        DNP_CHECK_CUDA(cudaMemcpyAsync(slot_dev, slot_host.data(), (size_t)P * 4, cudaMemcpyHostToDevice, stream));
+    const int32_t* slot = shard ? slot_dev : nullptr;
 
     slab_targets_kernel<<<(unsigned)((T + 255) / 256), 256, 0, stream>>>(pts, ld, perm, offsets_dev, (int)P, T, patch_of, nrm);
     count_launch(1);
     // A
     const int rc = run_upairs_patch_slabs(pts, ld, perm, offsets_dev, offsets_host, pad_off_dev, pad_off.data(), P,
-                                          shard ? skip_host.data() : nullptr, perm, T, eps, packed, slabs,
+                                          shard ? slot_host.data() : nullptr, perm, T, eps, packed, slabs,
                                           L.slab_stride, stream);
     if (rc != DNP_OK) return rc;
     // (the host vectors above are read by pageable-memory copies, which return once the data is staged)
@@ -331,7 +340,7 @@ int run_patch_loop_slab(float* pts, int64_t N, int64_t ld, const int64_t* perm, 
     if (shard) DNP_CHECK_CUDA(cudaMemsetAsync(W, 0, (size_t)P * P * 4, stream));     // rows of other ranks: exact zeros
     {
         const dim3 grid((unsigned)P, (unsigned)((P + kInterPerBlock - 1) / kInterPerBlock));
-        slab_interactions_kernel<<<grid, kInterBlock, 0, stream>>>(slabs, L.slab_stride, nrm, offsets_dev, (int)P, skip, W);
+        slab_interactions_kernel<<<grid, kInterBlock, 0, stream>>>(slabs, L.slab_stride, nrm, offsets_dev, (int)P, slot, W);
         count_launch(1);
     }
     if (shard) {                                                     // x + 0 is exact: every rank gets the owners' rows
@@ -343,14 +352,14 @@ int run_patch_loop_slab(float* pts, int64_t N, int64_t ld, const int64_t* perm, 
     count_launch(1);
     // D
     slab_accumulate_kernel<<<(unsigned)((T + 255) / 256), 256, 0, stream>>>(
-        slabs, L.slab_stride, (int)P, T, patch_of, order_dev, sigma, rank, skip, diffuse, perm, shard ? dense : E, ld_e,
+        slabs, L.slab_stride, (int)P, T, patch_of, order_dev, sigma, rank, slot, diffuse, perm, shard ? dense : E, ld_e,
         shard ? 1 : 0, pts, ld);
     count_launch(1);
     if (shard) {     // every rank added the slabs it holds: sum over ranks, keep the rows of the own patches (the
                      // sharded call's contract: E of the other ranks' rows is left as it was)
         const int rcc = shard->combine(shard->ctx, dense, T * 3, stream);
         if (rcc != DNP_OK) return rcc;
-        slab_scatter_owned_kernel<<<(unsigned)((T + 255) / 256), 256, 0, stream>>>(dense, T, patch_of, skip, perm, E, ld_e);
+        slab_scatter_owned_kernel<<<(unsigned)((T + 255) / 256), 256, 0, stream>>>(dense, T, patch_of, slot, perm, E, ld_e);
         count_launch(1);
     }
     if (R > 0) {

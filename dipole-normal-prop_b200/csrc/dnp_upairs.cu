@@ -831,13 +831,13 @@ size_t upairs_slab_packed_bytes(int64_t total_pad) {
     return (size_t)round_up_u((total_pad > 0 ? total_pad : 4) * 9 * (int64_t)sizeof(float), 256);
 }
 
-// slabs[p][m][0..3) = field of patch p's rows (current normals) at target m = row tgt_idx[m] of pts, for every patch
-// with skip_host[p] == 0: one whole-tile launch per (patch, chunk of <= one window slot), launches of different
+// slabs[slot(p)][m][0..3) = field of patch p's rows (current normals) at target m = row tgt_idx[m] of pts, for every
+// patch with slot(p) = slot_host[p] >= 0 (slot_host == NULL: slot(p) = p): one whole-tile launch per (patch, chunk of <= one window slot), launches of different
 // patches rotating over the lanes -- independent launches, so the tail wave of one overlaps the head of the next and
 // the whole batch runs at the rate of one large call.  Empty patches get a zeroed slab.  Asynchronous.
 int run_upairs_patch_slabs(const float* pts, int64_t ld, const int64_t* perm, const int64_t* offsets_dev,
                            const int64_t* offsets_host, const int64_t* pad_off_dev, const int64_t* pad_off_host,
-                           int64_t P, const uint8_t* skip_host, const int64_t* tgt_idx, int64_t M, float eps,
+                           int64_t P, const int32_t* slot_host, const int64_t* tgt_idx, int64_t M, float eps,
                            float* packed, float* slabs, int64_t slab_stride, cudaStream_t stream) {
     if (P <= 0 || M <= 0) return DNP_OK;
     int dev = 0;
@@ -854,7 +854,7 @@ int run_upairs_patch_slabs(const float* pts, int64_t ld, const int64_t* perm, co
     // more lanes leave fewer CTA slots idle at the tail of every launch
     int64_t max_n4 = kSlabQuantum;
     for (int64_t p = 0; p < P; ++p) {
-        if (skip_host && skip_host[p]) continue;
+        if (slot_host && slot_host[p] < 0) continue;
         const int64_t n4 = round_up_u(offsets_host[p + 1] - offsets_host[p], kSlabQuantum);
         if (n4 > max_n4) max_n4 = n4;
     }
@@ -882,10 +882,10 @@ int run_upairs_patch_slabs(const float* pts, int64_t ld, const int64_t* perm, co
     for (int l = 0; l < lanes; ++l) DNP_CHECK_CUDA(cudaStreamWaitEvent(ring.lane[l], ring.fork, 0));
     int64_t launches = 0, turn = 0;
     for (int64_t p = 0; p < P && rc == DNP_OK; ++p) {
-        if (skip_host && skip_host[p]) continue;
+        if (slot_host && slot_host[p] < 0) continue;
         const int64_t n = offsets_host[p + 1] - offsets_host[p];
         const int l = (int)(turn++ % lanes);
-        float* slab = slabs + p * slab_stride;
+        float* slab = slabs + (slot_host ? (int64_t)slot_host[p] : p) * slab_stride;
         if (n <= 0) {
             cudaError_t e = cudaMemsetAsync(slab, 0, (size_t)M * 3 * sizeof(float), ring.lane[l]);
             if (e != cudaSuccess) rc = cuda_fail(e, "slab clear");

@@ -40,6 +40,7 @@ SYMBOLS = [
     ("dnp_points_workspace_bytes", _sz, [_i64]),
     ("dnp_points_propagate_f32", _i32, [_vp, _i64, _i64, _i64, _f32, _i32, _vp, _vp, _vp, _sz, _vp]),
     ("dnp_patch_propagate_workspace_bytes", _sz, [_i64, _i64, _i64, _i64]),
+    ("dnp_patch_propagate_sharded_workspace_bytes", _sz, [_i64, _i64, _i64, _i64, _i64, _i64]),
     ("dnp_patch_propagate_f32", _i32, [_vp, _i64, _i64, _vp, _vp, _vp, _i64, _vp, _vp, _vp, _i64, _i64, _f32, _i32,
                                        _vp, _i64, _vp, _vp, _vp, _sz, _vp]),
     ("dnp_points_batched_max_n", _i64, []),
@@ -453,10 +454,11 @@ def patch_propagate(pts, perm, offsets, start_patch, E, diffuse=False, eps=1e-5,
     N = p.shape[0]
     with torch.cuda.device(dev):
         def query():
-            n = lib.dnp_patch_propagate_workspace_bytes(N, P, max_patch, n_tgt)
-            if owned is not None:     # the slab schedule takes ALL patch rows as targets on every rank (dnp_slab.cu)
-                n = max(n, lib.dnp_patch_propagate_workspace_bytes(N, P, max_patch, int(perm.numel())))
-            return n
+            if owned is None:
+                return lib.dnp_patch_propagate_workspace_bytes(N, P, max_patch, n_tgt)
+            # the slab schedule takes ALL patch rows as targets on every rank and holds one slab per OWNED patch
+            return lib.dnp_patch_propagate_sharded_workspace_bytes(N, P, max_patch, n_tgt, int(perm.numel()),
+                                                                   int(owned.sum().item()))
         nbytes = query()
         slab_was = os.environ.get("DNP_SLAB")
         try:

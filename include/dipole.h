@@ -404,11 +404,12 @@ DNP_API int dnp_microbench(int kind, int iters, float* ms_out, double* ops_out, 
  *       ncclAllReduce(sum) of the P-vector (zeros for patches owned elsewhere: the sum is exact, all ranks see identical
  *       values) precedes the arg-max, which every rank takes itself -- so all ranks visit and flip the same patches and
  *       end with identical pts.  E holds the final field on this rank's rows only.  All ranks pass the same
- *       start_patch.  workspace: dnp_patch_propagate_workspace_bytes(N, P, max_patch, n_tgt).  With a workspace of
- *       dnp_patch_propagate_workspace_bytes(N, P, max_patch, offsets[P]) bytes (if larger) large loops take the slab
- *       schedule instead, split by SOURCE patch: every rank computes the slabs of the patches it owns against all
- *       patch rows, ONE ncclAllReduce of the P x P matrix (rows of other ranks are zeros) replaces the per-step
- *       all-reduces, every rank takes the same decisions on it, and one all-reduce of the [T, 3] partial fields gives E.
+ *       start_patch.  workspace: dnp_patch_propagate_sharded_workspace_bytes(N, P, max_patch, n_tgt, patch_rows =
+ *       offsets[P], n_owned = patches this rank owns) -- every rank must size its workspace with this call, because
+ *       large loops take the slab schedule instead (all ranks or none), split by SOURCE patch: every rank computes and
+ *       holds the slabs of the patches it owns (n_owned x patch_rows x 12 bytes) against all patch rows, ONE
+ *       ncclAllReduce of the P x P matrix (rows of other ranks are zeros) replaces the per-step all-reduces, every
+ *       rank takes the same decisions on it, and one all-reduce of the [T, 3] partial fields gives E.
  * workspace of the first three: dnp_sharded_workspace_bytes(S, M, P, patch_rows) device bytes.                         */
 DNP_API int dnp_comm_unique_id(void* id128);
 DNP_API int dnp_comm_init(const void* id128, int rank, int world);
@@ -426,6 +427,8 @@ DNP_API int dnp_edge_interactions_sharded_f32(const float* pts, int64_t ld,
                                       void* workspace, size_t workspace_bytes, void* stream);
 DNP_API int dnp_lattice_mean_potential_sharded_f32(const float* src, int64_t S, int64_t ld_s, int n, float* mean_out,
                                            void* workspace, size_t workspace_bytes, void* stream);
+DNP_API size_t dnp_patch_propagate_sharded_workspace_bytes(int64_t N, int64_t P, int64_t max_patch, int64_t n_tgt,
+                                                           int64_t patch_rows, int64_t n_owned);
 DNP_API int dnp_patch_propagate_sharded_f32(float* pts, int64_t N, int64_t ld,
                                     const int64_t* perm, const int64_t* offsets_dev, const int64_t* offsets_host,
                                     int64_t P, const int64_t* rest_perm, const int64_t* rest_offsets_host,
