@@ -261,7 +261,7 @@ int dnp_edge_interactions_sharded_f32(const float* pts, int64_t ld, const int64_
 
 size_t dnp_patch_propagate_sharded_workspace_bytes(int64_t N, int64_t P, int64_t max_patch, int64_t n_tgt,
                                                    int64_t patch_rows, int64_t n_owned) {
-    return patch_propagate_sharded_workspace_bytes(N, P, max_patch, n_tgt, patch_rows, n_owned);
+    return patch_propagate_sharded_workspace_bytes(N, P, max_patch, n_tgt, patch_rows, n_owned, g_world);
 }
 
 int dnp_patch_propagate_sharded_f32(float* pts, int64_t N, int64_t ld, const int64_t* perm, const int64_t* offsets_dev,
@@ -282,6 +282,7 @@ int dnp_patch_propagate_sharded_f32(float* pts, int64_t N, int64_t ld, const int
     ShardHook hook;
     hook.owned = owned;
     hook.combine = combine_interactions;
+    hook.world = g_world;
     // a rank that owns no patch still takes part in every all-reduce: its target list is empty, not absent
     static const int64_t no_rows[1] = {0};
     return run_patch_propagate(pts, N, ld, perm, offsets_dev, offsets_host, P, rest_perm, rest_offsets_host,

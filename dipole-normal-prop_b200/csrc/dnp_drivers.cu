@@ -171,10 +171,10 @@ __global__ void cur_init_kernel(int32_t* cur, int32_t start, int32_t* order, flo
 inline size_t up256(size_t v) { return (v + 255) & ~(size_t)255; }
 
 // DNP_PATCH_LOOP=slab forces the slab schedule wherever it fits; unforced it is taken where it pays
-bool slab_wanted(int64_t P, int64_t T, int64_t max_patch) {
+bool slab_wanted(int64_t P, int64_t T, int64_t max_patch, int world = 1) {
     const char* forced = getenv("DNP_PATCH_LOOP");
-    if (forced) return forced[0] == 's' && slab_schedule_fits(P, T, max_patch);
-    return slab_schedule_pays(P, T, max_patch);
+    if (forced) return forced[0] == 's' && slab_schedule_fits(P, T, max_patch, world);
+    return slab_schedule_pays(P, T, max_patch, world);
 }
 
 struct DriverLayout {
@@ -214,13 +214,13 @@ size_t patch_propagate_workspace_bytes(int64_t N, int64_t P, int64_t max_patch, 
 }
 
 size_t patch_propagate_sharded_workspace_bytes(int64_t N, int64_t P, int64_t max_patch, int64_t n_tgt,
-                                               int64_t patch_rows, int64_t n_owned) {
+                                               int64_t patch_rows, int64_t n_owned, int world) {
     if (N < 0 || P < 0 || max_patch < 0 || n_tgt < 0 || patch_rows < 0 || n_owned < 0) return 0;
     // the per-step protocol's buffers for this rank's rows, and -- where the slab schedule applies to the loop over
     // ALL patch rows -- its buffers with one slab per OWNED patch, laid over the same area
     const DriverLayout L = driver_layout(N, P, max_patch, n_tgt > 0 ? n_tgt : 1, false);
     size_t total = L.total;
-    if (slab_wanted(P, patch_rows, max_patch)) {
+    if (slab_wanted(P, patch_rows, max_patch, world)) {
         const size_t with_slabs = L.loop + patch_slab_workspace_bytes(N, P, patch_rows, n_owned);
         if (with_slabs > total) total = with_slabs;
     }
@@ -281,7 +281,8 @@ int run_patch_propagate(float* pts, int64_t N, int64_t ld, const int64_t* perm, 
     // and loses to the slab schedule from there on (tools/loop_size_probe2.py: 150 000 rows 22.0 vs 15.8 ms, 300 000
     // rows 80.6 vs 53.3 ms); not diffuse it wins wherever it fits (300 000 rows: 47.0 vs 53.3 ms)
     const int64_t T_rows = offsets_host[P] - offsets_host[0];
-    const bool slab_first = !forced && diffuse && T_rows >= 98304 && slab_wanted(P, T_rows, max_patch);
+    const int world = shard ? shard->world : 1;
+    const bool slab_first = !forced && diffuse && T_rows >= 98304 && slab_wanted(P, T_rows, max_patch, world);
     if (!shard && !slab_first && (!forced || forced[0] == 'p')) {
         // small cloud, disjoint patches covering the targets: the whole loop in one cooperative launch (dnp_loop.cu)
         int taken = 0;
@@ -298,7 +299,7 @@ int run_patch_propagate(float* pts, int64_t N, int64_t ld, const int64_t* perm, 
     // large loops: all per-patch fields as independent launches, then the loop on the interaction matrix (dnp_slab.cu)
     {
         const int64_t T_all = offsets_host[P] - offsets_host[0];
-        if (slab_wanted(P, T_all, max_patch) && workspace_bytes > L.loop) {
+        if (slab_wanted(P, T_all, max_patch, world) && workspace_bytes > L.loop) {
             int taken = 0;
             const int rc = run_patch_loop_slab(pts, N, ld, perm, offsets_dev, offsets_host, P, rest_perm,
                                                rest_offsets_host, tgt_idx, n_tgt, start_patch, eps, diffuse, E, ld_e,

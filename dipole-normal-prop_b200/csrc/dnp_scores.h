@@ -62,6 +62,7 @@ struct ShardHook {
     const uint8_t* owned = nullptr;
     int (*combine)(void* ctx, float* vals, int64_t n, cudaStream_t stream) = nullptr;
     void* ctx = nullptr;
+    int world = 1;
 };
 
 int run_patch_interactions(const float* E, int64_t ld_e, const float* normals, int64_t ld_n, const int64_t* perm,
@@ -86,8 +87,9 @@ int check_patch_cover(const int64_t* perm, int64_t T, int64_t N, const int64_t* 
 
 // The greedy patch loop as P independent per-patch field launches + a loop on the P x P interaction matrix
 // (dnp_slab.cu); *taken = 0 when the preconditions do not hold.
-bool slab_schedule_fits(int64_t P, int64_t T, int64_t max_patch);
-bool slab_schedule_pays(int64_t P, int64_t T, int64_t max_patch);
+// world: ranks the slabs are split over (every rank holds ~P / world of them: the budget is per GPU)
+bool slab_schedule_fits(int64_t P, int64_t T, int64_t max_patch, int world = 1);
+bool slab_schedule_pays(int64_t P, int64_t T, int64_t max_patch, int world = 1);
 size_t patch_slab_workspace_bytes(int64_t N, int64_t P, int64_t T, int64_t n_slabs = -1);
 int run_patch_loop_slab(float* pts, int64_t N, int64_t ld, const int64_t* perm, const int64_t* offsets_dev,
                         const int64_t* offsets_host, int64_t P, const int64_t* rest_perm,
@@ -113,7 +115,7 @@ int run_points_propagate(float* pts, int64_t N, int64_t ld, int64_t start, float
 size_t patch_propagate_workspace_bytes(int64_t N, int64_t P, int64_t max_patch, int64_t n_tgt);
 // the sharded loop: n_tgt = rows of this rank's patches, patch_rows = offsets[P], n_owned = patches this rank owns
 size_t patch_propagate_sharded_workspace_bytes(int64_t N, int64_t P, int64_t max_patch, int64_t n_tgt,
-                                               int64_t patch_rows, int64_t n_owned);
+                                               int64_t patch_rows, int64_t n_owned, int world);
 int run_patch_propagate(float* pts, int64_t N, int64_t ld, const int64_t* perm, const int64_t* offsets_dev,
                         const int64_t* offsets_host, int64_t P, const int64_t* rest_perm,
                         const int64_t* rest_offsets_host, const int64_t* tgt_idx, int64_t n_tgt, int64_t start_patch,

@@ -222,13 +222,14 @@ SlabLayout slab_layout(int64_t N, int64_t P, int64_t T, int64_t n_slabs) {
 
 // Whether a call of this shape is planned for the slab schedule (the workspace query and the driver must agree).
 // DNP_SLAB_MAX_MB: budget for the slabs (default 65536); DNP_SLAB=0 turns the schedule off.
-bool slab_schedule_fits(int64_t P, int64_t T, int64_t max_patch) {
+bool slab_schedule_fits(int64_t P, int64_t T, int64_t max_patch, int world) {
     const char* off = getenv("DNP_SLAB");
     if (off && off[0] == '0') return false;
     if (P < 1 || P > 8192 || T < 1 || max_patch < 1) return false;
     const char* cap_env = getenv("DNP_SLAB_MAX_MB");
     const double cap = (cap_env ? atof(cap_env) : 65536.0) * 1048576.0;
-    return (double)P * (double)T * 12.0 <= cap;
+    if (world < 1) world = 1;
+    return (double)((P + world - 1) / world) * (double)T * 12.0 <= cap;      // per GPU
 }
 
 // ... and whether it is WORTH it when nothing is forced (tools/loop_size_probe2.py, profiles/README.md r02d): against
@@ -237,8 +238,8 @@ bool slab_schedule_fits(int64_t P, int64_t T, int64_t max_patch) {
 // ~224 target tiles the machine (444 resident CTAs) is not full, so few LARGE patches on a small target set stay with
 // the device-driven launches, whose all-pairs kernel shapes its grid to the target set; patches of >= 128 rows on
 // average keep the per-launch overheads small.  (The persistent kernel is tried first by the driver where IT wins.)
-bool slab_schedule_pays(int64_t P, int64_t T, int64_t max_patch) {
-    if (!slab_schedule_fits(P, T, max_patch)) return false;
+bool slab_schedule_pays(int64_t P, int64_t T, int64_t max_patch, int world) {
+    if (!slab_schedule_fits(P, T, max_patch, world)) return false;
     const char* min_rows = getenv("DNP_SLAB_MIN_ROWS");                 // tests: any loop of at least that many rows
     if (min_rows) return T >= atoll(min_rows);
     if (T < 128 * P) return false;
@@ -273,7 +274,7 @@ int run_patch_loop_slab(float* pts, int64_t N, int64_t ld, const int64_t* perm, 
         const int64_t n = offsets_host[p + 1] - offsets_host[p];
         if (n > max_patch) max_patch = n;
     }
-    if (!slab_schedule_fits(P, T, max_patch)) return DNP_OK;
+    if (!slab_schedule_fits(P, T, max_patch, shard ? shard->world : 1)) return DNP_OK;
     // multi-GPU: this rank computes and holds the slabs of the patches it owns, slot[p] = its slab or -1
     std::vector<int32_t> slot_host;
     int64_t n_slabs = P;

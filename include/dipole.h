@@ -405,7 +405,8 @@ DNP_API int dnp_microbench(int kind, int iters, float* ms_out, double* ops_out, 
  *       values) precedes the arg-max, which every rank takes itself -- so all ranks visit and flip the same patches and
  *       end with identical pts.  E holds the final field on this rank's rows only.  All ranks pass the same
  *       start_patch.  workspace: dnp_patch_propagate_sharded_workspace_bytes(N, P, max_patch, n_tgt, patch_rows =
- *       offsets[P], n_owned = patches this rank owns) -- every rank must size its workspace with this call, because
+ *       offsets[P], n_owned = patches this rank owns; call it after dnp_comm_init: DNP_SLAB_MAX_MB is a budget per
+ *       GPU, i.e. for ~P / world slabs) -- every rank must size its workspace with this call, because
  *       large loops take the slab schedule instead (all ranks or none), split by SOURCE patch: every rank computes and
  *       holds the slabs of the patches it owns (n_owned x patch_rows x 12 bytes) against all patch rows, ONE
  *       ncclAllReduce of the P x P matrix (rows of other ranks are zeros) replaces the per-step all-reduces, every

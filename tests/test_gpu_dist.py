@@ -165,7 +165,9 @@ def _prop_worker(rank, world, port, out_dir, loop):
             sys.path.insert(0, p)
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
     if loop:
-        os.environ["DNP_PATCH_LOOP"] = loop
+        os.environ["DNP_PATCH_LOOP"] = "slab"
+        if loop == "slab_split":      # 8 MB of slabs per GPU: the 60 000- and 20 000-point cases (13.8 and 8.9 MB of
+            os.environ["DNP_SLAB_MAX_MB"] = "8"     # slabs) only fit because each rank holds half of them
     torch.cuda.set_device(rank)
     dev = torch.device("cuda", rank)
     dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
@@ -188,7 +190,7 @@ def _prop_worker(rank, world, port, out_dir, loop):
 
 
 @pytest.mark.timeout(900)
-@pytest.mark.parametrize("loop", [None, "slab"])
+@pytest.mark.parametrize("loop", [None, "slab", "slab_split"])
 def test_sharded_greedy_propagation_world_size_2_nccl(tmp_path, dev, loop, monkeypatch):
     """dnp_patch_propagate_sharded_f32 (targets sharded by patch ownership, one ncclAllReduce per greedy step; or, loop =
     "slab", the slab schedule split by source patch with one all-reduce of the P x P matrix and one of the field) behind
