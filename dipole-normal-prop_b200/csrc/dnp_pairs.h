@@ -96,8 +96,9 @@ int upairs_slab_quantum();                 // patches are padded to a multiple o
 size_t upairs_slab_packed_bytes(int64_t total_pad);
 int run_upairs_patch_slabs(const float* pts, int64_t ld, const int64_t* perm, const int64_t* offsets_dev,
                            const int64_t* offsets_host, const int64_t* pad_off_dev, const int64_t* pad_off_host,
-                           int64_t P, const int32_t* slot_host, const int64_t* tgt_idx, int64_t M, float eps,
-                           float* packed, float* slabs, int64_t slab_stride, cudaStream_t stream);
+                           int64_t P, const int32_t* slot_host, const int64_t* first_target_host,
+                           const int64_t* tgt_idx, int64_t M, float eps, float* packed, float* slabs,
+                           int64_t slab_stride, cudaStream_t stream);
 // Mean potential over the n^3 lattice with the sources in registers and the nodes as uniform operands (dnp_lattice.cu).
 size_t lattice_mean_workspace_bytes();
 int run_lattice_mean(const float* src, int64_t S, int64_t ld_s, int n, float* mean_out, void* workspace,

@@ -61,7 +61,7 @@ __global__ void slab_targets_kernel(const float* __restrict__ pts, int64_t ld, c
 // independent partial sums per lane, fixed shuffle tree: deterministic.
 __global__ void __launch_bounds__(kInterBlock)
 slab_interactions_kernel(const float* __restrict__ slabs, int64_t slab_stride, const float* __restrict__ nrm,
-                         const int64_t* __restrict__ offsets, int P, const int32_t* __restrict__ slot,
+                         const int64_t* __restrict__ offsets, int P, const int32_t* __restrict__ slot, int upper,
                          float* __restrict__ W) {
     const int p = blockIdx.x;
     const int64_t o = offsets[p] * 3, n3 = (offsets[p + 1] - offsets[p]) * 3;
@@ -71,6 +71,7 @@ slab_interactions_kernel(const float* __restrict__ slabs, int64_t slab_stride, c
     for (int s = blockIdx.y * kInterPerBlock + warp; s < s_end; s += kInterBlock / 32) {
         const int sl = slot ? slot[s] : s;
         if (sl < 0) continue;                                           // slab of another rank
+        if (upper && s >= p) continue;                                  // symmetric form: only s < p was computed
         const float* __restrict__ e = slabs + (int64_t)sl * slab_stride + o;
         float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
         int64_t i = lane;
@@ -84,6 +85,15 @@ slab_interactions_kernel(const float* __restrict__ slabs, int64_t slab_stride, c
         const float v = warp_sum((a0 + a1) + (a2 + a3));
         if (lane == 0) W[(int64_t)s * P + p] = v;
     }
+}
+
+// symmetric form: W[s][p] = W[p][s] for s > p (the interaction energy of two dipole sets does not depend on which one
+// is called the source: n_j . E_i(q_j) = w [n_i . n_j - 3 (n_i . R)(n_j . R) / r^2] is symmetric in i and j)
+__global__ void slab_symmetrize_kernel(float* __restrict__ W, int P) {
+    const int p = blockIdx.x * blockDim.x + threadIdx.x, s = blockIdx.y;
+    if (p >= P) return;
+    if (s > p) W[(int64_t)s * P + p] = W[(int64_t)p * P + s];
+    else if (s == p) W[(int64_t)s * P + p] = 0.f;
 }
 
 // The greedy loop on the matrix (one CTA).  inter[p] = interaction of patch p with the field of the visited patches
@@ -132,12 +142,12 @@ __global__ void __launch_bounds__(256)
 slab_accumulate_kernel(const float* __restrict__ slabs, int64_t slab_stride, int P, int64_t T,
                        const int32_t* __restrict__ patch_of, const int32_t* __restrict__ order,
                        const float* __restrict__ sigma, const int32_t* __restrict__ rank,
-                       const int32_t* __restrict__ slot, int diffuse, const int64_t* __restrict__ perm,
+                       const int32_t* __restrict__ slot, int diffuse, int no_field, const int64_t* __restrict__ perm,
                        float* __restrict__ E, int64_t ld_e, int dense, float* __restrict__ pts, int64_t ld) {
     const int64_t m = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (m >= T) return;
     const int own = patch_of[m];
-    const int k_end = diffuse ? P : min(P, rank[own]);
+    const int k_end = no_field ? 0 : (diffuse ? P : min(P, rank[own]));   // symmetric form: half the slabs do not exist
     const float* __restrict__ col = slabs + 3 * m;
     float ex = 0.f, ey = 0.f, ez = 0.f;
 #pragma unroll 4
@@ -329,11 +339,21 @@ int run_patch_loop_slab(float* pts, int64_t N, int64_t ld, const int64_t* perm, 
         DNP_CHECK_CUDA(cudaMemcpyAsync(slot_dev, slot_host.data(), (size_t)P * 4, cudaMemcpyHostToDevice, stream));
     const int32_t* slot = shard ? slot_dev : nullptr;
 
+    // not diffuse: nobody reads the running field afterwards (field_utils.py:264-276 recomputes what it needs), the
+    // decisions only need W, and W is symmetric -- every patch pair once: patch s acts on the targets of the patches
+    // AFTER it only (half the pairs), W[p][s] is copied from W[s][p], and E is returned as zeros.
+    // DNP_SLAB_SYMMETRIC=0: the full form (E = the running field, as the other schedules leave it).
+    const char* sym_env = getenv("DNP_SLAB_SYMMETRIC");
+    const bool symmetric = !diffuse && !shard && !(sym_env && sym_env[0] == '0');
+    std::vector<int64_t> first_target;
+    if (symmetric) first_target.assign(offsets_host + 1, offsets_host + P + 1);
+
     slab_targets_kernel<<<(unsigned)((T + 255) / 256), 256, 0, stream>>>(pts, ld, perm, offsets_dev, (int)P, T, patch_of, nrm);
     count_launch(1);
     // A
     const int rc = run_upairs_patch_slabs(pts, ld, perm, offsets_dev, offsets_host, pad_off_dev, pad_off.data(), P,
-                                          shard ? slot_host.data() : nullptr, perm, T, eps, packed, slabs,
+                                          shard ? slot_host.data() : nullptr, symmetric ? first_target.data() : nullptr, perm, T,
+                                          eps, packed, slabs,
                                           L.slab_stride, stream);
     if (rc != DNP_OK) return rc;
     // (the host vectors above are read by pageable-memory copies, which return once the data is staged)
@@ -341,8 +361,13 @@ int run_patch_loop_slab(float* pts, int64_t N, int64_t ld, const int64_t* perm, 
     if (shard) DNP_CHECK_CUDA(cudaMemsetAsync(W, 0, (size_t)P * P * 4, stream));     // rows of other ranks: exact zeros
     {
         const dim3 grid((unsigned)P, (unsigned)((P + kInterPerBlock - 1) / kInterPerBlock));
-        slab_interactions_kernel<<<grid, kInterBlock, 0, stream>>>(slabs, L.slab_stride, nrm, offsets_dev, (int)P, slot, W);
+        slab_interactions_kernel<<<grid, kInterBlock, 0, stream>>>(slabs, L.slab_stride, nrm, offsets_dev, (int)P, slot,
+                                                                   symmetric ? 1 : 0, W);
         count_launch(1);
+        if (symmetric) {
+            slab_symmetrize_kernel<<<dim3((unsigned)((P + 255) / 256), (unsigned)P), 256, 0, stream>>>(W, (int)P);
+            count_launch(1);
+        }
     }
     if (shard) {                                                     // x + 0 is exact: every rank gets the owners' rows
         const int rcc = shard->combine(shard->ctx, W, P * P, stream);
@@ -353,7 +378,8 @@ int run_patch_loop_slab(float* pts, int64_t N, int64_t ld, const int64_t* perm, 
     count_launch(1);
     // D
     slab_accumulate_kernel<<<(unsigned)((T + 255) / 256), 256, 0, stream>>>(
-        slabs, L.slab_stride, (int)P, T, patch_of, order_dev, sigma, rank, slot, diffuse, perm, shard ? dense : E, ld_e,
+        slabs, L.slab_stride, (int)P, T, patch_of, order_dev, sigma, rank, slot, diffuse, symmetric ? 1 : 0, perm,
+        shard ? dense : E, ld_e,
         shard ? 1 : 0, pts, ld);
     count_launch(1);
     if (shard) {     // every rank added the slabs it holds: sum over ranks, keep the rows of the own patches (the

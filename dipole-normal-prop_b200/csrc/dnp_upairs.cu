@@ -835,10 +835,14 @@ size_t upairs_slab_packed_bytes(int64_t total_pad) {
 // patch with slot(p) = slot_host[p] >= 0 (slot_host == NULL: slot(p) = p): one whole-tile launch per (patch, chunk of <= one window slot), launches of different
 // patches rotating over the lanes -- independent launches, so the tail wave of one overlaps the head of the next and
 // the whole batch runs at the rate of one large call.  Empty patches get a zeroed slab.  Asynchronous.
+// first_target_host (optional): patch p only acts on the targets m >= first_target_host[p] (rows below stay unwritten)
+// -- the symmetric form of the slab schedule, which needs each patch PAIR once; patches are then launched from both
+// ends of the list alternately, so that large and small launches share the machine.
 int run_upairs_patch_slabs(const float* pts, int64_t ld, const int64_t* perm, const int64_t* offsets_dev,
                            const int64_t* offsets_host, const int64_t* pad_off_dev, const int64_t* pad_off_host,
-                           int64_t P, const int32_t* slot_host, const int64_t* tgt_idx, int64_t M, float eps,
-                           float* packed, float* slabs, int64_t slab_stride, cudaStream_t stream) {
+                           int64_t P, const int32_t* slot_host, const int64_t* first_target_host,
+                           const int64_t* tgt_idx, int64_t M, float eps, float* packed, float* slabs,
+                           int64_t slab_stride, cudaStream_t stream) {
     if (P <= 0 || M <= 0) return DNP_OK;
     int dev = 0;
     DNP_CHECK_CUDA(cudaGetDevice(&dev));
@@ -864,7 +868,6 @@ int run_upairs_patch_slabs(const float* pts, int64_t ld, const int64_t* perm, co
     { const int forced = env_int_u("DNP_RING_LANES", 0); if (forced >= 2 && forced <= 4) lanes = forced; }
     const int slot_floats = kWindowFloats / lanes;                            // 8064 / 5376 / 4032: multiples of 4
     const int cap = slot_floats / 9 / kSlabQuantum * kSlabQuantum;            // 888 / 588 / 444 sources per launch
-    const UTargets T{pts, M, ld, tgt_idx, nullptr};
     DeviceRing& ring = g_ring[dev];
     int rc = DNP_OK;
     std::lock_guard<std::mutex> lock(ring.mu);
@@ -881,13 +884,19 @@ int run_upairs_patch_slabs(const float* pts, int64_t ld, const int64_t* perm, co
     DNP_CHECK_CUDA(cudaEventRecord(ring.fork, stream));
     for (int l = 0; l < lanes; ++l) DNP_CHECK_CUDA(cudaStreamWaitEvent(ring.lane[l], ring.fork, 0));
     int64_t launches = 0, turn = 0;
-    for (int64_t p = 0; p < P && rc == DNP_OK; ++p) {
+    for (int64_t k = 0; k < P && rc == DNP_OK; ++k) {
+        const int64_t p = first_target_host ? ((k & 1) ? P - 1 - (k >> 1) : (k >> 1)) : k;
         if (slot_host && slot_host[p] < 0) continue;
         const int64_t n = offsets_host[p + 1] - offsets_host[p];
+        int64_t m0 = first_target_host ? first_target_host[p] : 0;
+        if (m0 < 0) m0 = 0;
+        if (m0 >= M) continue;
+        const UTargets T{tgt_idx ? pts : pts + m0 * ld, M - m0, ld, tgt_idx ? tgt_idx + m0 : nullptr, nullptr};
+        const int64_t tiles_p = (M - m0 + (int64_t)kUBlock * 8 - 1) / ((int64_t)kUBlock * 8);
         const int l = (int)(turn++ % lanes);
-        float* slab = slabs + (slot_host ? (int64_t)slot_host[p] : p) * slab_stride;
+        float* slab = slabs + (slot_host ? (int64_t)slot_host[p] : p) * slab_stride + 3 * m0;
         if (n <= 0) {
-            cudaError_t e = cudaMemsetAsync(slab, 0, (size_t)M * 3 * sizeof(float), ring.lane[l]);
+            cudaError_t e = cudaMemsetAsync(slab, 0, (size_t)(M - m0) * 3 * sizeof(float), ring.lane[l]);
             if (e != cudaSuccess) rc = cuda_fail(e, "slab clear");
             continue;
         }
@@ -900,8 +909,8 @@ int run_upairs_patch_slabs(const float* pts, int64_t ld, const int64_t* perm, co
             cudaError_t e = fill_slot(ring, win_off, packed + (size_t)(pad_off_host[p] + c0) * 9,
                                       (size_t)cn * 9 * sizeof(float), ring.lane[l]);
             if (e != cudaSuccess) { rc = cuda_fail(e, "window fill"); break; }
-            upairs_tile_kernel<false, 4, true><<<(unsigned)tiles, kUBlock, 0, ring.lane[l]>>>(win_off >> 2, cn, T, eps, slab,
-                                                                                              c0 == 0 ? 1 : 0);
+            upairs_tile_kernel<false, 4, true><<<(unsigned)tiles_p, kUBlock, 0, ring.lane[l]>>>(win_off >> 2, cn, T, eps, slab,
+                                                                                                c0 == 0 ? 1 : 0);
             ++launches;
         }
     }

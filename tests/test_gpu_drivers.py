@@ -438,8 +438,11 @@ def test_slab_schedule_edge_cases_and_field(fu, dev, monkeypatch):
         flipped[pt, 3:] *= -1
     perm = torch.cat(ragged).to(dev)
     offsets = torch.tensor(cuts, dtype=torch.int64)
-    for diffuse in (False, True):
+    # (not diffuse the schedule computes every patch pair once and mirrors the interaction matrix -- E is then
+    # returned as zeros; DNP_SLAB_SYMMETRIC=0 selects the full form, whose E is the running field)
+    for diffuse, symmetric in ((False, "1"), (False, "0"), (True, "1")):
         res = {}
+        monkeypatch.setenv("DNP_SLAB_SYMMETRIC", symmetric)
         for loop in ("slab", "host"):
             monkeypatch.setenv("DNP_PATCH_LOOP", loop)
             work, E = flipped.clone().to(dev), torch.zeros(9000, 3, device=dev)
@@ -450,7 +453,11 @@ def test_slab_schedule_edge_cases_and_field(fu, dev, monkeypatch):
         assert torch.equal(a[2], b[2])
         assert np.allclose(a[1], b[1], rtol=2e-4, atol=1e-4 * np.abs(b[1]).max())
         scale = b[3].norm(dim=-1).max()
-        assert ((a[3] - b[3]).norm(dim=-1).max() / scale).item() < 1e-5
+        if diffuse or symmetric == "0":
+            assert ((a[3] - b[3]).norm(dim=-1).max() / scale).item() < 1e-5
+        else:
+            assert not a[3].any()
+    monkeypatch.delenv("DNP_SLAB_SYMMETRIC")
     # representatives + rest rows through the reference-facing call
     reps = [(pt[:(len(pt) + 1) // 2], pt[(len(pt) + 1) // 2:]) for pt in ragged if len(pt) > 0]
     out = {}

@@ -11,7 +11,7 @@ import numpy as np
 import pytest
 
 
-def slab_schedule(orc, pts, patches, start, diffuse, f32):
+def slab_schedule(orc, pts, patches, start, diffuse, f32, symmetric=False):
     """Phases A-D of dnp_slab.cu.  patches: index arrays (disjoint, the targets are their union in CSR order).
     Returns (visit order, sigma per patch, E over the CSR rows)."""
     P = len(patches)
@@ -27,6 +27,8 @@ def slab_schedule(orc, pts, patches, start, diffuse, f32):
     nrm = tgt[:, 3:].astype(dt)
     dots = (slabs * nrm[None]).sum(-1)                                            # [P, T]
     W = np.stack([dots[:, offsets[p]:offsets[p + 1]].sum(-1) for p in range(P)], axis=1).astype(dt)
+    if symmetric:       # every patch pair once (s < p), the other half copied: the interaction energy is symmetric
+        W = np.triu(W, 1) + np.triu(W, 1).T
     # C: the greedy loop on W (field_utils.py:244-252 / :316-323)
     inter = np.zeros(P, dt)
     active = np.ones(P, bool)
@@ -120,3 +122,41 @@ def test_running_field_equals_the_loops(golden, orc):
             if mask.any():
                 E_loop[mask] += orc.field_grad(work[reps[s]], work[mask])
         assert np.abs(E - E_loop[perm]).max() <= 1e-10 * np.abs(E_loop).max()
+
+
+@pytest.mark.parametrize("f32", [False, True])
+def test_symmetric_form_takes_the_reference_decisions(golden, orc, f32):
+    """Not diffuse, the schedule computes every patch PAIR once (patch s acts on the patches after it) and mirrors the
+    matrix: n_j . E_i(q_j) = w [n_i . n_j - 3 (n_i . R)(n_j . R) / r^2] is symmetric in i and j.  Same decisions as the
+    reference on both fixtures, and the two halves of the full matrix agree to rounding."""
+    g = golden("reps_prop")
+    pts = g["pc_in"].astype(np.float32)
+    reps = _patches(g["rep_perm"], g["rep_off"])
+    want_order = list(g["plain_order"])
+    order, sigma, _, _, _ = slab_schedule(orc, pts, reps, want_order[0], False, f32, symmetric=True)
+    assert order == want_order
+    g2 = golden("patch_prop")
+    pts2 = g2["pc_in"].astype(np.float32)
+    patches = _patches(g2["perm"], g2["offsets"])
+    want2 = list(g2["plain_order"])
+    order2, sigma2, _, _, _ = slab_schedule(orc, pts2, patches, want2[0], False, f32, symmetric=True)
+    assert order2 == want2
+    got = pts2.copy()
+    for p, rows in enumerate(patches):
+        got[rows, 3:] *= sigma2[p]
+    assert np.array_equal(np.sign(got[:, 3:]), np.sign(g2["plain_normals"]))
+
+
+def test_interaction_matrix_is_symmetric(golden, orc):
+    g = golden("reps_prop")
+    pts = g["pc_in"].astype(np.float32)
+    reps = _patches(g["rep_perm"], g["rep_off"])
+    perm = np.concatenate(reps)
+    off = np.concatenate([[0], np.cumsum([len(p) for p in reps])])
+    tgt = pts[perm]
+    W = np.zeros((len(reps), len(reps)))
+    for s, rows in enumerate(reps):
+        dots = (orc.field_grad(pts[rows], tgt) * tgt[:, 3:]).sum(-1)
+        W[s] = [dots[off[p]:off[p + 1]].sum() for p in range(len(reps))]
+    np.fill_diagonal(W, 0.0)
+    assert np.abs(W - W.T).max() <= 1e-12 * np.abs(W).max()
