@@ -277,12 +277,13 @@ int run_patch_propagate(float* pts, int64_t N, int64_t ld, const int64_t* perm, 
     // DNP_PATCH_LOOP=persistent|device|host overrides the schedule (tests run all of them and compare)
     const char* forced = getenv("DNP_PATCH_LOOP");
     // (sharded over ranks: the targets are this rank's patches only, so the one-kernel loop does not apply)
-    // diffuse loops of >= 98 304 rows: the persistent kernel walks every row at every step (nothing to compact away)
-    // and loses to the slab schedule from there on (tools/loop_size_probe2.py: 150 000 rows 22.0 vs 15.8 ms, 300 000
-    // rows 80.6 vs 53.3 ms); not diffuse it wins wherever it fits (300 000 rows: 47.0 vs 53.3 ms)
+    // loops of >= 98 304 rows: the slab schedule ahead of the persistent kernel (tools/loop_size_probe2.py, persistent
+    // vs slab: diffuse 150 000 rows 22.0 vs 15.8 ms, 300 000 rows 80.6 vs 53.3 ms; not diffuse -- where the slab
+    // schedule computes every patch pair once -- 100 000 rows 6.3 vs 5.9 ms, 300 000 rows 47.1 vs 27.0 ms; below
+    // that the persistent kernel wins: 60 000 rows 2.6 vs 3.2 ms)
     const int64_t T_rows = offsets_host[P] - offsets_host[0];
     const int world = shard ? shard->world : 1;
-    const bool slab_first = !forced && diffuse && T_rows >= 98304 && slab_wanted(P, T_rows, max_patch, world);
+    const bool slab_first = !forced && T_rows >= 98304 && slab_wanted(P, T_rows, max_patch, world);
     if (!shard && !slab_first && (!forced || forced[0] == 'p')) {
         // small cloud, disjoint patches covering the targets: the whole loop in one cooperative launch (dnp_loop.cu)
         int taken = 0;

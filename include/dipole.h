@@ -201,7 +201,8 @@ DNP_API int dnp_points_propagate_f32(float* pts, int64_t N, int64_t ld, int64_t 
  * targets (the non-representative points of a patch, field_utils.py:250-252).
  * tgt_idx (optional, device, n_tgt rows): the target rows (all representatives, :239); NULL = all N rows.
  * diffuse != 0: only the source patch is skipped as a target (:256-261,326-331), else every visited patch.
- * E: [N, ld_e >= 3] running field, ZEROED by the caller, holds the final field on return.
+ * E: [N, ld_e >= 3] running field, ZEROED by the caller, holds the final field on return (diffuse loops; a loop that
+ * is not diffuse leaves each row at the field accumulated until its patch was visited, or at zero -- see the slab schedule).
  * order_host / value_host (optional, host, P entries): visit order and the signed interaction that chose each
  * patch.  Schedule: the step winner stays on the device.  Small clouds (largest patch <= 1024 rows, disjoint patches
  * that are exactly the target rows -- checked with one 8-byte read per call) run all P steps inside ONE persistent
@@ -210,12 +211,14 @@ DNP_API int dnp_points_propagate_f32(float* pts, int64_t N, int64_t ld, int64_t 
  * last launch has been enqueued.  Only when a patch is large enough for the constant-window all-pairs kernel (>= 16 384
  * rows; its launches are planned on the host) does the loop read the winner back once per step (8 bytes).  With a trace
  * requested the call synchronises `stream` once at the end.  Large loops (>= 229 376 target rows, or >= 65 536 with patches of <= 2048
- * rows; patches of >= 128 rows on average; same disjointness check; when diffuse already from 98 304 rows on, ahead of
- * the persistent kernel) take the SLAB schedule when P x T x 12 bytes fit DNP_SLAB_MAX_MB (default
+ * rows; patches of >= 128 rows on average; same disjointness check; from 98 304 rows on ahead of the persistent
+ * kernel) take the SLAB schedule when P x T x 12 bytes fit DNP_SLAB_MAX_MB (default
  * 65536): the field of every patch at every target is computed first -- P independent whole-tile launches at the rate
  * of one large call, one [T, 3] slab per patch inside the workspace -- then the greedy decisions run on the P x P
  * matrix of per-patch sums in one CTA and E is assembled from the slabs in visit order; same decisions, no chain of
- * dependent one-wave field launches (dnp_slab.cu).  DNP_PATCH_LOOP=persistent|slab|device|host forces a schedule
+ * dependent one-wave field launches (dnp_slab.cu).  When the loop is NOT diffuse the slab schedule computes every patch
+ * pair once (the interaction matrix is symmetric) and returns E as ZEROS -- nothing in the reference reads the running
+ * field of such a loop; DNP_SLAB_SYMMETRIC=0 keeps the full form.  DNP_PATCH_LOOP=persistent|slab|device|host forces a schedule
  * (the workspace query reads the same variable), DNP_SLAB=0 turns the slab schedule off.                       */
 DNP_API size_t dnp_patch_propagate_workspace_bytes(int64_t N, int64_t P, int64_t max_patch, int64_t n_tgt);
 DNP_API int dnp_patch_propagate_f32(float* pts, int64_t N, int64_t ld,
