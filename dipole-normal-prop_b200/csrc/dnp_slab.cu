@@ -341,10 +341,11 @@ int run_patch_loop_slab(float* pts, int64_t N, int64_t ld, const int64_t* perm, 
 
     // not diffuse: nobody reads the running field afterwards (field_utils.py:264-276 recomputes what it needs), the
     // decisions only need W, and W is symmetric -- every patch pair once: patch s acts on the targets of the patches
-    // AFTER it only (half the pairs), W[p][s] is copied from W[s][p], and E is returned as zeros.
+    // AFTER it only (half the pairs), W[p][s] is copied from W[s][p], and E is returned as zeros (sharded: E is not
+    // touched; round-robin ownership spreads the long and the short patches over the ranks).
     // DNP_SLAB_SYMMETRIC=0: the full form (E = the running field, as the other schedules leave it).
     const char* sym_env = getenv("DNP_SLAB_SYMMETRIC");
-    const bool symmetric = !diffuse && !shard && !(sym_env && sym_env[0] == '0');
+    const bool symmetric = !diffuse && !(sym_env && sym_env[0] == '0');
     std::vector<int64_t> first_target;
     if (symmetric) first_target.assign(offsets_host + 1, offsets_host + P + 1);
 
@@ -364,14 +365,14 @@ int run_patch_loop_slab(float* pts, int64_t N, int64_t ld, const int64_t* perm, 
         slab_interactions_kernel<<<grid, kInterBlock, 0, stream>>>(slabs, L.slab_stride, nrm, offsets_dev, (int)P, slot,
                                                                    symmetric ? 1 : 0, W);
         count_launch(1);
-        if (symmetric) {
-            slab_symmetrize_kernel<<<dim3((unsigned)((P + 255) / 256), (unsigned)P), 256, 0, stream>>>(W, (int)P);
-            count_launch(1);
-        }
     }
     if (shard) {                                                     // x + 0 is exact: every rank gets the owners' rows
         const int rcc = shard->combine(shard->ctx, W, P * P, stream);
         if (rcc != DNP_OK) return rcc;
+    }
+    if (symmetric) {                                                 // (sharded: once all owners' rows have arrived)
+        slab_symmetrize_kernel<<<dim3((unsigned)((P + 255) / 256), (unsigned)P), 256, 0, stream>>>(W, (int)P);
+        count_launch(1);
     }
     // C
     slab_greedy_kernel<<<1, 1024, 0, stream>>>(W, (int)P, (int)start_patch, inter, active, sigma, rank, order_dev, value_dev);
@@ -382,8 +383,8 @@ int run_patch_loop_slab(float* pts, int64_t N, int64_t ld, const int64_t* perm, 
         shard ? dense : E, ld_e,
         shard ? 1 : 0, pts, ld);
     count_launch(1);
-    if (shard) {     // every rank added the slabs it holds: sum over ranks, keep the rows of the own patches (the
-                     // sharded call's contract: E of the other ranks' rows is left as it was)
+    if (shard && !symmetric) {     // every rank added the slabs it holds: sum over ranks, keep the rows of the own patches
+                     // (the sharded call's contract: E of the other ranks' rows is left as it was)
         const int rcc = shard->combine(shard->ctx, dense, T * 3, stream);
         if (rcc != DNP_OK) return rcc;
         slab_scatter_owned_kernel<<<(unsigned)((T + 255) / 256), 256, 0, stream>>>(dense, T, patch_of, slot, perm, E, ld_e);
